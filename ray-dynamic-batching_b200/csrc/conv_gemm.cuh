@@ -1,0 +1,44 @@
+// Host interface of the tcgen05 implicit-GEMM convolution (1x1 / 3x3, stride 1 / 2) on NHWC bf16.
+#pragma once
+#include "common.h"
+
+namespace b200 {
+
+struct ConvSpec {
+  View in, out;
+  View res;                  // optional residual (base == nullptr -> none); same geometry as `out`
+  const void* w = nullptr;   // bf16 [Cout][k*k][Cin], BatchNorm already folded in
+  const float* bias = nullptr;  // fp32 [Cout]
+  int ksize = 1, stride = 1, pad = 0;
+  int act = 0;               // b200::Act
+};
+
+struct alignas(64) ConvMaps {
+  CUtensorMap a[4];  // input views (index = parity (py*2+px) for stride 2, else 0)
+  CUtensorMap b;     // weights [Cin, taps, Cout]
+  CUtensorMap d;     // output
+  CUtensorMap r;     // residual (aliases d's geometry)
+};
+
+struct ConvParams {
+  int tiles_w, tiles_h, tiles_n;  // M-tile grid (pixels)
+  int tw, th, tn;                 // pixels per tile along W, H, N  (tw*th*tn == 128)
+  int n_tiles;                    // tiles along Cout
+  int num_taps, kb_per_tap;
+  int cout, act, has_res;
+  signed char tap_map[9], tap_dx[9], tap_dy[9];
+  const float* bias;
+};
+
+struct ConvLaunch {
+  ConvMaps maps;
+  ConvParams p;
+  unsigned grid = 0;
+  int block_n = 0;
+  double flops = 0;  // 2*M*N*K (useful, un-padded)
+};
+
+int conv_prepare(const ConvSpec& spec, ConvLaunch* out);
+int conv_launch(const ConvLaunch& l, cudaStream_t stream);
+
+}  // namespace b200

@@ -1,0 +1,72 @@
+"""ctypes binding of libb200infer.so (the C ABI declared in include/b200infer.h).
+
+The library is the product: there is no Python/torch fallback.  If it cannot be built or loaded, `load()` raises.
+"""
+import ctypes
+import os
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libb200infer.so")
+_lock = threading.Lock()
+_lib = None
+
+c_void_p, c_int, c_float, c_size_t, c_char_p = (ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t,
+                                                ctypes.c_char_p)
+c_float_p = ctypes.POINTER(ctypes.c_float)
+c_int_p = ctypes.POINTER(ctypes.c_int)
+
+# name -> (restype, argtypes); every symbol include/b200infer.h declares must be listed (tests check both ways)
+SIGNATURES = {
+    "b200_last_error": (c_char_p, []),
+    "b200_abi_version": (c_int, []),
+    "b200_conv2d_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
+                                 c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+}
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _LIB_PATH
+
+
+def load(build_if_missing=True):
+    """Returns the loaded CDLL; builds it first when the sources are newer or the .so is missing (needs nvcc)."""
+    global _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if build_if_missing:
+            from . import build as _build
+            _build.build()
+        if not os.path.exists(_LIB_PATH):
+            raise B200Error("libb200infer.so is missing (%s): run `python ray-dynamic-batching_b200/build.py`; "
+                            "there is no fallback path" % _LIB_PATH)
+        lib = ctypes.CDLL(_LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
+            fn.restype = res
+            fn.argtypes = args
+        if lib.b200_abi_version() != 1:
+            raise B200Error("libb200infer ABI version mismatch")
+        _lib = lib
+        return _lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = load().b200_last_error()
+        raise B200Error("%s failed (rc=%d): %s" % (what or "libb200infer call", rc, msg.decode() if msg else "?"))
+
+
+def ptr(t):
+    """Device/host pointer of a torch tensor (or None) as c_void_p."""
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def stream_ptr():
+    import torch
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)

@@ -1,0 +1,97 @@
+"""Parity of the tcgen05 implicit-GEMM convolution (through the C ABI) against a plain PyTorch fp32 conv2d.
+
+Inputs and weights are bf16-representable, so the only differences are fp32 accumulation order and the final
+rounding of the output to bf16: tolerance = 1 bf16 ulp of the result (2^-8 relative) + a small absolute term.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+import rdb_b200
+from rdb_b200.lib import check, ptr, stream_ptr
+
+pytestmark = pytest.mark.gpu
+
+ACT = {"none": 0, "relu": 1, "silu": 2}
+
+
+def ref_conv(x, w, b, res, stride, pad, act):
+    y = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), b, stride=stride, padding=pad)
+    if res is not None:
+        y = y + res.float().permute(0, 3, 1, 2)
+    if act == "relu":
+        y = F.relu(y)
+    elif act == "silu":
+        y = F.silu(y)
+    return y.permute(0, 2, 3, 1).contiguous()
+
+
+def run_conv(lib, x, w, b, res, stride, pad, act):
+    n, h, wd, cin = x.shape
+    cout, k = w.shape[0], w.shape[1]
+    ho, wo = (h + 2 * pad - k) // stride + 1, (wd + 2 * pad - k) // stride + 1
+    out = torch.full((n, ho, wo, cout), float("nan"), device=x.device, dtype=torch.bfloat16)
+    check(lib.b200_conv2d_nhwc(ptr(x), n, h, wd, cin, 0, ptr(w), ptr(b), ptr(res), 0, ptr(out), cout, 0, k, stride,
+                               pad, ACT[act], stream_ptr()), "b200_conv2d_nhwc")
+    torch.cuda.synchronize()
+    return out
+
+
+CASES = [
+    # n, h, w, cin, cout, k, stride, pad, act, residual
+    (2, 8, 8, 64, 64, 1, 1, 0, "none", False),       # one k-block, one tile
+    (2, 56, 56, 64, 256, 1, 1, 0, "relu", True),     # ResNet layer1 conv3 + residual
+    (3, 28, 28, 512, 128, 1, 1, 0, "relu", False),   # multi k-block, ragged M (2352 = 18.4 tiles)
+    (2, 56, 56, 64, 64, 3, 1, 1, "relu", False),     # 3x3, 8x8x2 tiles
+    (4, 14, 14, 256, 256, 3, 1, 1, "relu", False),   # 3x3 at 14x14
+    (3, 7, 7, 512, 512, 3, 1, 1, "relu", False),     # 3x3 at 7x7 (padded tiles, odd batch)
+    (2, 56, 56, 128, 128, 3, 2, 1, "relu", False),   # stride-2 3x3 (ResNet v1.5 layer2.0.conv2)
+    (2, 56, 56, 256, 512, 1, 2, 0, "none", False),   # stride-2 1x1 downsample
+    (1, 28, 28, 24, 96, 3, 1, 1, "silu", False),     # EfficientNet-style odd channels (Cin not multiple of 64)
+    (2, 14, 14, 160, 200, 1, 1, 0, "silu", True),    # Cout not a multiple of 64, residual
+    (1, 15, 15, 64, 64, 3, 2, 1, "silu", False),     # odd spatial size with stride 2
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=[str(c) for c in CASES])
+def test_conv_matches_fp32_reference(b200lib, cuda, case):
+    n, h, w, cin, cout, k, stride, pad, act, use_res = case
+    g = torch.Generator(device="cpu").manual_seed(hash(case) % (2 ** 31))
+    x = torch.randn(n, h, w, cin, generator=g).to(cuda).to(torch.bfloat16)
+    wt = (torch.randn(cout, k, k, cin, generator=g) / (k * k * cin) ** 0.5).to(cuda).to(torch.bfloat16)
+    b = torch.randn(cout, generator=g).to(cuda)
+    ho, wo = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    res = torch.randn(n, ho, wo, cout, generator=g).to(cuda).to(torch.bfloat16) if use_res else None
+    out = run_conv(b200lib, x, wt, b, res, stride, pad, act)
+    ref = ref_conv(x, wt, b, res, stride, pad, act)
+    assert not torch.isnan(out.float()).any(), "unwritten output elements"
+    err = (out.float() - ref).abs()
+    tol = ref.abs() * 2.0 ** -8 + 2e-3
+    bad = (err > tol).sum().item()
+    assert bad == 0, "max err %.4g (tol %.4g), %d bad of %d" % (err.max().item(), tol.max().item(), bad, err.numel())
+
+
+def test_conv_channel_slices(b200lib, cuda):
+    """Reads a channel slice of a wider buffer and writes into a slice of another (chunk / concat without copies)."""
+    g = torch.Generator(device="cpu").manual_seed(7)
+    n, h, w = 2, 14, 14
+    xin = torch.randn(n, h, w, 128, generator=g).to(cuda).to(torch.bfloat16)
+    wt = (torch.randn(64, 1, 1, 64, generator=g) / 8).to(cuda).to(torch.bfloat16)
+    b = torch.randn(64, generator=g).to(cuda)
+    out = torch.zeros(n, h, w, 192, device=cuda, dtype=torch.bfloat16)
+    x_slice = xin[..., 64:128]
+    o_slice = out[..., 128:192]
+    check(b200lib.b200_conv2d_nhwc(x_slice.data_ptr(), n, h, w, 64, 128, ptr(wt), ptr(b), None, 0,
+                                   o_slice.data_ptr(), 64, 192, 1, 1, 0, 1, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = ref_conv(x_slice.contiguous(), wt, b, None, 1, 0, "relu")
+    assert (out[..., :128] == 0).all()
+    err = (out[..., 128:].float() - ref).abs()
+    assert (err <= ref.abs() * 2.0 ** -8 + 2e-3).all(), err.max().item()
+
+
+def test_conv_rejects_bad_shapes(b200lib, cuda):
+    x = torch.zeros(1, 8, 8, 12, device=cuda, dtype=torch.bfloat16)
+    rc = b200lib.b200_conv2d_nhwc(ptr(x), 1, 8, 8, 12, 0, ptr(x), ptr(x), None, 0, ptr(x), 12, 0, 1, 1, 0, 0, None)
+    assert rc == -1
+    assert b"multiples of 8" in b200lib.b200_last_error()
