@@ -54,6 +54,83 @@ B200_API int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int 
                      const float* bias, const void* residual, int res_pix_stride, void* out, int cout,
                      int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
 
+/* Stem convolution with 3 input channels (input NHWC with C padded to 4) + folded BN + activation, direct FP32-pipe kernel.
+ * Replaces tv resnet.py:268-270 (conv1 7x7/2 + bn1 + relu), shufflenetv2.py:112-116, efficientnet.py:283-287 (3x3/2 stems).
+ * weight: fp32 [k*k][3][cout_pad], cout_pad = cout rounded up to the channel tile b200_stem_cout_tile(cout). */
+B200_API int b200_stem_cout_tile(int cout);
+B200_API int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight, const float* bias, void* out,
+                                 int cout, int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
+
+/* Depthwise 3x3 (pad 1) + folded BN + activation. Replaces tv shufflenetv2.py:62-76 `depthwise_conv` and the depthwise
+ * stage of MBConv (tv efficientnet.py:140-151). weight: fp32 [9][c]; bias fp32 [c]. */
+B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
+                                 const float* bias, void* out, int out_pix_stride, int stride, int act, void* stream);
+
+/* Max pooling (k, stride, pad). Replaces nn.MaxPool2d(3,2,1) (tv resnet.py:271, shufflenetv2.py:118) and SPPF's 5x5/1/2. */
+B200_API int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
+                               int out_pix_stride, int ksize, int stride, int pad, void* stream);
+
+/* Global average pool to fp32 [n][c]. Replaces nn.AdaptiveAvgPool2d(1) (tv resnet.py:278) / x.mean([2,3]) (shufflenetv2.py:161). */
+B200_API int b200_global_avgpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, float* out,
+                                      void* stream);
+
+/* out[n][j] = act(x_scale * sum_k x[n][k] w[j][k] + b[j]), all fp32. Replaces nn.Linear (tv resnet.py:280) and the two
+ * 1x1 convs of SqueezeExcitation (tv ops/misc.py). */
+B200_API int b200_fc(const float* x, const float* w, const float* b, float* out, int n, int k, int j, float x_scale,
+                     int act, void* stream);
+
+/* y = x * gate[n][c] (SE excitation; tv ops/misc.py SqueezeExcitation.forward `scale * input`). */
+B200_API int b200_channel_scale_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* gate,
+                                     void* out, int out_pix_stride, void* stream);
+
+/* Channel-slice copy / nearest 2x upsample / ShuffleNetV2 concat+channel_shuffle(groups=2) interleave
+ * (tv shufflenetv2.py:28-40,98-104: out[2i] = a[i], out[2i+1] = b[i]). */
+B200_API int b200_copy_channels_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
+                                     int out_pix_stride, void* stream);
+B200_API int b200_upsample2x_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
+                                  int out_pix_stride, void* stream);
+B200_API int b200_shuffle_concat_nhwc(const void* a, int a_pix_stride, const void* b, int b_pix_stride, int n, int h,
+                                      int w, int c_half, void* out, int out_pix_stride, void* stream);
+
+/* ---- engine level (what B200Model / B200GPUWorker.process_batch bind) ------------------------------------------ */
+
+typedef struct b200_engine b200_engine;
+
+/* Builds an engine from a plan+weights blob (produced by rdb_b200.lowering from a torchvision-style module; BatchNorm
+ * folded, bf16 conv weights). Replaces GPUWorker model load `model_registry[name].cpu().to(device).eval()`
+ * (scheduler.py:409-417, 508-515). model_kind may be NULL/"" (accept whatever the blob holds). Allocates all device
+ * memory for `max_batch` up front. Not thread-safe: one engine per actor process, like the reference's models dict. */
+B200_API int b200_engine_create(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
+                                b200_engine** out);
+B200_API void b200_engine_destroy(b200_engine* e);
+B200_API int b200_engine_info(b200_engine* e, int* in_h, int* in_w, int* out_dim, int* max_batch, int* n_ops);
+B200_API int b200_engine_set_graphs(b200_engine* e, int enabled); /* CUDA-graph replay per batch size (default on) */
+B200_API long long b200_engine_launch_count(b200_engine* e);      /* kernels launched so far by this engine */
+/* Device pointer of an activation buffer (-1 = model input NHWC4 bf16, -2 = model output fp32), for tests/zero-copy. */
+B200_API int b200_engine_buffer(b200_engine* e, int buf, void** dev_ptr, size_t* bytes_per_image);
+
+/* Synchronising debug read of an activation buffer (first `batch` images) into host memory; used by per-layer parity tests. */
+B200_API int b200_engine_read_buffer(b200_engine* e, int buf, int batch, void* host_dst);
+
+/* Batch collate fused with preprocessing: n uint8 HWC images (packed in one buffer at `offsets`, sizes hw[n][2]) ->
+ * padded NHWC(C=4) bf16 batch of `padded_batch` images, normalised with the blob's mean/std; slots >= n are zero.
+ * Replaces torch.stack(batch.inputs) (scheduler.py:443) + the client-side ToTensor/Normalize/Resize
+ * (profiling/run_profiler.py:63-70). mode: 0 identity (sizes must equal the model input), 1 pad top-left, 2 bilinear
+ * resize, 3 letterbox. src_on_device=0: `packed` is host memory (pinned for an async copy) and is staged with one H2D
+ * copy; 1: it is already a device pointer. out = NULL writes straight into the engine's input buffer. */
+B200_API int b200_collate(b200_engine* e, const void* packed, const uint64_t* offsets, const int32_t* hw, int n,
+                          int padded_batch, int mode, int src_on_device, size_t packed_bytes, void* out_nhwc_bf16,
+                          void* stream);
+/* Same for reference-native requests: n already-normalised fp32 CHW tensors stacked as [n][3][H][W]
+ * (293-project/src/test_scheduler.py:89 submits torch.randn(3,224,224)). */
+B200_API int b200_collate_f32(b200_engine* e, const float* stacked_chw, int n, int padded_batch, int src_on_device,
+                              void* out_nhwc_bf16, void* stream);
+
+/* Forward pass of `batch` images. in = NULL or the engine input buffer: run in place; otherwise it is copied in first.
+ * out (host or device, fp32 [batch][out_dim]) receives the result with an async copy on `stream`; NULL skips the copy.
+ * Replaces `outputs = model(inputs)` and `outputs.cpu()` (scheduler.py:449-450, 468). No host synchronisation inside. */
+B200_API int b200_infer(b200_engine* e, const void* in_nhwc_bf16, int batch, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,126 @@
+"""ORACLE (test infrastructure only — never imported by the product path).
+
+CPU interpreter of a libb200infer plan blob in plain PyTorch fp32.  It replays the fused op list with the same storage
+precision as the CUDA engine (bf16 activations / conv weights, fp32 accumulation, fp32 heads), so it serves two checks:
+  * lowering check (no GPU needed): interpreter(plan(model)) ~= model(x) of the torchvision fp32 reference
+    (scheduler.py:449-450 `outputs = model(inputs)`) within the north-star tolerance;
+  * kernel check (GPU): every activation buffer of the CUDA engine ~= the interpreter's buffer of the same id.
+Parity of this interpreter is pinned by tests/test_lowering.py against torchvision's own forward.
+"""
+import struct
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
+    OP_YOLO_DECODE = range(1, 12)
+
+
+def _bf16(x):
+    return x.to(torch.bfloat16).float()
+
+
+def _act(y, a):
+    if a == 1:
+        return F.relu(y)
+    if a == 2:
+        return F.silu(y)
+    if a == 3:
+        return torch.sigmoid(y)
+    return y
+
+
+def stem_cout_tile(cout):
+    return 32 if cout % 32 == 0 else (24 if cout % 24 == 0 else 16)
+
+
+class PlanInterpreter:
+    def __init__(self, blob, parse_blob):
+        self.hdr, self.bufs, self.ops, self.weights = parse_blob(blob)
+        self.wbytes = np.frombuffer(self.weights, dtype=np.uint8)
+
+    def _f32(self, off, n):
+        return torch.from_numpy(self.wbytes[off:off + 4 * n].view(np.float32).copy())
+
+    def _bf16w(self, off, n):
+        bits = self.wbytes[off:off + 2 * n].view(np.uint16).astype(np.int32) << 16
+        return torch.from_numpy(bits.view(np.float32).copy())
+
+    def run(self, x_nhwc4, keep_all=False):
+        """x_nhwc4: float tensor [N, H, W, 4] holding bf16-representable values. Returns (out [N, out_dim], buffers)."""
+        n = x_nhwc4.shape[0]
+        B = [None] * len(self.bufs)
+        for i, (h, w, c, dt) in enumerate(self.bufs):
+            B[i] = torch.zeros(n, h, w, c)
+        B[self.hdr["in_buf"]] = _bf16(x_nhwc4.float())
+        for op in self.ops:
+            t, p = op["type"], op["p"]
+            if t == OP_CONV:
+                cin, cout, k, s, pad, act = p[2], p[5], p[8], p[9], p[10], p[11]
+                x = B[p[0]][..., p[1]:p[1] + cin].permute(0, 3, 1, 2)
+                w = self._bf16w(op["w_off"], cout * k * k * cin).view(cout, k, k, cin).permute(0, 3, 1, 2)
+                b = self._f32(op["b_off"], cout)
+                y = F.conv2d(x, w, b, stride=s, padding=pad)
+                if p[6] >= 0:
+                    y = y + B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
+                B[p[3]][..., p[4]:p[4] + cout] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+            elif t == OP_STEM:
+                cout, k, s, pad, act = p[5], p[8], p[9], p[10], p[11]
+                ct = stem_cout_tile(cout)
+                cpad = (cout + ct - 1) // ct * ct
+                x = B[p[0]][..., :3].permute(0, 3, 1, 2)
+                w = self._f32(op["w_off"], k * k * 3 * cpad).view(k, k, 3, cpad)[..., :cout].permute(3, 2, 0, 1)
+                b = self._f32(op["b_off"], cpad)[:cout]
+                y = F.conv2d(x, w, b, stride=s, padding=pad)
+                B[p[3]][..., p[4]:p[4] + cout] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+            elif t == OP_DWCONV:
+                c, s, act = p[2], p[9], p[11]
+                x = B[p[0]][..., p[1]:p[1] + c].permute(0, 3, 1, 2)
+                w = self._f32(op["w_off"], 9 * c).view(3, 3, c).permute(2, 0, 1).unsqueeze(1)
+                b = self._f32(op["b_off"], c)
+                y = F.conv2d(x, w, b, stride=s, padding=1, groups=c)
+                B[p[3]][..., p[4]:p[4] + c] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+            elif t == OP_MAXPOOL:
+                c, k, s, pad = p[2], p[8], p[9], p[10]
+                x = B[p[0]][..., p[1]:p[1] + c].permute(0, 3, 1, 2)
+                B[p[3]][..., p[4]:p[4] + c] = F.max_pool2d(x, k, s, pad).permute(0, 2, 3, 1)
+            elif t == OP_AVGPOOL:
+                c = p[2]
+                x = B[p[0]][..., p[1]:p[1] + c]
+                B[p[3]] = x.mean(dim=(1, 2)).view(n, 1, 1, c)
+            elif t == OP_FC:
+                k, j, act = p[2], p[5], p[11]
+                scale = struct.unpack("<f", struct.pack("<i", p[12]))[0]
+                x = B[p[0]].view(n, -1)[:, :k]
+                w = self._f32(op["w_off"], j * k).view(j, k)
+                b = self._f32(op["b_off"], j)
+                B[p[3]] = _act((x @ w.t()) * scale + b, act).view(n, 1, 1, j)
+            elif t == OP_SCALE:
+                c = p[2]
+                g = B[p[12]].view(n, 1, 1, -1)[..., :c]
+                B[p[3]][..., p[4]:p[4] + c] = _bf16(B[p[0]][..., p[1]:p[1] + c] * g)
+            elif t == OP_COPY:
+                c = p[2]
+                B[p[3]][..., p[4]:p[4] + c] = B[p[0]][..., p[1]:p[1] + c]
+            elif t == OP_UPSAMPLE:
+                c = p[2]
+                x = B[p[0]][..., p[1]:p[1] + c]
+                B[p[3]][..., p[4]:p[4] + c] = x.repeat_interleave(2, dim=1).repeat_interleave(2, dim=2)
+            elif t == OP_SHUFFLE:
+                c = p[2]
+                a = B[p[0]][..., p[1]:p[1] + c]
+                b = B[p[12]][..., p[13]:p[13] + c]
+                B[p[3]][..., p[4]:p[4] + 2 * c] = torch.stack([a, b], dim=-1).reshape(*a.shape[:-1], 2 * c)
+            else:
+                raise NotImplementedError("op type %d" % t)
+        out = B[self.hdr["out_buf"]].view(n, -1)
+        return out, (B if keep_all else None)
+
+
+def to_nhwc4(x_nchw):
+    """[N,3,H,W] float -> [N,H,W,4] float with bf16-rounded values (what the collate kernel produces)."""
+    n, c, h, w = x_nchw.shape
+    out = torch.zeros(n, h, w, 4)
+    out[..., :3] = _bf16(x_nchw.float()).permute(0, 2, 3, 1)
+    return out

@@ -3,6 +3,7 @@
 #include "../../include/b200infer.h"
 #include "common.h"
 #include "conv_gemm.cuh"
+#include "kernels.cuh"
 
 using namespace b200;
 
@@ -30,6 +31,66 @@ int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_st
   ConvLaunch l;
   B200_TRY(conv_prepare(s, &l));
   return conv_launch(l, static_cast<cudaStream_t>(stream));
+}
+
+int b200_stem_cout_tile(int cout) { return stem_cout_tile(cout); }
+
+int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight, const float* bias, void* out, int cout,
+                        int out_pix_stride, int ksize, int stride, int pad, int act, void* stream) {
+  const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;
+  return stem_conv_launch(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, cout, out_pix_stride),
+                          weight, bias, ksize, stride, pad, act, static_cast<cudaStream_t>(stream));
+}
+
+int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
+                        const float* bias, void* out, int out_pix_stride, int stride, int act, void* stream) {
+  const int ho = (h - 1) / stride + 1, wo = (w - 1) / stride + 1;
+  return dwconv3x3_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                          make_view(out, n, ho, wo, c, out_pix_stride), weight, bias, stride, act, nullptr,
+                          static_cast<cudaStream_t>(stream));
+}
+
+int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out, int out_pix_stride,
+                      int ksize, int stride, int pad, void* stream) {
+  const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;
+  return maxpool_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                        make_view(out, n, ho, wo, c, out_pix_stride), ksize, stride, pad,
+                        static_cast<cudaStream_t>(stream));
+}
+
+int b200_global_avgpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, float* out, void* stream) {
+  return global_avgpool_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride), out,
+                               static_cast<cudaStream_t>(stream));
+}
+
+int b200_fc(const float* x, const float* w, const float* b, float* out, int n, int k, int j, float x_scale, int act,
+            void* stream) {
+  return fc_launch(x, w, b, out, n, k, j, x_scale, act, static_cast<cudaStream_t>(stream));
+}
+
+int b200_channel_scale_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* gate, void* out,
+                            int out_pix_stride, void* stream) {
+  return channel_scale_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                              make_view(out, n, h, w, c, out_pix_stride), gate, static_cast<cudaStream_t>(stream));
+}
+
+int b200_copy_channels_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out, int out_pix_stride,
+                            void* stream) {
+  return copy_channels_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                              make_view(out, n, h, w, c, out_pix_stride), static_cast<cudaStream_t>(stream));
+}
+
+int b200_upsample2x_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out, int out_pix_stride,
+                         void* stream) {
+  return upsample2x_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                           make_view(out, n, 2 * h, 2 * w, c, out_pix_stride), static_cast<cudaStream_t>(stream));
+}
+
+int b200_shuffle_concat_nhwc(const void* a, int a_pix_stride, const void* b, int b_pix_stride, int n, int h, int w,
+                             int c_half, void* out, int out_pix_stride, void* stream) {
+  return shuffle_concat_launch(make_view(const_cast<void*>(a), n, h, w, c_half, a_pix_stride),
+                               make_view(const_cast<void*>(b), n, h, w, c_half, b_pix_stride),
+                               make_view(out, n, h, w, 2 * c_half, out_pix_stride), static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

@@ -1,0 +1,342 @@
+#include "engine.h"
+
+#include <algorithm>
+
+using namespace b200;
+
+namespace b200 {
+
+Engine::~Engine() {
+  cudaSetDevice(device);
+  for (auto& kv : plans)
+    if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
+  for (char* p : buf_dev) cudaFree(p);
+  cudaFree(weights_dev);
+  cudaFree(lut_dev);
+  cudaFree(stage_dev);
+  cudaFree(items_dev);
+  cudaFree(stage_f32_dev);
+  if (items_host) cudaFreeHost(items_host);
+  if (capture_stream) cudaStreamDestroy(capture_stream);
+}
+
+int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_batch_in, int device_in) {
+  if (!blob || nbytes < sizeof(BlobHeader)) return fail(B200_ERR_BLOB, "engine: blob too small");
+  memcpy(&hdr, blob, sizeof(hdr));
+  if (memcmp(hdr.magic, "B200PLAN", 8) != 0 || hdr.version != 1) return fail(B200_ERR_BLOB, "engine: bad magic/version");
+  hdr.model_kind[31] = 0;
+  kind = hdr.model_kind;
+  if (kind_in && kind_in[0] && kind != kind_in)
+    return fail(B200_ERR_BLOB, "engine: blob is for model '" + kind + "', not '" + kind_in + "'");
+  const size_t tables = sizeof(BlobHeader) + size_t(hdr.n_bufs) * sizeof(BufRec) + size_t(hdr.n_ops) * sizeof(OpRec);
+  if (tables > nbytes || hdr.weights_offset < tables || hdr.weights_offset + hdr.weights_bytes > nbytes)
+    return fail(B200_ERR_BLOB, "engine: truncated blob");
+  if (max_batch_in <= 0) return fail(B200_ERR_INVALID, "engine: max_batch must be positive");
+  max_batch = max_batch_in;
+  device = device_in;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(B200_ERR_NO_DEVICE, "engine: no CUDA device");
+  B200_CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B200_CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(B200_ERR_NO_DEVICE, std::string("engine: needs an sm_100 device, found ") + prop.name);
+
+  const char* base = static_cast<const char*>(blob);
+  bufs.resize(hdr.n_bufs);
+  memcpy(bufs.data(), base + sizeof(BlobHeader), size_t(hdr.n_bufs) * sizeof(BufRec));
+  ops.resize(hdr.n_ops);
+  memcpy(ops.data(), base + sizeof(BlobHeader) + size_t(hdr.n_bufs) * sizeof(BufRec), size_t(hdr.n_ops) * sizeof(OpRec));
+  if (hdr.in_buf < 0 || hdr.in_buf >= int(hdr.n_bufs) || hdr.out_buf < 0 || hdr.out_buf >= int(hdr.n_bufs))
+    return fail(B200_ERR_BLOB, "engine: bad in/out buffer ids");
+  for (const OpRec& o : ops) {
+    const int ids[3] = {o.p[0], o.p[3], o.p[6]};
+    for (int k = 0; k < 3; ++k)
+      if (ids[k] >= int(hdr.n_bufs) || (k < 2 && ids[k] < 0)) return fail(B200_ERR_BLOB, "engine: op references unknown buffer");
+    const int64_t offs[4] = {o.w_off, o.b_off, o.w2_off, o.b2_off};
+    for (int64_t off : offs)
+      if (off >= int64_t(hdr.weights_bytes)) return fail(B200_ERR_BLOB, "engine: weight offset out of range");
+  }
+
+  B200_CUDA_OK(cudaMalloc(&weights_dev, std::max<uint64_t>(hdr.weights_bytes, 256)));
+  B200_CUDA_OK(cudaMemcpy(weights_dev, base + hdr.weights_offset, hdr.weights_bytes, cudaMemcpyHostToDevice));
+  buf_dev.assign(hdr.n_bufs, nullptr);
+  for (uint32_t b = 0; b < hdr.n_bufs; ++b) {
+    const size_t bytes = buf_bytes_per_image(b) * size_t(max_batch) + 256;
+    B200_CUDA_OK(cudaMalloc(&buf_dev[b], bytes));
+    B200_CUDA_OK(cudaMemset(buf_dev[b], 0, bytes));
+  }
+  uint16_t lut[3 * 256];
+  build_norm_lut(hdr.mean, hdr.stdv, lut);
+  B200_CUDA_OK(cudaMalloc(&lut_dev, sizeof(lut)));
+  B200_CUDA_OK(cudaMemcpy(lut_dev, lut, sizeof(lut), cudaMemcpyHostToDevice));
+  B200_CUDA_OK(cudaMalloc(&items_dev, sizeof(CollateItem) * max_batch));
+  B200_CUDA_OK(cudaMallocHost(&items_host, sizeof(CollateItem) * max_batch));
+  B200_CUDA_OK(cudaStreamCreateWithFlags(&capture_stream, cudaStreamNonBlocking));
+  return B200_OK;
+}
+
+View Engine::view(int buf, int coff, int c, int batch) const {
+  const BufRec& b = bufs[buf];
+  return make_view(buf_dev[buf], batch, b.h, b.w, c, b.c, coff);
+}
+
+int Engine::plan_for(int batch, BatchPlan** out) {
+  auto it = plans.find(batch);
+  if (it != plans.end()) {
+    *out = it->second.get();
+    return B200_OK;
+  }
+  std::unique_ptr<BatchPlan> plan(new BatchPlan);
+  plan->batch = batch;
+  plan->ops.resize(ops.size());
+  for (size_t i = 0; i < ops.size(); ++i) {
+    PreparedOp& po = plan->ops[i];
+    po.rec = ops[i];
+    const int32_t* p = po.rec.p;
+    if (po.rec.type == OP_CONV) {
+      ConvSpec s;
+      s.in = view(p[0], p[1], p[2], batch);
+      s.out = view(p[3], p[4], p[5], batch);
+      if (p[6] >= 0) s.res = view(p[6], p[7], p[5], batch);
+      s.w = weights_dev + po.rec.w_off;
+      s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
+      s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];
+      int rc = conv_prepare(s, &po.conv);
+      if (rc != 0) return fail(rc, "op " + std::to_string(i) + ": " + last_error_cstr());
+    }
+  }
+  *out = plan.get();
+  plans[batch] = std::move(plan);
+  return B200_OK;
+}
+
+int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
+  const int batch = plan.batch;
+  for (int i = first; i <= last; ++i) {
+    PreparedOp& po = plan.ops[i];
+    const int32_t* p = po.rec.p;
+    const char* W = weights_dev;
+    int rc = B200_OK;
+    switch (po.rec.type) {
+      case OP_CONV:
+        rc = conv_launch(po.conv, stream);
+        break;
+      case OP_STEM:
+        rc = stem_conv_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
+                              reinterpret_cast<const float*>(W + po.rec.w_off),
+                              reinterpret_cast<const float*>(W + po.rec.b_off), p[8], p[9], p[10], p[11], stream);
+        break;
+      case OP_MAXPOOL:
+        rc = maxpool_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), p[8], p[9], p[10], stream);
+        break;
+      case OP_AVGPOOL:
+        rc = global_avgpool_launch(view(p[0], p[1], p[2], batch), reinterpret_cast<float*>(buf_dev[p[3]]), stream);
+        break;
+      case OP_FC: {
+        float scale;
+        memcpy(&scale, &p[12], 4);
+        rc = fc_launch(reinterpret_cast<const float*>(buf_dev[p[0]]), reinterpret_cast<const float*>(W + po.rec.w_off),
+                       reinterpret_cast<const float*>(W + po.rec.b_off), reinterpret_cast<float*>(buf_dev[p[3]]), batch,
+                       p[2], p[5], scale, p[11], stream);
+        break;
+      }
+      case OP_DWCONV:
+        rc = dwconv3x3_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
+                              reinterpret_cast<const float*>(W + po.rec.w_off),
+                              reinterpret_cast<const float*>(W + po.rec.b_off), p[9], p[11], nullptr, stream);
+        break;
+      case OP_SCALE:
+        rc = channel_scale_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
+                                  reinterpret_cast<const float*>(buf_dev[p[12]]), stream);
+        break;
+      case OP_COPY:
+        rc = copy_channels_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), stream);
+        break;
+      case OP_UPSAMPLE:
+        rc = upsample2x_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), stream);
+        break;
+      case OP_SHUFFLE:
+        rc = shuffle_concat_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[2], batch),
+                                   view(p[3], p[4], p[5], batch), stream);
+        break;
+      default:
+        rc = fail(B200_ERR_BLOB, "engine: unknown op type " + std::to_string(po.rec.type));
+    }
+    if (rc != 0) return fail(rc, "op " + std::to_string(i) + " (type " + std::to_string(po.rec.type) + "): " + last_error_cstr());
+  }
+  return B200_OK;
+}
+
+int Engine::run(int batch, cudaStream_t stream) {
+  if (batch <= 0 || batch > max_batch)
+    return fail(B200_ERR_INVALID, "engine: batch " + std::to_string(batch) + " outside [1, " + std::to_string(max_batch) + "]");
+  BatchPlan* plan = nullptr;
+  B200_TRY(plan_for(batch, &plan));
+  const int n = static_cast<int>(plan->ops.size());
+  if (!use_graphs || !plan->warmed) {
+    // first run of a batch size is eager: it sets kernel attributes and surfaces shape errors before any capture
+    B200_TRY(run_ops(*plan, stream, 0, n - 1));
+    plan->warmed = true;
+    launches += n;
+    return B200_OK;
+  }
+  if (!plan->graph) {
+    cudaGraph_t g = nullptr;
+    B200_CUDA_OK(cudaStreamBeginCapture(capture_stream, cudaStreamCaptureModeThreadLocal));
+    int rc = run_ops(*plan, capture_stream, 0, n - 1);
+    cudaError_t e = cudaStreamEndCapture(capture_stream, &g);
+    if (rc != 0) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    if (e != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&plan->graph, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(e));
+  }
+  B200_CUDA_OK(cudaGraphLaunch(plan->graph, stream));
+  launches += n;
+  return B200_OK;
+}
+
+}  // namespace b200
+
+// ================================================================================================ C ABI, engine level
+struct b200_engine {
+  Engine e;
+};
+
+extern "C" {
+
+int b200_engine_create(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
+                       b200_engine** out) {
+  if (!out) return fail(B200_ERR_INVALID, "b200_engine_create: out is null");
+  *out = nullptr;
+  b200_engine* h = new (std::nothrow) b200_engine;
+  if (!h) return fail(B200_ERR_INVALID, "b200_engine_create: out of host memory");
+  int rc = h->e.init(model_kind, blob, nbytes, max_batch, device);
+  if (rc != 0) {
+    std::string msg = last_error_cstr();
+    delete h;
+    return fail(rc, msg);
+  }
+  *out = h;
+  return B200_OK;
+}
+
+void b200_engine_destroy(b200_engine* h) { delete h; }
+
+int b200_engine_info(b200_engine* h, int* in_h, int* in_w, int* out_dim, int* max_batch, int* n_ops) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  if (in_h) *in_h = h->e.hdr.in_h;
+  if (in_w) *in_w = h->e.hdr.in_w;
+  if (out_dim) *out_dim = h->e.hdr.out_dim;
+  if (max_batch) *max_batch = h->e.max_batch;
+  if (n_ops) *n_ops = static_cast<int>(h->e.ops.size());
+  return B200_OK;
+}
+
+int b200_engine_set_graphs(b200_engine* h, int enabled) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  h->e.use_graphs = enabled != 0;
+  return B200_OK;
+}
+
+long long b200_engine_launch_count(b200_engine* h) { return h ? h->e.launches : 0; }
+
+int b200_engine_buffer(b200_engine* h, int buf, void** dev_ptr, size_t* bytes_per_image) {
+  if (!h || buf < -2 || buf >= static_cast<int>(h->e.bufs.size())) return fail(B200_ERR_INVALID, "bad buffer id");
+  if (buf == -1) buf = h->e.hdr.in_buf;
+  if (buf == -2) buf = h->e.hdr.out_buf;
+  if (dev_ptr) *dev_ptr = h->e.buf_dev[buf];
+  if (bytes_per_image) *bytes_per_image = h->e.buf_bytes_per_image(buf);
+  return B200_OK;
+}
+
+int b200_engine_read_buffer(b200_engine* h, int buf, int batch, void* host_dst) {
+  if (!h || buf < -2 || buf >= static_cast<int>(h->e.bufs.size())) return fail(B200_ERR_INVALID, "bad buffer id");
+  if (batch <= 0 || batch > h->e.max_batch || !host_dst) return fail(B200_ERR_INVALID, "bad batch / destination");
+  if (buf == -1) buf = h->e.hdr.in_buf;
+  if (buf == -2) buf = h->e.hdr.out_buf;
+  B200_CUDA_OK(cudaDeviceSynchronize());
+  B200_CUDA_OK(cudaMemcpy(host_dst, h->e.buf_dev[buf], h->e.buf_bytes_per_image(buf) * batch, cudaMemcpyDeviceToHost));
+  return B200_OK;
+}
+
+int b200_collate(b200_engine* h, const void* packed, const uint64_t* offsets, const int32_t* hw, int n, int padded_batch,
+                 int mode, int src_on_device, size_t packed_bytes, void* out_nhwc_bf16, void* stream_) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  Engine& e = h->e;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n < 0 || padded_batch < n || padded_batch > e.max_batch || padded_batch <= 0)
+    return fail(B200_ERR_INVALID, "b200_collate: need 0 <= n <= padded_batch <= max_batch");
+  if (n > 0 && (!packed || !offsets || !hw)) return fail(B200_ERR_INVALID, "b200_collate: null input");
+  for (int i = 0; i < n; ++i) {
+    e.items_host[i].offset = offsets[i];
+    e.items_host[i].h = hw[2 * i];
+    e.items_host[i].w = hw[2 * i + 1];
+    if (hw[2 * i] <= 0 || hw[2 * i + 1] <= 0) return fail(B200_ERR_INVALID, "b200_collate: empty image");
+    if (offsets[i] + uint64_t(hw[2 * i]) * hw[2 * i + 1] * 3 > packed_bytes)
+      return fail(B200_ERR_INVALID, "b200_collate: image " + std::to_string(i) + " exceeds the packed buffer");
+    if (mode == COLLATE_IDENTITY && (hw[2 * i] != e.hdr.in_h || hw[2 * i + 1] != e.hdr.in_w))
+      return fail(B200_ERR_INVALID, "b200_collate: image " + std::to_string(i) + " is not the model input size");
+  }
+  const uint8_t* src = static_cast<const uint8_t*>(packed);
+  if (!src_on_device && n > 0) {
+    if (packed_bytes > e.stage_bytes) {
+      if (e.stage_dev) B200_CUDA_OK(cudaFree(e.stage_dev));
+      e.stage_dev = nullptr;
+      e.stage_bytes = 0;
+      const size_t want = packed_bytes + packed_bytes / 4 + 4096;
+      B200_CUDA_OK(cudaMalloc(&e.stage_dev, want));
+      e.stage_bytes = want;
+    }
+    B200_CUDA_OK(cudaMemcpyAsync(e.stage_dev, packed, packed_bytes, cudaMemcpyHostToDevice, stream));
+    src = e.stage_dev;
+  }
+  if (n > 0)
+    B200_CUDA_OK(cudaMemcpyAsync(e.items_dev, e.items_host, sizeof(CollateItem) * n, cudaMemcpyHostToDevice, stream));
+  void* out = out_nhwc_bf16 ? out_nhwc_bf16 : e.buf_dev[e.hdr.in_buf];
+  B200_TRY(collate_u8_launch(src, e.items_dev, e.items_host, n, padded_batch, e.hdr.in_h, e.hdr.in_w, mode,
+                             e.hdr.pre_fill, e.lut_dev, out, stream));
+  e.launches += 1;
+  return B200_OK;
+}
+
+int b200_collate_f32(b200_engine* h, const float* stacked_chw, int n, int padded_batch, int src_on_device,
+                     void* out_nhwc_bf16, void* stream_) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  Engine& e = h->e;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n < 0 || padded_batch < n || padded_batch > e.max_batch || padded_batch <= 0)
+    return fail(B200_ERR_INVALID, "b200_collate_f32: need 0 <= n <= padded_batch <= max_batch");
+  const size_t per = size_t(3) * e.hdr.in_h * e.hdr.in_w;
+  const float* src = stacked_chw;
+  if (!src_on_device && n > 0) {
+    if (!e.stage_f32_dev) B200_CUDA_OK(cudaMalloc(&e.stage_f32_dev, per * sizeof(float) * e.max_batch));
+    B200_CUDA_OK(cudaMemcpyAsync(e.stage_f32_dev, stacked_chw, per * sizeof(float) * n, cudaMemcpyHostToDevice, stream));
+    src = e.stage_f32_dev;
+  }
+  void* out = out_nhwc_bf16 ? out_nhwc_bf16 : e.buf_dev[e.hdr.in_buf];
+  B200_TRY(collate_f32chw_launch(src, n, padded_batch, e.hdr.in_h, e.hdr.in_w, out, stream));
+  e.launches += 1;
+  return B200_OK;
+}
+
+int b200_infer(b200_engine* h, const void* in_nhwc_bf16, int batch, float* out, void* stream_) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  Engine& e = h->e;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (batch <= 0 || batch > e.max_batch) return fail(B200_ERR_INVALID, "b200_infer: batch outside [1, max_batch]");
+  char* in_buf = e.buf_dev[e.hdr.in_buf];
+  if (in_nhwc_bf16 && in_nhwc_bf16 != in_buf)
+    B200_CUDA_OK(cudaMemcpyAsync(in_buf, in_nhwc_bf16, e.buf_bytes_per_image(e.hdr.in_buf) * batch,
+                                 cudaMemcpyDeviceToDevice, stream));
+  B200_TRY(e.run(batch, stream));
+  if (out)
+    B200_CUDA_OK(cudaMemcpyAsync(out, e.buf_dev[e.hdr.out_buf], size_t(e.hdr.out_dim) * sizeof(float) * batch,
+                                 cudaMemcpyDefault, stream));
+  return B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,126 @@
+// Fully-connected heads (classifier FC, Squeeze-Excitation FCs) and the SE channel scaling.
+//
+// fc: out[n][j] = act(x_scale * sum_k x[n][k] * w[j][k] + b[j]) in fp32 (the classifier is kept in fp32: logits carry the
+// parity bound).  A block stages 8 batch rows of x in shared memory; each warp produces 4 outputs for those 8 rows,
+// lanes split K with float4 loads (coalesced over a weight row) and combine with warp shuffles.
+// Replaces nn.Linear (tv resnet.py:280 `fc`, shufflenetv2.py:162, efficientnet.py:306 classifier) and the two 1x1
+// convolutions of SqueezeExcitation (tv ops/misc.py `SqueezeExcitation._scale`).
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace b200 {
+
+static constexpr int FC_NB = 8;   // batch rows per block
+static constexpr int FC_JW = 4;   // outputs per warp
+static constexpr int FC_WARPS = 8;
+
+__global__ void __launch_bounds__(FC_WARPS * 32)
+fc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, float* __restrict__ out,
+          int N, int K, int J, float x_scale, int act) {
+  extern __shared__ __align__(16) float s_x[];  // [FC_NB][K]
+  const int n0 = blockIdx.y * FC_NB;
+  const int K4 = K >> 2;
+  for (int i = threadIdx.x; i < FC_NB * K4; i += blockDim.x) {
+    const int r = i / K4, c = i - r * K4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n0 + r < N) v = reinterpret_cast<const float4*>(x + static_cast<size_t>(n0 + r) * K)[c];
+    reinterpret_cast<float4*>(s_x)[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int j0 = (blockIdx.x * FC_WARPS + warp) * FC_JW;
+  if (j0 >= J) return;
+  float acc[FC_JW][FC_NB];
+#pragma unroll
+  for (int a = 0; a < FC_JW; ++a)
+#pragma unroll
+    for (int r = 0; r < FC_NB; ++r) acc[a][r] = 0.f;
+  const float4* wr[FC_JW];
+#pragma unroll
+  for (int a = 0; a < FC_JW; ++a) wr[a] = reinterpret_cast<const float4*>(w + static_cast<size_t>(min(j0 + a, J - 1)) * K);
+  for (int c = lane; c < K4; c += 32) {
+    float4 wv[FC_JW];
+#pragma unroll
+    for (int a = 0; a < FC_JW; ++a) wv[a] = wr[a][c];
+#pragma unroll
+    for (int r = 0; r < FC_NB; ++r) {
+      const float4 xv = reinterpret_cast<const float4*>(s_x)[r * K4 + c];
+#pragma unroll
+      for (int a = 0; a < FC_JW; ++a) {
+        acc[a][r] = fmaf(xv.x, wv[a].x, acc[a][r]);
+        acc[a][r] = fmaf(xv.y, wv[a].y, acc[a][r]);
+        acc[a][r] = fmaf(xv.z, wv[a].z, acc[a][r]);
+        acc[a][r] = fmaf(xv.w, wv[a].w, acc[a][r]);
+      }
+    }
+  }
+#pragma unroll
+  for (int a = 0; a < FC_JW; ++a)
+#pragma unroll
+    for (int r = 0; r < FC_NB; ++r) {
+      float v = acc[a][r];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      acc[a][r] = v;
+    }
+  // lane (a * FC_NB + r) writes output (j0 + a, n0 + r)
+  const int a = lane / FC_NB, r = lane % FC_NB;
+  float v = 0.f;
+#pragma unroll
+  for (int aa = 0; aa < FC_JW; ++aa)
+#pragma unroll
+    for (int rr = 0; rr < FC_NB; ++rr)
+      if (aa == a && rr == r) v = acc[aa][rr];
+  if (j0 + a < J && n0 + r < N) out[static_cast<size_t>(n0 + r) * J + j0 + a] = apply_act(v * x_scale + b[j0 + a], act);
+}
+
+int fc_launch(const float* x, const float* w, const float* b, float* out, int n, int k, int j, float x_scale, int act,
+              cudaStream_t stream) {
+  if (k % 4) return fail(B200_ERR_INVALID, "fc: K must be a multiple of 4");
+  if (k > 6144) return fail(B200_ERR_INVALID, "fc: K too large (max 6144)");
+  const size_t smem = size_t(FC_NB) * k * sizeof(float);
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FC_NB * 6144 * 4));
+    configured[dev & 63] = true;
+  }
+  dim3 grid((j + FC_WARPS * FC_JW - 1) / (FC_WARPS * FC_JW), (n + FC_NB - 1) / FC_NB);
+  fc_kernel<<<grid, FC_WARPS * 32, smem, stream>>>(x, w, b, out, n, k, j, x_scale, act);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+// y[n,h,w,c] = x[n,h,w,c] * gate[n][c]
+__global__ void __launch_bounds__(256)
+channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C8,
+                     const float* __restrict__ gate, long long total) {
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int c8 = static_cast<int>(idx % C8);
+  const long long pix = idx / C8;
+  const int n = static_cast<int>(pix / HW);
+  const uint4 v = *reinterpret_cast<const uint4*>(in + pix * in_ps + c8 * 8);
+  const float4 g0 = *reinterpret_cast<const float4*>(gate + static_cast<size_t>(n) * C8 * 8 + c8 * 8);
+  const float4 g1 = *reinterpret_cast<const float4*>(gate + static_cast<size_t>(n) * C8 * 8 + c8 * 8 + 4);
+  uint4 o;
+  o.x = pack_bf16x2(bf16_lo(v.x) * g0.x, bf16_hi(v.x) * g0.y);
+  o.y = pack_bf16x2(bf16_lo(v.y) * g0.z, bf16_hi(v.y) * g0.w);
+  o.z = pack_bf16x2(bf16_lo(v.z) * g1.x, bf16_hi(v.z) * g1.y);
+  o.w = pack_bf16x2(bf16_lo(v.w) * g1.z, bf16_hi(v.w) * g1.w);
+  *reinterpret_cast<uint4*>(out + pix * out_ps + c8 * 8) = o;
+}
+
+int channel_scale_launch(const View& in, const View& out, const float* gate, cudaStream_t stream) {
+  if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W)
+    return fail(B200_ERR_INVALID, "channel_scale: shape mismatch");
+  const long long total = static_cast<long long>(in.N) * in.H * in.W * (in.C / 8);
+  channel_scale_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
+      static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride,
+      in.H * in.W, in.C / 8, gate, total);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200

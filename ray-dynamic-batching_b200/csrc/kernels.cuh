@@ -1,0 +1,45 @@
+// Host-side launchers of the bandwidth-bound kernels (collate, small-Cin stem conv, depthwise conv, pooling, FC, SE,
+// upsample/concat, YOLO head decode).  All activations NHWC bf16 described by b200::View.
+#pragma once
+#include "common.h"
+
+namespace b200 {
+
+// ---- collate (collate.cu) ----
+struct CollateItem {
+  uint64_t offset;  // byte offset of the image inside the staged uint8 buffer (multiple of 16 for the fast path)
+  int32_t h, w;     // source height / width (HWC, 3 channels)
+};
+enum : int { COLLATE_IDENTITY = 0, COLLATE_PAD = 1, COLLATE_RESIZE = 2, COLLATE_LETTERBOX = 3 };
+void build_norm_lut(const float mean[3], const float stdv[3], uint16_t lut[3 * 256]);
+int collate_u8_launch(const uint8_t* src_base, const CollateItem* items_dev, const CollateItem* items_host, int n,
+                      int padded_batch, int out_h, int out_w, int mode, int fill, const uint16_t* lut_dev, void* out,
+                      cudaStream_t stream);
+int collate_f32chw_launch(const float* src, int n, int padded_batch, int h, int w, void* out, cudaStream_t stream);
+
+// ---- small-Cin direct convolution for the network stems (stem.cu): in C==4 (3 real), fp32 weights [k*k][4][cout] ----
+int stem_cout_tile(int cout);
+int stem_conv_launch(const View& in, const View& out, const float* w, const float* bias, int ksize, int stride, int pad,
+                     int act, cudaStream_t stream);
+
+// ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional per-(n,c) fp32 sum output for SE squeeze ----
+int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
+                     float* se_sum /* [N][C] or null, must be zeroed */, cudaStream_t stream);
+
+// ---- pooling (pool.cu) ----
+int maxpool_launch(const View& in, const View& out, int ksize, int stride, int pad, cudaStream_t stream);
+int global_avgpool_launch(const View& in, float* out /* [N][C] fp32 */, cudaStream_t stream);
+
+// ---- heads (head.cu) ----
+// out[n][j] = act(sum_k x[n][k] * w[j][k] + b[j]);  x fp32 [N][K] (optionally pre-scaled), w fp32 [J][K]
+int fc_launch(const float* x, const float* w, const float* b, float* out, int n, int k, int j, float x_scale, int act,
+              cudaStream_t stream);
+// y = x * gate[n][c]  (SE excitation), gate fp32 already passed through sigmoid
+int channel_scale_launch(const View& in, const View& out, const float* gate, cudaStream_t stream);
+
+// ---- data movement (move.cu) ----
+int copy_channels_launch(const View& in, const View& out, cudaStream_t stream);             // slice -> slice copy
+int upsample2x_launch(const View& in, const View& out, cudaStream_t stream);                // nearest, into a slice
+int shuffle_concat_launch(const View& a, const View& b, const View& out, cudaStream_t stream);  // out[2i]=a[i], out[2i+1]=b[i]
+
+}  // namespace b200

@@ -1,0 +1,147 @@
+"""B200Model: the callable that takes the place of a torchvision nn.Module in the reference's `model_registry` /
+`GPUWorker.models[name]` (293-project/src/scheduler.py:40-44, 441-450).
+
+    model = B200Model("resnet50", module)         # lowering + blob + b200_engine_create
+    logits = model(inputs)                        # inputs: [B,3,H,W] fp32 (cuda or cpu), like the reference call site
+    logits = model.infer_u8(list_of_uint8_HWC)    # engine-native path: fused collate + preprocess on the GPU
+
+Everything numeric happens in libb200infer.so; torch is used for device memory, streams and pinned host buffers only.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import lib as _lib
+from . import lowering as _lowering
+
+COLLATE_IDENTITY, COLLATE_PAD, COLLATE_RESIZE, COLLATE_LETTERBOX = 0, 1, 2, 3
+
+
+class B200Model:
+    def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True):
+        if not torch.cuda.is_available():
+            raise _lib.B200Error("B200Model needs a CUDA device (sm_100); there is no CPU fallback")
+        self.lib = _lib.load()
+        self.kind = kind
+        self.device = torch.device("cuda", device)
+        if blob is None:
+            if module is None:
+                raise ValueError("need a module to lower or a prebuilt blob")
+            pb = _lowering.lower(kind, module)
+            blob = pb.to_blob()
+            self.out_logical = pb.out_logical
+            self.op_names = list(pb.names)
+        else:
+            self.out_logical = None
+            self.op_names = None
+        self.blob = blob
+        self.max_batch = max_batch
+        self._h = ctypes.c_void_p()
+        torch.cuda.set_device(self.device)
+        _lib.check(self.lib.b200_engine_create(kind.encode(), blob, len(blob), max_batch, device,
+                                               ctypes.byref(self._h)), "b200_engine_create")
+        ih, iw, od, mb, nops = (ctypes.c_int() for _ in range(5))
+        _lib.check(self.lib.b200_engine_info(self._h, ih, iw, od, mb, nops))
+        self.in_h, self.in_w, self.out_dim, self.n_ops = ih.value, iw.value, od.value, nops.value
+        if self.out_logical is None:
+            self.out_logical = self.out_dim
+        if not use_graphs:
+            _lib.check(self.lib.b200_engine_set_graphs(self._h, 0))
+        self._pinned = None
+
+    # ---- lifecycle (mirrors .eval()/.to()/.cpu() so the reference's load/unload code keeps working) ----
+    def eval(self):
+        return self
+
+    def to(self, *_a, **_k):
+        return self
+
+    def cpu(self):
+        return self
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            self.lib.b200_engine_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- helpers ----
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def launch_count(self):
+        return int(self.lib.b200_engine_launch_count(self._h))
+
+    def buffer(self, buf_id, batch):
+        """Debug copy of an engine activation buffer: uint8 host tensor [batch, bytes_per_image] (-1 input, -2 output)."""
+        p, nb = ctypes.c_void_p(), ctypes.c_size_t()
+        _lib.check(self.lib.b200_engine_buffer(self._h, buf_id, ctypes.byref(p), ctypes.byref(nb)))
+        host = torch.empty(batch * nb.value, dtype=torch.uint8)
+        _lib.check(self.lib.b200_engine_read_buffer(self._h, buf_id, batch, _lib.ptr(host)), "b200_engine_read_buffer")
+        return host.view(batch, nb.value)
+
+    # ---- reference call site: outputs = model(inputs) ----
+    def __call__(self, inputs):
+        return self.forward(inputs)
+
+    def forward(self, inputs):
+        if inputs.dim() != 4 or inputs.shape[1] != 3 or inputs.shape[2] != self.in_h or inputs.shape[3] != self.in_w:
+            raise _lib.B200Error("expected [B,3,%d,%d] input, got %s" % (self.in_h, self.in_w, tuple(inputs.shape)))
+        b = inputs.shape[0]
+        if b > self.max_batch:
+            raise _lib.B200Error("batch %d exceeds engine max_batch %d" % (b, self.max_batch))
+        x = inputs.contiguous().float()
+        on_dev = 1 if x.is_cuda else 0
+        s = self._stream()
+        _lib.check(self.lib.b200_collate_f32(self._h, _lib.ptr(x), b, b, on_dev, None, s), "b200_collate_f32")
+        out = torch.empty(b, self.out_dim, device=self.device, dtype=torch.float32)
+        _lib.check(self.lib.b200_infer(self._h, None, b, _lib.ptr(out), s), "b200_infer")
+        return out[:, :self.out_logical]
+
+    # ---- engine-native path ----
+    def pack_u8(self, images):
+        """Packs uint8 HWC images into one pinned buffer (16-byte aligned slots). Returns (packed, offsets, hw)."""
+        n = len(images)
+        offsets = np.zeros(n, dtype=np.uint64)
+        hw = np.zeros((n, 2), dtype=np.int32)
+        total = 0
+        for i, im in enumerate(images):
+            offsets[i] = total
+            hw[i] = (im.shape[0], im.shape[1])
+            total += (im.numel() + 15) // 16 * 16
+        if self._pinned is None or self._pinned.numel() < total:
+            self._pinned = torch.empty(max(total, 1), dtype=torch.uint8, pin_memory=True)
+        for i, im in enumerate(images):
+            o = int(offsets[i])
+            self._pinned[o:o + im.numel()].copy_(im.reshape(-1))
+        return self._pinned, offsets, hw, total
+
+    def collate_u8(self, packed, offsets, hw, n, padded_batch=None, mode=COLLATE_IDENTITY, total_bytes=None):
+        padded_batch = padded_batch or n
+        on_dev = 1 if packed.is_cuda else 0
+        total = int(total_bytes if total_bytes is not None else packed.numel())
+        _lib.check(self.lib.b200_collate(self._h, _lib.ptr(packed), offsets.ctypes.data_as(ctypes.c_void_p),
+                                         hw.ctypes.data_as(ctypes.c_void_p), n, padded_batch, mode, on_dev, total, None,
+                                         self._stream()), "b200_collate")
+
+    def infer_u8(self, images, padded_batch=None, mode=COLLATE_IDENTITY, out=None):
+        """images: list of uint8 HWC tensors (host). Returns fp32 logits [n, out] on the device (padding rows dropped)."""
+        n = len(images)
+        packed, offsets, hw, total = self.pack_u8(images)
+        pb = padded_batch or n
+        self.collate_u8(packed, offsets, hw, n, pb, mode, total)
+        if out is None:
+            out = torch.empty(pb, self.out_dim, device=self.device, dtype=torch.float32)
+        _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(out), self._stream()), "b200_infer")
+        return out[:n, :self.out_logical]
+
+    def infer_resident(self, batch, out):
+        """Forward over whatever the engine input buffer holds (inputs already resident in HBM)."""
+        _lib.check(self.lib.b200_infer(self._h, None, batch, _lib.ptr(out), self._stream()), "b200_infer")
+        return out

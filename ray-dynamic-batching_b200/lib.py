@@ -22,6 +22,32 @@ SIGNATURES = {
     "b200_abi_version": (c_int, []),
     "b200_conv2d_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                  c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b200_stem_cout_tile": (c_int, [c_int]),
+    "b200_stem_conv_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                    c_int, c_int, c_int, c_void_p]),
+    "b200_dwconv3x3_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
+                                    c_int, c_int, c_void_p]),
+    "b200_maxpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int,
+                                  c_void_p]),
+    "b200_global_avgpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b200_fc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p]),
+    "b200_channel_scale_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int,
+                                        c_void_p]),
+    "b200_copy_channels_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
+    "b200_upsample2x_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
+    "b200_shuffle_concat_nhwc": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
+                                         c_void_p]),
+    "b200_engine_create": (c_int, [c_char_p, c_void_p, c_size_t, c_int, c_int, ctypes.POINTER(c_void_p)]),
+    "b200_engine_destroy": (None, [c_void_p]),
+    "b200_engine_info": (c_int, [c_void_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p]),
+    "b200_engine_set_graphs": (c_int, [c_void_p, c_int]),
+    "b200_engine_launch_count": (ctypes.c_longlong, [c_void_p]),
+    "b200_engine_buffer": (c_int, [c_void_p, c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_size_t)]),
+    "b200_engine_read_buffer": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "b200_collate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_size_t, c_void_p,
+                             c_void_p]),
+    "b200_collate_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b200_infer": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
 }
 
 

@@ -1,0 +1,292 @@
+"""Lowers torchvision-style eval-mode modules into the flat plan + weights blob that libb200infer executes.
+
+What is fused here (so that every conv kernel reads its input once and writes its output once):
+  * BatchNorm2d is folded into the preceding convolution (fp32 fold, then weights rounded to bf16, bias kept fp32);
+  * ReLU / SiLU, the residual add of a block and channel concatenation (writing into a slice) go into the conv epilogue.
+
+Blob layout (little endian): BlobHeader | BufRec[n_bufs] | OpRec[n_ops] | pad to 256 | weights section.
+See csrc/engine.h for the record definitions; `parse_blob` below is the inverse (used by the CPU plan interpreter in
+oracle/ to check the lowering without a GPU).
+"""
+import struct
+from dataclasses import dataclass
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
+    OP_YOLO_DECODE = range(1, 12)
+ACT_NONE, ACT_RELU, ACT_SILU, ACT_SIGMOID = 0, 1, 2, 3
+HEADER_FMT = "<8sIIII32siiiiii3f3fQQ"
+HEADER_SIZE = struct.calcsize(HEADER_FMT)
+BUF_FMT = "<iiii"
+OP_FMT = "<i23iqqqq"
+assert struct.calcsize(OP_FMT) == 128
+
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+
+
+def pad8(c):
+    return (c + 7) // 8 * 8
+
+
+def stem_cout_tile(cout):
+    """Mirror of b200_stem_cout_tile (csrc/stem.cu)."""
+    return 32 if cout % 32 == 0 else (24 if cout % 24 == 0 else 16)
+
+
+@dataclass
+class T:
+    """A channel slice of an activation buffer: logical tensor [N, h, w, c] stored at channel offset `coff`."""
+    buf: int
+    coff: int
+    c: int
+    h: int
+    w: int
+
+
+def act_code(m):
+    if m is None or isinstance(m, nn.Identity):
+        return ACT_NONE
+    if isinstance(m, nn.ReLU):
+        return ACT_RELU
+    if isinstance(m, nn.SiLU):
+        return ACT_SILU
+    if isinstance(m, nn.Sigmoid):
+        return ACT_SIGMOID
+    raise NotImplementedError("activation %r" % (m,))
+
+
+def fold_bn(conv: nn.Conv2d, bn: Optional[nn.BatchNorm2d]):
+    """fp32 fold of an eval-mode BatchNorm into the conv: returns (weight [Cout,Cin/g,kh,kw], bias [Cout]) in float64->32."""
+    w = conv.weight.detach().double()
+    b = conv.bias.detach().double() if conv.bias is not None else torch.zeros(w.shape[0], dtype=torch.float64)
+    if bn is not None:
+        scale = bn.weight.detach().double() / torch.sqrt(bn.running_var.detach().double() + bn.eps)
+        w = w * scale.view(-1, 1, 1, 1)
+        b = (b - bn.running_mean.detach().double()) * scale + bn.bias.detach().double()
+    return w.float(), b.float()
+
+
+class PlanBuilder:
+    def __init__(self, kind, in_h, in_w, mean=IMAGENET_MEAN, std=IMAGENET_STD, pre_fill=0):
+        self.kind = kind
+        self.in_h, self.in_w = in_h, in_w
+        self.mean, self.std, self.pre_fill = mean, std, pre_fill
+        self.bufs = []      # (h, w, c, dtype)
+        self.ops = []       # (type, p[23], w_off, b_off, w2_off, b2_off)
+        self.weights = bytearray()
+        self.in_buf = self.new_buf(in_h, in_w, 4)
+        self.out_buf = -1
+        self.out_dim = 0
+        self.names = []     # op index -> human readable name (kept out of the blob)
+
+    # ---- buffers / weights ----
+    def new_buf(self, h, w, c, dtype=0):
+        self.bufs.append((h, w, c, dtype))
+        return len(self.bufs) - 1
+
+    def new_act(self, h, w, c):
+        return T(self.new_buf(h, w, pad8(c)), 0, c, h, w)
+
+    def input(self):
+        return T(self.in_buf, 0, 3, self.in_h, self.in_w)
+
+    def add_weights(self, arr: np.ndarray):
+        while len(self.weights) % 256:
+            self.weights.append(0)
+        off = len(self.weights)
+        self.weights += np.ascontiguousarray(arr).tobytes()
+        return off
+
+    @staticmethod
+    def bf16_bits(t: torch.Tensor) -> np.ndarray:
+        return t.contiguous().to(torch.bfloat16).view(torch.int16).numpy().astype(np.uint16)
+
+    def _op(self, typ, p, w_off=-1, b_off=-1, w2_off=-1, b2_off=-1, name=""):
+        p = list(p) + [0] * (23 - len(p))
+        self.ops.append((typ, p, w_off, b_off, w2_off, b2_off))
+        self.names.append(name)
+
+    # ---- ops ----
+    def conv(self, x: T, weight, bias, stride, pad, act, res: Optional[T] = None, out: Optional[T] = None, name=""):
+        """weight: fp32 [Cout, Cin, k, k] (already BN-folded); x.c == Cin logical channels; physical channels padded to 8."""
+        cout, cin, k, _ = weight.shape
+        assert cin == x.c, (cin, x.c)
+        ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
+        if out is None:
+            out = self.new_act(ho, wo, cout)
+        assert (out.h, out.w, out.c) == (ho, wo, cout)
+        cin_p, cout_p = pad8(cin), pad8(cout)
+        wp = torch.zeros(cout_p, k * k, cin_p)
+        wp[:cout, :, :cin] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
+        bp = torch.zeros(cout_p)
+        bp[:cout] = bias
+        w_off = self.add_weights(self.bf16_bits(wp))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        rb, rc = (res.buf, res.coff) if res is not None else (-1, 0)
+        if res is not None:
+            assert (res.h, res.w, res.c) == (ho, wo, cout)
+        self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act], w_off, b_off,
+                 name=name)
+        return out
+
+    def stem(self, x: T, weight, bias, stride, pad, act, name=""):
+        cout, cin, k, _ = weight.shape
+        assert cin == 3 and x.buf == self.in_buf
+        ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
+        out = self.new_act(ho, wo, cout)
+        ct = stem_cout_tile(pad8(cout))
+        cpad = (pad8(cout) + ct - 1) // ct * ct
+        wp = torch.zeros(k * k, 3, cpad)
+        wp[:, :, :cout] = weight.permute(2, 3, 1, 0).reshape(k * k, 3, cout)
+        bp = torch.zeros(cpad)
+        bp[:cout] = bias
+        w_off = self.add_weights(wp.numpy().astype(np.float32))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, pad8(cout), -1, 0, k, stride, pad, act], w_off, b_off,
+                 name=name)
+        return out
+
+    def dwconv(self, x: T, weight, bias, stride, act, out: Optional[T] = None, name=""):
+        c = weight.shape[0]
+        assert weight.shape[1] == 1 and weight.shape[2] == 3 and c == x.c
+        ho, wo = (x.h - 1) // stride + 1, (x.w - 1) // stride + 1
+        if out is None:
+            out = self.new_act(ho, wo, c)
+        cp = pad8(c)
+        wp = torch.zeros(9, cp)
+        wp[:, :c] = weight.reshape(c, 9).t()
+        bp = torch.zeros(cp)
+        bp[:c] = bias
+        w_off = self.add_weights(wp.numpy().astype(np.float32))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        self._op(OP_DWCONV, [x.buf, x.coff, cp, out.buf, out.coff, cp, -1, 0, 3, stride, 1, act], w_off, b_off, name=name)
+        return out
+
+    def maxpool(self, x: T, k, stride, pad, out: Optional[T] = None, name=""):
+        ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
+        if out is None:
+            out = self.new_act(ho, wo, x.c)
+        self._op(OP_MAXPOOL, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c), -1, 0, k, stride, pad, 0], name=name)
+        return out
+
+    def avgpool(self, x: T, name=""):
+        """Global average pool -> fp32 vector buffer [c]."""
+        out_buf = self.new_buf(1, 1, pad8(x.c), dtype=1)
+        self._op(OP_AVGPOOL, [x.buf, x.coff, pad8(x.c), out_buf, 0, pad8(x.c)], name=name)
+        return T(out_buf, 0, x.c, 1, 1)
+
+    def fc(self, x: T, weight, bias, act=ACT_NONE, name=""):
+        """x: fp32 vector buffer; weight fp32 [J, K]."""
+        j, k = weight.shape
+        assert k == x.c and self.bufs[x.buf][3] == 1
+        kp = self.bufs[x.buf][2]
+        jp = (j + 3) // 4 * 4
+        wp = torch.zeros(jp, kp)
+        wp[:j, :k] = weight
+        bp = torch.zeros(jp)
+        bp[:j] = bias
+        out_buf = self.new_buf(1, 1, jp, dtype=1)
+        w_off = self.add_weights(wp.numpy().astype(np.float32))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        one = struct.unpack("<i", struct.pack("<f", 1.0))[0]
+        self._op(OP_FC, [x.buf, 0, kp, out_buf, 0, jp, -1, 0, 0, 0, 0, act, one], w_off, b_off, name=name)
+        return T(out_buf, 0, j, 1, 1)
+
+    def scale(self, x: T, gate: T, name=""):
+        out = self.new_act(x.h, x.w, x.c)
+        self._op(OP_SCALE, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c), -1, 0, 0, 0, 0, 0, gate.buf], name=name)
+        return out
+
+    def copy(self, x: T, out: T, name=""):
+        self._op(OP_COPY, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c)], name=name)
+        return out
+
+    def upsample2x(self, x: T, out: T, name=""):
+        self._op(OP_UPSAMPLE, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c)], name=name)
+        return out
+
+    def set_output(self, t: T):
+        assert self.bufs[t.buf][3] == 1, "model output must be an fp32 vector buffer"
+        self.out_buf = t.buf
+        self.out_dim = self.bufs[t.buf][2]
+        self.out_logical = t.c
+
+    # ---- serialisation ----
+    def to_blob(self) -> bytes:
+        assert self.out_buf >= 0
+        tables = HEADER_SIZE + len(self.bufs) * struct.calcsize(BUF_FMT) + len(self.ops) * 128
+        w_offset = (tables + 255) // 256 * 256
+        hdr = struct.pack(HEADER_FMT, b"B200PLAN", 1, len(self.bufs), len(self.ops), 0, self.kind.encode()[:31],
+                          self.in_h, self.in_w, self.in_buf, self.out_buf, self.out_dim, self.pre_fill, *self.mean,
+                          *self.std, w_offset, len(self.weights))
+        out = bytearray(hdr)
+        for b in self.bufs:
+            out += struct.pack(BUF_FMT, *b)
+        for typ, p, w, b, w2, b2 in self.ops:
+            out += struct.pack(OP_FMT, typ, *p, w, b, w2, b2)
+        out += b"\0" * (w_offset - len(out))
+        out += self.weights
+        return bytes(out)
+
+
+def parse_blob(blob: bytes):
+    """Inverse of PlanBuilder.to_blob: returns (header dict, bufs, ops, weights bytes)."""
+    f = struct.unpack_from(HEADER_FMT, blob, 0)
+    hdr = dict(magic=f[0], version=f[1], n_bufs=f[2], n_ops=f[3], kind=f[5].split(b"\0")[0].decode(), in_h=f[6],
+               in_w=f[7], in_buf=f[8], out_buf=f[9], out_dim=f[10], pre_fill=f[11], mean=f[12:15], std=f[15:18],
+               weights_offset=f[18], weights_bytes=f[19])
+    off = HEADER_SIZE
+    bufs = []
+    for _ in range(hdr["n_bufs"]):
+        bufs.append(struct.unpack_from(BUF_FMT, blob, off))
+        off += struct.calcsize(BUF_FMT)
+    ops = []
+    for _ in range(hdr["n_ops"]):
+        r = struct.unpack_from(OP_FMT, blob, off)
+        ops.append(dict(type=r[0], p=list(r[1:24]), w_off=r[24], b_off=r[25], w2_off=r[26], b2_off=r[27]))
+        off += 128
+    weights = blob[hdr["weights_offset"]:hdr["weights_offset"] + hdr["weights_bytes"]]
+    return hdr, bufs, ops, weights
+
+
+# ================================================================================================ model lowerings
+
+def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
+    """torchvision ResNet (Bottleneck, stride on the 3x3 = v1.5): tv models/resnet.py:108-165, 266-285."""
+    pb = PlanBuilder("resnet50", in_hw[0], in_hw[1])
+    w, b = fold_bn(model.conv1, model.bn1)
+    x = pb.stem(pb.input(), w, b, 2, 3, ACT_RELU, name="conv1")
+    x = pb.maxpool(x, 3, 2, 1, name="maxpool")
+    for li, layer in enumerate([model.layer1, model.layer2, model.layer3, model.layer4], 1):
+        for bi, blk in enumerate(layer):
+            nm = "layer%d.%d." % (li, bi)
+            identity = x
+            w, b = fold_bn(blk.conv1, blk.bn1)
+            o = pb.conv(x, w, b, 1, 0, ACT_RELU, name=nm + "conv1")
+            w, b = fold_bn(blk.conv2, blk.bn2)
+            o = pb.conv(o, w, b, blk.conv2.stride[0], 1, ACT_RELU, name=nm + "conv2")
+            if blk.downsample is not None:
+                w, b = fold_bn(blk.downsample[0], blk.downsample[1])
+                identity = pb.conv(x, w, b, blk.downsample[0].stride[0], 0, ACT_NONE, name=nm + "downsample")
+            w, b = fold_bn(blk.conv3, blk.bn3)
+            x = pb.conv(o, w, b, 1, 0, ACT_RELU, res=identity, name=nm + "conv3")
+    v = pb.avgpool(x, name="avgpool")
+    y = pb.fc(v, model.fc.weight.detach().float(), model.fc.bias.detach().float(), name="fc")
+    pb.set_output(y)
+    return pb
+
+
+LOWERINGS = {"resnet50": lower_resnet}
+
+
+def lower(kind: str, model, **kw) -> PlanBuilder:
+    if kind not in LOWERINGS:
+        raise KeyError("no lowering for model kind %r (have %s)" % (kind, sorted(LOWERINGS)))
+    model.eval()
+    with torch.no_grad():
+        return LOWERINGS[kind](model, **kw)
