@@ -109,6 +109,11 @@ B200_API long long b200_engine_launch_count(b200_engine* e);      /* kernels lau
 /* Device pointer of an activation buffer (-1 = model input NHWC4 bf16, -2 = model output fp32), for tests/zero-copy. */
 B200_API int b200_engine_buffer(b200_engine* e, int buf, void** dev_ptr, size_t* bytes_per_image);
 
+/* Per-op device time of one eager pass (CUDA events on `stream` around every op; synchronises). ms_per_op / flops_per_op
+ * have n_ops entries (b200_engine_info); flops are 2*M*N*K of the tensor-core convolutions, 0 for other ops. */
+B200_API int b200_engine_profile(b200_engine* e, int batch, float* ms_per_op, double* flops_per_op, int n_ops,
+                                 void* stream);
+
 /* Synchronising debug read of an activation buffer (first `batch` images) into host memory; used by per-layer parity tests. */
 B200_API int b200_engine_read_buffer(b200_engine* e, int buf, int batch, void* host_dst);
 

@@ -17,6 +17,8 @@ Engine::~Engine() {
   cudaFree(items_dev);
   cudaFree(stage_f32_dev);
   if (items_host) cudaFreeHost(items_host);
+  for (auto& ev : item_events)
+    if (ev) cudaEventDestroy(ev);
   if (capture_stream) cudaStreamDestroy(capture_stream);
 }
 
@@ -70,7 +72,8 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
   B200_CUDA_OK(cudaMalloc(&lut_dev, sizeof(lut)));
   B200_CUDA_OK(cudaMemcpy(lut_dev, lut, sizeof(lut), cudaMemcpyHostToDevice));
   B200_CUDA_OK(cudaMalloc(&items_dev, sizeof(CollateItem) * max_batch));
-  B200_CUDA_OK(cudaMallocHost(&items_host, sizeof(CollateItem) * max_batch));
+  B200_CUDA_OK(cudaMallocHost(&items_host, sizeof(CollateItem) * max_batch * ITEM_SLOTS));
+  for (auto& ev : item_events) B200_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   B200_CUDA_OK(cudaStreamCreateWithFlags(&capture_stream, cudaStreamNonBlocking));
   return B200_OK;
 }
@@ -253,6 +256,32 @@ int b200_engine_buffer(b200_engine* h, int buf, void** dev_ptr, size_t* bytes_pe
   return B200_OK;
 }
 
+int b200_engine_profile(b200_engine* h, int batch, float* ms_per_op, double* flops_per_op, int n_ops, void* stream_) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  Engine& e = h->e;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (n_ops != static_cast<int>(e.ops.size())) return fail(B200_ERR_INVALID, "b200_engine_profile: n_ops mismatch");
+  if (batch <= 0 || batch > e.max_batch) return fail(B200_ERR_INVALID, "b200_engine_profile: bad batch");
+  BatchPlan* plan = nullptr;
+  B200_TRY(e.plan_for(batch, &plan));
+  std::vector<cudaEvent_t> ev(n_ops + 1);
+  for (auto& x : ev) B200_CUDA_OK(cudaEventCreate(&x));
+  B200_CUDA_OK(cudaEventRecord(ev[0], stream));
+  for (int i = 0; i < n_ops; ++i) {
+    int rc = e.run_ops(*plan, stream, i, i);
+    if (rc != 0) return rc;
+    B200_CUDA_OK(cudaEventRecord(ev[i + 1], stream));
+  }
+  B200_CUDA_OK(cudaStreamSynchronize(stream));
+  e.launches += n_ops;
+  for (int i = 0; i < n_ops; ++i) {
+    B200_CUDA_OK(cudaEventElapsedTime(&ms_per_op[i], ev[i], ev[i + 1]));
+    if (flops_per_op) flops_per_op[i] = plan->ops[i].rec.type == OP_CONV ? plan->ops[i].conv.flops : 0.0;
+  }
+  for (auto& x : ev) cudaEventDestroy(x);
+  return B200_OK;
+}
+
 int b200_engine_read_buffer(b200_engine* h, int buf, int batch, void* host_dst) {
   if (!h || buf < -2 || buf >= static_cast<int>(h->e.bufs.size())) return fail(B200_ERR_INVALID, "bad buffer id");
   if (batch <= 0 || batch > h->e.max_batch || !host_dst) return fail(B200_ERR_INVALID, "bad batch / destination");
@@ -271,10 +300,14 @@ int b200_collate(b200_engine* h, const void* packed, const uint64_t* offsets, co
   if (n < 0 || padded_batch < n || padded_batch > e.max_batch || padded_batch <= 0)
     return fail(B200_ERR_INVALID, "b200_collate: need 0 <= n <= padded_batch <= max_batch");
   if (n > 0 && (!packed || !offsets || !hw)) return fail(B200_ERR_INVALID, "b200_collate: null input");
+  // the item table is the source of an async copy: rotate through pinned slots, waiting only if a slot is still in flight
+  const unsigned slot = e.item_slot++ % Engine::ITEM_SLOTS;
+  B200_CUDA_OK(cudaEventSynchronize(e.item_events[slot]));
+  CollateItem* items_host = e.items_host + size_t(slot) * e.max_batch;
   for (int i = 0; i < n; ++i) {
-    e.items_host[i].offset = offsets[i];
-    e.items_host[i].h = hw[2 * i];
-    e.items_host[i].w = hw[2 * i + 1];
+    items_host[i].offset = offsets[i];
+    items_host[i].h = hw[2 * i];
+    items_host[i].w = hw[2 * i + 1];
     if (hw[2 * i] <= 0 || hw[2 * i + 1] <= 0) return fail(B200_ERR_INVALID, "b200_collate: empty image");
     if (offsets[i] + uint64_t(hw[2 * i]) * hw[2 * i + 1] * 3 > packed_bytes)
       return fail(B200_ERR_INVALID, "b200_collate: image " + std::to_string(i) + " exceeds the packed buffer");
@@ -294,10 +327,12 @@ int b200_collate(b200_engine* h, const void* packed, const uint64_t* offsets, co
     B200_CUDA_OK(cudaMemcpyAsync(e.stage_dev, packed, packed_bytes, cudaMemcpyHostToDevice, stream));
     src = e.stage_dev;
   }
-  if (n > 0)
-    B200_CUDA_OK(cudaMemcpyAsync(e.items_dev, e.items_host, sizeof(CollateItem) * n, cudaMemcpyHostToDevice, stream));
+  if (n > 0) {
+    B200_CUDA_OK(cudaMemcpyAsync(e.items_dev, items_host, sizeof(CollateItem) * n, cudaMemcpyHostToDevice, stream));
+    B200_CUDA_OK(cudaEventRecord(e.item_events[slot], stream));
+  }
   void* out = out_nhwc_bf16 ? out_nhwc_bf16 : e.buf_dev[e.hdr.in_buf];
-  B200_TRY(collate_u8_launch(src, e.items_dev, e.items_host, n, padded_batch, e.hdr.in_h, e.hdr.in_w, mode,
+  B200_TRY(collate_u8_launch(src, e.items_dev, items_host, n, padded_batch, e.hdr.in_h, e.hdr.in_w, mode,
                              e.hdr.pre_fill, e.lut_dev, out, stream));
   e.launches += 1;
   return B200_OK;

@@ -71,7 +71,10 @@ struct Engine {
   uint8_t* stage_dev = nullptr;
   size_t stage_bytes = 0;
   CollateItem* items_dev = nullptr;
-  CollateItem* items_host = nullptr;  // pinned
+  CollateItem* items_host = nullptr;  // pinned ring of ITEM_SLOTS x max_batch records (async H2D source)
+  static constexpr int ITEM_SLOTS = 8;
+  cudaEvent_t item_events[ITEM_SLOTS] = {};
+  unsigned item_slot = 0;
   float* stage_f32_dev = nullptr;
   std::unordered_map<int, std::unique_ptr<BatchPlan>> plans;
   cudaStream_t capture_stream = nullptr;

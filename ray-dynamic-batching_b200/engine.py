@@ -86,6 +86,15 @@ class B200Model:
         _lib.check(self.lib.b200_engine_read_buffer(self._h, buf_id, batch, _lib.ptr(host)), "b200_engine_read_buffer")
         return host.view(batch, nb.value)
 
+    def profile_ops(self, batch):
+        """One eager pass with CUDA events around every op: returns (ms_per_op, flops_per_op) as numpy arrays."""
+        ms = np.zeros(self.n_ops, dtype=np.float32)
+        fl = np.zeros(self.n_ops, dtype=np.float64)
+        _lib.check(self.lib.b200_engine_profile(self._h, batch, ms.ctypes.data_as(ctypes.c_void_p),
+                                                fl.ctypes.data_as(ctypes.c_void_p), self.n_ops, self._stream()),
+                   "b200_engine_profile")
+        return ms, fl
+
     # ---- reference call site: outputs = model(inputs) ----
     def __call__(self, inputs):
         return self.forward(inputs)

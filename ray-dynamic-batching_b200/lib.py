@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200_engine_set_graphs": (c_int, [c_void_p, c_int]),
     "b200_engine_launch_count": (ctypes.c_longlong, [c_void_p]),
     "b200_engine_buffer": (c_int, [c_void_p, c_int, ctypes.POINTER(c_void_p), ctypes.POINTER(c_size_t)]),
+    "b200_engine_profile": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "b200_engine_read_buffer": (c_int, [c_void_p, c_int, c_int, c_void_p]),
     "b200_collate": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_size_t, c_void_p,
                              c_void_p]),
