@@ -126,6 +126,22 @@ B200_API int b200_engine_read_buffer(b200_engine* e, int buf, int batch, void* h
 B200_API int b200_collate(b200_engine* e, const void* packed, const uint64_t* offsets, const int32_t* hw, int n,
                           int padded_batch, int mode, int src_on_device, size_t packed_bytes, void* out_nhwc_bf16,
                           void* stream);
+/* (No counterpart in the reference.)  b200_collate for callers that may not allocate device memory while serving: an
+ * actor placed on a GPU by the profiled peak memory of its sessions has no headroom for, and cannot afford the
+ * device-wide synchronisation of, a cudaMalloc inside its duty cycle.  The caller passes the packed uint8 images (already
+ * on the device) and the output; the per-image table and the normalisation table -- the only other memory the kernel
+ * touches -- live in a fixed array inside the library image: B200_NOALLOC_MAX_IMAGES * 16 B + 1.5 KB = 17.5 KB held by every
+ * GPU that loads the library, until exit.  n > B200_NOALLOC_MAX_IMAGES is refused with B200_ERR_INVALID.  Never calls
+ * cudaMalloc/cudaFree or any allocating routine.  The first call on each device also resolves the array's device
+ * address: make that first call before starting any stream capture.  All calls share the one array, which keeps the last
+ * call's tables: two calls whose GPU work overlaps (different streams, or threads) race on it -- keep them on one
+ * stream, or order them with events.  mean3/std3: per-channel normalisation ((u8/255 - mean) / std); other arguments as
+ * b200_collate. */
+#define B200_NOALLOC_MAX_IMAGES 1024
+B200_API int b200_collate_u8_noalloc(const void* packed_dev, const uint64_t* offsets, const int32_t* hw, int n,
+                                     int padded_batch, int out_h, int out_w, int mode, int fill, const float* mean3,
+                                     const float* std3, size_t packed_bytes, void* out_nhwc4_bf16_dev, void* stream);
+
 /* Same for reference-native requests: n already-normalised fp32 CHW tensors stacked as [n][3][H][W]
  * (293-project/src/test_scheduler.py:89 submits torch.randn(3,224,224)). */
 B200_API int b200_collate_f32(b200_engine* e, const float* stacked_chw, int n, int padded_batch, int src_on_device,
