@@ -83,14 +83,16 @@ B200_API int b200_fc(const float* x, const float* w, const float* b, float* out,
 B200_API int b200_channel_scale_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* gate,
                                      void* out, int out_pix_stride, void* stream);
 
-/* Channel-slice copy / nearest 2x upsample / ShuffleNetV2 concat+channel_shuffle(groups=2) interleave
- * (tv shufflenetv2.py:28-40,98-104: out[2i] = a[i], out[2i+1] = b[i]). */
+/* Channel-slice copy / nearest 2x upsample / ShuffleNetV2 concat + channel_shuffle(groups=2)
+ * (tv shufflenetv2.py:28-40,98-104: logical out[2i] = a[i], out[2i+1] = b[i], i < c). a and b hold c channels padded to
+ * cp = ceil8(c); out has 2*cp channels stored as two halves: logical l at physical (l < c ? l : cp + l - c), pads zero,
+ * so the next unit's x.chunk(2) is two 16-byte aligned slices. */
 B200_API int b200_copy_channels_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
                                      int out_pix_stride, void* stream);
 B200_API int b200_upsample2x_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
                                   int out_pix_stride, void* stream);
 B200_API int b200_shuffle_concat_nhwc(const void* a, int a_pix_stride, const void* b, int b_pix_stride, int n, int h,
-                                      int w, int c_half, void* out, int out_pix_stride, void* stream);
+                                      int w, int c, void* out, int out_pix_stride, void* stream);
 
 /* ---- engine level (what B200Model / B200GPUWorker.process_batch bind) ------------------------------------------ */
 

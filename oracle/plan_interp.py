@@ -63,8 +63,11 @@ class PlanInterpreter:
                 b = self._f32(op["b_off"], cout)
                 y = F.conv2d(x, w, b, stride=s, padding=pad)
                 if p[6] >= 0:
-                    y = y + B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
-                B[p[3]][..., p[4]:p[4] + cout] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+                    r = B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
+                    y = _act(y, act) + r if p[12] else _act(y + r, act)
+                else:
+                    y = _act(y, act)
+                B[p[3]][..., p[4]:p[4] + cout] = _bf16(y).permute(0, 2, 3, 1)
             elif t == OP_STEM:
                 cout, k, s, pad, act = p[5], p[8], p[9], p[10], p[11]
                 ct = stem_cout_tile(cout)
@@ -108,10 +111,14 @@ class PlanInterpreter:
                 x = B[p[0]][..., p[1]:p[1] + c]
                 B[p[3]][..., p[4]:p[4] + c] = x.repeat_interleave(2, dim=1).repeat_interleave(2, dim=2)
             elif t == OP_SHUFFLE:
-                c = p[2]
+                c, cp = p[14], p[15]
                 a = B[p[0]][..., p[1]:p[1] + c]
                 b = B[p[12]][..., p[13]:p[13] + c]
-                B[p[3]][..., p[4]:p[4] + 2 * c] = torch.stack([a, b], dim=-1).reshape(*a.shape[:-1], 2 * c)
+                sh = torch.stack([a, b], dim=-1).reshape(*a.shape[:-1], 2 * c)   # channel_shuffle(cat(a, b), 2)
+                o = B[p[3]]
+                o[..., p[4]:p[4] + 2 * cp] = 0
+                o[..., p[4]:p[4] + c] = sh[..., :c]
+                o[..., p[4] + cp:p[4] + cp + c] = sh[..., c:]
             else:
                 raise NotImplementedError("op type %d" % t)
         out = B[self.hdr["out_buf"]].view(n, -1)

@@ -87,10 +87,11 @@ int b200_upsample2x_nhwc(const void* in, int n, int h, int w, int c, int in_pix_
 }
 
 int b200_shuffle_concat_nhwc(const void* a, int a_pix_stride, const void* b, int b_pix_stride, int n, int h, int w,
-                             int c_half, void* out, int out_pix_stride, void* stream) {
-  return shuffle_concat_launch(make_view(const_cast<void*>(a), n, h, w, c_half, a_pix_stride),
-                               make_view(const_cast<void*>(b), n, h, w, c_half, b_pix_stride),
-                               make_view(out, n, h, w, 2 * c_half, out_pix_stride), static_cast<cudaStream_t>(stream));
+                             int c, void* out, int out_pix_stride, void* stream) {
+  const int cp = (c + 7) / 8 * 8;
+  return shuffle_concat_launch(make_view(const_cast<void*>(a), n, h, w, cp, a_pix_stride),
+                               make_view(const_cast<void*>(b), n, h, w, cp, b_pix_stride),
+                               make_view(out, n, h, w, 2 * cp, out_pix_stride), c, cp, static_cast<cudaStream_t>(stream));
 }
 
 }  // extern "C"

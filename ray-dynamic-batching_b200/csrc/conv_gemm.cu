@@ -154,16 +154,20 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         float f[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(v[g * 8 + i]) + bias_s[cc * 32 + g * 8 + i];
+        float rr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
         if (p.has_res) {
           uint32_t r0, r1, r2, r3;
           asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
-          f[0] += bf16_lo(r0); f[1] += bf16_hi(r0);
-          f[2] += bf16_lo(r1); f[3] += bf16_hi(r1);
-          f[4] += bf16_lo(r2); f[5] += bf16_hi(r2);
-          f[6] += bf16_lo(r3); f[7] += bf16_hi(r3);
+          rr[0] = bf16_lo(r0); rr[1] = bf16_hi(r0); rr[2] = bf16_lo(r1); rr[3] = bf16_hi(r1);
+          rr[4] = bf16_lo(r2); rr[5] = bf16_hi(r2); rr[6] = bf16_lo(r3); rr[7] = bf16_hi(r3);
         }
+        if (p.has_res == 2) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) f[i] = apply_act(f[i], p.act);
+          for (int i = 0; i < 8; ++i) f[i] = apply_act(f[i], p.act) + rr[i];
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = apply_act(f[i] + rr[i], p.act);
+        }
         const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
         const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
         asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
@@ -240,7 +244,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.kb_per_tap = (in.C + BLOCK_K - 1) / BLOCK_K;
   p.cout = out.C;
   p.act = s.act;
-  p.has_res = has_res ? 1 : 0;
+  p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
   p.bias = s.bias;
   const int block_n = out.C <= 64 ? 64 : 128;
   L->block_n = block_n;

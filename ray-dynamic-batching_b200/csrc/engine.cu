@@ -104,6 +104,7 @@ int Engine::plan_for(int batch, BatchPlan** out) {
       s.w = weights_dev + po.rec.w_off;
       s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
       s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];
+      s.res_after_act = p[12] != 0;
       int rc = conv_prepare(s, &po.conv);
       if (rc != 0) return fail(rc, "op " + std::to_string(i) + ": " + last_error_cstr());
     }
@@ -160,7 +161,7 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
         break;
       case OP_SHUFFLE:
         rc = shuffle_concat_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[2], batch),
-                                   view(p[3], p[4], p[5], batch), stream);
+                                   view(p[3], p[4], p[5], batch), p[14], p[15], stream);
         break;
       default:
         rc = fail(B200_ERR_BLOB, "engine: unknown op type " + std::to_string(po.rec.type));

@@ -40,6 +40,7 @@ int channel_scale_launch(const View& in, const View& out, const float* gate, cud
 // ---- data movement (move.cu) ----
 int copy_channels_launch(const View& in, const View& out, cudaStream_t stream);             // slice -> slice copy
 int upsample2x_launch(const View& in, const View& out, cudaStream_t stream);                // nearest, into a slice
-int shuffle_concat_launch(const View& a, const View& b, const View& out, cudaStream_t stream);  // out[2i]=a[i], out[2i+1]=b[i]
+// logical out[2i] = a[i], out[2i+1] = b[i] (i < c); logical channel l is stored at physical (l < c ? l : cp + l - c)
+int shuffle_concat_launch(const View& a, const View& b, const View& out, int c, int cp, cudaStream_t stream);
 
 }  // namespace b200

@@ -56,35 +56,46 @@ int upsample2x_launch(const View& in, const View& out, cudaStream_t stream) {
   return B200_OK;
 }
 
-// out[..., 2i] = a[..., i]; out[..., 2i+1] = b[..., i]   == channel_shuffle(cat(a, b), groups=2).
-// A thread reads 16 B (8 channels) from each of a and b and writes 32 contiguous bytes.
+// ShuffleNetV2 concat + channel_shuffle(groups=2): logical out[2i] = a[i], out[2i+1] = b[i] (i < c).  The output keeps
+// the two halves of the *shuffled* tensor in separately padded slices (logical l -> physical l < c ? l : cp + l - c), so the
+// next unit's chunk(2) needs no copy.  A thread assembles 8 output channels (16 B store) from 2-byte gathers that hit L1.
 __global__ void __launch_bounds__(256)
 shuffle_concat_kernel(const uint16_t* __restrict__ a, int a_ps, const uint16_t* __restrict__ b, int b_ps,
-                      uint16_t* __restrict__ out, int out_ps, int C8, long long total) {
+                      uint16_t* __restrict__ out, int out_ps, int c, int cp, long long total) {
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % C8);
-  const long long pix = idx / C8;
-  const uint4 va = *reinterpret_cast<const uint4*>(a + pix * a_ps + c8 * 8);
-  const uint4 vb = *reinterpret_cast<const uint4*>(b + pix * b_ps + c8 * 8);
-  uint4 o0, o1;
-  o0.x = __byte_perm(va.x, vb.x, 0x5410); o0.y = __byte_perm(va.x, vb.x, 0x7632);
-  o0.z = __byte_perm(va.y, vb.y, 0x5410); o0.w = __byte_perm(va.y, vb.y, 0x7632);
-  o1.x = __byte_perm(va.z, vb.z, 0x5410); o1.y = __byte_perm(va.z, vb.z, 0x7632);
-  o1.z = __byte_perm(va.w, vb.w, 0x5410); o1.w = __byte_perm(va.w, vb.w, 0x7632);
-  uint4* dst = reinterpret_cast<uint4*>(out + pix * out_ps + c8 * 16);
-  dst[0] = o0;
-  dst[1] = o1;
+  const int chunks = (2 * cp) >> 3;
+  const int ch = static_cast<int>(idx % chunks);
+  const long long pix = idx / chunks;
+  const uint16_t* pa = a + pix * a_ps;
+  const uint16_t* pb = b + pix * b_ps;
+  uint16_t v[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int p = ch * 8 + e;
+    const int half = p >= cp ? 1 : 0;
+    const int q = p - half * cp;
+    uint16_t x = 0;
+    if (q < c) {
+      const int l = half * c + q;
+      x = (l & 1) ? pb[l >> 1] : pa[l >> 1];
+    }
+    v[e] = x;
+  }
+  uint4 o;
+  o.x = uint32_t(v[0]) | (uint32_t(v[1]) << 16); o.y = uint32_t(v[2]) | (uint32_t(v[3]) << 16);
+  o.z = uint32_t(v[4]) | (uint32_t(v[5]) << 16); o.w = uint32_t(v[6]) | (uint32_t(v[7]) << 16);
+  *reinterpret_cast<uint4*>(out + pix * out_ps + ch * 8) = o;
 }
 
-int shuffle_concat_launch(const View& a, const View& b, const View& out, cudaStream_t stream) {
-  if (a.C != b.C || out.C != 2 * a.C || a.C % 8 || a.N != out.N || a.H != out.H || a.W != out.W || b.N != a.N ||
-      b.H != a.H || b.W != a.W)
+int shuffle_concat_launch(const View& a, const View& b, const View& out, int c, int cp, cudaStream_t stream) {
+  if (cp % 8 || c > cp || c <= 0 || a.C < c || b.C < c || out.C != 2 * cp || a.N != out.N || a.H != out.H ||
+      a.W != out.W || b.N != a.N || b.H != a.H || b.W != a.W || out.pix_stride % 8)
     return fail(B200_ERR_INVALID, "shuffle_concat: shape mismatch");
-  const long long total = static_cast<long long>(a.N) * a.H * a.W * (a.C / 8);
+  const long long total = static_cast<long long>(a.N) * a.H * a.W * (2 * cp / 8);
   shuffle_concat_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
       static_cast<const uint16_t*>(a.base), a.pix_stride, static_cast<const uint16_t*>(b.base), b.pix_stride,
-      static_cast<uint16_t*>(out.base), out.pix_stride, a.C / 8, total);
+      static_cast<uint16_t*>(out.base), out.pix_stride, c, cp, total);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }

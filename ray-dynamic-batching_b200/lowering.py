@@ -40,12 +40,22 @@ def stem_cout_tile(cout):
 
 @dataclass
 class T:
-    """A channel slice of an activation buffer: logical tensor [N, h, w, c] stored at channel offset `coff`."""
+    """A channel slice of an activation buffer: logical tensor [N, h, w, c] stored at channel offset `coff`.
+    `cphys` physical channels are occupied (>= c, multiple of 8); logical channel l lives at physical offset cmap[l]
+    inside the slice (identity unless the tensor is stored as padded groups, e.g. ShuffleNet's two halves)."""
     buf: int
     coff: int
     c: int
     h: int
     w: int
+    cphys: int = 0
+    cmap: Optional[np.ndarray] = None
+
+    def __post_init__(self):
+        if not self.cphys:
+            self.cphys = pad8(self.c)
+        if self.cmap is None:
+            self.cmap = np.arange(self.c)
 
 
 def act_code(m):
@@ -112,7 +122,8 @@ class PlanBuilder:
         self.names.append(name)
 
     # ---- ops ----
-    def conv(self, x: T, weight, bias, stride, pad, act, res: Optional[T] = None, out: Optional[T] = None, name=""):
+    def conv(self, x: T, weight, bias, stride, pad, act, res: Optional[T] = None, out: Optional[T] = None, name="",
+             res_after_act=False):
         """weight: fp32 [Cout, Cin, k, k] (already BN-folded); x.c == Cin logical channels; physical channels padded to 8."""
         cout, cin, k, _ = weight.shape
         assert cin == x.c, (cin, x.c)
@@ -120,18 +131,20 @@ class PlanBuilder:
         if out is None:
             out = self.new_act(ho, wo, cout)
         assert (out.h, out.w, out.c) == (ho, wo, cout)
-        cin_p, cout_p = pad8(cin), pad8(cout)
+        cin_p, cout_p = x.cphys, out.cphys
         wp = torch.zeros(cout_p, k * k, cin_p)
-        wp[:cout, :, :cin] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
+        wfull = torch.zeros(cout, k * k, cin_p)
+        wfull[:, :, torch.as_tensor(x.cmap)] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
+        wp[torch.as_tensor(out.cmap)] = wfull
         bp = torch.zeros(cout_p)
-        bp[:cout] = bias
+        bp[torch.as_tensor(out.cmap)] = bias
         w_off = self.add_weights(self.bf16_bits(wp))
         b_off = self.add_weights(bp.numpy().astype(np.float32))
         rb, rc = (res.buf, res.coff) if res is not None else (-1, 0)
         if res is not None:
-            assert (res.h, res.w, res.c) == (ho, wo, cout)
-        self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act], w_off, b_off,
-                 name=name)
+            assert (res.h, res.w, res.c, res.cphys) == (ho, wo, cout, cout_p) and np.array_equal(res.cmap, out.cmap)
+        self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act,
+                           1 if res_after_act else 0], w_off, b_off, name=name)
         return out
 
     def stem(self, x: T, weight, bias, stride, pad, act, name=""):
@@ -156,12 +169,14 @@ class PlanBuilder:
         assert weight.shape[1] == 1 and weight.shape[2] == 3 and c == x.c
         ho, wo = (x.h - 1) // stride + 1, (x.w - 1) // stride + 1
         if out is None:
-            out = self.new_act(ho, wo, c)
-        cp = pad8(c)
+            ob = self.new_buf(ho, wo, x.cphys)
+            out = T(ob, 0, c, ho, wo, x.cphys, x.cmap)      # same physical channel arrangement as the input
+        assert out.cphys == x.cphys and np.array_equal(out.cmap, x.cmap)
+        cp = x.cphys
         wp = torch.zeros(9, cp)
-        wp[:, :c] = weight.reshape(c, 9).t()
+        wp[:, torch.as_tensor(x.cmap)] = weight.reshape(c, 9).t()
         bp = torch.zeros(cp)
-        bp[:c] = bias
+        bp[torch.as_tensor(x.cmap)] = bias
         w_off = self.add_weights(wp.numpy().astype(np.float32))
         b_off = self.add_weights(bp.numpy().astype(np.float32))
         self._op(OP_DWCONV, [x.buf, x.coff, cp, out.buf, out.coff, cp, -1, 0, 3, stride, 1, act], w_off, b_off, name=name)
@@ -170,24 +185,25 @@ class PlanBuilder:
     def maxpool(self, x: T, k, stride, pad, out: Optional[T] = None, name=""):
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
         if out is None:
-            out = self.new_act(ho, wo, x.c)
-        self._op(OP_MAXPOOL, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c), -1, 0, k, stride, pad, 0], name=name)
+            out = T(self.new_buf(ho, wo, x.cphys), 0, x.c, ho, wo, x.cphys, x.cmap)
+        assert out.cphys == x.cphys
+        self._op(OP_MAXPOOL, [x.buf, x.coff, x.cphys, out.buf, out.coff, x.cphys, -1, 0, k, stride, pad, 0], name=name)
         return out
 
     def avgpool(self, x: T, name=""):
         """Global average pool -> fp32 vector buffer [c]."""
-        out_buf = self.new_buf(1, 1, pad8(x.c), dtype=1)
-        self._op(OP_AVGPOOL, [x.buf, x.coff, pad8(x.c), out_buf, 0, pad8(x.c)], name=name)
-        return T(out_buf, 0, x.c, 1, 1)
+        out_buf = self.new_buf(1, 1, x.cphys, dtype=1)
+        self._op(OP_AVGPOOL, [x.buf, x.coff, x.cphys, out_buf, 0, x.cphys], name=name)
+        return T(out_buf, 0, x.c, 1, 1, x.cphys, x.cmap)
 
     def fc(self, x: T, weight, bias, act=ACT_NONE, name=""):
         """x: fp32 vector buffer; weight fp32 [J, K]."""
         j, k = weight.shape
         assert k == x.c and self.bufs[x.buf][3] == 1
         kp = self.bufs[x.buf][2]
-        jp = (j + 3) // 4 * 4
+        jp = pad8(j)
         wp = torch.zeros(jp, kp)
-        wp[:j, :k] = weight
+        wp[:j, torch.as_tensor(x.cmap)] = weight
         bp = torch.zeros(jp)
         bp[:j] = bias
         out_buf = self.new_buf(1, 1, jp, dtype=1)
@@ -195,23 +211,46 @@ class PlanBuilder:
         b_off = self.add_weights(bp.numpy().astype(np.float32))
         one = struct.unpack("<i", struct.pack("<f", 1.0))[0]
         self._op(OP_FC, [x.buf, 0, kp, out_buf, 0, jp, -1, 0, 0, 0, 0, act, one], w_off, b_off, name=name)
-        return T(out_buf, 0, j, 1, 1)
+        return T(out_buf, 0, j, 1, 1, jp)
 
     def scale(self, x: T, gate: T, name=""):
-        out = self.new_act(x.h, x.w, x.c)
-        self._op(OP_SCALE, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c), -1, 0, 0, 0, 0, 0, gate.buf], name=name)
+        assert gate.cphys == x.cphys and self.bufs[gate.buf][2] == x.cphys
+        out = T(self.new_buf(x.h, x.w, x.cphys), 0, x.c, x.h, x.w, x.cphys, x.cmap)
+        self._op(OP_SCALE, [x.buf, x.coff, x.cphys, out.buf, out.coff, x.cphys, -1, 0, 0, 0, 0, 0, gate.buf], name=name)
         return out
 
+    def shuffle(self, a: T, b: T, name=""):
+        """ShuffleNetV2 cat + channel_shuffle(groups=2): logical out[2i] = a[i], out[2i+1] = b[i]. The result is stored
+        as two halves [0, cp) and [cp, 2cp) (cp = pad8(c)) holding logical [0, c) and [c, 2c): chunk(2) of the next unit
+        is then two 16-byte aligned slices."""
+        assert a.c == b.c and (a.h, a.w) == (b.h, b.w)
+        assert np.array_equal(a.cmap, np.arange(a.c)) and np.array_equal(b.cmap, np.arange(b.c))
+        c, cp = a.c, pad8(a.c)
+        ob = self.new_buf(a.h, a.w, 2 * cp)
+        cmap = np.concatenate([np.arange(c), cp + np.arange(c)])
+        self._op(OP_SHUFFLE, [a.buf, a.coff, a.cphys, ob, 0, 2 * cp, -1, 0, 0, 0, 0, 0, b.buf, b.coff, c, cp], name=name)
+        return T(ob, 0, 2 * c, a.h, a.w, 2 * cp, cmap)
+
+    @staticmethod
+    def chunk2(x: T):
+        """x.chunk(2, dim=1) of a halves-layout tensor: two aligned slices, no copy."""
+        c, cp = x.c // 2, x.cphys // 2
+        assert np.array_equal(x.cmap, np.concatenate([np.arange(c), cp + np.arange(c)]))
+        return T(x.buf, x.coff, c, x.h, x.w, cp), T(x.buf, x.coff + cp, c, x.h, x.w, cp)
+
     def copy(self, x: T, out: T, name=""):
-        self._op(OP_COPY, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c)], name=name)
+        assert x.cphys == out.cphys
+        self._op(OP_COPY, [x.buf, x.coff, x.cphys, out.buf, out.coff, x.cphys], name=name)
         return out
 
     def upsample2x(self, x: T, out: T, name=""):
-        self._op(OP_UPSAMPLE, [x.buf, x.coff, pad8(x.c), out.buf, out.coff, pad8(x.c)], name=name)
+        assert x.cphys == out.cphys
+        self._op(OP_UPSAMPLE, [x.buf, x.coff, x.cphys, out.buf, out.coff, x.cphys], name=name)
         return out
 
     def set_output(self, t: T):
         assert self.bufs[t.buf][3] == 1, "model output must be an fp32 vector buffer"
+        assert np.array_equal(t.cmap, np.arange(t.c))
         self.out_buf = t.buf
         self.out_dim = self.bufs[t.buf][2]
         self.out_logical = t.c
@@ -281,7 +320,94 @@ def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
     return pb
 
 
-LOWERINGS = {"resnet50": lower_resnet}
+def lower_shufflenet(model, in_hw=(224, 224)) -> PlanBuilder:
+    """torchvision ShuffleNetV2 x1.0: tv models/shufflenetv2.py:43-104 (InvertedResidual), 149-163 (_forward_impl)."""
+    pb = PlanBuilder("shufflenet_v2_x1_0", in_hw[0], in_hw[1])
+    w, b = fold_bn(model.conv1[0], model.conv1[1])
+    x = pb.stem(pb.input(), w, b, 2, 1, ACT_RELU, name="conv1")
+    x = pb.maxpool(x, 3, 2, 1, name="maxpool")
+    for sname in ("stage2", "stage3", "stage4"):
+        for ui, unit in enumerate(getattr(model, sname)):
+            nm = "%s.%d." % (sname, ui)
+            b2 = unit.branch2
+            if unit.stride == 1:
+                x1, x2 = pb.chunk2(x)
+                a = x1
+                src = x2
+            else:
+                b1 = unit.branch1
+                w, b = fold_bn(b1[0], b1[1])
+                t = pb.dwconv(x, w, b, unit.stride, ACT_NONE, name=nm + "branch1.dw")
+                w, b = fold_bn(b1[2], b1[3])
+                a = pb.conv(t, w, b, 1, 0, ACT_RELU, name=nm + "branch1.pw")
+                src = x
+            w, b = fold_bn(b2[0], b2[1])
+            t = pb.conv(src, w, b, 1, 0, ACT_RELU, name=nm + "branch2.pw1")
+            w, b = fold_bn(b2[3], b2[4])
+            t = pb.dwconv(t, w, b, unit.stride, ACT_NONE, name=nm + "branch2.dw")
+            w, b = fold_bn(b2[5], b2[6])
+            t = pb.conv(t, w, b, 1, 0, ACT_RELU, name=nm + "branch2.pw2")
+            x = pb.shuffle(a, t, name=nm + "shuffle")
+    w, b = fold_bn(model.conv5[0], model.conv5[1])
+    x = pb.conv(x, w, b, 1, 0, ACT_RELU, name="conv5")
+    v = pb.avgpool(x, name="mean")
+    y = pb.fc(v, model.fc.weight.detach().float(), model.fc.bias.detach().float(), name="fc")
+    pb.set_output(y)
+    return pb
+
+
+def lower_efficientnet_v2(model, in_hw=(224, 224)) -> PlanBuilder:
+    """torchvision EfficientNetV2-S: tv models/efficientnet.py:105-170 (MBConv), 172-231 (FusedMBConv), 333-345;
+    SqueezeExcitation: tv ops/misc.py. stochastic_depth is the identity in eval mode."""
+    from torchvision.models.efficientnet import FusedMBConv, MBConv
+    pb = PlanBuilder("efficientnet_v2_s", in_hw[0], in_hw[1])
+    feats = model.features
+    w, b = fold_bn(feats[0][0], feats[0][1])
+    x = pb.stem(pb.input(), w, b, 2, 1, ACT_SILU, name="features.0")
+    for si in range(1, len(feats) - 1):
+        for bi, blk in enumerate(feats[si]):
+            nm = "features.%d.%d." % (si, bi)
+            res = x if blk.use_res_connect else None
+            if isinstance(blk, FusedMBConv):
+                layers = list(blk.block)
+                if len(layers) == 1:      # expand_ratio == 1: conv3x3 + BN + SiLU, then (+ input)
+                    cna = layers[0]
+                    w, b = fold_bn(cna[0], cna[1])
+                    x = pb.conv(x, w, b, cna[0].stride[0], 1, ACT_SILU, res=res, res_after_act=True, name=nm + "fused")
+                else:
+                    cna, proj = layers
+                    w, b = fold_bn(cna[0], cna[1])
+                    t = pb.conv(x, w, b, cna[0].stride[0], 1, ACT_SILU, name=nm + "expand3x3")
+                    w, b = fold_bn(proj[0], proj[1])
+                    x = pb.conv(t, w, b, 1, 0, ACT_NONE, res=res, name=nm + "project")
+            elif isinstance(blk, MBConv):
+                layers = list(blk.block)
+                exp, dw, se, proj = layers
+                w, b = fold_bn(exp[0], exp[1])
+                t = pb.conv(x, w, b, 1, 0, ACT_SILU, name=nm + "expand")
+                w, b = fold_bn(dw[0], dw[1])
+                t = pb.dwconv(t, w, b, dw[0].stride[0], ACT_SILU, name=nm + "dw")
+                s = pb.avgpool(t, name=nm + "se.squeeze")
+                s = pb.fc(s, se.fc1.weight.detach().float().flatten(1), se.fc1.bias.detach().float(), ACT_SILU,
+                          name=nm + "se.fc1")
+                s = pb.fc(s, se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float(), ACT_SIGMOID,
+                          name=nm + "se.fc2")
+                t = pb.scale(t, s, name=nm + "se.scale")
+                w, b = fold_bn(proj[0], proj[1])
+                x = pb.conv(t, w, b, 1, 0, ACT_NONE, res=res, name=nm + "project")
+            else:
+                raise NotImplementedError(type(blk))
+    last = feats[-1]
+    w, b = fold_bn(last[0], last[1])
+    x = pb.conv(x, w, b, 1, 0, ACT_SILU, name="features.last")
+    v = pb.avgpool(x, name="avgpool")
+    fc = model.classifier[1]
+    y = pb.fc(v, fc.weight.detach().float(), fc.bias.detach().float(), name="classifier")
+    pb.set_output(y)
+    return pb
+
+
+LOWERINGS = {"resnet50": lower_resnet, "shufflenet_v2_x1_0": lower_shufflenet, "efficientnet_v2_s": lower_efficientnet_v2}
 
 
 def lower(kind: str, model, **kw) -> PlanBuilder:

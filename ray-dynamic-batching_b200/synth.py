@@ -13,13 +13,23 @@ Recipe (seeded, so every machine builds bit-identical weights):
 import torch
 import torch.nn as nn
 
+IMAGENET_MEAN = (0.485, 0.456, 0.406)
+IMAGENET_STD = (0.229, 0.224, 0.225)
+
 
 def synthetic_images(n, h=224, w=224, seed=1000, dtype=torch.uint8):
-    """Engine-native synthetic requests: uint8 HWC images, seed = 1000 + request index."""
+    """Engine-native synthetic requests: uint8 HWC images, one generator per request (seed + request index).
+    Each image is a random coarse colour layout (7x7 control grid, bilinearly upsampled) plus pixel noise: unlike pure
+    noise, different requests then differ in their low-frequency content, so the pooled features of different requests
+    are well separated (what a classifier needs to have a top-1 at all)."""
     out = torch.empty(n, h, w, 3, dtype=torch.uint8)
     for i in range(n):
         g = torch.Generator().manual_seed(seed + i)
-        out[i] = torch.randint(0, 256, (h, w, 3), generator=g, dtype=torch.uint8)
+        grid = torch.rand(1, 3, 7, 7, generator=g)
+        base = torch.nn.functional.interpolate(grid, size=(h, w), mode="bilinear", align_corners=False)[0]
+        noise = (torch.rand(3, h, w, generator=g) - 0.5) * 0.25
+        img = ((base + noise).clamp_(0, 1) * 255).round_()
+        out[i] = img.permute(1, 2, 0).to(torch.uint8)
     return out
 
 
@@ -29,6 +39,8 @@ def reference_requests(n, h=224, w=224, seed=2000):
 
 
 def _calibrate_bn(model, shape, seed, batches=2, batch_size=16):
+    """BatchNorm running statistics from seeded synthetic requests (half structured images, half randn tensors — the two
+    request kinds the engine serves), cumulative average."""
     bns = [m for m in model.modules() if isinstance(m, nn.BatchNorm2d)]
     for m in bns:
         m.reset_running_stats()
@@ -36,8 +48,12 @@ def _calibrate_bn(model, shape, seed, batches=2, batch_size=16):
     model.train()
     g = torch.Generator().manual_seed(seed)
     with torch.no_grad():
-        for _ in range(batches):
-            model(torch.randn(batch_size, *shape, generator=g))
+        for b in range(batches):
+            half = batch_size // 2
+            imgs = synthetic_images(half, shape[1], shape[2], seed=500000 + seed * 1000 + b * half)
+            x = torch.cat([normalize_u8(imgs, IMAGENET_MEAN, IMAGENET_STD),
+                           torch.randn(batch_size - half, *shape, generator=g)])
+            model(x)
     model.eval()
     for m in bns:
         m.momentum = 0.1
@@ -51,9 +67,11 @@ def normalize_u8(imgs_u8, mean, std):
     return x.sub_(m).div_(s)
 
 
-def _plant_classifier(model, fc: nn.Linear, in_hw, seed, n_proto, alpha, mean, std):
-    """Nearest-prototype classifier: class j < n_proto fires on synthetic image j (seed 1000 + j); the remaining rows are
-    random directions of the same scale.  logit_j(x) = alpha * <p_j, f(x) - mu>, p_j = (f_j - mu) / mean||f - mu||."""
+def _plant_classifier(model, fc: nn.Linear, in_hw, seed, n_proto, planted, mean, std, ridge=0.05):
+    """Ridge-whitened nearest-prototype classifier: class j < n_proto fires on synthetic image j (seed 1000 + j) with a
+    logit of about `planted` and stays near 0 on the other prototype images; the remaining rows are random directions
+    of the same norm.  With D the centred pooled features of the prototype images (fp32 reference forward),
+    W[:n_proto] = planted' * (D D^T + ridge * mean diag)^-1 D,  b = -W mu."""
     feats = []
     hook = fc.register_forward_pre_hook(lambda mod, inp: feats.append(inp[0].detach().clone()))
     imgs = synthetic_images(n_proto, in_hw[0], in_hw[1])
@@ -64,22 +82,23 @@ def _plant_classifier(model, fc: nn.Linear, in_hw, seed, n_proto, alpha, mean, s
     f = torch.cat(feats).double()
     mu = f.mean(0)
     d = f - mu
-    scale = d.norm(dim=1).mean()
+    gram = d @ d.t()
+    lam = ridge * gram.diag().mean()
+    wp = torch.linalg.solve(gram + lam * torch.eye(n_proto, dtype=torch.float64), d)
     g = torch.Generator().manual_seed(seed)
     w = torch.randn(fc.out_features, fc.in_features, generator=g, dtype=torch.float64)
-    w = w / w.norm(dim=1, keepdim=True) * (d.norm(dim=1).mean() / scale)
-    w[:n_proto] = d / scale
+    w = w / w.norm(dim=1, keepdim=True) * wp.norm(dim=1).mean()
+    w[:n_proto] = wp
+    gain = planted / float((wp * d).sum(1).mean())
     with torch.no_grad():
-        fc.weight.copy_((alpha * w).float())
-        fc.bias.copy_((-alpha * (w @ mu)).float())
+        fc.weight.copy_((gain * w).float())
+        fc.bias.copy_((-gain * (w @ mu)).float())
 
 
-IMAGENET_MEAN = (0.485, 0.456, 0.406)
-IMAGENET_STD = (0.229, 0.224, 0.225)
 N_PROTO = 128  # classes 0..N_PROTO-1 are planted on synthetic images 1000..1000+N_PROTO-1
 
 
-def make_resnet50(seed=0, damp=0.25, alpha=0.35, n_proto=N_PROTO):
+def make_resnet50(seed=0, damp=0.25, planted=1.5, n_proto=N_PROTO):
     import torchvision
     torch.manual_seed(seed)
     m = torchvision.models.resnet50(weights=None)
@@ -87,11 +106,41 @@ def make_resnet50(seed=0, damp=0.25, alpha=0.35, n_proto=N_PROTO):
         for blk in [b for l in (m.layer1, m.layer2, m.layer3, m.layer4) for b in l]:
             blk.bn3.weight.fill_(damp)
     _calibrate_bn(m, (3, 224, 224), seed + 1)
-    _plant_classifier(m, m.fc, (224, 224), seed + 2, n_proto, alpha, IMAGENET_MEAN, IMAGENET_STD)
+    _plant_classifier(m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
     return m.eval()
 
 
-MODEL_BUILDERS = {"resnet50": make_resnet50}
+def make_shufflenet(seed=0, planted=0.8, n_proto=N_PROTO, bn_bias=1.0):
+    """No residual adds to damp here; a positive BatchNorm beta keeps most ReLU inputs positive, i.e. the random network
+    out of the chaotic regime where a 2^-9 rounding perturbation grows ~1.4x per unit (measured with the CPU interpreter)."""
+    import torchvision
+    torch.manual_seed(seed)
+    m = torchvision.models.shufflenet_v2_x1_0(weights=None)
+    with torch.no_grad():
+        for mod in m.modules():
+            if isinstance(mod, nn.BatchNorm2d):
+                mod.bias.fill_(bn_bias)
+    _calibrate_bn(m, (3, 224, 224), seed + 1)
+    _plant_classifier(m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
+    return m.eval()
+
+
+def make_efficientnet_v2_s(seed=0, damp=0.25, planted=1.0, n_proto=N_PROTO, in_hw=(224, 224)):
+    import torchvision
+    torch.manual_seed(seed)
+    m = torchvision.models.efficientnet_v2_s(weights=None)
+    with torch.no_grad():
+        for stage in m.features:
+            for blk in stage:
+                if getattr(blk, "use_res_connect", False):
+                    blk.block[-1][1].weight.fill_(damp)     # BatchNorm of the block's last conv (residual branch)
+    _calibrate_bn(m, (3, in_hw[0], in_hw[1]), seed + 1, batches=2, batch_size=8)
+    _plant_classifier(m, m.classifier[1], in_hw, seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
+    return m.eval()
+
+
+MODEL_BUILDERS = {"resnet50": make_resnet50, "shufflenet_v2_x1_0": make_shufflenet,
+                  "efficientnet_v2_s": make_efficientnet_v2_s}
 
 
 def make_model(kind, seed=0, **kw):

@@ -1,4 +1,4 @@
-"""End-to-end parity of the B200 engine (collate -> ResNet-50 forward) through the C ABI.
+"""End-to-end parity of the B200 engine (collate -> forward) through the C ABI, for every served model family.
 
 Reference arm: the torchvision fp32 CPU forward the reference actor runs (scheduler.py:443-450), same synthetic weights.
 Tolerances are the north-star ones: logits max-abs <= 2e-2, top-1 agreement >= 99.9 % on the synthetic set,
@@ -18,11 +18,15 @@ pytestmark = pytest.mark.gpu
 LOGIT_TOL = 2e-2
 
 
-@pytest.fixture(scope="module")
-def resnet(cuda):
-    torch.set_num_threads(max(1, torch.get_num_threads()))
-    module = synth.make_model("resnet50")
-    model = B200Model("resnet50", module, max_batch=64)
+KINDS = ["resnet50", "shufflenet_v2_x1_0", "efficientnet_v2_s"]
+
+
+@pytest.fixture(scope="module", params=KINDS)
+def resnet(request, cuda):
+    """(torchvision fp32 module, B200 engine) for each model family; the name is historical."""
+    kind = request.param
+    module = synth.make_model(kind)
+    model = B200Model(kind, module, max_batch=64)
     yield module, model
     model.close()
 
@@ -76,8 +80,8 @@ def test_per_layer_against_plan_interpreter(resnet):
         err = (got - want).abs().max().item()
         scale = want.abs().max().item() + 1e-6
         worst.append((err / scale, op_i, model.op_names[op_i], err, scale))
-        # storage rounding differences (1 bf16 ulp = 2^-8 relative) propagate and grow slowly through 50 layers
-        assert err <= 0.05 * scale, "op %d (%s): max err %.4g vs scale %.4g" % (op_i, model.op_names[op_i], err, scale)
+        # storage rounding differences (1 bf16 ulp = 2^-8 relative) propagate and grow slowly through 50-230 layers
+        assert err <= 0.06 * scale, "op %d (%s): max err %.4g vs scale %.4g" % (op_i, model.op_names[op_i], err, scale)
     worst.sort(reverse=True)
     print("worst layers:", worst[:3])
 
@@ -93,7 +97,9 @@ def test_logits_and_top1_vs_fp32_cpu_reference(resnet):
     err = (got - ref).abs().max().item()
     rel = err / ref.std().item()
     agree = (got.argmax(1) == ref.argmax(1)).float().mean().item()
-    print("logits max-abs err %.4g (%.2f%% of logit std %.3g); top-1 agreement %.4f" % (err, 100 * rel, ref.std().item(), agree))
+    planted = ref.diag().mean().item()
+    print("%s: logits max-abs err %.4g (%.2f%% of the planted logit %.3g); top-1 agreement %.4f"
+          % (model.kind, err, 100 * err / planted, planted, agree))
     assert err <= LOGIT_TOL
     assert agree >= 0.999
     assert (ref.argmax(1) == torch.arange(n)).all(), "reference itself must recover the planted classes"

@@ -1,0 +1,138 @@
+"""Operator-level parity of the bandwidth-bound kernels (through the C ABI) against plain PyTorch fp32 on the same
+bf16-representable inputs.  Pure data movement and max-pooling are bit-exact; arithmetic kernels are compared within
+1 bf16 ulp of the result (2^-8 relative + small absolute term), fp32 outputs within 1e-4 relative."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+import rdb_b200
+from rdb_b200.lib import check, ptr, stream_ptr
+
+pytestmark = pytest.mark.gpu
+
+
+def rnd(shape, seed, dev, dtype=torch.bfloat16):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randn(*shape, generator=g).to(dev).to(dtype)
+
+
+def close_bf16(out, ref):
+    err = (out.float() - ref).abs()
+    return bool((err <= ref.abs() * 2.0 ** -8 + 2e-3).all()), err.max().item()
+
+
+@pytest.mark.parametrize("k,s,p,cout,cfg", [(7, 2, 3, 64, (2, 224, 224)), (3, 2, 1, 24, (3, 224, 224)),
+                                            (3, 2, 1, 16, (1, 97, 131)), (3, 2, 1, 32, (2, 64, 64))])
+def test_stem_conv(b200lib, cuda, k, s, p, cout, cfg):
+    n, h, w = cfg
+    x4 = torch.zeros(n, h, w, 4, device=cuda, dtype=torch.bfloat16)
+    x4[..., :3] = rnd((n, h, w, 3), 1, cuda)
+    wt = rnd((cout, 3, k, k), 2, cuda, torch.float32) / (27 ** 0.5)
+    b = rnd((cout,), 3, cuda, torch.float32)
+    ct = b200lib.b200_stem_cout_tile(cout)
+    cpad = (cout + ct - 1) // ct * ct
+    wp = torch.zeros(k * k, 3, cpad, device=cuda)
+    wp[:, :, :cout] = wt.permute(2, 3, 1, 0).reshape(k * k, 3, cout)
+    bp = torch.zeros(cpad, device=cuda)
+    bp[:cout] = b
+    ho, wo = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    out = torch.full((n, ho, wo, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_conv_nhwc(ptr(x4), n, h, w, ptr(wp), ptr(bp), ptr(out), cout, 0, k, s, p, 2, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.silu(F.conv2d(x4[..., :3].float().permute(0, 3, 1, 2), wt, b, stride=s, padding=p)).permute(0, 2, 3, 1)
+    ok, e = close_bf16(out, ref)
+    assert ok, e
+
+
+@pytest.mark.parametrize("n,h,w,c,stride,act", [(2, 28, 28, 64, 1, 0), (3, 56, 56, 24, 2, 0), (1, 15, 17, 960, 1, 2),
+                                                (2, 14, 14, 232, 2, 2)])
+def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
+    x = rnd((n, h, w, c), 1, cuda)
+    wt = rnd((c, 1, 3, 3), 2, cuda, torch.float32) / 3
+    b = rnd((c,), 3, cuda, torch.float32)
+    ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
+    out = torch.full((n, ho, wo, c), float("nan"), device=cuda, dtype=torch.bfloat16)
+    w9 = wt.reshape(c, 9).t().contiguous()
+    check(b200lib.b200_dwconv3x3_nhwc(ptr(x), n, h, w, c, 0, ptr(w9), ptr(b), ptr(out), 0, stride, act, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt, b, stride=stride, padding=1, groups=c)
+    ref = (F.silu(ref) if act == 2 else ref).permute(0, 2, 3, 1)
+    ok, e = close_bf16(out, ref)
+    assert ok, e
+
+
+@pytest.mark.parametrize("n,h,w,c,k,s,p", [(2, 112, 112, 64, 3, 2, 1), (1, 20, 20, 128, 5, 1, 2), (3, 7, 9, 24, 3, 2, 1)])
+def test_maxpool_bit_exact(b200lib, cuda, n, h, w, c, k, s, p):
+    x = rnd((n, h, w, c), 4, cuda)
+    ho, wo = (h + 2 * p - k) // s + 1, (w + 2 * p - k) // s + 1
+    out = torch.empty(n, ho, wo, c, device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_maxpool_nhwc(ptr(x), n, h, w, c, 0, ptr(out), 0, k, s, p, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.max_pool2d(x.float().permute(0, 3, 1, 2), k, s, p).permute(0, 2, 3, 1)
+    assert torch.equal(out.float(), ref)
+
+
+@pytest.mark.parametrize("n,h,w,c", [(5, 7, 7, 2048), (2, 7, 7, 1280), (3, 7, 7, 1024), (1, 14, 14, 96), (2, 3, 5, 8)])
+def test_global_avgpool(b200lib, cuda, n, h, w, c):
+    x = rnd((n, h, w, c), 5, cuda)
+    out = torch.empty(n, c, device=cuda)
+    check(b200lib.b200_global_avgpool_nhwc(ptr(x), n, h, w, c, 0, ptr(out), stream_ptr()))
+    torch.cuda.synchronize()
+    ref = x.float().mean(dim=(1, 2))
+    assert torch.allclose(out, ref, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n,k,j,act", [(1, 2048, 1000, 0), (19, 1280, 1000, 0), (256, 1024, 1000, 0), (7, 1536, 64, 2),
+                                        (7, 40, 960, 3), (3, 16, 256, 3)])
+def test_fc(b200lib, cuda, n, k, j, act):
+    x = rnd((n, k), 6, cuda, torch.float32)
+    w = rnd((j, k), 7, cuda, torch.float32) / k ** 0.5
+    b = rnd((j,), 8, cuda, torch.float32)
+    out = torch.full((n, j), float("nan"), device=cuda)
+    check(b200lib.b200_fc(ptr(x), ptr(w), ptr(b), ptr(out), n, k, j, 1.0, act, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = x.double() @ w.double().t() + b.double()
+    ref = (F.silu(ref) if act == 2 else torch.sigmoid(ref) if act == 3 else ref).float()
+    assert torch.allclose(out, ref, rtol=1e-4, atol=1e-5), (out - ref).abs().max().item()
+
+
+def test_channel_scale(b200lib, cuda):
+    n, h, w, c = 3, 14, 14, 960
+    x = rnd((n, h, w, c), 9, cuda)
+    gate = torch.sigmoid(rnd((n, c), 10, cuda, torch.float32))
+    out = torch.empty_like(x)
+    check(b200lib.b200_channel_scale_nhwc(ptr(x), n, h, w, c, 0, ptr(gate), ptr(out), 0, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = (x.float() * gate.view(n, 1, 1, c)).to(torch.bfloat16)
+    assert torch.equal(out, ref)
+
+
+def test_copy_and_upsample_into_slices_bit_exact(b200lib, cuda):
+    n, h, w, c = 2, 10, 12, 64
+    x = rnd((n, h, w, c), 11, cuda)
+    cat = torch.zeros(n, 2 * h, 2 * w, 192, device=cuda, dtype=torch.bfloat16)
+    up_slice = cat[..., 128:192]
+    check(b200lib.b200_upsample2x_nhwc(ptr(x), n, h, w, c, 0, up_slice.data_ptr(), 192, stream_ptr()))
+    y = rnd((n, 2 * h, 2 * w, 128), 12, cuda)
+    check(b200lib.b200_copy_channels_nhwc(ptr(y), n, 2 * h, 2 * w, 128, 0, cat.data_ptr(), 192, stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(cat[..., :128], y)
+    assert torch.equal(cat[..., 128:], x.repeat_interleave(2, dim=1).repeat_interleave(2, dim=2))
+
+
+@pytest.mark.parametrize("c", [58, 116, 232, 8])
+def test_shuffle_concat_matches_torchvision_channel_shuffle(b200lib, cuda, c):
+    from torchvision.models.shufflenetv2 import channel_shuffle
+    n, h, w = 2, 7, 9
+    cp = (c + 7) // 8 * 8
+    a = torch.zeros(n, h, w, cp, device=cuda, dtype=torch.bfloat16)
+    b = torch.zeros(n, h, w, cp, device=cuda, dtype=torch.bfloat16)
+    a[..., :c] = rnd((n, h, w, c), 13, cuda)
+    b[..., :c] = rnd((n, h, w, c), 14, cuda)
+    out = torch.full((n, h, w, 2 * cp), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_shuffle_concat_nhwc(ptr(a), 0, ptr(b), 0, n, h, w, c, ptr(out), 0, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = channel_shuffle(torch.cat([a[..., :c], b[..., :c]], dim=-1).permute(0, 3, 1, 2).float(), 2).permute(0, 2, 3, 1)
+    assert torch.equal(out[..., :c].float(), ref[..., :c])
+    assert torch.equal(out[..., cp:cp + c].float(), ref[..., c:])
+    assert not out[..., c:cp].float().abs().any() and not out[..., cp + c:].float().abs().any()
