@@ -149,6 +149,14 @@ B200_API int b200_collate_u8_noalloc(const void* packed_dev, const uint64_t* off
 B200_API int b200_collate_f32(b200_engine* e, const float* stacked_chw, int n, int padded_batch, int src_on_device,
                               void* out_nhwc_bf16, void* stream);
 
+/* YOLOv8 post-processing on the device: class-aware greedy NMS over the engine's [batch][84][A] head output (head = NULL
+ * uses the engine's output buffer; otherwise a device pointer of that layout). boxes: device fp32 [batch][max_det][6]
+ * = x1,y1,x2,y2,score,class (input pixels); counts: device int32 [batch]. max_det <= 300. Restates ultralytics
+ * utils/ops.py non_max_suppression (conf 0.25 / IoU 0.45 / max_det 300 are its defaults); no counterpart runs in the
+ * reference (YOLOv8 is workload-only there). */
+B200_API int b200_decode_yolo(b200_engine* e, const float* head, int batch, float conf, float iou, int max_det,
+                              float* boxes, int32_t* counts, void* stream);
+
 /* Forward pass of `batch` images. in = NULL or the engine input buffer: run in place; otherwise it is copied in first.
  * out (host or device, fp32 [batch][out_dim]) receives the result with an async copy on `stream`; NULL skips the copy.
  * Replaces `outputs = model(inputs)` and `outputs.cpu()` (scheduler.py:449-450, 468). No host synchronisation inside. */

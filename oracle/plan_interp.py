@@ -119,6 +119,28 @@ class PlanInterpreter:
                 o[..., p[4]:p[4] + 2 * cp] = 0
                 o[..., p[4]:p[4] + c] = sh[..., :c]
                 o[..., p[4] + cp:p[4] + cp + c] = sh[..., c:]
+            elif t == OP_YOLO_DECODE:
+                hb = B[p[0]][..., p[1]:p[1] + 64]
+                hc = B[p[12]][..., p[13]:p[13] + 80]
+                a_off, stride, a_total = p[15], float(p[16]), p[17]
+                wb = self._f32(op["w_off"], 64 * 64).view(64, 64)
+                bb = self._f32(op["b_off"], 64)
+                wc = self._f32(op["w2_off"], 80 * 80).view(80, 80)
+                bc = self._f32(op["b2_off"], 80)
+                h, w = hb.shape[1], hb.shape[2]
+                box = (hb.reshape(n, h * w, 64) @ wb.t() + bb).view(n, h * w, 4, 16).softmax(3)
+                dist = (box * torch.arange(16, dtype=torch.float32)).sum(3)            # [n, hw, 4] l t r b
+                yy, xx = torch.meshgrid(torch.arange(h, dtype=torch.float32) + 0.5,
+                                        torch.arange(w, dtype=torch.float32) + 0.5, indexing="ij")
+                ax, ay = xx.reshape(-1), yy.reshape(-1)
+                x1, y1, x2, y2 = ax - dist[..., 0], ay - dist[..., 1], ax + dist[..., 2], ay + dist[..., 3]
+                cls = torch.sigmoid(hc.reshape(n, h * w, 80) @ wc.t() + bc)
+                o = B[p[3]].view(n, 84, a_total)
+                o[:, 0, a_off:a_off + h * w] = (x1 + x2) * 0.5 * stride
+                o[:, 1, a_off:a_off + h * w] = (y1 + y2) * 0.5 * stride
+                o[:, 2, a_off:a_off + h * w] = (x2 - x1) * stride
+                o[:, 3, a_off:a_off + h * w] = (y2 - y1) * stride
+                o[:, 4:, a_off:a_off + h * w] = cls.permute(0, 2, 1)
             else:
                 raise NotImplementedError("op type %d" % t)
         out = B[self.hdr["out_buf"]].view(n, -1)

@@ -12,6 +12,8 @@
 #include "conv_gemm.cuh"
 #include "ptx.cuh"
 
+#include <stdlib.h>
+
 namespace b200 {
 
 static constexpr int BLOCK_M = 128;
@@ -194,6 +196,264 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   }
 }
 
+// ================================================================================================================
+// Persistent variant: one CTA per SM loops over tiles; loads, MMAs, the epilogue and the stores of consecutive tiles
+// overlap (smem ring continues across tiles, two TMEM accumulators, three output-staging buffers).
+//   warp 0 : TMA producer (A/B ring)              warp 1 : MMA issuer (TMEM accumulator it & 1)
+//   warp 2 : "DMA" thread: prefetches the residual tile into staging[it % 3] and issues the TMA store of tile it-1
+//   warps 4-7 : epilogue (TMEM -> +bias/+res/act -> bf16 -> staging, in place over the residual)
+// ================================================================================================================
+static constexpr int PCONV_THREADS = 256;
+
+template <int BLOCK_N>
+struct PConvCfg {
+  static constexpr int STAGES = BLOCK_N == 64 ? 4 : 3;      // A/B ring
+  static constexpr int OUT_BUFS = BLOCK_N == 64 ? 6 : 4;    // output / residual staging ring
+  static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
+  static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int OUT_BYTES = BLOCK_M * BLOCK_N * 2;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + 1024;
+  static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
+};
+
+__device__ __forceinline__ void tile_coords(const ConvParams& p, int tile, int& n_tile, int& w0, int& h0, int& nb0) {
+  n_tile = tile % p.n_tiles;
+  int m = tile / p.n_tiles;
+  const int t_w = m % p.tiles_w;
+  m /= p.tiles_w;
+  const int t_h = m % p.tiles_h;
+  const int t_n = m / p.tiles_h;
+  w0 = t_w * p.tw; h0 = t_h * p.th; nb0 = t_n * p.tn;
+}
+
+template <int ACT>
+__device__ __forceinline__ float act_t(float x) {
+  if (ACT == ACT_RELU) return fmaxf(x, 0.f);
+  if (ACT == ACT_SILU) return x / (1.f + __expf(-x));
+  if (ACT == ACT_SIGMOID) return 1.f / (1.f + __expf(-x));
+  return x;
+}
+
+// RES: 0 no residual, 1 act(acc + bias + res), 2 act(acc + bias) + res.  ACT: b200::Act.
+template <int BLOCK_N, int RES, int ACT>
+__global__ void __launch_bounds__(PCONV_THREADS, 1)
+conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
+                            const int total_tiles) {
+  using Cfg = PConvCfg<BLOCK_N>;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int NB = Cfg::OUT_BUFS;
+  constexpr int LA = Cfg::LOOKAHEAD;
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[STAGES];
+  __shared__ __align__(8) uint64_t bar_empty[STAGES];
+  __shared__ __align__(8) uint64_t bar_tmem_full[2];
+  __shared__ __align__(8) uint64_t bar_tmem_empty[2];
+  __shared__ __align__(8) uint64_t bar_stage_ready[NB];  // staging buffer free (and residual landed, if any)
+  __shared__ __align__(8) uint64_t bar_out_ready[NB];    // epilogue finished writing the staging buffer
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[2][BLOCK_N];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t staging = ring + STAGES * Cfg::STAGE_BYTES;
+  const int num_kb = p.num_taps * p.kb_per_tap;
+  const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b);
+    tma_prefetch_desc(&maps.d);
+    if (RES) tma_prefetch_desc(&maps.r);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bar_tmem_full[b]), 1);
+      mbar_init(smem_u32(&bar_tmem_empty[b]), 128);
+    }
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(smem_u32(&bar_stage_ready[b]), 1);
+      mbar_init(smem_u32(&bar_out_ready[b]), 128);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc<2 * BLOCK_N>(smem_u32(&tmem_base_s));
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    // =========================== TMA producer ===========================
+    if (lane == 0) {
+      uint32_t g = 0;  // k-block counter across all tiles of this CTA
+      for (int it = 0; it < my_tiles; ++it) {
+        const int tile = blockIdx.x + it * gridDim.x;
+        int n_tile, w0, h0, nb0;
+        tile_coords(p, tile, n_tile, w0, h0, nb0);
+        const int n0 = n_tile * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb, ++g) {
+          const int s = g % STAGES;
+          const uint32_t ph = (g / STAGES) & 1;
+          mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
+          const uint32_t full = smem_u32(&bar_full[s]);
+          mbar_expect_tx(full, Cfg::STAGE_BYTES);
+          const int t = kb / p.kb_per_tap;
+          const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+          const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
+          tma_load_4d(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
+          tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer ===========================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, BLOCK_N);
+      uint32_t g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int b = it & 1;
+        mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it >> 1) & 1) ^ 1);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t acc = tmem_base + b * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb, ++g) {
+          const int s = g % STAGES;
+          const uint32_t ph = (g / STAGES) & 1;
+          mbar_wait(smem_u32(&bar_full[s]), ph);
+          tc_fence_after();
+          const uint32_t a_src = ring + s * Cfg::STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_src);
+          const uint64_t bdesc = umma_desc_sw128(a_src + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit(smem_u32(&bar_empty[s]));
+        }
+        umma_commit(smem_u32(&bar_tmem_full[b]));
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // =========================== DMA: residual prefetch (LA tiles ahead) + output stores ===========================
+    if (lane == 0) {
+      auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
+        const int tile = blockIdx.x + j * gridDim.x;
+        const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
+        if (RES) {
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * BLOCK_N + q * 64,
+                        w0, h0, nb0);
+        } else {
+          mbar_arrive(rdy);
+        }
+      };
+      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
+      for (int it = 0; it < my_tiles; ++it) {
+        // store of tile it, once its epilogue is done
+        {
+          const int tile = blockIdx.x + it * gridDim.x;
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          const int n0 = n_tile * BLOCK_N;
+          const int ob = it % NB;
+          mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            if (n0 + q * 64 < p.cout)
+              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+          tma_store_commit();
+        }
+        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
+        // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
+        const int j = it + LA;
+        if (j < my_tiles) {
+          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          acquire_staging(j);
+        }
+      }
+      tma_store_wait_all();
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // =========================== epilogue ===========================
+    const int epi_tid = threadIdx.x - 128;  // 0..127
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t row_off = row * 128;
+    const int sw = row & 7;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int tile = blockIdx.x + it * gridDim.x;
+      const int b = it & 1;
+      const int ob = it % NB;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      for (int i = epi_tid; i < BLOCK_N; i += 128) {
+        const int c = n0 + i;
+        bias_s[b][i] = (c < p.cout) ? p.bias[c] : 0.f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
+      tc_fence_after();
+      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
+      const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
+      const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+      for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + cc * 32, v);
+        tmem_ld_wait();
+        const uint32_t sub = stage_d + (cc >> 1) * (BLOCK_M * 128) + row_off;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int chunk = (cc & 1) * 4 + g;
+          const uint32_t addr = sub + ((chunk ^ sw) << 4);
+          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8]);
+          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8 + 4]);
+          float f[8];
+          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
+          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
+          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
+          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+          if (RES) {
+            uint32_t r0, r1, r2, r3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+            const float rr[8] = {bf16_lo(r0), bf16_hi(r0), bf16_lo(r1), bf16_hi(r1),
+                                 bf16_lo(r2), bf16_hi(r2), bf16_lo(r3), bf16_hi(r3)};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = (RES == 2) ? act_t<ACT>(f[i]) + rr[i] : act_t<ACT>(f[i] + rr[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+          }
+          const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+          const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
+                       : "memory");
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_tmem_empty[b]));   // accumulator may be overwritten by tile it+2
+      fence_proxy_async_smem();                    // staging writes -> visible to the TMA store
+      mbar_arrive(smem_u32(&bar_out_ready[ob]));
+    }
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<2 * BLOCK_N>(tmem_base);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 
 static void pick_tile(int W, int H, int N, int* tw, int* th, int* tn) {
@@ -315,6 +575,51 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   return B200_OK;
 }
 
+static bool use_persistent() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_PERSISTENT");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+template <int BLOCK_N, int RES, int ACT>
+static int launch_persistent_t(const ConvLaunch& l, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, PConvCfg<BLOCK_N>::SMEM_BYTES));
+    configured[dev & 63] = true;
+  }
+  const int total = static_cast<int>(l.grid);
+  const int ctas = total < device_sm_count() ? total : device_sm_count();
+  conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>
+      <<<ctas, PCONV_THREADS, PConvCfg<BLOCK_N>::SMEM_BYTES, stream>>>(l.maps, l.p, total);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+template <int BLOCK_N, int RES>
+static int launch_persistent_act(const ConvLaunch& l, cudaStream_t stream) {
+  switch (l.p.act) {
+    case ACT_NONE: return launch_persistent_t<BLOCK_N, RES, ACT_NONE>(l, stream);
+    case ACT_RELU: return launch_persistent_t<BLOCK_N, RES, ACT_RELU>(l, stream);
+    case ACT_SILU: return launch_persistent_t<BLOCK_N, RES, ACT_SILU>(l, stream);
+    case ACT_SIGMOID: return launch_persistent_t<BLOCK_N, RES, ACT_SIGMOID>(l, stream);
+  }
+  return fail(B200_ERR_INVALID, "conv: unknown activation");
+}
+
+template <int BLOCK_N>
+static int launch_persistent_res(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.p.has_res == 0) return launch_persistent_act<BLOCK_N, 0>(l, stream);
+  if (l.p.has_res == 1) return launch_persistent_act<BLOCK_N, 1>(l, stream);
+  return launch_persistent_act<BLOCK_N, 2>(l, stream);
+}
+
 template <int BLOCK_N>
 static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
   static bool configured[64] = {};
@@ -331,6 +636,10 @@ static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
 }
 
 int conv_launch(const ConvLaunch& l, cudaStream_t stream) {
+  if (use_persistent()) {
+    if (l.block_n == 64) return launch_persistent_res<64>(l, stream);
+    return launch_persistent_res<128>(l, stream);
+  }
   if (l.block_n == 64) return launch_t<64>(l, stream);
   return launch_t<128>(l, stream);
 }

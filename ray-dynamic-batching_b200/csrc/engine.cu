@@ -163,6 +163,14 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
         rc = shuffle_concat_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[2], batch),
                                    view(p[3], p[4], p[5], batch), p[14], p[15], stream);
         break;
+      case OP_YOLO_DECODE:
+        rc = yolo_decode_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[14], batch),
+                                reinterpret_cast<const float*>(W + po.rec.w_off),
+                                reinterpret_cast<const float*>(W + po.rec.b_off),
+                                reinterpret_cast<const float*>(W + po.rec.w2_off),
+                                reinterpret_cast<const float*>(W + po.rec.b2_off), reinterpret_cast<float*>(buf_dev[p[3]]),
+                                p[15], p[17], static_cast<float>(p[16]), stream);
+        break;
       default:
         rc = fail(B200_ERR_BLOB, "engine: unknown op type " + std::to_string(po.rec.type));
     }
@@ -355,6 +363,19 @@ int b200_collate_f32(b200_engine* h, const float* stacked_chw, int n, int padded
   }
   void* out = out_nhwc_bf16 ? out_nhwc_bf16 : e.buf_dev[e.hdr.in_buf];
   B200_TRY(collate_f32chw_launch(src, n, padded_batch, e.hdr.in_h, e.hdr.in_w, out, stream));
+  e.launches += 1;
+  return B200_OK;
+}
+
+int b200_decode_yolo(b200_engine* h, const float* head, int batch, float conf, float iou, int max_det, float* boxes,
+                     int32_t* counts, void* stream_) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  Engine& e = h->e;
+  if (batch <= 0 || batch > e.max_batch || !boxes || !counts) return fail(B200_ERR_INVALID, "b200_decode_yolo: bad arguments");
+  if (e.hdr.out_dim % 84 != 0) return fail(B200_ERR_INVALID, "b200_decode_yolo: engine output is not a [84][A] detection head");
+  const float* pred = head ? head : reinterpret_cast<const float*>(e.buf_dev[e.hdr.out_buf]);
+  B200_TRY(yolo_nms_launch(pred, batch, 80, e.hdr.out_dim / 84, conf, iou, max_det, boxes, counts,
+                           static_cast<cudaStream_t>(stream_)));
   e.launches += 1;
   return B200_OK;
 }

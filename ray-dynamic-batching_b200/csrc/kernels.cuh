@@ -43,4 +43,12 @@ int upsample2x_launch(const View& in, const View& out, cudaStream_t stream);    
 // logical out[2i] = a[i], out[2i+1] = b[i] (i < c); logical channel l is stored at physical (l < c ? l : cp + l - c)
 int shuffle_concat_launch(const View& a, const View& b, const View& out, int c, int cp, cudaStream_t stream);
 
+// ---- YOLOv8 head (yolo.cu) ----
+// hb/hc: hidden activations of the box / class branch (64 / 80 channels); wb [64][64], wc [80][80] fp32 final 1x1 convs;
+// out fp32 [N][84][a_total], this level's anchors at [a_off, a_off + H*W)
+int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const float* bb, const float* wc, const float* bc,
+                       float* out, int a_off, int a_total, float stride, cudaStream_t stream);
+int yolo_nms_launch(const float* pred, int batch, int nc, int a_total, float conf, float iou, int max_det, float* boxes,
+                    int* counts, cudaStream_t stream);
+
 }  // namespace b200

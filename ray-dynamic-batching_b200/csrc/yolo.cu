@@ -1,0 +1,231 @@
+// YOLOv8 Detect head: fused final 1x1 convolutions (fp32) + DFL + dist2bbox + stride scaling + class sigmoid, and NMS.
+//
+// The reference names YOLOv8n only through its image workload (sample-models/yolov8/workload); the arithmetic restated
+// here is ultralytics' Detect.forward / DFL / dist2bbox / non_max_suppression (see ray-dynamic-batching_b200/yolov8n_arch.py).
+//
+// decode: one thread per anchor.  It reads the two hidden vectors of its pixel (64 box-branch + 80 class-branch bf16
+// channels, outputs of the tensor-core 3x3 convs), applies the last 1x1 convs in fp32 with weights broadcast from shared
+// memory (so the DFL logits never see bf16 rounding), turns 4 x 16 bins into distances by a softmax expectation, builds
+// the xywh box around (grid + 0.5) * stride and writes [84][A] channel-major, coalesced over anchors.
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace b200 {
+
+static constexpr int YD_THREADS = 128;
+static constexpr int REG_MAX = 16;
+
+template <int CB, int NC>  // CB: box-branch hidden channels (= 4*REG_MAX outputs), NC: classes (= class-branch hidden channels)
+__global__ void __launch_bounds__(YD_THREADS)
+yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* __restrict__ hc, int hc_ps, int H, int W,
+                   int N, const float* __restrict__ wb, const float* __restrict__ bb, const float* __restrict__ wc,
+                   const float* __restrict__ bc, float* __restrict__ out, int a_off, int a_total, float stride) {
+  extern __shared__ __align__(16) float s_w[];  // wb [64][CB] | wc [NC][NC] | bb [64] | bc [NC]
+  float* s_wb = s_w;
+  float* s_wc = s_wb + 4 * REG_MAX * CB;
+  float* s_bb = s_wc + NC * NC;
+  float* s_bc = s_bb + 4 * REG_MAX;
+  for (int i = threadIdx.x; i < 4 * REG_MAX * CB; i += YD_THREADS) s_wb[i] = wb[i];
+  for (int i = threadIdx.x; i < NC * NC; i += YD_THREADS) s_wc[i] = wc[i];
+  for (int i = threadIdx.x; i < 4 * REG_MAX; i += YD_THREADS) s_bb[i] = bb[i];
+  for (int i = threadIdx.x; i < NC; i += YD_THREADS) s_bc[i] = bc[i];
+  __syncthreads();
+  const long long idx = static_cast<long long>(blockIdx.x) * YD_THREADS + threadIdx.x;
+  if (idx >= static_cast<long long>(N) * H * W) return;
+  const int a = static_cast<int>(idx % (H * W));
+  const int n = static_cast<int>(idx / (H * W));
+  const int y = a / W, x = a - y * W;
+  float* o = out + (static_cast<size_t>(n) * (4 + NC)) * a_total + a_off + a;
+
+  {  // ---- box branch ----
+    float h[CB];
+    const uint4* src = reinterpret_cast<const uint4*>(hb + idx * hb_ps);
+#pragma unroll
+    for (int i = 0; i < CB / 8; ++i) {
+      const uint4 v = src[i];
+      h[i * 8 + 0] = bf16_lo(v.x); h[i * 8 + 1] = bf16_hi(v.x); h[i * 8 + 2] = bf16_lo(v.y); h[i * 8 + 3] = bf16_hi(v.y);
+      h[i * 8 + 4] = bf16_lo(v.z); h[i * 8 + 5] = bf16_hi(v.z); h[i * 8 + 6] = bf16_lo(v.w); h[i * 8 + 7] = bf16_hi(v.w);
+    }
+    float dist[4];
+#pragma unroll 1
+    for (int s = 0; s < 4; ++s) {
+      float lg[REG_MAX];
+#pragma unroll
+      for (int j = 0; j < REG_MAX; ++j) {
+        const float4* wr = reinterpret_cast<const float4*>(s_wb + (s * REG_MAX + j) * CB);
+        float acc = s_bb[s * REG_MAX + j];
+#pragma unroll
+        for (int k4 = 0; k4 < CB / 4; ++k4) {
+          const float4 w4 = wr[k4];
+          acc = fmaf(h[k4 * 4 + 0], w4.x, acc); acc = fmaf(h[k4 * 4 + 1], w4.y, acc);
+          acc = fmaf(h[k4 * 4 + 2], w4.z, acc); acc = fmaf(h[k4 * 4 + 3], w4.w, acc);
+        }
+        lg[j] = acc;
+      }
+      float m = lg[0];
+#pragma unroll
+      for (int j = 1; j < REG_MAX; ++j) m = fmaxf(m, lg[j]);
+      float den = 0.f, num = 0.f;
+#pragma unroll
+      for (int j = 0; j < REG_MAX; ++j) {
+        const float e = expf(lg[j] - m);
+        den += e;
+        num += e * static_cast<float>(j);
+      }
+      dist[s] = num / den;
+    }
+    const float ax = static_cast<float>(x) + 0.5f, ay = static_cast<float>(y) + 0.5f;
+    const float x1 = ax - dist[0], y1 = ay - dist[1], x2 = ax + dist[2], y2 = ay + dist[3];
+    o[0] = (x1 + x2) * 0.5f * stride;
+    o[static_cast<size_t>(a_total)] = (y1 + y2) * 0.5f * stride;
+    o[static_cast<size_t>(2) * a_total] = (x2 - x1) * stride;
+    o[static_cast<size_t>(3) * a_total] = (y2 - y1) * stride;
+  }
+  {  // ---- class branch ----
+    float h[NC];
+    const uint4* src = reinterpret_cast<const uint4*>(hc + idx * hc_ps);
+#pragma unroll
+    for (int i = 0; i < NC / 8; ++i) {
+      const uint4 v = src[i];
+      h[i * 8 + 0] = bf16_lo(v.x); h[i * 8 + 1] = bf16_hi(v.x); h[i * 8 + 2] = bf16_lo(v.y); h[i * 8 + 3] = bf16_hi(v.y);
+      h[i * 8 + 4] = bf16_lo(v.z); h[i * 8 + 5] = bf16_hi(v.z); h[i * 8 + 6] = bf16_lo(v.w); h[i * 8 + 7] = bf16_hi(v.w);
+    }
+#pragma unroll 1
+    for (int j = 0; j < NC; ++j) {
+      const float4* wr = reinterpret_cast<const float4*>(s_wc + j * NC);
+      float acc = s_bc[j];
+#pragma unroll
+      for (int k4 = 0; k4 < NC / 4; ++k4) {
+        const float4 w4 = wr[k4];
+        acc = fmaf(h[k4 * 4 + 0], w4.x, acc); acc = fmaf(h[k4 * 4 + 1], w4.y, acc);
+        acc = fmaf(h[k4 * 4 + 2], w4.z, acc); acc = fmaf(h[k4 * 4 + 3], w4.w, acc);
+      }
+      o[static_cast<size_t>(4 + j) * a_total] = 1.f / (1.f + expf(-acc));
+    }
+  }
+}
+
+int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const float* bb, const float* wc, const float* bc,
+                       float* out, int a_off, int a_total, float stride, cudaStream_t stream) {
+  if (hb.C != 64 || hc.C != 80) return fail(B200_ERR_INVALID, "yolo_decode: expects 64 box-hidden and 80 class-hidden channels");
+  if (hb.N != hc.N || hb.H != hc.H || hb.W != hc.W) return fail(B200_ERR_INVALID, "yolo_decode: branch shapes differ");
+  if (a_off < 0 || a_off + hb.H * hb.W > a_total) return fail(B200_ERR_INVALID, "yolo_decode: anchor range out of bounds");
+  const size_t smem = (size_t(64) * 64 + 80 * 80 + 64 + 80) * sizeof(float);
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(yolo_decode_kernel<64, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    configured[dev & 63] = true;
+  }
+  const long long total = static_cast<long long>(hb.N) * hb.H * hb.W;
+  yolo_decode_kernel<64, 80><<<static_cast<unsigned>((total + YD_THREADS - 1) / YD_THREADS), YD_THREADS, smem, stream>>>(
+      static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H,
+      hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+// ----------------------------------------------------------------------------------------------------------------
+// NMS: one block per image.  (1) best class per anchor, keep score > conf; (2) bitonic sort of the candidates by
+// (score desc, anchor asc) in shared memory; (3) greedy suppression, class-aware via the max_wh class offset, each
+// candidate checked against the kept list in parallel.  Output [max_det][6] = x1,y1,x2,y2,score,class + count.
+// ----------------------------------------------------------------------------------------------------------------
+static constexpr int NMS_THREADS = 1024;
+static constexpr int NMS_CAP = 16384;  // >= anchors (8400 at 640x640), power of two for the bitonic network
+
+__global__ void __launch_bounds__(NMS_THREADS)
+yolo_nms_kernel(const float* __restrict__ pred, int nc, int a_total, float conf, float iou_thr, int max_det,
+                float max_wh, float* __restrict__ boxes, int* __restrict__ counts) {
+  extern __shared__ __align__(16) unsigned long long s_key[];  // [NMS_CAP] (score bits << 32) | ~anchor
+  __shared__ int s_n;
+  __shared__ float s_kept[300 * 5];  // shifted x1,y1,x2,y2 + unused
+  __shared__ int s_nkept, s_sup;
+  const int n = blockIdx.x;
+  const float* p = pred + static_cast<size_t>(n) * (4 + nc) * a_total;
+  if (threadIdx.x == 0) { s_n = 0; s_nkept = 0; }
+  for (int i = threadIdx.x; i < NMS_CAP; i += NMS_THREADS) s_key[i] = 0ull;
+  __syncthreads();
+  for (int a = threadIdx.x; a < a_total; a += NMS_THREADS) {
+    float best = -1.f;
+    for (int c = 0; c < nc; ++c) best = fmaxf(best, p[static_cast<size_t>(4 + c) * a_total + a]);
+    if (best > conf) {
+      const int slot = atomicAdd(&s_n, 1);
+      // scores are in (0,1): their float bits order like unsigned ints; ~anchor makes the lower anchor win ties
+      s_key[slot] = (static_cast<unsigned long long>(__float_as_uint(best)) << 32) | (0xFFFFFFFFu - static_cast<unsigned>(a));
+    }
+  }
+  __syncthreads();
+  const int ncand = s_n;
+  int len = 1;
+  while (len < ncand) len <<= 1;
+  for (int k = 2; k <= len; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < len; i += NMS_THREADS) {
+        const int ixj = i ^ j;
+        if (ixj > i) {
+          const unsigned long long x = s_key[i], y = s_key[ixj];
+          const bool desc = (i & k) == 0;  // descending overall
+          if (desc ? (x < y) : (x > y)) { s_key[i] = y; s_key[ixj] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  float* ob = boxes + static_cast<size_t>(n) * max_det * 6;
+  const int cap = max_det < 300 ? max_det : 300;
+  for (int i = 0; i < ncand; ++i) {
+    if (s_nkept >= cap) break;
+    const unsigned long long key = s_key[i];
+    const int a = static_cast<int>(0xFFFFFFFFu - static_cast<unsigned>(key & 0xFFFFFFFFull));
+    const float score = __uint_as_float(static_cast<unsigned>(key >> 32));
+    int cls = 0;
+    {  // first class attaining the best score (torch.max semantics)
+      for (int c = 0; c < nc; ++c)
+        if (p[static_cast<size_t>(4 + c) * a_total + a] == score) { cls = c; break; }
+    }
+    const float cx = p[a], cy = p[static_cast<size_t>(a_total) + a], w = p[static_cast<size_t>(2) * a_total + a],
+                h = p[static_cast<size_t>(3) * a_total + a];
+    const float x1 = cx - w / 2, y1 = cy - h / 2, x2 = cx + w / 2, y2 = cy + h / 2;
+    const float off = static_cast<float>(cls) * max_wh;
+    const float sx1 = x1 + off, sy1 = y1 + off, sx2 = x2 + off, sy2 = y2 + off;
+    if (threadIdx.x == 0) s_sup = 0;
+    __syncthreads();
+    const int nk = s_nkept;
+    for (int k = threadIdx.x; k < nk; k += NMS_THREADS) {
+      const float kx1 = s_kept[k * 5], ky1 = s_kept[k * 5 + 1], kx2 = s_kept[k * 5 + 2], ky2 = s_kept[k * 5 + 3];
+      const float iw = fmaxf(fminf(sx2, kx2) - fmaxf(sx1, kx1), 0.f), ih = fmaxf(fminf(sy2, ky2) - fmaxf(sy1, ky1), 0.f);
+      const float inter = iw * ih;
+      const float iou = inter / ((sx2 - sx1) * (sy2 - sy1) + (kx2 - kx1) * (ky2 - ky1) - inter + 1e-7f);
+      if (iou > iou_thr) s_sup = 1;
+    }
+    __syncthreads();
+    if (!s_sup) {
+      if (threadIdx.x == 0) {
+        s_kept[nk * 5] = sx1; s_kept[nk * 5 + 1] = sy1; s_kept[nk * 5 + 2] = sx2; s_kept[nk * 5 + 3] = sy2;
+        ob[nk * 6] = x1; ob[nk * 6 + 1] = y1; ob[nk * 6 + 2] = x2; ob[nk * 6 + 3] = y2; ob[nk * 6 + 4] = score;
+        ob[nk * 6 + 5] = static_cast<float>(cls);
+        s_nkept = nk + 1;
+      }
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) counts[n] = s_nkept;
+}
+
+int yolo_nms_launch(const float* pred, int batch, int nc, int a_total, float conf, float iou, int max_det, float* boxes,
+                    int* counts, cudaStream_t stream) {
+  if (a_total > NMS_CAP) return fail(B200_ERR_INVALID, "yolo_nms: too many anchors");
+  if (max_det <= 0 || max_det > 300) return fail(B200_ERR_INVALID, "yolo_nms: max_det must be in [1, 300]");
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NMS_CAP * 8));
+    configured[dev & 63] = true;
+  }
+  yolo_nms_kernel<<<batch, NMS_THREADS, NMS_CAP * 8, stream>>>(pred, nc, a_total, conf, iou, max_det, 7680.f, boxes, counts);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200

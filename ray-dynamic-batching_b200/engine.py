@@ -150,6 +150,15 @@ class B200Model:
         _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(out), self._stream()), "b200_infer")
         return out[:n, :self.out_logical]
 
+    def decode_yolo(self, batch, conf=0.25, iou=0.45, max_det=300, head=None):
+        """Class-aware NMS on the device over the [batch, 84, A] head output of the last forward (or `head`).
+        Returns (boxes [batch, max_det, 6] = x1,y1,x2,y2,score,class ; counts [batch]) as device tensors."""
+        boxes = torch.zeros(batch, max_det, 6, device=self.device, dtype=torch.float32)
+        counts = torch.zeros(batch, device=self.device, dtype=torch.int32)
+        _lib.check(self.lib.b200_decode_yolo(self._h, _lib.ptr(head), batch, conf, iou, max_det, _lib.ptr(boxes),
+                                             _lib.ptr(counts), self._stream()), "b200_decode_yolo")
+        return boxes, counts
+
     def infer_resident(self, batch, out):
         """Forward over whatever the engine input buffer holds (inputs already resident in HBM)."""
         _lib.check(self.lib.b200_infer(self._h, None, batch, _lib.ptr(out), self._stream()), "b200_infer")

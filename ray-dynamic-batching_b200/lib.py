@@ -50,6 +50,7 @@ SIGNATURES = {
     "b200_collate_u8_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                         c_void_p, c_size_t, c_void_p, c_void_p]),
     "b200_collate_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b200_decode_yolo": (c_int, [c_void_p, c_void_p, c_int, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_infer": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
 }
 

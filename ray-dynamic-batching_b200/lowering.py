@@ -248,6 +248,19 @@ class PlanBuilder:
         self._op(OP_UPSAMPLE, [x.buf, x.coff, x.cphys, out.buf, out.coff, x.cphys], name=name)
         return out
 
+    def yolo_decode(self, hb: T, hc: T, wb, bb, wc, bc, out_buf, a_off, a_total, stride, name=""):
+        """Final 1x1 convs of one Detect level (fp32) + DFL + dist2bbox + sigmoid into the [84][A] output buffer."""
+        assert hb.c == 64 and hc.c == 80 and wb.shape == (64, 64) and wc.shape == (80, 80)
+        w_off = self.add_weights(wb.numpy().astype(np.float32))
+        b_off = self.add_weights(bb.numpy().astype(np.float32))
+        w2_off = self.add_weights(wc.numpy().astype(np.float32))
+        b2_off = self.add_weights(bc.numpy().astype(np.float32))
+        p = [hb.buf, hb.coff, 64, out_buf, 0, 0, -1, 0, 0, 0, 0, 0, hc.buf, hc.coff, 80, a_off, int(stride), a_total]
+        self._op(OP_YOLO_DECODE, p, w_off, b_off, w2_off, b2_off, name=name)
+
+    def slice(self, buf, coff, c, h, w):
+        return T(buf, coff, c, h, w)
+
     def set_output(self, t: T):
         assert self.bufs[t.buf][3] == 1, "model output must be an fp32 vector buffer"
         assert np.array_equal(t.cmap, np.arange(t.c))
@@ -407,7 +420,83 @@ def lower_efficientnet_v2(model, in_hw=(224, 224)) -> PlanBuilder:
     return pb
 
 
-LOWERINGS = {"resnet50": lower_resnet, "shufflenet_v2_x1_0": lower_shufflenet, "efficientnet_v2_s": lower_efficientnet_v2}
+def lower_yolov8n(model, in_hw=(640, 640)) -> PlanBuilder:
+    """YOLOv8n (ultralytics yolov8.yaml, scale n; see yolov8n_arch.py). Accepts either our plain-PyTorch module (layers
+    m0..m22) or an ultralytics DetectionModel (`.model[i]`). Concats are written in place: every producer of a concat
+    operand stores straight into its channel slice of the concat buffer."""
+    def L(i):
+        return model.model[i] if hasattr(model, "model") else getattr(model, "m%d" % i)
+
+    pb = PlanBuilder("yolov8n", in_hw[0], in_hw[1], mean=(0.0, 0.0, 0.0), std=(1.0, 1.0, 1.0), pre_fill=114)
+
+    def conv_bn_act(x, m, out=None, res=None, name=""):
+        w, b = fold_bn(m.conv, m.bn)
+        k, s = m.conv.kernel_size[0], m.conv.stride[0]
+        return pb.conv(x, w, b, s, k // 2, ACT_SILU, res=res, out=out, res_after_act=res is not None, name=name)
+
+    def c2f(x, m, out=None, name=""):
+        c, n = m.c, len(m.m)
+        cat = pb.new_buf(x.h, x.w, (2 + n) * c)
+        conv_bn_act(x, m.cv1, out=T(cat, 0, 2 * c, x.h, x.w), name=name + ".cv1")
+        last = T(cat, c, c, x.h, x.w)
+        for i, bt in enumerate(m.m):
+            t = conv_bn_act(last, bt.cv1, name="%s.m.%d.cv1" % (name, i))
+            dst = T(cat, (2 + i) * c, c, x.h, x.w)
+            conv_bn_act(t, bt.cv2, out=dst, res=last if bt.add else None, name="%s.m.%d.cv2" % (name, i))
+            last = dst
+        return conv_bn_act(T(cat, 0, (2 + n) * c, x.h, x.w), m.cv2, out=out, name=name + ".cv2")
+
+    H, W = in_hw
+    w, b = fold_bn(L(0).conv, L(0).bn)
+    x = pb.stem(pb.input(), w, b, 2, 1, ACT_SILU, name="0")                    # 320x320x16
+    x = conv_bn_act(x, L(1), name="1")                                         # 160x160x32
+    x = c2f(x, L(2), name="2")
+    x = conv_bn_act(x, L(3), name="3")                                         # 80x80x64
+    cat14 = pb.new_buf(H // 8, W // 8, 128 + 64)                                # [up(12) | p3]
+    p3 = c2f(x, L(4), out=T(cat14, 128, 64, H // 8, W // 8), name="4")
+    x = conv_bn_act(p3, L(5), name="5")                                        # 40x40x128
+    cat11 = pb.new_buf(H // 16, W // 16, 256 + 128)                             # [up(9) | p4]
+    p4 = c2f(x, L(6), out=T(cat11, 256, 128, H // 16, W // 16), name="6")
+    x = conv_bn_act(p4, L(7), name="7")                                        # 20x20x256
+    x = c2f(x, L(8), name="8")
+    # SPPF
+    sp = L(9)
+    c_ = sp.cv1.conv.out_channels
+    spcat = pb.new_buf(H // 32, W // 32, 4 * c_)
+    y = conv_bn_act(x, sp.cv1, out=T(spcat, 0, c_, H // 32, W // 32), name="9.cv1")
+    for i in range(3):
+        y = pb.maxpool(y, 5, 1, 2, out=T(spcat, (i + 1) * c_, c_, H // 32, W // 32), name="9.m%d" % i)
+    cat20 = pb.new_buf(H // 32, W // 32, 128 + 256)                             # [conv19 | p5]
+    p5 = conv_bn_act(T(spcat, 0, 4 * c_, H // 32, W // 32), sp.cv2, out=T(cat20, 128, 256, H // 32, W // 32), name="9.cv2")
+    # head
+    pb.upsample2x(p5, T(cat11, 0, 256, H // 16, W // 16), name="10")
+    cat17 = pb.new_buf(H // 16, W // 16, 64 + 128)                              # [conv16 | h12]
+    h12 = c2f(T(cat11, 0, 384, H // 16, W // 16), L(12), out=T(cat17, 64, 128, H // 16, W // 16), name="12")
+    pb.upsample2x(h12, T(cat14, 0, 128, H // 8, W // 8), name="13")
+    h15 = c2f(T(cat14, 0, 192, H // 8, W // 8), L(15), name="15")              # P3 out, 64 ch
+    conv_bn_act(h15, L(16), out=T(cat17, 0, 64, H // 16, W // 16), name="16")
+    h18 = c2f(T(cat17, 0, 192, H // 16, W // 16), L(18), name="18")            # P4 out, 128 ch
+    conv_bn_act(h18, L(19), out=T(cat20, 0, 128, H // 32, W // 32), name="19")
+    h21 = c2f(T(cat20, 0, 384, H // 32, W // 32), L(21), name="21")            # P5 out, 256 ch
+    # Detect
+    det = L(22)
+    feats = [h15, h18, h21]
+    a_total = sum(f.h * f.w for f in feats)
+    out_buf = pb.new_buf(1, 1, 84 * a_total, dtype=1)
+    a_off = 0
+    for i, f in enumerate(feats):
+        hb = conv_bn_act(conv_bn_act(f, det.cv2[i][0], name="22.cv2.%d.0" % i), det.cv2[i][1], name="22.cv2.%d.1" % i)
+        hc = conv_bn_act(conv_bn_act(f, det.cv3[i][0], name="22.cv3.%d.0" % i), det.cv3[i][1], name="22.cv3.%d.1" % i)
+        fb, fc_ = det.cv2[i][2], det.cv3[i][2]
+        pb.yolo_decode(hb, hc, fb.weight.detach().float().flatten(1), fb.bias.detach().float(),
+                       fc_.weight.detach().float().flatten(1), fc_.bias.detach().float(), out_buf, a_off, a_total,
+                       int(det.stride[i]), name="22.decode.%d" % i)
+        a_off += f.h * f.w
+    pb.set_output(T(out_buf, 0, 84 * a_total, 1, 1, 84 * a_total))
+    return pb
+
+
+LOWERINGS = {"yolov8n": lower_yolov8n, "resnet50": lower_resnet, "shufflenet_v2_x1_0": lower_shufflenet, "efficientnet_v2_s": lower_efficientnet_v2}
 
 
 def lower(kind: str, model, **kw) -> PlanBuilder:

@@ -139,7 +139,41 @@ def make_efficientnet_v2_s(seed=0, damp=0.25, planted=1.0, n_proto=N_PROTO, in_h
     return m.eval()
 
 
-MODEL_BUILDERS = {"resnet50": make_resnet50, "shufflenet_v2_x1_0": make_shufflenet,
+def make_yolov8n(seed=0, damp=0.25, cls_bias=-6.0, cls_gain=3.0, box_gain=0.5, bn_bias=1.0, in_hw=(640, 640)):
+    """Seeded YOLOv8n: default PyTorch init, last BN of every shortcut bottleneck damped, BN statistics calibrated on seeded
+    640x640 requests (scaled to [0,1], no mean/std: YOLO preprocessing), Detect biases set so that only a small fraction
+    of anchors clears the 0.25 confidence threshold (a usable NMS workload)."""
+    from .yolov8n_arch import YOLOv8n, Bottleneck
+    torch.manual_seed(seed)
+    m = YOLOv8n()
+    with torch.no_grad():
+        for mod in m.modules():
+            if isinstance(mod, nn.BatchNorm2d):
+                mod.bias.fill_(bn_bias)            # keeps the random net out of the chaotic regime (see make_shufflenet)
+        for mod in m.modules():
+            if isinstance(mod, Bottleneck) and mod.add:
+                mod.cv2.bn.weight.fill_(damp)
+        for i in range(3):
+            m.m22.cv2[i][2].bias.fill_(1.0)
+            m.m22.cv2[i][2].weight.mul_(box_gain)
+            m.m22.cv3[i][2].bias.fill_(cls_bias)
+            m.m22.cv3[i][2].weight.mul_(cls_gain)
+    bns = [x for x in m.modules() if isinstance(x, nn.BatchNorm2d)]
+    for b in bns:
+        b.reset_running_stats()
+        b.momentum = None
+    m.train()
+    with torch.no_grad():
+        for bi in range(2):
+            imgs = synthetic_images(4, in_hw[0], in_hw[1], seed=700000 + seed * 100 + bi * 4)
+            m.features(imgs.permute(0, 3, 1, 2).float().div(255))
+    m.eval()
+    for b in bns:
+        b.momentum = 0.03
+    return m
+
+
+MODEL_BUILDERS = {"yolov8n": make_yolov8n, "resnet50": make_resnet50, "shufflenet_v2_x1_0": make_shufflenet,
                   "efficientnet_v2_s": make_efficientnet_v2_s}
 
 
