@@ -61,6 +61,14 @@ B200_API int b200_stem_cout_tile(int cout);
 B200_API int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight, const float* bias, void* out,
                                  int cout, int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
 
+/* Tensor-core variant of the stem (7x7/2 pad 3 or 3x3/2 pad 1): the producer warps build the im2col tile in shared
+ * memory with 16-byte cp.async copies, tcgen05.mma consumes it. weight: bf16 [b200_stem_tc_nout(cout)][b200_stem_tc_kpad(k)],
+ * GEMM-K index = r * (k == 7 ? 32 : 16) + (s + 1) * 4 + c (kernel row r, kernel column s, channel c), zero elsewhere. */
+B200_API int b200_stem_tc_kpad(int ksize);
+B200_API int b200_stem_tc_nout(int cout);
+B200_API int b200_stem_conv_tc_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                                    int cout, int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
+
 /* Depthwise 3x3 (pad 1) + folded BN + activation. Replaces tv shufflenetv2.py:62-76 `depthwise_conv` and the depthwise
  * stage of MBConv (tv efficientnet.py:140-151). weight: fp32 [9][c]; bias fp32 [c]. */
 B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,

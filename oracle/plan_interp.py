@@ -73,8 +73,18 @@ class PlanInterpreter:
                 ct = stem_cout_tile(cout)
                 cpad = (cout + ct - 1) // ct * ct
                 x = B[p[0]][..., :3].permute(0, 3, 1, 2)
-                w = self._f32(op["w_off"], k * k * 3 * cpad).view(k, k, 3, cpad)[..., :cout].permute(3, 2, 0, 1)
-                b = self._f32(op["b_off"], cpad)[:cout]
+                if p[12] == 1:      # tensor-core stem layout: bf16 [nout][kpad], K = r*row + (s+1)*4 + c
+                    row, kpad = (32, 256) if k == 7 else (16, 64)
+                    nout = 16 if cout <= 16 else (32 if cout <= 32 else 64)
+                    wt = self._bf16w(op["w_off"], nout * kpad).view(nout, kpad)
+                    w = torch.zeros(cout, 3, k, k)
+                    for r in range(k):
+                        for q in range(k):
+                            w[:, :, r, q] = wt[:cout, r * row + (q + 1) * 4:r * row + (q + 1) * 4 + 3]
+                    b = self._f32(op["b_off"], nout)[:cout]
+                else:
+                    w = self._f32(op["w_off"], k * k * 3 * cpad).view(k, k, 3, cpad)[..., :cout].permute(3, 2, 0, 1)
+                    b = self._f32(op["b_off"], cpad)[:cout]
                 y = F.conv2d(x, w, b, stride=s, padding=pad)
                 B[p[3]][..., p[4]:p[4] + cout] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
             elif t == OP_DWCONV:

@@ -42,6 +42,16 @@ int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight
                           weight, bias, ksize, stride, pad, act, static_cast<cudaStream_t>(stream));
 }
 
+int b200_stem_tc_kpad(int ksize) { return stem_tc_kpad(ksize); }
+int b200_stem_tc_nout(int cout) { return stem_tc_nout(cout); }
+
+int b200_stem_conv_tc_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out, int cout,
+                           int out_pix_stride, int ksize, int stride, int pad, int act, void* stream) {
+  const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;
+  return stem_tc_launch(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, cout, out_pix_stride),
+                        weight, bias, ksize, stride, pad, act, static_cast<cudaStream_t>(stream));
+}
+
 int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
                         const float* bias, void* out, int out_pix_stride, int stride, int act, void* stream) {
   const int ho = (h - 1) / stride + 1, wo = (w - 1) / stride + 1;

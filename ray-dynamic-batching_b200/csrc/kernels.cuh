@@ -22,6 +22,12 @@ int stem_cout_tile(int cout);
 int stem_conv_launch(const View& in, const View& out, const float* w, const float* bias, int ksize, int stride, int pad,
                      int act, cudaStream_t stream);
 
+// tensor-core variant (stem_tc.cu): bf16 weights [stem_tc_nout(cout)][stem_tc_kpad(k)], K index = r*ROW + (s+1)*4 + c
+int stem_tc_kpad(int ksize);
+int stem_tc_nout(int cout);
+int stem_tc_launch(const View& in, const View& out, const void* w, const float* bias, int ksize, int stride, int pad,
+                   int act, cudaStream_t stream);
+
 // ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional per-(n,c) fp32 sum output for SE squeeze ----
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
                      float* se_sum /* [N][C] or null, must be zeroed */, cudaStream_t stream);

@@ -25,6 +25,10 @@ SIGNATURES = {
     "b200_stem_cout_tile": (c_int, [c_int]),
     "b200_stem_conv_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                     c_int, c_int, c_int, c_void_p]),
+    "b200_stem_tc_kpad": (c_int, [c_int]),
+    "b200_stem_tc_nout": (c_int, [c_int]),
+    "b200_stem_conv_tc_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                       c_int, c_int, c_int, c_void_p]),
     "b200_dwconv3x3_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                     c_int, c_int, c_void_p]),
     "b200_maxpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int,

@@ -58,6 +58,23 @@ class T:
             self.cmap = np.arange(self.c)
 
 
+def stem_tc_weights(weight, bias):
+    """[Cout,3,k,k] fp32 -> (bf16 bits [nout][kpad], fp32 bias [nout]) in the layout of csrc/stem_tc.cu:
+    GEMM-K index = r * row_elems + (s + 1) * 4 + c, window pixel 0 / channel 3 / padded rows are zero."""
+    cout, _, k, _ = weight.shape
+    row_elems = 32 if k == 7 else 16
+    kpad = 256 if k == 7 else 64
+    nout = 16 if cout <= 16 else (32 if cout <= 32 else 64)
+    w = torch.zeros(nout, kpad)
+    for r in range(k):
+        for s_ in range(k):
+            base = r * row_elems + (s_ + 1) * 4
+            w[:cout, base:base + 3] = weight[:, :, r, s_]
+    b = torch.zeros(nout)
+    b[:cout] = bias
+    return PlanBuilder.bf16_bits(w), b.numpy().astype(np.float32)
+
+
 def act_code(m):
     if m is None or isinstance(m, nn.Identity):
         return ACT_NONE
@@ -93,6 +110,7 @@ class PlanBuilder:
         self.out_buf = -1
         self.out_dim = 0
         self.names = []     # op index -> human readable name (kept out of the blob)
+        self.tensor_core_stem = True
 
     # ---- buffers / weights ----
     def new_buf(self, h, w, c, dtype=0):
@@ -152,6 +170,14 @@ class PlanBuilder:
         assert cin == 3 and x.buf == self.in_buf
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
         out = self.new_act(ho, wo, cout)
+        if self.tensor_core_stem and stride == 2 and ((k == 7 and pad == 3) or (k == 3 and pad == 1)) and cout <= 64 \
+                and x.w % 2 == 0:
+            wb, bb = stem_tc_weights(weight, bias)
+            w_off = self.add_weights(wb)
+            b_off = self.add_weights(bb)
+            self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, pad8(cout), -1, 0, k, stride, pad, act, 1], w_off, b_off,
+                     name=name)
+            return out
         ct = stem_cout_tile(pad8(cout))
         cpad = (pad8(cout) + ct - 1) // ct * ct
         wp = torch.zeros(k * k, 3, cpad)

@@ -44,6 +44,31 @@ def test_stem_conv(b200lib, cuda, k, s, p, cout, cfg):
     assert ok, e
 
 
+@pytest.mark.parametrize("k,p,cout,cfg,act", [(7, 3, 64, (2, 224, 224), 1), (3, 1, 24, (3, 224, 224), 2),
+                                              (3, 1, 16, (1, 96, 130), 2), (7, 3, 64, (5, 38, 50), 1),
+                                              (3, 1, 32, (2, 64, 64), 0)])
+def test_stem_conv_tensor_core(b200lib, cuda, k, p, cout, cfg, act):
+    from rdb_b200.lowering import stem_tc_weights
+    n, h, w = cfg
+    x4 = torch.zeros(n, h, w, 4, device=cuda, dtype=torch.bfloat16)
+    x4[..., :3] = rnd((n, h, w, 3), 1, cuda)
+    wt = (rnd((cout, 3, k, k), 2, cuda, torch.float32) / (3 * k * k) ** 0.5).to(torch.bfloat16).float()
+    b = rnd((cout,), 3, cuda, torch.float32)
+    wb, bb = stem_tc_weights(wt.cpu(), b.cpu())
+    wdev = torch.from_numpy(wb.astype("int16")).to(cuda)
+    bdev = torch.from_numpy(bb).to(cuda)
+    ho, wo = (h + 2 * p - k) // 2 + 1, (w + 2 * p - k) // 2 + 1
+    out = torch.full((n, ho, wo, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_conv_tc_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(out), cout, 0, k, 2, p, act,
+                                         stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x4[..., :3].float().permute(0, 3, 1, 2), wt, b, stride=2, padding=p)
+    ref = (F.relu(ref) if act == 1 else F.silu(ref) if act == 2 else ref).permute(0, 2, 3, 1)
+    assert not torch.isnan(out.float()).any()
+    ok, e = close_bf16(out, ref)
+    assert ok, e
+
+
 @pytest.mark.parametrize("n,h,w,c,stride,act", [(2, 28, 28, 64, 1, 0), (3, 56, 56, 24, 2, 0), (1, 15, 17, 960, 1, 2),
                                                 (2, 14, 14, 232, 2, 2)])
 def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
