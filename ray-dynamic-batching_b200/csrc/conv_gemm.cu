@@ -454,7 +454,267 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   }
 }
 
+// ================================================================================================================
+// CTA-pair variant (tcgen05.mma.cta_group::2): two CTAs on the two SMs of a TPC compute one 256-pixel x BLOCK_N tile.
+// Each CTA loads its own 128 pixels of A and *half* of the weight tile (BLOCK_N/2 rows); the leader issues M=256 MMAs
+// that read both halves, so per SM the shared-memory operand traffic per FLOP halves -- single-CTA tiles are bound by
+// shared-memory bandwidth (write by TMA + read by the tensor core) at ~50 % of the tensor peak for N=128.
+// Accumulator rows 0-127 live in the leader's TMEM, 128-255 in the peer's; epilogue, residual prefetch and stores are
+// per CTA exactly as in the single-CTA persistent kernel.  Barrier plumbing: both CTAs' TMA loads credit the leader's
+// `full` barrier; tcgen05.commit multicasts `empty` / `tmem_full` arrivals to both CTAs; both epilogues release the
+// accumulator on the leader's `tmem_empty` barrier (count 256).
+// ================================================================================================================
+template <int BLOCK_N>
+struct P2ConvCfg {
+  static constexpr int STAGES = BLOCK_N == 256 ? 3 : 4;
+  static constexpr int OUT_BUFS = BLOCK_N == 256 ? 2 : 4;
+  static constexpr int LOOKAHEAD = OUT_BUFS - 2;
+  static constexpr int B_STAGE_BYTES = (BLOCK_N / 2) * BLOCK_K * 2;  // this CTA's half of the weight tile
+  static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+  static constexpr int OUT_BYTES = BLOCK_M * BLOCK_N * 2;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + 1024;
+  static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
+  static_assert(2 * BLOCK_N <= 512, "TMEM budget");
+};
+
+template <int BLOCK_N, int RES, int ACT>
+__global__ void __launch_bounds__(PCONV_THREADS, 1)
+conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
+                      const int total_pair_tiles, const int m_tiles) {
+  using Cfg = P2ConvCfg<BLOCK_N>;
+  constexpr int STAGES = Cfg::STAGES;
+  constexpr int NB = Cfg::OUT_BUFS;
+  constexpr int LA = Cfg::LOOKAHEAD;
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[STAGES];
+  __shared__ __align__(8) uint64_t bar_empty[STAGES];
+  __shared__ __align__(8) uint64_t bar_tmem_full[2];
+  __shared__ __align__(8) uint64_t bar_tmem_empty[2];
+  __shared__ __align__(8) uint64_t bar_stage_ready[NB];
+  __shared__ __align__(8) uint64_t bar_out_ready[NB];
+  __shared__ uint32_t tmem_base_s;
+  constexpr int NBIAS = BLOCK_N == 256 ? 1 : 2;   // N=256 is 128 bytes short of smem with two bias buffers
+  __shared__ __align__(16) float bias_s[NBIAS][BLOCK_N];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();        // 0 = leader
+  const int pair = blockIdx.x >> 1;
+  const int num_pairs = gridDim.x >> 1;
+  const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t staging = ring + STAGES * Cfg::STAGE_BYTES;
+  const int num_kb = p.num_taps * p.kb_per_tap;
+  const int my_tiles = (total_pair_tiles - pair + num_pairs - 1) / num_pairs;
+
+  // pair tile -> this CTA's 128-pixel m-tile and the shared n-tile
+  auto my_coords = [&](int it, int& n0, int& w0, int& h0, int& nb0) {
+    const int pt = pair + it * num_pairs;
+    const int n_tile = pt % p.n_tiles;
+    int m = (pt / p.n_tiles) * 2 + static_cast<int>(rank);
+    if (m >= m_tiles) m = m_tiles;            // phantom tile of an odd tail: coordinates past the tensor (TMA clips)
+    const int t_w = m % p.tiles_w;
+    m /= p.tiles_w;
+    const int t_h = m % p.tiles_h;
+    const int t_n = m / p.tiles_h;
+    w0 = t_w * p.tw; h0 = t_h * p.th; nb0 = t_n * p.tn;
+    n0 = n_tile * BLOCK_N;
+  };
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b);
+    tma_prefetch_desc(&maps.d);
+    if (RES) tma_prefetch_desc(&maps.r);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bar_tmem_full[b]), 1);
+      mbar_init(smem_u32(&bar_tmem_empty[b]), 256);   // 128 epilogue threads of each CTA (used on the leader only)
+    }
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(smem_u32(&bar_stage_ready[b]), 1);
+      mbar_init(smem_u32(&bar_out_ready[b]), 128);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc_2cta<2 * BLOCK_N>(smem_u32(&tmem_base_s));
+  }
+  tc_fence_before();
+  cluster_sync_all();      // peer barriers are initialised and TMEM is allocated in both CTAs
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    // =========================== TMA producer (both CTAs) ===========================
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        int n0, w0, h0, nb0;
+        my_coords(it, n0, w0, h0, nb0);
+        for (int kb = 0; kb < num_kb; ++kb, ++g) {
+          const int s = g % STAGES;
+          const uint32_t ph = (g / STAGES) & 1;
+          mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
+          const uint32_t full = smem_u32(&bar_full[s]);
+          if (rank == 0) mbar_expect_tx(full, 2 * Cfg::STAGE_BYTES);   // both CTAs' bytes land on the leader's barrier
+          const int t = kb / p.kb_per_tap;
+          const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+          const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
+          tma_load_4d_2cta(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
+          tma_load_3d_2cta(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0 + static_cast<int>(rank) * (BLOCK_N / 2));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer (leader CTA only) ===========================
+    if (rank == 0 && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(2 * BLOCK_M, BLOCK_N);
+      uint32_t g = 0;
+      for (int it = 0; it < my_tiles; ++it) {
+        const int b = it & 1;
+        mbar_wait_cluster(smem_u32(&bar_tmem_empty[b]), ((it >> 1) & 1) ^ 1);  // both epilogues drained this accumulator
+        tc_fence_after();
+        const uint32_t acc = tmem_base + b * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb, ++g) {
+          const int s = g % STAGES;
+          const uint32_t ph = (g / STAGES) & 1;
+          mbar_wait_cluster(smem_u32(&bar_full[s]), ph);
+          tc_fence_after();
+          const uint32_t a_src = ring + s * Cfg::STAGE_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_src);
+          const uint64_t bdesc = umma_desc_sw128(a_src + A_STAGE_BYTES);
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16_2cta(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+          umma_commit_2cta(smem_u32(&bar_empty[s]));       // frees the slot in both CTAs
+        }
+        umma_commit_2cta(smem_u32(&bar_tmem_full[b]));     // accumulator ready in both CTAs
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // =========================== DMA: residual prefetch + output stores (per CTA) ===========================
+    if (lane == 0) {
+      auto acquire_staging = [&](int j) {
+        const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
+        if (RES) {
+          int n0, w0, h0, nb0;
+          my_coords(j, n0, w0, h0, nb0);
+          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+        } else {
+          mbar_arrive(rdy);
+        }
+      };
+      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
+      for (int it = 0; it < my_tiles; ++it) {
+        if (LA == 0) {
+          // the staging buffer of tile it was last read by the store of tile it - NB
+          if (NB == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          acquire_staging(it);
+        }
+        {
+          int n0, w0, h0, nb0;
+          my_coords(it, n0, w0, h0, nb0);
+          const int ob = it % NB;
+          mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            if (n0 + q * 64 < p.cout)
+              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+          tma_store_commit();
+        }
+        if (LA > 0) {
+          const int j = it + LA;
+          if (j < my_tiles) {
+            asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+            acquire_staging(j);
+          }
+        }
+      }
+      tma_store_wait_all();
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // =========================== epilogue (per CTA, its own 128 rows) ===========================
+    const int epi_tid = threadIdx.x - 128;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t row_off = row * 128;
+    const int sw = row & 7;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int b = it & 1;
+      const int ob = it % NB;
+      const int n0 = ((pair + it * num_pairs) % p.n_tiles) * BLOCK_N;
+      for (int i = epi_tid; i < BLOCK_N; i += 128) {
+        const int c = n0 + i;
+        bias_s[b % NBIAS][i] = (c < p.cout) ? p.bias[c] : 0.f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait_cluster(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
+      tc_fence_after();
+      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
+      const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
+      const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+      for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + cc * 32, v);
+        tmem_ld_wait();
+        const uint32_t sub = stage_d + (cc >> 1) * (BLOCK_M * 128) + row_off;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int chunk = (cc & 1) * 4 + g;
+          const uint32_t addr = sub + ((chunk ^ sw) << 4);
+          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][cc * 32 + g * 8]);
+          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][cc * 32 + g * 8 + 4]);
+          float f[8];
+          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
+          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
+          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
+          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+          if (RES) {
+            uint32_t r0, r1, r2, r3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+            const float rr[8] = {bf16_lo(r0), bf16_hi(r0), bf16_lo(r1), bf16_hi(r1),
+                                 bf16_lo(r2), bf16_hi(r2), bf16_lo(r3), bf16_hi(r3)};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = (RES == 2) ? act_t<ACT>(f[i]) + rr[i] : act_t<ACT>(f[i] + rr[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+          }
+          const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+          const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
+                       : "memory");
+        }
+      }
+      tc_fence_before();
+      mbar_arrive_leader(smem_u32(&bar_tmem_empty[b]));   // release the accumulator to the leader's MMA issuer
+      fence_proxy_async_smem();
+      mbar_arrive(smem_u32(&bar_out_ready[ob]));
+      if (NBIAS == 1) named_bar_sync(1, 128);             // everyone is done reading the single bias buffer
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();      // neither CTA may free TMEM or exit while the peer still uses the pair's resources
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2cta<2 * BLOCK_N>(tmem_base);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ host side
+
+static int use_2cta();
 
 static void pick_tile(int W, int H, int N, int* tw, int* th, int* tn) {
   // Rectangular 128-pixel tile (powers of two) with the least padding waste; ties -> wider in W, then H.
@@ -506,8 +766,22 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.act = s.act;
   p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
   p.bias = s.bias;
-  const int block_n = out.C <= 64 ? 64 : 128;
+  // Tile choice.  Layers with enough arithmetic per byte (K >= 256, Cout >= 128) are bound by shared-memory operand
+  // bandwidth in single-CTA mode -> CTA pairs (M = 256), N = 256 when Cout allows.  Thin layers stay single-CTA.
+  const int k_total = in.C * taps;
+  static int res_mode = -1;   // residual layers: 0 single CTA, 1 CTA pair N=128 (deep residual prefetch), 2 CTA pair N=256
+  if (res_mode < 0) {
+    const char* e = getenv("B200_2CTA_RES_MODE");
+    res_mode = e ? atoi(e) : 0;
+  }
+  bool two_cta = use_2cta() && out.C >= 256 && k_total >= 256;
+  int block_n = two_cta ? 256 : (out.C <= 64 ? 64 : 128);
+  if (two_cta && has_res) {
+    if (res_mode == 0) { two_cta = false; block_n = 128; }
+    else if (res_mode == 1) block_n = 128;
+  }
   L->block_n = block_n;
+  L->two_cta = two_cta;
   p.n_tiles = (out.C + block_n - 1) / block_n;
 
   const uint64_t ips = uint64_t(in.pix_stride) * 2, ops = uint64_t(out.pix_stride) * 2;
@@ -565,7 +839,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   {
     const uint64_t dims[3] = {uint64_t(in.C), uint64_t(taps), uint64_t(out.C)};
     const uint64_t str[2] = {uint64_t(in.C) * 2, uint64_t(in.C) * 2 * taps};
-    const uint32_t box[3] = {64u, 1u, uint32_t(block_n)};
+    const uint32_t box[3] = {64u, 1u, uint32_t(two_cta ? block_n / 2 : block_n)};  // a CTA pair loads half each
     B200_TRY(encode_tmap(&L->maps.b, s.w, 3, dims, str, box, SWZ_128B));
   }
   const long long m_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
@@ -573,6 +847,15 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   L->grid = unsigned(m_tiles * p.n_tiles);
   L->flops = 2.0 * double(out.N) * out.H * out.W * out.C * double(in.C) * taps;
   return B200_OK;
+}
+
+static int use_2cta() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_2CTA");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v;
 }
 
 static bool use_persistent() {
@@ -620,6 +903,54 @@ static int launch_persistent_res(const ConvLaunch& l, cudaStream_t stream) {
   return launch_persistent_act<BLOCK_N, 2>(l, stream);
 }
 
+template <int BLOCK_N, int RES, int ACT>
+static int launch_2cta_t(const ConvLaunch& l, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  auto kern = conv_gemm_2cta_kernel<BLOCK_N, RES, ACT>;
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P2ConvCfg<BLOCK_N>::SMEM_BYTES));
+    configured[dev & 63] = true;
+  }
+  const int m_tiles = l.p.tiles_w * l.p.tiles_h * l.p.tiles_n;
+  const int pair_tiles = ((m_tiles + 1) / 2) * l.p.n_tiles;
+  const int max_pairs = device_sm_count() / 2;
+  const int pairs = pair_tiles < max_pairs ? pair_tiles : max_pairs;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(PCONV_THREADS);
+  cfg.dynamicSmemBytes = P2ConvCfg<BLOCK_N>::SMEM_BYTES;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, l.maps, l.p, pair_tiles, m_tiles));
+  return B200_OK;
+}
+
+template <int BLOCK_N, int RES>
+static int launch_2cta_act(const ConvLaunch& l, cudaStream_t stream) {
+  switch (l.p.act) {
+    case ACT_NONE: return launch_2cta_t<BLOCK_N, RES, ACT_NONE>(l, stream);
+    case ACT_RELU: return launch_2cta_t<BLOCK_N, RES, ACT_RELU>(l, stream);
+    case ACT_SILU: return launch_2cta_t<BLOCK_N, RES, ACT_SILU>(l, stream);
+    case ACT_SIGMOID: return launch_2cta_t<BLOCK_N, RES, ACT_SIGMOID>(l, stream);
+  }
+  return fail(B200_ERR_INVALID, "conv: unknown activation");
+}
+
+template <int BLOCK_N>
+static int launch_2cta_res(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.p.has_res == 0) return launch_2cta_act<BLOCK_N, 0>(l, stream);
+  if (l.p.has_res == 1) return launch_2cta_act<BLOCK_N, 1>(l, stream);
+  return launch_2cta_act<BLOCK_N, 2>(l, stream);
+}
+
 template <int BLOCK_N>
 static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
   static bool configured[64] = {};
@@ -636,6 +967,10 @@ static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
 }
 
 int conv_launch(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.two_cta) {
+    if (l.block_n == 256) return launch_2cta_res<256>(l, stream);
+    return launch_2cta_res<128>(l, stream);
+  }
   if (use_persistent()) {
     if (l.block_n == 64) return launch_persistent_res<64>(l, stream);
     return launch_persistent_res<128>(l, stream);

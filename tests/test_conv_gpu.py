@@ -50,6 +50,10 @@ CASES = [
     (1, 28, 28, 24, 96, 3, 1, 1, "silu", False),     # EfficientNet-style odd channels (Cin not multiple of 64)
     (2, 14, 14, 160, 200, 1, 1, 0, "silu", True),    # Cout not a multiple of 64, residual
     (1, 15, 15, 64, 64, 3, 2, 1, "silu", False),     # odd spatial size with stride 2
+    (2, 14, 14, 256, 1024, 1, 1, 0, "relu", True),   # CTA-pair kernel (N=256) with residual (layer3 conv3)
+    (1, 7, 7, 512, 512, 1, 1, 0, "relu", False),     # CTA-pair kernel with a single (odd) m-tile: phantom peer tile
+    (5, 14, 14, 1024, 256, 1, 1, 0, "relu", False),  # CTA-pair, 16 k-blocks, odd number of m-tiles (980 px -> 8 tiles) 
+    (3, 28, 28, 128, 128, 3, 1, 1, "silu", True),    # CTA-pair N=128 with post-activation residual geometry (3x3)
 ]
 
 
