@@ -49,6 +49,8 @@ class B200Model:
         if not use_graphs:
             _lib.check(self.lib.b200_engine_set_graphs(self._h, 0))
         self._pinned = None
+        self._slots = None
+        self._slot_i = 0
 
     # ---- lifecycle (mirrors .eval()/.to()/.cpu() so the reference's load/unload code keeps working) ----
     def eval(self):
@@ -149,6 +151,46 @@ class B200Model:
             out = torch.empty(pb, self.out_dim, device=self.device, dtype=torch.float32)
         _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(out), self._stream()), "b200_infer")
         return out[:n, :self.out_logical]
+
+    # ---- pipelined host path: the H2D copy of batch i+1 overlaps the forward of batch i ----
+    class _Slot:
+        def __init__(self, model):
+            self.staging = None
+            self.out_host = torch.empty(model.max_batch, model.out_dim, dtype=torch.float32, pin_memory=True)
+            self.copied = torch.cuda.Event()
+            self.done = torch.cuda.Event()
+            self.n = 0
+            self.out_logical = model.out_logical
+
+        def result(self):
+            """Blocks until this batch is finished; returns the fp32 outputs [n, out] in pinned host memory."""
+            self.done.synchronize()
+            return self.out_host[:self.n, :self.out_logical]
+
+    def infer_packed_async(self, packed_host, offsets, hw, n, padded_batch=None, mode=COLLATE_IDENTITY, total_bytes=None):
+        """Asynchronous engine-native call: `packed_host` (pinned uint8) -> H2D on a side stream -> collate -> forward ->
+        D2H into a pinned slot.  Returns a handle whose .result() waits for this batch only.  Two slots: at most two
+        batches are in flight, and the copy of one overlaps the compute of the other."""
+        if self._slots is None:
+            self._slots = [B200Model._Slot(self), B200Model._Slot(self)]
+            self._copy_stream = torch.cuda.Stream(self.device)
+        slot = self._slots[self._slot_i % 2]
+        self._slot_i += 1
+        slot.done.synchronize()                      # the previous user of this slot has been consumed
+        total = int(total_bytes if total_bytes is not None else packed_host.numel())
+        if slot.staging is None or slot.staging.numel() < total:
+            slot.staging = torch.empty(total + total // 4 + 4096, dtype=torch.uint8, device=self.device)
+        compute = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self._copy_stream):
+            slot.staging[:total].copy_(packed_host[:total], non_blocking=True)
+            slot.copied.record(self._copy_stream)
+        compute.wait_event(slot.copied)
+        pb = padded_batch or n
+        self.collate_u8(slot.staging, offsets, hw, n, pb, mode, total)
+        _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(slot.out_host), self._stream()), "b200_infer")
+        slot.n = n
+        slot.done.record(compute)
+        return slot
 
     def decode_yolo(self, batch, conf=0.25, iou=0.45, max_det=300, head=None):
         """Class-aware NMS on the device over the [batch, 84, A] head output of the last forward (or `head`).
