@@ -183,10 +183,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the B200 engine has no CPU fallback")
     torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from rdb_b200 import replicas
+    dist = replicas.init_process_group("nccl") if world > 1 else None
     dev = torch.device("cuda", local)
     W = max(3, args.warmup)
     K = max(1, args.steps)
@@ -246,11 +244,7 @@ def main():
             drain()
         e1.record(stream)
         torch.cuda.synchronize(dev)
-        ms = e0.elapsed_time(e1)
-        if dist is not None:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
+        ms = replicas.max_over_ranks(e0.elapsed_time(e1), dist, dev)   # the job is as slow as its slowest replica
         barrier()
         return ms
 
@@ -318,8 +312,8 @@ def main():
                    "l2": "working set >> L2: %d rotating input batches, ~%.1f GB activation traffic per step"
                          % (NSETS, B * RESNET50_FUSED_BYTES_PER_IMG / 1e9),
                    "cuda_graph": True},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(B * per + B * 16),
-                "d2h_bytes_per_step": int(B * model.out_dim * 4), "ms_per_step": ms_e2e / K,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(world * (B * per + B * 16)),
+                "d2h_bytes_per_step": int(world * B * model.out_dim * 4), "ms_per_step": ms_e2e / K,
                 "pipeline": "2 batches in flight (H2D of step i overlaps the forward of step i-1)"},
         "gpu_launches": int(launches),
         "roofline": roofline,

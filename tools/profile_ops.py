@@ -19,7 +19,7 @@ def main():
     kind = sys.argv[1] if len(sys.argv) > 1 else "resnet50"
     batch = int(sys.argv[2]) if len(sys.argv) > 2 else 256
     reps = int(sys.argv[3]) if len(sys.argv) > 3 else 5
-    module = synth.make_model(kind, n_proto=8)
+    module = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
     model = B200Model(kind, module, max_batch=batch)
     imgs = list(synth.synthetic_images(min(batch, 8), model.in_h, model.in_w)) * (batch // min(batch, 8))
     model.infer_u8(imgs[:batch])
@@ -32,7 +32,15 @@ def main():
     ms /= reps
     tr = plan_traffic(model.blob, batch)
     print("%-34s %9s %9s %9s" % ("op", "us", "GB/s", "TFLOP/s"))
-    for i in range(model.n_ops):
+    order = range(model.n_ops)
+    top = int(os.environ.get("TOP", "0"))
+    if top:
+        order = sorted(order, key=lambda i: -ms[i])[:top]
+        by_type = {}
+        for i in range(model.n_ops):
+            by_type[tr[i][0]] = by_type.get(tr[i][0], 0.0) + ms[i]
+        print("time by op type (ms):", {k: round(v, 3) for k, v in sorted(by_type.items())})
+    for i in order:
         t, b, fl = tr[i]
         print("%-34s %9.1f %9.0f %9.1f" % (model.op_names[i], ms[i] * 1e3, b / (ms[i] * 1e-3) / 1e9, fl / (ms[i] * 1e-3) / 1e12))
     tot_b, tot_f = sum(x[1] for x in tr), sum(x[2] for x in tr)
