@@ -102,7 +102,7 @@ def plan_traffic(blob, batch):
         es_out = 4 if bufs[p[3]][3] else 2
         b = batch * (ih * iw * p[2] * es_in + oh * ow * p[5] * es_out)
         fl = 0.0
-        if t == lowering.OP_CONV:
+        if t in (lowering.OP_CONV, lowering.OP_GATHER_CONV):
             k = p[8]
             b += p[5] * k * k * p[2] * 2 + p[5] * 4
             if p[6] >= 0:

@@ -54,6 +54,17 @@ B200_API int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int 
                      const float* bias, const void* residual, int res_pix_stride, void* out, int cout,
                      int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
 
+/* Same contract as b200_conv2d_nhwc for layers with few input channels (cin <= 56, cout <= 256): GEMM-K packs the filter
+ * taps (k = tap * cin + c), the im2col tile is gathered into shared memory by cp.async producers. Serves the
+ * FusedMBConv 3x3 convolutions of EfficientNetV2 (tv efficientnet.py:172-231) and YOLOv8n's early layers.
+ * weight: bf16 [b200_gather_conv_npad(cout)][b200_gather_conv_kpad(cin, k)], zero padded. */
+B200_API int b200_gather_conv_npad(int cout);
+B200_API int b200_gather_conv_kpad(int cin, int ksize);
+B200_API int b200_gather_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* weight,
+                                     const float* bias, const void* residual, int res_pix_stride, void* out, int cout,
+                                     int out_pix_stride, int ksize, int stride, int pad, int act, int res_after_act,
+                                     void* stream);
+
 /* Stem convolution with 3 input channels (input NHWC with C padded to 4) + folded BN + activation, direct FP32-pipe kernel.
  * Replaces tv resnet.py:268-270 (conv1 7x7/2 + bn1 + relu), shufflenetv2.py:112-116, efficientnet.py:283-287 (3x3/2 stems).
  * weight: fp32 [k*k][3][cout_pad], cout_pad = cout rounded up to the channel tile b200_stem_cout_tile(cout). */

@@ -14,7 +14,7 @@ import torch
 import torch.nn.functional as F
 
 OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
-    OP_YOLO_DECODE = range(1, 12)
+    OP_YOLO_DECODE, OP_GATHER_CONV = range(1, 13)
 
 
 def _bf16(x):
@@ -61,6 +61,21 @@ class PlanInterpreter:
                 x = B[p[0]][..., p[1]:p[1] + cin].permute(0, 3, 1, 2)
                 w = self._bf16w(op["w_off"], cout * k * k * cin).view(cout, k, k, cin).permute(0, 3, 1, 2)
                 b = self._f32(op["b_off"], cout)
+                y = F.conv2d(x, w, b, stride=s, padding=pad)
+                if p[6] >= 0:
+                    r = B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
+                    y = _act(y, act) + r if p[12] else _act(y + r, act)
+                else:
+                    y = _act(y, act)
+                B[p[3]][..., p[4]:p[4] + cout] = _bf16(y).permute(0, 2, 3, 1)
+            elif t == OP_GATHER_CONV:
+                cin, cout, k, s, pad, act = p[2], p[5], p[8], p[9], p[10], p[11]
+                npad = 32 if cout <= 32 else (64 if cout <= 64 else (128 if cout <= 128 else 256))
+                kpad = (k * k * (cin // 8) + 7) // 8 * 64
+                x = B[p[0]][..., p[1]:p[1] + cin].permute(0, 3, 1, 2)
+                wt = self._bf16w(op["w_off"], npad * kpad).view(npad, kpad)[:cout, :k * k * cin]
+                w = wt.reshape(cout, k, k, cin).permute(0, 3, 1, 2)
+                b = self._f32(op["b_off"], npad)[:cout]
                 y = F.conv2d(x, w, b, stride=s, padding=pad)
                 if p[6] >= 0:
                     r = B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)

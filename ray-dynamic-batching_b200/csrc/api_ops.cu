@@ -33,6 +33,20 @@ int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_st
   return conv_launch(l, static_cast<cudaStream_t>(stream));
 }
 
+int b200_gather_conv_npad(int cout) { return gather_conv_npad(cout); }
+int b200_gather_conv_kpad(int cin, int ksize) { return gather_conv_kpad(cin, ksize); }
+
+int b200_gather_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* weight,
+                            const float* bias, const void* residual, int res_pix_stride, void* out, int cout,
+                            int out_pix_stride, int ksize, int stride, int pad, int act, int res_after_act, void* stream) {
+  const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;
+  View res;
+  if (residual) res = make_view(const_cast<void*>(residual), n, ho, wo, cout, res_pix_stride);
+  return gather_conv_launch(make_view(const_cast<void*>(in), n, h, w, cin, in_pix_stride),
+                            make_view(out, n, ho, wo, cout, out_pix_stride), res, weight, bias, ksize, stride, pad, act,
+                            res_after_act != 0, static_cast<cudaStream_t>(stream));
+}
+
 int b200_stem_cout_tile(int cout) { return stem_cout_tile(cout); }
 
 int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight, const float* bias, void* out, int cout,

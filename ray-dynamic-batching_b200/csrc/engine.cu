@@ -168,6 +168,14 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
         rc = shuffle_concat_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[2], batch),
                                    view(p[3], p[4], p[5], batch), p[14], p[15], stream);
         break;
+      case OP_GATHER_CONV: {
+        View res;
+        if (p[6] >= 0) res = view(p[6], p[7], p[5], batch);
+        rc = gather_conv_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), res, W + po.rec.w_off,
+                                reinterpret_cast<const float*>(W + po.rec.b_off), p[8], p[9], p[10], p[11], p[12] != 0,
+                                stream);
+        break;
+      }
       case OP_YOLO_DECODE:
         rc = yolo_decode_launch(view(p[0], p[1], p[2], batch), view(p[12], p[13], p[14], batch),
                                 reinterpret_cast<const float*>(W + po.rec.w_off),

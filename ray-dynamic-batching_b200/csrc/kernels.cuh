@@ -28,6 +28,12 @@ int stem_tc_nout(int cout);
 int stem_tc_launch(const View& in, const View& out, const void* w, const float* bias, int ksize, int stride, int pad,
                    int act, cudaStream_t stream);
 
+// ---- packed-K gather convolution for small Cin (gather_conv.cu): bf16 weights [npad][kpad], K index = tap*cin_p + c ----
+int gather_conv_npad(int cout);
+int gather_conv_kpad(int cin_p, int ksize);
+int gather_conv_launch(const View& in, const View& out, const View& res, const void* w, const float* bias, int ksize,
+                       int stride, int pad, int act, bool res_after_act, cudaStream_t stream);
+
 // ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional per-(n,c) fp32 sum output for SE squeeze ----
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
                      float* se_sum /* [N][C] or null, must be zeroed */, cudaStream_t stream);

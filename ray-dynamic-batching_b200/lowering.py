@@ -17,7 +17,7 @@ import torch
 import torch.nn as nn
 
 OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
-    OP_YOLO_DECODE = range(1, 12)
+    OP_YOLO_DECODE, OP_GATHER_CONV = range(1, 13)
 ACT_NONE, ACT_RELU, ACT_SILU, ACT_SIGMOID = 0, 1, 2, 3
 HEADER_FMT = "<8sIIII32siiiiii3f3fQQ"
 HEADER_SIZE = struct.calcsize(HEADER_FMT)
@@ -111,6 +111,8 @@ class PlanBuilder:
         self.out_dim = 0
         self.names = []     # op index -> human readable name (kept out of the blob)
         self.tensor_core_stem = True
+        self.gather_small_cin = True
+        self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
     # ---- buffers / weights ----
     def new_buf(self, h, w, c, dtype=0):
@@ -150,6 +152,9 @@ class PlanBuilder:
             out = self.new_act(ho, wo, cout)
         assert (out.h, out.w, out.c) == (ho, wo, cout)
         cin_p, cout_p = x.cphys, out.cphys
+        if self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
+                                                       (k == 1 and cin_p % 64 != 0 and cin_p <= self.gather_1x1_max_cin)):
+            return self._gather_conv(x, weight, bias, stride, pad, act, res, out, name, res_after_act)
         wp = torch.zeros(cout_p, k * k, cin_p)
         wfull = torch.zeros(cout, k * k, cin_p)
         wfull[:, :, torch.as_tensor(x.cmap)] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
@@ -163,6 +168,27 @@ class PlanBuilder:
             assert (res.h, res.w, res.c, res.cphys) == (ho, wo, cout, cout_p) and np.array_equal(res.cmap, out.cmap)
         self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act,
                            1 if res_after_act else 0], w_off, b_off, name=name)
+        return out
+
+    def _gather_conv(self, x, weight, bias, stride, pad, act, res, out, name, res_after_act):
+        """Packed-K layout of csrc/gather_conv.cu: bf16 [npad][kpad], GEMM-K index = tap * cin_p + physical channel."""
+        cout, cin, k, _ = weight.shape
+        cin_p, cout_p = x.cphys, out.cphys
+        npad = 32 if cout_p <= 32 else (64 if cout_p <= 64 else (128 if cout_p <= 128 else 256))
+        kpad = (k * k * (cin_p // 8) + 7) // 8 * 64
+        wfull = torch.zeros(cout, k * k, cin_p)
+        wfull[:, :, torch.as_tensor(x.cmap)] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
+        wp = torch.zeros(npad, kpad)
+        wp[torch.as_tensor(out.cmap), :k * k * cin_p] = wfull.reshape(cout, k * k * cin_p)
+        bp = torch.zeros(npad)
+        bp[torch.as_tensor(out.cmap)] = bias
+        w_off = self.add_weights(self.bf16_bits(wp))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        rb, rc = (res.buf, res.coff) if res is not None else (-1, 0)
+        if res is not None:
+            assert (res.h, res.w, res.c, res.cphys) == (out.h, out.w, cout, cout_p) and np.array_equal(res.cmap, out.cmap)
+        self._op(OP_GATHER_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act,
+                                  1 if res_after_act else 0], w_off, b_off, name=name)
         return out
 
     def stem(self, x: T, weight, bias, stride, pad, act, name=""):

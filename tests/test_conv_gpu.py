@@ -99,3 +99,49 @@ def test_conv_rejects_bad_shapes(b200lib, cuda):
     rc = b200lib.b200_conv2d_nhwc(ptr(x), 1, 8, 8, 12, 0, ptr(x), ptr(x), None, 0, ptr(x), 12, 0, 1, 1, 0, 0, None)
     assert rc == -1
     assert b"multiples of 8" in b200lib.b200_last_error()
+
+
+GATHER_CASES = [
+    # n, h, w, cin, cout, k, stride, pad, act, residual, res_after_act
+    (2, 112, 112, 24, 24, 3, 1, 1, "silu", True, True),     # EfficientNetV2 features.1 FusedMBConv (expand 1)
+    (2, 112, 112, 24, 96, 3, 2, 1, "silu", False, False),   # features.2.0 expand3x3, stride 2
+    (3, 56, 56, 48, 192, 3, 1, 1, "silu", False, False),    # features.2.x expand3x3
+    (1, 160, 160, 16, 16, 3, 1, 1, "silu", True, True),     # YOLOv8n C2f bottleneck, c = 16
+    (2, 80, 80, 32, 32, 3, 1, 1, "silu", False, False),     # YOLOv8n c = 32
+    (1, 33, 47, 16, 32, 3, 2, 1, "relu", False, False),     # ragged sizes, stride 2
+    (5, 9, 7, 56, 200, 3, 1, 1, "none", True, False),       # widest supported cin, odd cout
+]
+
+
+@pytest.mark.parametrize("case", GATHER_CASES, ids=[str(c) for c in GATHER_CASES])
+def test_gather_conv_matches_fp32_reference(b200lib, cuda, case):
+    n, h, w, cin, cout, k, stride, pad, act, use_res, after = case
+    g = torch.Generator(device="cpu").manual_seed(abs(hash(case)) % (2 ** 31))
+    x = torch.randn(n, h, w, cin, generator=g).to(cuda).to(torch.bfloat16)
+    wt = (torch.randn(cout, k, k, cin, generator=g) / (k * k * cin) ** 0.5).to(torch.bfloat16)
+    b = torch.randn(cout, generator=g)
+    npad = b200lib.b200_gather_conv_npad(cout)
+    kpad = b200lib.b200_gather_conv_kpad(cin, k)
+    wp = torch.zeros(npad, kpad, dtype=torch.bfloat16)
+    wp[:cout, :k * k * cin] = wt.reshape(cout, k * k * cin)
+    bp = torch.zeros(npad)
+    bp[:cout] = b
+    wp, bp, wt, b = wp.to(cuda), bp.to(cuda), wt.to(cuda), b.to(cuda)
+    ho, wo = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    res = torch.randn(n, ho, wo, cout, generator=g).to(cuda).to(torch.bfloat16) if use_res else None
+    out = torch.full((n, ho, wo, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_gather_conv2d_nhwc(ptr(x), n, h, w, cin, 0, ptr(wp), ptr(bp), ptr(res), 0, ptr(out), cout, 0, k,
+                                          stride, pad, ACT[act], 1 if after else 0, stream_ptr()), "b200_gather_conv2d_nhwc")
+    torch.cuda.synchronize()
+    y = F.conv2d(x.float().permute(0, 3, 1, 2), wt.float().permute(0, 3, 1, 2), b, stride=stride, padding=pad)
+    fa = {"none": lambda t: t, "relu": F.relu, "silu": F.silu}[act]
+    if res is not None:
+        r = res.float().permute(0, 3, 1, 2)
+        y = fa(y) + r if after else fa(y + r)
+    else:
+        y = fa(y)
+    ref = y.permute(0, 2, 3, 1)
+    assert not torch.isnan(out.float()).any(), "unwritten output elements"
+    err = (out.float() - ref).abs()
+    tol = ref.abs() * 2.0 ** -8 + 2e-3
+    assert (err <= tol).all(), "max err %.4g" % err.max().item()
