@@ -288,10 +288,14 @@ def main():
     per_img_s = step_ms * 1e-3 / B
     model_bound_s = max(RESNET50_FLOPS_PER_IMG / (peaks["tensor_sustained"] * 1e12),
                         (RESNET50_FUSED_BYTES_PER_IMG + RESNET50_WEIGHT_BYTES / B) / (peaks["hbm"] * 1e9))
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01b_conv_traffic.json")
+    if B == 256 and os.path.exists(tpath):      # dram bytes per launch from the committed ncu capture of this command
+        traffic = json.load(open(tpath))["traffic_bytes_per_launch"]
     roofline = {
         "kernel": "conv_gemm_kernel (tcgen05 implicit GEMM), %d launches per step" % n_conv,
         "bound": "hbm", "achieved": achieved_gbs / 1.0, "peak": peaks["hbm"], "unit": "GB/s",
-        "frac": achieved_gbs / peaks["hbm"], "traffic": None, "peak_source": peaks["source"],
+        "frac": achieved_gbs / peaks["hbm"], "traffic": traffic, "peak_source": peaks["source"],
         "bytes_per_launch_avg": conv_bytes / n_conv, "ms_per_launch_avg": conv_ms / n_conv,
         "share_of_step": conv_ms / float(ms_ops.sum()),
         "tensor_achieved_tflops": achieved_tf, "tensor_peak_tflops": peaks["tensor_sustained"],

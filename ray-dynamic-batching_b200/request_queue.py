@@ -38,6 +38,7 @@ class BatchRequest:
     request_ids: List[str]
     arrival_time: float
     slab_offsets: Optional[List[int]] = field(default=None, compare=False)   # pinned-slab positions (engine-native)
+    slab: Any = field(default=None, compare=False, repr=False)               # the PinnedSlab those offsets refer to
 
 
 class _DequeBacking:
@@ -159,7 +160,7 @@ class B200RequestQueue:
             if inputs:
                 slab_offsets = offs if all(o is not None for o in offs) else None
                 return BatchRequest(self.model_name, inputs, len(inputs), request_ids, earliest_arrival,
-                                    slab_offsets), discard
+                                    slab_offsets, self.slab if slab_offsets is not None else None), discard
         except Exception as e:  # noqa: BLE001 - reference: log, fall through to (None, 0)
             self._logger.error("Error creating batch: %s", e)
         return None, 0
