@@ -80,6 +80,14 @@ B200_API int b200_stem_tc_nout(int cout);
 B200_API int b200_stem_conv_tc_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
                                     int cout, int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
 
+/* ResNet stem (7x7/2 pad 3, 3 -> 64, + folded BN + ReLU) with no im2col copy: one TMA box brings the 7 input rows of an
+ * output row and non-swizzled tcgen05 descriptors (LBO 16 B, SBO 128 B) read the overlapping 8-pixel windows in place.
+ * Replaces tv resnet.py:268-270. weight: bf16 image [7][4][64][8] (b200_stem_row_weight_bytes() bytes): element e of K chunk
+ * k of kernel row r = weight[cout][c = e % 4][r][s = 2k + e / 4 - 1], zero where c == 3 or s outside [0, 6]. */
+B200_API int b200_stem_row_weight_bytes(void);
+B200_API int b200_stem_row_conv_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                                     int out_pix_stride, void* stream);
+
 /* Depthwise 3x3 (pad 1) + folded BN + activation. Replaces tv shufflenetv2.py:62-76 `depthwise_conv` and the depthwise
  * stage of MBConv (tv efficientnet.py:140-151). weight: fp32 [9][c]; bias fp32 [c]. */
 B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,

@@ -56,6 +56,15 @@ int b200_stem_conv_nhwc(const void* in, int n, int h, int w, const float* weight
                           weight, bias, ksize, stride, pad, act, static_cast<cudaStream_t>(stream));
 }
 
+int b200_stem_row_weight_bytes(void) { return stem_row_weight_bytes(); }
+
+int b200_stem_row_conv_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                            int out_pix_stride, void* stream) {
+  const int ho = (h + 6 - 7) / 2 + 1, wo = (w + 6 - 7) / 2 + 1;
+  return stem_row_launch(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, 64, out_pix_stride),
+                         weight, bias, static_cast<cudaStream_t>(stream));
+}
+
 int b200_stem_tc_kpad(int ksize) { return stem_tc_kpad(ksize); }
 int b200_stem_tc_nout(int cout) { return stem_tc_nout(cout); }
 

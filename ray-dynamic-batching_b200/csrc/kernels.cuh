@@ -28,6 +28,10 @@ int stem_tc_nout(int cout);
 int stem_tc_launch(const View& in, const View& out, const void* w, const float* bias, int ksize, int stride, int pad,
                    int act, cudaStream_t stream);
 
+// Toeplitz-descriptor ResNet stem (stem_row.cu): 7x7/2 pad 3, cout 64, ReLU; weights = bf16 smem image (stem_row_weight_bytes())
+int stem_row_weight_bytes();
+int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream);
+
 // ---- packed-K gather convolution for small Cin (gather_conv.cu): bf16 weights [npad][kpad], K index = tap*cin_p + c ----
 int gather_conv_npad(int cout);
 int gather_conv_kpad(int cin_p, int ksize);

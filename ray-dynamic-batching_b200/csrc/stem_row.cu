@@ -1,0 +1,232 @@
+// ResNet stem (7x7 / stride 2 / pad 3, 3 -> 64, + folded BN + ReLU) without any im2col copy: the tensor core reads the
+// sliding windows straight out of the staged input rows.
+//
+// With the input stored NHWC with C padded to 4, the 8-pixel aligned window of output pixel ow in kernel row r is the 64
+// contiguous bytes starting at pixel 2*ow - 4 of input row 2*oh + r - 3, i.e. at byte ow * 16 of the row: consecutive output
+// pixels' windows are the same bytes shifted by 16.  That Toeplitz structure is exactly what a *non-swizzled* K-major
+// shared-memory descriptor expresses when its strides are chosen as LBO (next 16-byte K chunk) = 16 B and SBO (next group
+// of 8 rows) = 128 B:  address(row m, chunk k) = base + m*16 + k*16.  So one TMA box per tile brings the 7 input rows of
+// an output row (zero-filled outside the image = the padding), and 7 x 2 tcgen05.mma (M=128, N=64, K=16) consume them in
+// place; GEMM-K is (kernel row, window pixel, channel) = 7 x 32 with zero weights for window pixel 0 and channel 3.
+//
+//   warp 0 : TMA producer (4-stage ring of 7-row boxes)        warp 1 : TMEM alloc + single-thread MMA issue
+//   warps 4-7 : epilogue (TMEM -> +bias -> ReLU -> bf16 -> swizzled smem -> TMA store clipped at the row end)
+//
+// Replaces tv resnet.py:268-270 (conv1 + bn1 + relu) as reached from scheduler.py:450.
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace b200 {
+
+static constexpr int SR_THREADS = 256;
+static constexpr int SR_STAGES = 4;
+static constexpr int SR_PAIRS = 132;                 // staged pixel pairs per input row: 2*128 + 8 pixels
+static constexpr int SR_ROW_BYTES = SR_PAIRS * 16;   // 2112
+static constexpr int SR_STAGE_BYTES = 116 * 128;     // 7 rows (14784 B) rounded up to a multiple of 128
+static constexpr int SR_W_BYTES = 7 * 4 * 64 * 16;   // weights: [kernel row][k chunk][cout][8 bf16] = 28672 B
+static constexpr int SR_OUT_BYTES = 128 * 128;       // one staged output tile (128 pixels x 64 channels bf16)
+
+// Non-swizzled K-major descriptor: start | LBO (stride between the two 16-byte K chunks of one MMA) | SBO (stride between
+// groups of 8 rows) | version 1 | layout type 0.
+__device__ __forceinline__ uint64_t umma_desc_noswz(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint32_t lo = ((addr >> 4) & 0x3FFFu) | ((lbo_bytes >> 4) << 16);
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14);
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
+
+struct StemRowParams {
+  const uint16_t* w;     // bf16, smem image of the weights (SR_W_BYTES)
+  const float* bias;     // [64]
+  int Ho, Wo, segs;      // segs = ceil(Wo / 128)
+  int total_tiles;       // N * Ho * segs
+};
+
+__global__ void __launch_bounds__(SR_THREADS, 1)
+stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
+                const __grid_constant__ StemRowParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[64];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = base;
+  const uint32_t wsm = ring + SR_STAGES * SR_STAGE_BYTES + 256;   // +256: rows m >= 112 of the last kernel row read past it
+  const uint32_t stage_out = (wsm + SR_W_BYTES + 1023u) & ~1023u;
+  const int per_cta = (p.total_tiles + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int tile0 = static_cast<int>(blockIdx.x) * per_cta;
+  const int my_tiles = max(0, min(per_cta, p.total_tiles - tile0));
+
+  // weights -> smem (already in the descriptor layout), bias
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SR_THREADS) {
+    const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  if (threadIdx.x < 64) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&in_map);
+    tma_prefetch_desc(&out_map);
+    for (int s = 0; s < SR_STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bar_t_full[b]), 1);
+      mbar_init(smem_u32(&bar_t_empty[b]), 128);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc<128>(smem_u32(&tmem_base_s));
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  auto tile_coords = [&](int it, int& n_oh, int& oh, int& ow0) {
+    const int t = tile0 + it;
+    const int seg = t % p.segs;
+    n_oh = t / p.segs;               // = n * Ho + oh
+    oh = n_oh % p.Ho;
+    ow0 = seg * 128;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int it = 0; it < my_tiles; ++it) {
+        int n_oh, oh, ow0;
+        tile_coords(it, n_oh, oh, ow0);
+        const int s = it % SR_STAGES;
+        mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
+        const uint32_t full = smem_u32(&bar_full[s]);
+        mbar_expect_tx(full, 7 * SR_ROW_BYTES);
+        // box [8 (pixel pair), 132 pairs, 7 rows, 1 image] at (0, ow0 - 2, 2*oh - 3, n); outside the image -> zeros
+        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 - 2, 2 * oh - 3, n_oh / p.Ho);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
+      for (int it = 0; it < my_tiles; ++it) {
+        const int b = it & 1, s = it % SR_STAGES;
+        mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
+        mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t a0 = ring + s * SR_STAGE_BYTES;
+#pragma unroll
+        for (int r = 0; r < 7; ++r) {
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) {
+            // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride 1024, 8-row stride 128
+            const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + kk * 32, 16, 128);
+            const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
+            umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(smem_u32(&bar_empty[s]));
+        umma_commit(smem_u32(&bar_t_full[b]));
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    const int epi_tid = threadIdx.x - 128;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const int sw = row & 7;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int b = it & 1;
+      int n_oh, oh, ow0;
+      tile_coords(it, n_oh, oh, ow0);
+      if (epi_tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // store of tile it-2 has read staging[b]
+      named_bar_sync(1, 128);
+      mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
+      tc_fence_after();
+      const uint32_t dst_row = stage_out + b * SR_OUT_BYTES + row * 128;
+      const uint32_t acc = tmem_base + b * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + cc * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int chunk = cc * 4 + g;
+          float f[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) f[i] = fmaxf(__uint_as_float(v[g * 8 + i]) + bias_s[chunk * 8 + i], 0.f);
+          const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+          const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((chunk ^ sw) << 4)), "r"(o0), "r"(o1),
+                       "r"(o2), "r"(o3)
+                       : "memory");
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_t_empty[b]));
+      fence_proxy_async_smem();
+      named_bar_sync(2, 128);
+      if (epi_tid == 0) {
+        // 3-D store [64 ch, 128 pixels, 1 row] at (0, ow0, n*Ho + oh): pixels past Wo are clipped
+        asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+                     ::"l"(reinterpret_cast<uint64_t>(&out_map)), "r"(stage_out + b * SR_OUT_BYTES), "r"(0), "r"(ow0), "r"(n_oh)
+                     : "memory");
+        tma_store_commit();
+      }
+    }
+    if (epi_tid == 0) tma_store_wait_all();
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<128>(tmem_base);
+  }
+}
+
+int stem_row_weight_bytes() { return SR_W_BYTES; }
+
+// weights: bf16 smem image [kernel row 7][k chunk 4][cout 64][8]: element e of chunk k = window pixel 2k + e/4 (= kernel
+// column + 1), channel e%4; zero for window pixel 0 and channel 3.  bias fp32 [64].
+int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
+  if (in.C != 4 || in.pix_stride != 4 || in.W % 2) return fail(B200_ERR_INVALID, "stem_row: input must be NHWC4 with even width");
+  if (out.C != 64 || out.pix_stride % 8) return fail(B200_ERR_INVALID, "stem_row: cout must be 64");
+  if ((in.H + 6 - 7) / 2 + 1 != out.H || (in.W + 6 - 7) / 2 + 1 != out.W || in.N != out.N)
+    return fail(B200_ERR_INVALID, "stem_row: output geometry mismatch");
+  CUtensorMap in_map, out_map;
+  {
+    const uint64_t dims[4] = {8, uint64_t(in.W / 2), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {16, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
+    const uint32_t box[4] = {8, uint32_t(SR_PAIRS), 7, 1};
+    B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
+  }
+  {
+    const uint64_t ops = uint64_t(out.pix_stride) * 2;
+    const uint64_t dims[3] = {64, uint64_t(out.W), uint64_t(out.N) * out.H};
+    const uint64_t str[2] = {ops, ops * out.W};
+    const uint32_t box[3] = {64, 128, 1};
+    B200_TRY(encode_tmap(&out_map, out.base, 3, dims, str, box, SWZ_128B));
+  }
+  StemRowParams p;
+  p.w = static_cast<const uint16_t*>(w);
+  p.bias = bias;
+  p.Ho = out.H; p.Wo = out.W;
+  p.segs = (out.W + 127) / 128;
+  p.total_tiles = out.N * out.H * p.segs;
+  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + 2 * SR_OUT_BYTES + 1024;
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev & 63] = true;
+  }
+  const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
+  stem_row_kernel<<<ctas, SR_THREADS, smem, stream>>>(in_map, out_map, p);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+}  // namespace b200

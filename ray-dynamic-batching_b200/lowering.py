@@ -75,6 +75,20 @@ def stem_tc_weights(weight, bias):
     return PlanBuilder.bf16_bits(w), b.numpy().astype(np.float32)
 
 
+def stem_row_weights(weight, bias):
+    """[64,3,7,7] fp32 -> bf16 bits of the shared-memory image of csrc/stem_row.cu: [kernel row 7][K chunk 4][cout 64][8],
+    element e of chunk k = window pixel 2k + e // 4 (= kernel column + 1), channel e % 4."""
+    cout = weight.shape[0]
+    assert weight.shape == (64, 3, 7, 7)
+    img = torch.zeros(7, 4, 64, 8)
+    for r in range(7):
+        for s_ in range(7):
+            wp = s_ + 1
+            k, half = wp // 2, wp % 2
+            img[r, k, :, half * 4:half * 4 + 3] = weight[:, :, r, s_]
+    return PlanBuilder.bf16_bits(img), bias.numpy().astype(np.float32)
+
+
 def act_code(m):
     if m is None or isinstance(m, nn.Identity):
         return ACT_NONE
@@ -111,6 +125,7 @@ class PlanBuilder:
         self.out_dim = 0
         self.names = []     # op index -> human readable name (kept out of the blob)
         self.tensor_core_stem = True
+        self.toeplitz_stem = True
         self.gather_small_cin = True
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
@@ -196,6 +211,12 @@ class PlanBuilder:
         assert cin == 3 and x.buf == self.in_buf
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
         out = self.new_act(ho, wo, cout)
+        if self.toeplitz_stem and (k, stride, pad, cout, act) == (7, 2, 3, 64, ACT_RELU) and x.w % 2 == 0:
+            wb, bb = stem_row_weights(weight, bias)
+            w_off = self.add_weights(wb)
+            b_off = self.add_weights(bb)
+            self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, 64, -1, 0, k, stride, pad, act, 2], w_off, b_off, name=name)
+            return out
         if self.tensor_core_stem and stride == 2 and ((k == 7 and pad == 3) or (k == 3 and pad == 1)) and cout <= 64 \
                 and x.w % 2 == 0:
             wb, bb = stem_tc_weights(weight, bias)

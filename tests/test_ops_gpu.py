@@ -44,6 +44,29 @@ def test_stem_conv(b200lib, cuda, k, s, p, cout, cfg):
     assert ok, e
 
 
+@pytest.mark.parametrize("cfg", [(2, 224, 224), (3, 64, 96), (1, 38, 300), (2, 640, 640)])
+def test_stem_row_toeplitz(b200lib, cuda, cfg):
+    """7x7/2 stem read in place through non-swizzled descriptors; includes widths that need several 128-pixel segments."""
+    from rdb_b200.lowering import stem_row_weights
+    n, h, w = cfg
+    x4 = torch.zeros(n, h, w, 4, device=cuda, dtype=torch.bfloat16)
+    x4[..., :3] = rnd((n, h, w, 3), 1, cuda)
+    wt = (rnd((64, 3, 7, 7), 2, cuda, torch.float32) / 147 ** 0.5).to(torch.bfloat16).float()
+    b = rnd((64,), 3, cuda, torch.float32)
+    wb, bb = stem_row_weights(wt.cpu(), b.cpu())
+    assert wb.nbytes == b200lib.b200_stem_row_weight_bytes()
+    wdev = torch.from_numpy(wb.astype("int16")).to(cuda)
+    bdev = torch.from_numpy(bb).to(cuda)
+    ho, wo = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    out = torch.full((n, ho, wo, 64), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_row_conv_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(out), 0, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.relu(F.conv2d(x4[..., :3].float().permute(0, 3, 1, 2), wt, b, stride=2, padding=3)).permute(0, 2, 3, 1)
+    assert not torch.isnan(out.float()).any()
+    ok, e = close_bf16(out, ref)
+    assert ok, e
+
+
 @pytest.mark.parametrize("k,p,cout,cfg,act", [(7, 3, 64, (2, 224, 224), 1), (3, 1, 24, (3, 224, 224), 2),
                                               (3, 1, 16, (1, 96, 130), 2), (7, 3, 64, (5, 38, 50), 1),
                                               (3, 1, 32, (2, 64, 64), 0)])
