@@ -111,7 +111,8 @@ def plan_traffic(blob, batch):
         elif t == lowering.OP_STEM:
             k = p[8]
             b += k * k * 3 * p[5] * 4
-            fl = 2.0 * batch * oh * ow * p[5] * 3 * k * k
+            sh, sw_ = (ih + 2 * p[10] - k) // p[9] + 1, (iw + 2 * p[10] - k) // p[9] + 1   # conv output size (pool may follow)
+            fl = 2.0 * batch * sh * sw_ * p[5] * 3 * k * k
         elif t == lowering.OP_FC:
             b += p[5] * p[2] * 4
             fl = 2.0 * batch * p[5] * p[2]

@@ -88,6 +88,11 @@ B200_API int b200_stem_row_weight_bytes(void);
 B200_API int b200_stem_row_conv_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
                                      int out_pix_stride, void* stream);
 
+/* Same stem fused with MaxPool2d(3,2,1) (tv resnet.py:268-271): the 112x112x64 activation stays in shared memory, `out` is
+ * the pooled [n][h/4][w/4][64] tensor. Stem width (w/2) must be <= 128; weight layout as b200_stem_row_conv_nhwc. */
+B200_API int b200_stem_pool_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                                 int out_pix_stride, void* stream);
+
 /* Depthwise 3x3 (pad 1) + folded BN + activation. Replaces tv shufflenetv2.py:62-76 `depthwise_conv` and the depthwise
  * stage of MBConv (tv efficientnet.py:140-151). weight: fp32 [9][c]; bias fp32 [c]. */
 B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,

@@ -88,7 +88,7 @@ class PlanInterpreter:
                 ct = stem_cout_tile(cout)
                 cpad = (cout + ct - 1) // ct * ct
                 x = B[p[0]][..., :3].permute(0, 3, 1, 2)
-                if p[12] == 2:      # Toeplitz stem: bf16 image [7][4][64][8], element e of chunk k = pixel 2k + e//4, channel e%4
+                if p[12] in (2, 3):      # Toeplitz stem (3: fused with MaxPool2d(3,2,1)): bf16 image [7][4][64][8], element e of chunk k = pixel 2k + e//4, channel e%4
                     img = self._bf16w(op["w_off"], 7 * 4 * 64 * 8).view(7, 4, 64, 8)
                     w = torch.zeros(64, 3, 7, 7)
                     for r in range(7):
@@ -108,8 +108,10 @@ class PlanInterpreter:
                 else:
                     w = self._f32(op["w_off"], k * k * 3 * cpad).view(k, k, 3, cpad)[..., :cout].permute(3, 2, 0, 1)
                     b = self._f32(op["b_off"], cpad)[:cout]
-                y = F.conv2d(x, w, b, stride=s, padding=pad)
-                B[p[3]][..., p[4]:p[4] + cout] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+                y = _bf16(_act(F.conv2d(x, w, b, stride=s, padding=pad), act))
+                if p[12] == 3:
+                    y = F.max_pool2d(y, 3, 2, 1)
+                B[p[3]][..., p[4]:p[4] + cout] = y.permute(0, 2, 3, 1)
             elif t == OP_DWCONV:
                 c, s, act = p[2], p[9], p[11]
                 x = B[p[0]][..., p[1]:p[1] + c].permute(0, 3, 1, 2)

@@ -65,6 +65,13 @@ int b200_stem_row_conv_nhwc(const void* in, int n, int h, int w, const void* wei
                          weight, bias, static_cast<cudaStream_t>(stream));
 }
 
+int b200_stem_pool_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                        int out_pix_stride, void* stream) {
+  const int ho = ((h + 6 - 7) / 2 + 1) / 2, wo = ((w + 6 - 7) / 2 + 1) / 2;
+  return stem_pool_launch(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, 64, out_pix_stride),
+                          weight, bias, static_cast<cudaStream_t>(stream));
+}
+
 int b200_stem_tc_kpad(int ksize) { return stem_tc_kpad(ksize); }
 int b200_stem_tc_nout(int cout) { return stem_tc_nout(cout); }
 

@@ -126,6 +126,11 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
         rc = conv_launch(po.conv, stream);
         break;
       case OP_STEM:
+        if (p[12] == 3) {
+          rc = stem_pool_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
+                                reinterpret_cast<const float*>(W + po.rec.b_off), stream);
+          break;
+        }
         if (p[12] == 2) {
           rc = stem_row_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
                                reinterpret_cast<const float*>(W + po.rec.b_off), stream);

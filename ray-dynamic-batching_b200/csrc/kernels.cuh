@@ -31,6 +31,8 @@ int stem_tc_launch(const View& in, const View& out, const void* w, const float* 
 // Toeplitz-descriptor ResNet stem (stem_row.cu): 7x7/2 pad 3, cout 64, ReLU; weights = bf16 smem image (stem_row_weight_bytes())
 int stem_row_weight_bytes();
 int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream);
+// fused conv1 + bn1 + relu + maxpool(3,2,1): `out` is the pooled tensor
+int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream);
 
 // ---- packed-K gather convolution for small Cin (gather_conv.cu): bf16 weights [npad][kpad], K index = tap*cin_p + c ----
 int gather_conv_npad(int cout);

@@ -186,6 +186,237 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   }
 }
 
+// ----------------------------------------------------------------------------------------------------------------
+// Fused stem + MaxPool2d(3, 2, 1): the 112x112x64 stem activation (1.6 MB per image) never goes to HBM.
+// A work unit is (image, band of SP_BAND pooled rows); the CTA walks the stem rows of the band in order, the epilogue
+// keeps the last three rows (bf16, swizzled) in shared memory and emits pooled row ph as soon as stem row 2*ph+1 exists.
+// One stem row per band is recomputed (its top halo).  Requires Wo <= 128 (one MMA tile per stem row) and even Ho, Wo.
+// Replaces tv resnet.py:268-271 (conv1, bn1, relu, maxpool).
+// ----------------------------------------------------------------------------------------------------------------
+static constexpr int SP_BAND = 7;
+
+struct StemPoolParams {
+  const uint16_t* w;
+  const float* bias;
+  uint16_t* out;        // pooled NHWC [N][Ho/2][Wo/2][out_ps]
+  int out_ps;
+  int Ho, Wo;           // stem output size
+  int bands;            // bands per image = ceil((Ho/2) / SP_BAND)
+  int total_units;      // N * bands
+};
+
+__device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
+  __nv_bfloat162 x = *reinterpret_cast<__nv_bfloat162*>(&a), y = *reinterpret_cast<__nv_bfloat162*>(&b);
+  __nv_bfloat162 m = __hmax2(x, y);
+  return *reinterpret_cast<uint32_t*>(&m);
+}
+
+__global__ void __launch_bounds__(SR_THREADS, 1)
+stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ StemPoolParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[64];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = base;
+  const uint32_t wsm = ring + SR_STAGES * SR_STAGE_BYTES + 256;
+  const uint32_t rows3 = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // three stem rows [128 px][128 B], chunk-swizzled
+  const int per_cta = (p.total_units + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int unit0 = static_cast<int>(blockIdx.x) * per_cta;
+  const int my_units = max(0, min(per_cta, p.total_units - unit0));
+  const int Hp = p.Ho >> 1, Wp = p.Wo >> 1;
+
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SR_THREADS) {
+    const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  if (threadIdx.x < 64) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&in_map);
+    for (int s = 0; s < SR_STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bar_t_full[b]), 1);
+      mbar_init(smem_u32(&bar_t_empty[b]), 128);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc<128>(smem_u32(&tmem_base_s));
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  // stem rows of unit u: y in [y_lo, y_hi]
+  auto unit_rows = [&](int u, int& n, int& ph0, int& ph1, int& y_lo, int& y_hi) {
+    n = u / p.bands;
+    ph0 = (u - n * p.bands) * SP_BAND;
+    ph1 = min(ph0 + SP_BAND, Hp);                 // pooled rows [ph0, ph1)
+    y_lo = max(0, 2 * ph0 - 1);
+    y_hi = 2 * (ph1 - 1) + 1;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int u = unit0; u < unit0 + my_units; ++u) {
+        int n, ph0, ph1, y_lo, y_hi;
+        unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+        for (int y = y_lo; y <= y_hi; ++y, ++it) {
+          const int s = it % SR_STAGES;
+          mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
+          const uint32_t full = smem_u32(&bar_full[s]);
+          mbar_expect_tx(full, 7 * SR_ROW_BYTES);
+          tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -2, 2 * y - 3, n);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
+      int it = 0;
+      for (int u = unit0; u < unit0 + my_units; ++u) {
+        int n, ph0, ph1, y_lo, y_hi;
+        unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+        for (int y = y_lo; y <= y_hi; ++y, ++it) {
+          const int b = it & 1, s = it % SR_STAGES;
+          mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
+          mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
+          tc_fence_after();
+          const uint32_t a0 = ring + s * SR_STAGE_BYTES;
+#pragma unroll
+          for (int r = 0; r < 7; ++r) {
+#pragma unroll
+            for (int kk = 0; kk < 2; ++kk) {
+              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + kk * 32, 16, 128);
+              const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
+              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(smem_u32(&bar_empty[s]));
+          umma_commit(smem_u32(&bar_t_full[b]));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    const int epi_tid = threadIdx.x - 128;
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;     // stem pixel (ow) owned by this thread
+    const int sw = row & 7;
+    int it = 0;
+    for (int u = unit0; u < unit0 + my_units; ++u) {
+      int n, ph0, ph1, y_lo, y_hi;
+      unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+      for (int y = y_lo; y <= y_hi; ++y, ++it) {
+        const int b = it & 1;
+        mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t dst_row = rows3 + (y % 3) * SR_OUT_BYTES + row * 128;
+        const uint32_t acc = tmem_base + b * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+          uint32_t v[32];
+          tmem_ld_32x32(acc + cc * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            const int chunk = cc * 4 + g;
+            float f[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = fmaxf(__uint_as_float(v[g * 8 + i]) + bias_s[chunk * 8 + i], 0.f);
+            const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+            const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((chunk ^ sw) << 4)), "r"(o0), "r"(o1),
+                         "r"(o2), "r"(o3)
+                         : "memory");
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(smem_u32(&bar_t_empty[b]));
+        named_bar_sync(1, 128);                       // stem row y is complete in shared memory
+        if ((y & 1) && (y >> 1) >= ph0) {              // y = 2*ph + 1: pooled row ph over stem rows y-2, y-1, y (the band's
+                                                       // first row 2*ph0-1 is only the top halo of pooled row ph0)
+          const int ph = y >> 1;
+          uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
+          for (int item = epi_tid; item < Wp * 8; item += 128) {
+            const int pw = item >> 3, chunk = item & 7;
+            uint4 m = make_uint4(0, 0, 0, 0);          // post-ReLU values are >= 0, so 0 is the identity of max
+#pragma unroll
+            for (int dy = 0; dy < 3; ++dy) {
+              const int yy = y - 2 + dy;
+              if (yy < 0) continue;
+              const uint32_t rbase = rows3 + (yy % 3) * SR_OUT_BYTES;
+#pragma unroll
+              for (int dx = 0; dx < 3; ++dx) {
+                const int xx = 2 * pw - 1 + dx;
+                if (xx < 0 || xx >= p.Wo) continue;
+                uint32_t a0, a1, a2, a3;
+                asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
+                             : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                             : "r"(rbase + xx * 128 + ((chunk ^ (xx & 7)) << 4)));
+                m.x = bf16x2_max_u32(m.x, a0); m.y = bf16x2_max_u32(m.y, a1);
+                m.z = bf16x2_max_u32(m.z, a2); m.w = bf16x2_max_u32(m.w, a3);
+              }
+            }
+            *reinterpret_cast<uint4*>(orow + static_cast<size_t>(pw) * p.out_ps + chunk * 8) = m;
+          }
+        }
+        named_bar_sync(2, 128);                       // pooling reads are done before the oldest row is overwritten
+      }
+    }
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<128>(tmem_base);
+  }
+}
+
+// Fused conv1 + bn1 + relu + maxpool(3,2,1).  `out` is the pooled tensor [N][Ho/2][Wo/2][64].
+int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
+  if (in.C != 4 || in.pix_stride != 4 || in.W % 2) return fail(B200_ERR_INVALID, "stem_pool: input must be NHWC4 with even width");
+  const int Ho = (in.H + 6 - 7) / 2 + 1, Wo = (in.W + 6 - 7) / 2 + 1;
+  if (Wo > 128 || (Ho & 1) || (Wo & 1)) return fail(B200_ERR_INVALID, "stem_pool: needs stem width <= 128 and even stem size");
+  if (out.C != 64 || out.pix_stride % 8 || out.H != Ho / 2 || out.W != Wo / 2 || out.N != in.N)
+    return fail(B200_ERR_INVALID, "stem_pool: output geometry mismatch");
+  CUtensorMap in_map;
+  {
+    const uint64_t dims[4] = {8, uint64_t(in.W / 2), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {16, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
+    const uint32_t box[4] = {8, uint32_t(SR_PAIRS), 7, 1};
+    B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
+  }
+  StemPoolParams p;
+  p.w = static_cast<const uint16_t*>(w);
+  p.bias = bias;
+  p.out = static_cast<uint16_t*>(out.base);
+  p.out_ps = out.pix_stride;
+  p.Ho = Ho; p.Wo = Wo;
+  p.bands = (Ho / 2 + SP_BAND - 1) / SP_BAND;
+  p.total_units = in.N * p.bands;
+  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + 3 * SR_OUT_BYTES + 1024;
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev & 63] = true;
+  }
+  const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
+  stem_pool_kernel<<<ctas, SR_THREADS, smem, stream>>>(in_map, p);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
 int stem_row_weight_bytes() { return SR_W_BYTES; }
 
 // weights: bf16 smem image [kernel row 7][k chunk 4][cout 64][8]: element e of chunk k = window pixel 2k + e/4 (= kernel

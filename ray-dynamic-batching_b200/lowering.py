@@ -126,6 +126,7 @@ class PlanBuilder:
         self.names = []     # op index -> human readable name (kept out of the blob)
         self.tensor_core_stem = True
         self.toeplitz_stem = True
+        self.fuse_stem_pool = __import__('os').environ.get('B200_FUSE_STEM_POOL', '0') == '1'
         self.gather_small_cin = True
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
@@ -235,6 +236,18 @@ class PlanBuilder:
         b_off = self.add_weights(bp.numpy().astype(np.float32))
         self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, pad8(cout), -1, 0, k, stride, pad, act], w_off, b_off,
                  name=name)
+        return out
+
+    def stem_pool(self, x: T, weight, bias, name=""):
+        """conv 7x7/2 pad 3 (3 -> 64) + bias + ReLU + MaxPool2d(3,2,1) in one kernel (csrc/stem_row.cu stem_pool_kernel)."""
+        assert weight.shape == (64, 3, 7, 7) and x.buf == self.in_buf
+        hs, ws = (x.h - 1) // 2 + 1, (x.w - 1) // 2 + 1
+        assert ws <= 128 and hs % 2 == 0 and ws % 2 == 0
+        out = self.new_act(hs // 2, ws // 2, 64)
+        wb, bb = stem_row_weights(weight, bias)
+        w_off = self.add_weights(wb)
+        b_off = self.add_weights(bb)
+        self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, 64, -1, 0, 7, 2, 3, ACT_RELU, 3], w_off, b_off, name=name)
         return out
 
     def dwconv(self, x: T, weight, bias, stride, act, out: Optional[T] = None, name=""):
@@ -385,8 +398,12 @@ def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
     """torchvision ResNet (Bottleneck, stride on the 3x3 = v1.5): tv models/resnet.py:108-165, 266-285."""
     pb = PlanBuilder("resnet50", in_hw[0], in_hw[1])
     w, b = fold_bn(model.conv1, model.bn1)
-    x = pb.stem(pb.input(), w, b, 2, 3, ACT_RELU, name="conv1")
-    x = pb.maxpool(x, 3, 2, 1, name="maxpool")
+    hs, ws = (in_hw[0] - 1) // 2 + 1, (in_hw[1] - 1) // 2 + 1
+    if pb.fuse_stem_pool and ws <= 128 and hs % 2 == 0 and ws % 2 == 0 and in_hw[1] % 2 == 0:
+        x = pb.stem_pool(pb.input(), w, b, name="conv1+maxpool")
+    else:
+        x = pb.stem(pb.input(), w, b, 2, 3, ACT_RELU, name="conv1")
+        x = pb.maxpool(x, 3, 2, 1, name="maxpool")
     for li, layer in enumerate([model.layer1, model.layer2, model.layer3, model.layer4], 1):
         for bi, blk in enumerate(layer):
             nm = "layer%d.%d." % (li, bi)

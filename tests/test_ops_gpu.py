@@ -67,6 +67,32 @@ def test_stem_row_toeplitz(b200lib, cuda, cfg):
     assert ok, e
 
 
+@pytest.mark.parametrize("cfg", [(2, 224, 224), (3, 64, 96), (1, 40, 256), (5, 224, 224)])
+def test_stem_pool_fused_bit_exact_vs_unfused_kernels(b200lib, cuda, cfg):
+    """conv1+bn1+relu+maxpool in one kernel == Toeplitz stem kernel followed by the max-pool kernel, bit for bit."""
+    from rdb_b200.lowering import stem_row_weights
+    n, h, w = cfg
+    x4 = torch.zeros(n, h, w, 4, device=cuda, dtype=torch.bfloat16)
+    x4[..., :3] = rnd((n, h, w, 3), 1, cuda)
+    wt = (rnd((64, 3, 7, 7), 2, cuda, torch.float32) / 147 ** 0.5).to(torch.bfloat16).float()
+    b = rnd((64,), 3, cuda, torch.float32)
+    wb, bb = stem_row_weights(wt.cpu(), b.cpu())
+    wdev = torch.from_numpy(wb.astype("int16")).to(cuda)
+    bdev = torch.from_numpy(bb).to(cuda)
+    hs, ws = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    stem = torch.empty(n, hs, ws, 64, device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_row_conv_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(stem), 0, stream_ptr()))
+    pooled = torch.empty(n, hs // 2, ws // 2, 64, device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_maxpool_nhwc(ptr(stem), n, hs, ws, 64, 0, ptr(pooled), 0, 3, 2, 1, stream_ptr()))
+    fused = torch.full((n, hs // 2, ws // 2, 64), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_pool_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(fused), 0, stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(fused, pooled)
+    ref = F.max_pool2d(F.relu(F.conv2d(x4[..., :3].float().permute(0, 3, 1, 2), wt, b, stride=2, padding=3)), 3, 2, 1)
+    ok, e = close_bf16(fused, ref.permute(0, 2, 3, 1))
+    assert ok, e
+
+
 @pytest.mark.parametrize("k,p,cout,cfg,act", [(7, 3, 64, (2, 224, 224), 1), (3, 1, 24, (3, 224, 224), 2),
                                               (3, 1, 16, (1, 96, 130), 2), (7, 3, 64, (5, 38, 50), 1),
                                               (3, 1, 32, (2, 64, 64), 0)])
