@@ -1,0 +1,83 @@
+"""Batch-size profiler for a B200 engine, in the reference's own CSV schema.
+
+The Nexus packing policy of the reference (293-project/src/nexus.py) consumes, per model, a dict
+batch_size -> {'avg_latency_ms', 'peak_memory_mb'} loaded from the `_summary.csv` files that
+profiling/ModelProfiler.py writes (columns at ModelProfiler.py:355-357; loader at scheduler.py:95-113).  This module
+measures the same quantities on the B200 engine — forward pass from device-resident inputs under CUDA events, warm-up
+runs then timed runs, exactly like ModelProfiler._measure_latency (:92-112) — so a maintainer can re-profile and keep
+nexus.py unchanged.
+"""
+import csv
+import logging
+import statistics
+from typing import Dict, List
+
+import torch
+
+from . import lowering as _lowering
+
+FIELDNAMES = ['batch_size', 'status', 'avg_latency_ms', 'std_latency_ms', 'throughput', 'throughput_efficiency',
+              'peak_memory_mb', 'memory_per_sample_mb', 'memory_utilization']
+
+
+def engine_memory_mb(model, batch_size: int) -> float:
+    """Device memory the engine needs for `batch_size`: weights + every activation buffer of the plan."""
+    hdr, bufs, _, weights = _lowering.parse_blob(model.blob)
+    per_image = sum(h * w * c * (4 if dt else 2) for h, w, c, dt in bufs)
+    return (len(weights) + per_image * batch_size) / (1024.0 * 1024.0)
+
+
+def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_runs: int = 10) -> List[dict]:
+    """One row per batch size (ModelProfiler.profile_batch_size, :114-178)."""
+    dev = model.device
+    total_mem_mb = torch.cuda.get_device_properties(dev).total_memory / (1024.0 * 1024.0)
+    rows = []
+    for bs in batch_sizes:
+        if bs > model.max_batch:
+            rows.append({'batch_size': bs, 'status': 'exceeds_max_batch'})
+            continue
+        out = torch.empty(bs, model.out_dim, device=dev, dtype=torch.float32)
+        for _ in range(warmup_runs + 2):            # +2: the first two calls of a batch size are eager / graph capture
+            model.infer_resident(bs, out)
+        torch.cuda.synchronize(dev)
+        lat = []
+        for _ in range(num_runs):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            model.infer_resident(bs, out)
+            e1.record()
+            e1.synchronize()
+            lat.append(e0.elapsed_time(e1))
+        avg = sum(lat) / len(lat)
+        mem = engine_memory_mb(model, bs)
+        thr = bs / (avg / 1000.0)
+        rows.append({'batch_size': bs, 'status': 'success', 'avg_latency_ms': avg,
+                     'std_latency_ms': statistics.pstdev(lat), 'throughput': thr, 'throughput_efficiency': thr / bs,
+                     'peak_memory_mb': mem, 'memory_per_sample_mb': mem / bs, 'memory_utilization': mem / total_mem_mb})
+    return rows
+
+
+def save_summary_csv(rows: List[dict], path: str) -> None:
+    with open(path, 'w', newline='') as f:
+        w = csv.DictWriter(f, fieldnames=FIELDNAMES)
+        w.writeheader()
+        for r in rows:
+            w.writerow({k: r[k] for k in FIELDNAMES if k in r})
+
+
+def load_csv_to_dict(file_path: str) -> Dict[int, Dict[str, float]]:
+    """Mirror of BatchProfiler.load_csv_to_dict (scheduler.py:95-113): batch_size -> {avg_latency_ms, peak_memory_mb}."""
+    column_list = ['avg_latency_ms', 'peak_memory_mb']
+    result = {}
+    try:
+        with open(file_path, 'r') as csvfile:
+            reader = csv.DictReader(csvfile)
+            headers = reader.fieldnames
+            key_column = headers[0] if headers else None
+            for row in reader:
+                key = int(row[key_column])
+                result[key] = {h: float(row[h]) for h in headers[1:] if h in column_list and row[h] != ''}
+    except (FileNotFoundError, ValueError) as e:
+        logging.error("Error loading batch profile from %s: %s", file_path, e)
+        return {}
+    return result
