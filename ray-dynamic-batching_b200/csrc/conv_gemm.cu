@@ -293,7 +293,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     if (lane == 0) {
       uint32_t g = 0;  // k-block counter across all tiles of this CTA
       for (int it = 0; it < my_tiles; ++it) {
-        const int tile = blockIdx.x + it * gridDim.x;
+        const int tile0_ = blockIdx.x + it * gridDim.x;
+        const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
         int n_tile, w0, h0, nb0;
         tile_coords(p, tile, n_tile, w0, h0, nb0);
         const int n0 = n_tile * BLOCK_N;
@@ -343,7 +344,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     // =========================== DMA: residual prefetch (LA tiles ahead) + output stores ===========================
     if (lane == 0) {
       auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
-        const int tile = blockIdx.x + j * gridDim.x;
+        const int tile0_ = blockIdx.x + j * gridDim.x;
+        const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
         const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
         if (RES) {
           int n_tile, w0, h0, nb0;
@@ -361,7 +363,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       for (int it = 0; it < my_tiles; ++it) {
         // store of tile it, once its epilogue is done
         {
-          const int tile = blockIdx.x + it * gridDim.x;
+          const int tile0_ = blockIdx.x + it * gridDim.x;
+          const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
           const int n0 = n_tile * BLOCK_N;
@@ -392,7 +395,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     const uint32_t row_off = row * 128;
     const int sw = row & 7;
     for (int it = 0; it < my_tiles; ++it) {
-      const int tile = blockIdx.x + it * gridDim.x;
+      const int tile0_ = blockIdx.x + it * gridDim.x;
+      const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
       const int b = it & 1;
       const int ob = it % NB;
       const int n0 = (tile % p.n_tiles) * BLOCK_N;
@@ -509,7 +513,8 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
 
   // pair tile -> this CTA's 128-pixel m-tile and the shared n-tile
   auto my_coords = [&](int it, int& n0, int& w0, int& h0, int& nb0) {
-    const int pt = pair + it * num_pairs;
+    const int pt0 = pair + it * num_pairs;
+    const int pt = p.reverse ? total_pair_tiles - 1 - pt0 : pt0;
     const int n_tile = pt % p.n_tiles;
     int m = (pt / p.n_tiles) * 2 + static_cast<int>(rank);
     if (m >= m_tiles) m = m_tiles;            // phantom tile of an odd tail: coordinates past the tensor (TMA clips)
@@ -651,7 +656,8 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     for (int it = 0; it < my_tiles; ++it) {
       const int b = it & 1;
       const int ob = it % NB;
-      const int n0 = ((pair + it * num_pairs) % p.n_tiles) * BLOCK_N;
+      const int pt0_ = pair + it * num_pairs;
+      const int n0 = ((p.reverse ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
         const int c = n0 + i;
         bias_s[b % NBIAS][i] = (c < p.cout) ? p.bias[c] : 0.f;
@@ -766,6 +772,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.act = s.act;
   p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
   p.bias = s.bias;
+  p.reverse = s.reverse_tiles ? 1 : 0;
   // Tile choice.  Layers with enough arithmetic per byte (K >= 256, Cout >= 128) are bound by shared-memory operand
   // bandwidth in single-CTA mode -> CTA pairs (M = 256), N = 256 when Cout allows.  Thin layers stay single-CTA.
   const int k_total = in.C * taps;

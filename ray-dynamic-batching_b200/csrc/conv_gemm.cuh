@@ -11,7 +11,8 @@ struct ConvSpec {
   const float* bias = nullptr;  // fp32 [Cout]
   int ksize = 1, stride = 1, pad = 0;
   int act = 0;               // b200::Act
-  bool res_after_act = false;  // false: act(acc + bias + res) (ResNet); true: act(acc + bias) + res (FusedMBConv e=1)
+  bool res_after_act = false;
+  bool reverse_tiles = false;  // false: act(acc + bias + res) (ResNet); true: act(acc + bias) + res (FusedMBConv e=1)
 };
 
 struct alignas(64) ConvMaps {
@@ -27,6 +28,7 @@ struct ConvParams {
   int n_tiles;                    // tiles along Cout
   int num_taps, kb_per_tap;
   int cout, act, has_res;  // has_res: 0 none, 1 add before the activation, 2 add after it
+  int reverse;             // walk the tiles last-to-first (alternated layer by layer so a layer starts on what is still in L2)
   signed char tap_map[9], tap_dx[9], tap_dy[9];
   const float* bias;
 };

@@ -1,6 +1,7 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <stdlib.h>
 
 using namespace b200;
 
@@ -92,6 +93,12 @@ int Engine::plan_for(int batch, BatchPlan** out) {
   std::unique_ptr<BatchPlan> plan(new BatchPlan);
   plan->batch = batch;
   plan->ops.resize(ops.size());
+  static int alt = -1;
+  if (alt < 0) {
+    const char* e = getenv("B200_ALTERNATE_TILES");
+    alt = (e && e[0] == '0') ? 0 : 1;
+  }
+  int conv_index = 0;
   for (size_t i = 0; i < ops.size(); ++i) {
     PreparedOp& po = plan->ops[i];
     po.rec = ops[i];
@@ -105,6 +112,7 @@ int Engine::plan_for(int batch, BatchPlan** out) {
       s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
       s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];
       s.res_after_act = p[12] != 0;
+      s.reverse_tiles = alt && (conv_index++ & 1);   // consecutive conv layers walk their tiles in opposite directions
       int rc = conv_prepare(s, &po.conv);
       if (rc != 0) return fail(rc, "op " + std::to_string(i) + ": " + last_error_cstr());
     }
