@@ -471,11 +471,13 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
 template <int BLOCK_N>
 struct P2ConvCfg {
   static constexpr int STAGES = BLOCK_N == 256 ? 3 : 4;
-  static constexpr int OUT_BUFS = BLOCK_N == 256 ? 2 : 4;
-  static constexpr int LOOKAHEAD = OUT_BUFS - 2;
+  static constexpr int SUB_N = 128;                  // the epilogue / residual / store pipeline works on 128-column units
+  static constexpr int SUBS = BLOCK_N / SUB_N;
+  static constexpr int OUT_BUFS = 4;
+  static constexpr int LOOKAHEAD = OUT_BUFS - 2;     // units the residual prefetch runs ahead
   static constexpr int B_STAGE_BYTES = (BLOCK_N / 2) * BLOCK_K * 2;  // this CTA's half of the weight tile
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int OUT_BYTES = BLOCK_M * BLOCK_N * 2;
+  static constexpr int OUT_BYTES = BLOCK_M * SUB_N * 2;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + 1024;
   static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
   static_assert(2 * BLOCK_N <= 512, "TMEM budget");
@@ -602,45 +604,44 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     }
     __syncwarp();
   } else if (warp == 2) {
-    // =========================== DMA: residual prefetch + output stores (per CTA) ===========================
+    // =========================== DMA: residual prefetch + output stores (per CTA, 128-column units) ===========================
     if (lane == 0) {
-      auto acquire_staging = [&](int j) {
-        const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
+      constexpr int SUBS = Cfg::SUBS, SUB_N = Cfg::SUB_N;
+      const int total_units = my_tiles * SUBS;
+      auto unit_coords = [&](int u, int& n0, int& w0, int& h0, int& nb0) {
+        my_coords(u / SUBS, n0, w0, h0, nb0);
+        n0 += (u % SUBS) * SUB_N;
+      };
+      auto acquire_staging = [&](int u) {
+        const uint32_t rdy = smem_u32(&bar_stage_ready[u % NB]);
         if (RES) {
           int n0, w0, h0, nb0;
-          my_coords(j, n0, w0, h0, nb0);
+          unit_coords(u, n0, w0, h0, nb0);
           mbar_expect_tx(rdy, Cfg::OUT_BYTES);
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
-            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+          for (int q = 0; q < SUB_N / 64; ++q)
+            tma_load_4d(&maps.r, rdy, staging + (u % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
         } else {
           mbar_arrive(rdy);
         }
       };
-      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
-      for (int it = 0; it < my_tiles; ++it) {
-        if (LA == 0) {
-          // the staging buffer of tile it was last read by the store of tile it - NB
-          if (NB == 2) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-          acquire_staging(it);
-        }
+      for (int u = 0; u < LA && u < total_units; ++u) acquire_staging(u);
+      for (int u = 0; u < total_units; ++u) {
         {
           int n0, w0, h0, nb0;
-          my_coords(it, n0, w0, h0, nb0);
-          const int ob = it % NB;
-          mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+          unit_coords(u, n0, w0, h0, nb0);
+          const int ob = u % NB;
+          mbar_wait(smem_u32(&bar_out_ready[ob]), (u / NB) & 1);
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
+          for (int q = 0; q < SUB_N / 64; ++q)
             if (n0 + q * 64 < p.cout)
               tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
           tma_store_commit();
         }
-        if (LA > 0) {
-          const int j = it + LA;
-          if (j < my_tiles) {
-            asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
-            acquire_staging(j);
-          }
+        const int j = u + LA;   // its buffer was last read by the store of unit j - NB = u - 2; stores issued so far: <= u
+        if (j < total_units) {
+          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          acquire_staging(j);
         }
       }
       tma_store_wait_all();
@@ -648,6 +649,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     __syncwarp();
   } else if (warp >= 4) {
     // =========================== epilogue (per CTA, its own 128 rows) ===========================
+    constexpr int SUBS = Cfg::SUBS, SUB_N = Cfg::SUB_N;
     const int epi_tid = threadIdx.x - 128;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
@@ -655,7 +657,6 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     const int sw = row & 7;
     for (int it = 0; it < my_tiles; ++it) {
       const int b = it & 1;
-      const int ob = it % NB;
       const int pt0_ = pair + it * num_pairs;
       const int n0 = ((p.reverse ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
@@ -665,47 +666,53 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
       named_bar_sync(1, 128);
       mbar_wait_cluster(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
       tc_fence_after();
-      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
-      const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
       const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
-      for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
-        uint32_t v[32];
-        tmem_ld_32x32(acc + cc * 32, v);
-        tmem_ld_wait();
-        const uint32_t sub = stage_d + (cc >> 1) * (BLOCK_M * 128) + row_off;
+      for (int h = 0; h < SUBS; ++h) {
+        const int u = it * SUBS + h;
+        const int ob = u % NB;
+        mbar_wait(smem_u32(&bar_stage_ready[ob]), (u / NB) & 1);
+        const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
+#pragma unroll 1
+        for (int cc = 0; cc < SUB_N / 32; ++cc) {
+          const int col = h * SUB_N + cc * 32;
+          uint32_t v[32];
+          tmem_ld_32x32(acc + col, v);
+          tmem_ld_wait();
+          const uint32_t sub = stage_d + (cc >> 1) * (BLOCK_M * 128) + row_off;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int chunk = (cc & 1) * 4 + g;
-          const uint32_t addr = sub + ((chunk ^ sw) << 4);
-          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][cc * 32 + g * 8]);
-          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][cc * 32 + g * 8 + 4]);
-          float f[8];
-          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
-          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
-          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
-          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
-          if (RES) {
-            uint32_t r0, r1, r2, r3;
-            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
-            const float rr[8] = {bf16_lo(r0), bf16_hi(r0), bf16_lo(r1), bf16_hi(r1),
-                                 bf16_lo(r2), bf16_hi(r2), bf16_lo(r3), bf16_hi(r3)};
+          for (int g = 0; g < 4; ++g) {
+            const int chunk = (cc & 1) * 4 + g;
+            const uint32_t addr = sub + ((chunk ^ sw) << 4);
+            const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][col + g * 8]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b % NBIAS][col + g * 8 + 4]);
+            float f[8];
+            f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
+            f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
+            f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
+            f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+            if (RES) {
+              uint32_t r0, r1, r2, r3;
+              asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+              const float rr[8] = {bf16_lo(r0), bf16_hi(r0), bf16_lo(r1), bf16_hi(r1),
+                                   bf16_lo(r2), bf16_hi(r2), bf16_lo(r3), bf16_hi(r3)};
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = (RES == 2) ? act_t<ACT>(f[i]) + rr[i] : act_t<ACT>(f[i] + rr[i]);
-          } else {
+              for (int i = 0; i < 8; ++i) f[i] = (RES == 2) ? act_t<ACT>(f[i]) + rr[i] : act_t<ACT>(f[i] + rr[i]);
+            } else {
 #pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+              for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+            }
+            const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+            const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
+                         : "memory");
           }
-          const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
-          const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
-          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
-                       : "memory");
         }
+        fence_proxy_async_smem();
+        mbar_arrive(smem_u32(&bar_out_ready[ob]));        // this 128-column unit may be stored
       }
       tc_fence_before();
       mbar_arrive_leader(smem_u32(&bar_tmem_empty[b]));   // release the accumulator to the leader's MMA issuer
-      fence_proxy_async_smem();
-      mbar_arrive(smem_u32(&bar_out_ready[ob]));
       if (NBIAS == 1) named_bar_sync(1, 128);             // everyone is done reading the single bias buffer
     }
   }
