@@ -294,7 +294,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       uint32_t g = 0;  // k-block counter across all tiles of this CTA
       for (int it = 0; it < my_tiles; ++it) {
         const int tile0_ = blockIdx.x + it * gridDim.x;
-        const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
+        const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
         int n_tile, w0, h0, nb0;
         tile_coords(p, tile, n_tile, w0, h0, nb0);
         const int n0 = n_tile * BLOCK_N;
@@ -345,7 +345,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     if (lane == 0) {
       auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
         const int tile0_ = blockIdx.x + j * gridDim.x;
-        const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
+        const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
         const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
         if (RES) {
           int n_tile, w0, h0, nb0;
@@ -364,7 +364,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         // store of tile it, once its epilogue is done
         {
           const int tile0_ = blockIdx.x + it * gridDim.x;
-          const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
+          const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
           const int n0 = n_tile * BLOCK_N;
@@ -396,7 +396,248 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     const int sw = row & 7;
     for (int it = 0; it < my_tiles; ++it) {
       const int tile0_ = blockIdx.x + it * gridDim.x;
-      const int tile = p.reverse ? total_tiles - 1 - tile0_ : tile0_;
+      const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+      const int b = it & 1;
+      const int ob = it % NB;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      for (int i = epi_tid; i < BLOCK_N; i += 128) {
+        const int c = n0 + i;
+        bias_s[b][i] = (c < p.cout) ? p.bias[c] : 0.f;
+      }
+      named_bar_sync(1, 128);
+      mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
+      tc_fence_after();
+      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
+      const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
+      const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
+#pragma unroll 1
+      for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(acc + cc * 32, v);
+        tmem_ld_wait();
+        const uint32_t sub = stage_d + (cc >> 1) * (BLOCK_M * 128) + row_off;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int chunk = (cc & 1) * 4 + g;
+          const uint32_t addr = sub + ((chunk ^ sw) << 4);
+          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8]);
+          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8 + 4]);
+          float f[8];
+          f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
+          f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
+          f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
+          f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+          if (RES) {
+            uint32_t r0, r1, r2, r3;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+            const float rr[8] = {bf16_lo(r0), bf16_hi(r0), bf16_lo(r1), bf16_hi(r1),
+                                 bf16_lo(r2), bf16_hi(r2), bf16_lo(r3), bf16_hi(r3)};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = (RES == 2) ? act_t<ACT>(f[i]) + rr[i] : act_t<ACT>(f[i] + rr[i]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+          }
+          const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
+          const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
+                       : "memory");
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_tmem_empty[b]));   // accumulator may be overwritten by tile it+2
+      fence_proxy_async_smem();                    // staging writes -> visible to the TMA store
+      mbar_arrive(smem_u32(&bar_out_ready[ob]));
+    }
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<2 * BLOCK_N>(tmem_base);
+  }
+}
+
+// ================================================================================================================
+// 3x3 / stride 1 / pad 1 convolution with Cin = Cout = 64 (ResNet layer1 conv2) from a halo tile.
+// The generic kernel loads the 128-pixel input tile nine times (once per tap) and the weights once per tile, which makes a
+// 64-wide layer shared-memory-bandwidth bound at ~31 % of the tensor peak.  Here a tile is 8 x 16 pixels of one image; ONE TMA
+// box brings its 18-row x 16-pixel halo (64 channels, 128-byte swizzle, 2 KB per row) and the nine taps are nine shifted
+// *views* of it: descriptor start = halo + (dy*16 + dx)*128 B, SBO = 2048 B (one halo row per 8-pixel group), base_offset 0
+// (the hardware swizzles on absolute address bits, so shifted starts stay consistent with what TMA wrote).  The 9 x 64 x 64 weights stay resident in shared memory.
+// ================================================================================================================
+static constexpr int HALO_ROWS = 18, HALO_PITCH_PX = 16;
+static constexpr int HALO_BYTES = HALO_ROWS * HALO_PITCH_PX * 128;   // 36864
+static constexpr int HALO_W_BYTES = 9 * 64 * 128;                    // 73728: nine taps of [64 cout][64 cin] bf16
+
+struct HaloCfg {
+  static constexpr int OUT_BUFS = 4;
+  static constexpr int LOOKAHEAD = 2;
+  static constexpr int OUT_BYTES = BLOCK_M * 64 * 2;
+  static constexpr int SMEM_BYTES = HALO_W_BYTES + 2 * HALO_BYTES + OUT_BUFS * OUT_BYTES + 1024;
+};
+
+// K-major SWIZZLE_128B descriptor with explicit 8-row-group stride and base offset (start not 1024-byte aligned)
+__device__ __forceinline__ uint64_t umma_desc_sw128_ex(uint32_t smem_addr, uint32_t sbo_bytes, uint32_t base_offset) {
+  const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) | (base_offset << 17) | (2u << 29);
+  return (static_cast<uint64_t>(hi) << 32) | lo;
+}
+
+template <int RES, int ACT>
+__global__ void __launch_bounds__(PCONV_THREADS, 1)
+conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p, const int total_tiles) {
+  using Cfg = HaloCfg;
+  constexpr int BLOCK_N = 64;
+  constexpr int NB = Cfg::OUT_BUFS;
+  constexpr int LA = Cfg::LOOKAHEAD;
+
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_halo_full[2];
+  __shared__ __align__(8) uint64_t bar_halo_empty[2];
+  __shared__ __align__(8) uint64_t bar_w_full;
+  __shared__ __align__(8) uint64_t bar_tmem_full[2];
+  __shared__ __align__(8) uint64_t bar_tmem_empty[2];
+  __shared__ __align__(8) uint64_t bar_stage_ready[NB];
+  __shared__ __align__(8) uint64_t bar_out_ready[NB];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[2][BLOCK_N];
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t wres = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t halo = wres + HALO_W_BYTES;
+  const uint32_t staging = halo + 2 * HALO_BYTES;
+  const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&maps.a[0]);
+    tma_prefetch_desc(&maps.b);
+    tma_prefetch_desc(&maps.d);
+    if (RES) tma_prefetch_desc(&maps.r);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bar_halo_full[b]), 1);
+      mbar_init(smem_u32(&bar_halo_empty[b]), 1);
+      mbar_init(smem_u32(&bar_tmem_full[b]), 1);
+      mbar_init(smem_u32(&bar_tmem_empty[b]), 128);
+    }
+    mbar_init(smem_u32(&bar_w_full), 1);
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(smem_u32(&bar_stage_ready[b]), 1);
+      mbar_init(smem_u32(&bar_out_ready[b]), 128);
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc<2 * BLOCK_N>(smem_u32(&tmem_base_s));
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (warp == 0) {
+    // =========================== TMA producer: weights once, one halo box per tile ===========================
+    if (lane == 0) {
+      mbar_expect_tx(smem_u32(&bar_w_full), HALO_W_BYTES);
+      for (int t = 0; t < 9; ++t) tma_load_3d(&maps.b, smem_u32(&bar_w_full), wres + t * (64 * 128), 0, t, 0);
+      for (int it = 0; it < my_tiles; ++it) {
+        const int tile0_ = blockIdx.x + it * gridDim.x;
+        const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+        int n_tile, w0, h0, nb0;
+        tile_coords(p, tile, n_tile, w0, h0, nb0);
+        const int hb = it & 1;
+        mbar_wait(smem_u32(&bar_halo_empty[hb]), ((it >> 1) & 1) ^ 1);
+        const uint32_t full = smem_u32(&bar_halo_full[hb]);
+        mbar_expect_tx(full, HALO_BYTES);
+        tma_load_4d(&maps.a[0], full, halo + hb * HALO_BYTES, 0, w0 - 1, h0 - 1, nb0);   // box [64, 16, 18, 1]
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =========================== MMA issuer: nine shifted views of the halo ===========================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, BLOCK_N);
+      mbar_wait(smem_u32(&bar_w_full), 0);
+      for (int it = 0; it < my_tiles; ++it) {
+        const int b = it & 1, hb = it & 1;
+        mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it >> 1) & 1) ^ 1);
+        mbar_wait(smem_u32(&bar_halo_full[hb]), (it >> 1) & 1);
+        tc_fence_after();
+        const uint32_t acc = tmem_base + b * BLOCK_N;
+        const uint32_t hbase = halo + hb * HALO_BYTES;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const int dy = t / 3, dx = t % 3;
+          // base_offset stays 0: measured on B200, the 128-byte swizzle is applied to the absolute shared-memory address
+          // bits, so a start shifted by dx * 128 B sees exactly the pattern TMA wrote (base_offset = dx gives garbage).
+          const uint64_t adesc = umma_desc_sw128_ex(hbase + (dy * HALO_PITCH_PX + dx) * 128, HALO_PITCH_PX * 128, 0);
+          const uint64_t bdesc = umma_desc_sw128(wres + t * (64 * 128));
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / 16; ++k)
+            umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (t | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(smem_u32(&bar_halo_empty[hb]));
+        umma_commit(smem_u32(&bar_tmem_full[b]));
+      }
+    }
+    __syncwarp();
+  } else if (warp == 2) {
+    // =========================== DMA: residual prefetch (LA tiles ahead) + output stores ===========================
+    if (lane == 0) {
+      auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
+        const int tile0_ = blockIdx.x + j * gridDim.x;
+        const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+        const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
+        if (RES) {
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * BLOCK_N + q * 64,
+                        w0, h0, nb0);
+        } else {
+          mbar_arrive(rdy);
+        }
+      };
+      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
+      for (int it = 0; it < my_tiles; ++it) {
+        // store of tile it, once its epilogue is done
+        {
+          const int tile0_ = blockIdx.x + it * gridDim.x;
+          const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          const int n0 = n_tile * BLOCK_N;
+          const int ob = it % NB;
+          mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+#pragma unroll
+          for (int q = 0; q < BLOCK_N / 64; ++q)
+            if (n0 + q * 64 < p.cout)
+              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+          tma_store_commit();
+        }
+        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
+        // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
+        const int j = it + LA;
+        if (j < my_tiles) {
+          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          acquire_staging(j);
+        }
+      }
+      tma_store_wait_all();
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // =========================== epilogue ===========================
+    const int epi_tid = threadIdx.x - 128;  // 0..127
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t row_off = row * 128;
+    const int sw = row & 7;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int tile0_ = blockIdx.x + it * gridDim.x;
+      const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
       const int b = it & 1;
       const int ob = it % NB;
       const int n0 = (tile % p.n_tiles) * BLOCK_N;
@@ -516,7 +757,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
   // pair tile -> this CTA's 128-pixel m-tile and the shared n-tile
   auto my_coords = [&](int it, int& n0, int& w0, int& h0, int& nb0) {
     const int pt0 = pair + it * num_pairs;
-    const int pt = p.reverse ? total_pair_tiles - 1 - pt0 : pt0;
+    const int pt = (p.reverse & 1) ? total_pair_tiles - 1 - pt0 : pt0;
     const int n_tile = pt % p.n_tiles;
     int m = (pt / p.n_tiles) * 2 + static_cast<int>(rank);
     if (m >= m_tiles) m = m_tiles;            // phantom tile of an odd tail: coordinates past the tensor (TMA clips)
@@ -658,7 +899,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     for (int it = 0; it < my_tiles; ++it) {
       const int b = it & 1;
       const int pt0_ = pair + it * num_pairs;
-      const int n0 = ((p.reverse ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
+      const int n0 = (((p.reverse & 1) ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
         const int c = n0 + i;
         bias_s[b % NBIAS][i] = (c < p.cout) ? p.bias[c] : 0.f;
@@ -794,6 +1035,16 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     if (res_mode == 0) { two_cta = false; block_n = 128; }
     else if (res_mode == 1) block_n = 128;
   }
+  static int use_halo = -1;
+  if (use_halo < 0) {
+    const char* e = getenv("B200_CONV_HALO");
+    use_halo = (e && e[0] == '0') ? 0 : 1;
+  }
+  // halo kernel: 3x3/s1/p1, Cin = Cout = 64, 8x16-pixel tiles with little padding waste
+  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C == 64 && out.C == 64 &&
+                    in.W % 8 == 0 && ((in.H + 15) / 16 * 16) * 100 <= in.H * 115;
+  if (halo) { two_cta = false; block_n = 64; }
+  L->halo = halo;
   L->block_n = block_n;
   L->two_cta = two_cta;
   p.n_tiles = (out.C + block_n - 1) / block_n;
@@ -806,6 +1057,13 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     p.tw = 128; p.th = 1; p.tn = 1;
     B200_TRY(encode_act_view(&L->maps.a[0], in.base, in.C, oW, 1, 1, ips, ips * oW, ips * oW, 128, 1, 1));
     p.tap_map[0] = 0; p.tap_dx[0] = 0; p.tap_dy[0] = 0;
+  } else if (halo) {
+    p.tw = 8; p.th = 16; p.tn = 1;
+    const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
+    const uint64_t dims[4] = {uint64_t(in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {ips, rowb, imgb};
+    const uint32_t box[4] = {64u, uint32_t(HALO_PITCH_PX), uint32_t(HALO_ROWS), 1u};
+    B200_TRY(encode_tmap(&L->maps.a[0], in.base, 4, dims, str, box, SWZ_128B));
   } else {
     pick_tile(oW, oH, oN, &p.tw, &p.th, &p.tn);
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
@@ -965,6 +1223,34 @@ static int launch_2cta_res(const ConvLaunch& l, cudaStream_t stream) {
   return launch_2cta_act<BLOCK_N, 2>(l, stream);
 }
 
+template <int RES, int ACT>
+static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<RES, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      HaloCfg::SMEM_BYTES));
+    configured[dev & 63] = true;
+  }
+  const int total = static_cast<int>(l.grid);
+  const int ctas = total < device_sm_count() ? total : device_sm_count();
+  conv3x3_halo_kernel<RES, ACT><<<ctas, PCONV_THREADS, HaloCfg::SMEM_BYTES, stream>>>(l.maps, l.p, total);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+template <int RES>
+static int launch_halo_act(const ConvLaunch& l, cudaStream_t stream) {
+  switch (l.p.act) {
+    case ACT_NONE: return launch_halo_t<RES, ACT_NONE>(l, stream);
+    case ACT_RELU: return launch_halo_t<RES, ACT_RELU>(l, stream);
+    case ACT_SILU: return launch_halo_t<RES, ACT_SILU>(l, stream);
+    case ACT_SIGMOID: return launch_halo_t<RES, ACT_SIGMOID>(l, stream);
+  }
+  return fail(B200_ERR_INVALID, "conv: unknown activation");
+}
+
 template <int BLOCK_N>
 static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
   static bool configured[64] = {};
@@ -981,6 +1267,11 @@ static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
 }
 
 int conv_launch(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.halo) {
+    if (l.p.has_res == 0) return launch_halo_act<0>(l, stream);
+    if (l.p.has_res == 1) return launch_halo_act<1>(l, stream);
+    return launch_halo_act<2>(l, stream);
+  }
   if (l.two_cta) {
     if (l.block_n == 256) return launch_2cta_res<256>(l, stream);
     return launch_2cta_res<128>(l, stream);

@@ -38,7 +38,8 @@ struct ConvLaunch {
   ConvParams p;
   unsigned grid = 0;
   int block_n = 0;
-  bool two_cta = false;  // CTA-pair kernel (tcgen05.mma.cta_group::2)
+  bool two_cta = false;
+  bool halo = false;     // 3x3 halo-tile kernel (Cin = Cout = 64)  // CTA-pair kernel (tcgen05.mma.cta_group::2)
   double flops = 0;  // 2*M*N*K (useful, un-padded)
 };
 
