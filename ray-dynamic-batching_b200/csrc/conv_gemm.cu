@@ -205,10 +205,12 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 // ================================================================================================================
 static constexpr int PCONV_THREADS = 256;
 
-template <int BLOCK_N>
+// Without a residual the staging ring only has to cover the store of the previous tile (2 buffers); the shared memory that
+// frees goes into a deeper A/B ring, which is what the HBM-bound layers need (bytes in flight per SM ~ latency x bandwidth).
+template <int BLOCK_N, int RES>
 struct PConvCfg {
-  static constexpr int STAGES = BLOCK_N == 64 ? 4 : 3;      // A/B ring
-  static constexpr int OUT_BUFS = BLOCK_N == 64 ? 6 : 4;    // output / residual staging ring
+  static constexpr int STAGES = RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 8 : 5);      // A/B ring
+  static constexpr int OUT_BUFS = RES ? (BLOCK_N == 64 ? 6 : 4) : 2;                           // output / residual staging ring
   static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -240,7 +242,7 @@ template <int BLOCK_N, int RES, int ACT>
 __global__ void __launch_bounds__(PCONV_THREADS, 1)
 conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
                             const int total_tiles) {
-  using Cfg = PConvCfg<BLOCK_N>;
+  using Cfg = PConvCfg<BLOCK_N, RES>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int NB = Cfg::OUT_BUFS;
   constexpr int LA = Cfg::LOOKAHEAD;
@@ -361,6 +363,11 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       };
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
+        if (LA == 0) {
+          // no prefetch distance: staging[it % NB] was last read by the store of tile it - NB; stores issued so far: <= it - 1
+          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          acquire_staging(it);
+        }
         // store of tile it, once its epilogue is done
         {
           const int tile0_ = blockIdx.x + it * gridDim.x;
@@ -379,7 +386,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
         // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
         const int j = it + LA;
-        if (j < my_tiles) {
+        if (LA > 0 && j < my_tiles) {
           asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
@@ -602,6 +609,11 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       };
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
+        if (LA == 0) {
+          // no prefetch distance: staging[it % NB] was last read by the store of tile it - NB; stores issued so far: <= it - 1
+          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          acquire_staging(it);
+        }
         // store of tile it, once its epilogue is done
         {
           const int tile0_ = blockIdx.x + it * gridDim.x;
@@ -620,7 +632,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
         // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
         const int j = it + LA;
-        if (j < my_tiles) {
+        if (LA > 0 && j < my_tiles) {
           asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
@@ -709,12 +721,12 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
 // `full` barrier; tcgen05.commit multicasts `empty` / `tmem_full` arrivals to both CTAs; both epilogues release the
 // accumulator on the leader's `tmem_empty` barrier (count 256).
 // ================================================================================================================
-template <int BLOCK_N>
+template <int BLOCK_N, int RES>
 struct P2ConvCfg {
-  static constexpr int STAGES = BLOCK_N == 256 ? 3 : 4;
+  static constexpr int STAGES = RES ? (BLOCK_N == 256 ? 3 : 4) : (BLOCK_N == 256 ? 5 : 6);
   static constexpr int SUB_N = 128;                  // the epilogue / residual / store pipeline works on 128-column units
   static constexpr int SUBS = BLOCK_N / SUB_N;
-  static constexpr int OUT_BUFS = 4;
+  static constexpr int OUT_BUFS = RES ? 4 : 2;
   static constexpr int LOOKAHEAD = OUT_BUFS - 2;     // units the residual prefetch runs ahead
   static constexpr int B_STAGE_BYTES = (BLOCK_N / 2) * BLOCK_K * 2;  // this CTA's half of the weight tile
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -728,7 +740,7 @@ template <int BLOCK_N, int RES, int ACT>
 __global__ void __launch_bounds__(PCONV_THREADS, 1)
 conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
                       const int total_pair_tiles, const int m_tiles) {
-  using Cfg = P2ConvCfg<BLOCK_N>;
+  using Cfg = P2ConvCfg<BLOCK_N, RES>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int NB = Cfg::OUT_BUFS;
   constexpr int LA = Cfg::LOOKAHEAD;
@@ -868,6 +880,10 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
       };
       for (int u = 0; u < LA && u < total_units; ++u) acquire_staging(u);
       for (int u = 0; u < total_units; ++u) {
+        if (LA == 0) {
+          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          acquire_staging(u);
+        }
         {
           int n0, w0, h0, nb0;
           unit_coords(u, n0, w0, h0, nb0);
@@ -880,7 +896,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
           tma_store_commit();
         }
         const int j = u + LA;   // its buffer was last read by the store of unit j - NB = u - 2; stores issued so far: <= u
-        if (j < total_units) {
+        if (LA > 0 && j < total_units) {
           asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
@@ -1146,13 +1162,13 @@ static int launch_persistent_t(const ConvLaunch& l, cudaStream_t stream) {
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
     B200_CUDA_OK(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, PConvCfg<BLOCK_N>::SMEM_BYTES));
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, PConvCfg<BLOCK_N, RES>::SMEM_BYTES));
     configured[dev & 63] = true;
   }
   const int total = static_cast<int>(l.grid);
   const int ctas = total < device_sm_count() ? total : device_sm_count();
   conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>
-      <<<ctas, PCONV_THREADS, PConvCfg<BLOCK_N>::SMEM_BYTES, stream>>>(l.maps, l.p, total);
+      <<<ctas, PCONV_THREADS, PConvCfg<BLOCK_N, RES>::SMEM_BYTES, stream>>>(l.maps, l.p, total);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }
@@ -1182,7 +1198,7 @@ static int launch_2cta_t(const ConvLaunch& l, cudaStream_t stream) {
   B200_CUDA_OK(cudaGetDevice(&dev));
   auto kern = conv_gemm_2cta_kernel<BLOCK_N, RES, ACT>;
   if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P2ConvCfg<BLOCK_N>::SMEM_BYTES));
+    B200_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, P2ConvCfg<BLOCK_N, RES>::SMEM_BYTES));
     configured[dev & 63] = true;
   }
   const int m_tiles = l.p.tiles_w * l.p.tiles_h * l.p.tiles_n;
@@ -1192,7 +1208,7 @@ static int launch_2cta_t(const ConvLaunch& l, cudaStream_t stream) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
   cfg.blockDim = dim3(PCONV_THREADS);
-  cfg.dynamicSmemBytes = P2ConvCfg<BLOCK_N>::SMEM_BYTES;
+  cfg.dynamicSmemBytes = P2ConvCfg<BLOCK_N, RES>::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
