@@ -19,10 +19,15 @@
 namespace b200 {
 
 static constexpr int SR_THREADS = 256;
+static constexpr int SR2_THREADS = 384;   // stem_row_kernel: two epilogue warpgroups (warps 4-7 and 8-11)
 static constexpr int SR_STAGES = 4;
-static constexpr int SR_PAIRS = 132;                 // staged pixel pairs per input row: 2*128 + 8 pixels
-static constexpr int SR_ROW_BYTES = SR_PAIRS * 16;   // 2112
-static constexpr int SR_STAGE_BYTES = 116 * 128;     // 7 rows (14784 B) rounded up to a multiple of 128
+// An input row is staged as 18 groups of 16 pixels (128 B each): TMA moves whole 128-byte lines (a box with a 16-byte inner
+// dimension costs 8x more TMA work).  The box starts 16 pixels left of the tile's first *output* pixel pair, i.e. 12 pixels
+// (96 B) before the first window, so descriptors start at +96.
+static constexpr int SR_GROUPS = 18;
+static constexpr int SR_ROW_BYTES = SR_GROUPS * 128; // 2304
+static constexpr int SR_LEAD_BYTES = 96;
+static constexpr int SR_STAGE_BYTES = 7 * SR_ROW_BYTES;   // 16128 = 126 * 128
 static constexpr int SR_W_BYTES = 7 * 4 * 64 * 16;   // weights: [kernel row][k chunk][cout][8 bf16] = 28672 B
 static constexpr int SR_OUT_BYTES = 128 * 128;       // one staged output tile (128 pixels x 64 channels bf16)
 
@@ -41,7 +46,7 @@ struct StemRowParams {
   int total_tiles;       // N * Ho * segs
 };
 
-__global__ void __launch_bounds__(SR_THREADS, 1)
+__global__ void __launch_bounds__(SR2_THREADS, 1)
 stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
                 const __grid_constant__ StemRowParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -59,7 +64,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   const int my_tiles = max(0, min(per_cta, p.total_tiles - tile0));
 
   // weights -> smem (already in the descriptor layout), bias
-  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SR_THREADS) {
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SR2_THREADS) {
     const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
@@ -102,8 +107,8 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
         mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_full[s]);
         mbar_expect_tx(full, 7 * SR_ROW_BYTES);
-        // box [8 (pixel pair), 132 pairs, 7 rows, 1 image] at (0, ow0 - 2, 2*oh - 3, n); outside the image -> zeros
-        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 - 2, 2 * oh - 3, n_oh / p.Ho);
+        // box [64 (16 pixels), 18 groups, 7 rows, 1 image] at (0, ow0/8 - 1, 2*oh - 3, n); outside the image -> zeros
+        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - 3, n_oh / p.Ho);
       }
     }
     __syncwarp();
@@ -121,7 +126,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
 #pragma unroll
           for (int kk = 0; kk < 2; ++kk) {
             // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride 1024, 8-row stride 128
-            const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + kk * 32, 16, 128);
+            const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
             const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
             umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
           }
@@ -132,16 +137,19 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     }
     __syncwarp();
   } else if (warp >= 4) {
-    const int epi_tid = threadIdx.x - 128;
+    // two epilogue warpgroups: group g drains accumulator g of every second tile, so the per-tile latency chain
+    // (TMEM load -> convert -> smem -> store) of one tile overlaps the next tile's
+    const int wg = (warp - 4) >> 2;              // 0 or 1
+    const int epi_tid = (threadIdx.x - 128) & 127;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int sw = row & 7;
-    for (int it = 0; it < my_tiles; ++it) {
-      const int b = it & 1;
+    for (int it = wg; it < my_tiles; it += 2) {
+      const int b = wg;
       int n_oh, oh, ow0;
       tile_coords(it, n_oh, oh, ow0);
-      if (epi_tid == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");   // store of tile it-2 has read staging[b]
-      named_bar_sync(1, 128);
+      if (epi_tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // this group's previous store has read staging[b]
+      named_bar_sync(1 + 2 * wg, 128);
       mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
       tc_fence_after();
       const uint32_t dst_row = stage_out + b * SR_OUT_BYTES + row * 128;
@@ -167,7 +175,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
       tc_fence_before();
       mbar_arrive(smem_u32(&bar_t_empty[b]));
       fence_proxy_async_smem();
-      named_bar_sync(2, 128);
+      named_bar_sync(2 + 2 * wg, 128);
       if (epi_tid == 0) {
         // 3-D store [64 ch, 128 pixels, 1 row] at (0, ow0, n*Ho + oh): pixels past Wo are clipped
         asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
@@ -211,10 +219,14 @@ __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
   return *reinterpret_cast<uint32_t*>(&m);
 }
 
-__global__ void __launch_bounds__(SR_THREADS, 1)
+static constexpr int SP_THREADS = 384;   // warps 0: TMA, 1: MMA, 4-7: accumulator drain, 8-11: pooling
+static constexpr int SP_RING = 4;        // stem rows kept in shared memory
+
+__global__ void __launch_bounds__(SP_THREADS, 1)
 stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ StemPoolParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ __align__(8) uint64_t bar_row_ready[SP_RING], bar_row_free[SP_RING];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[64];
 
@@ -222,13 +234,13 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring = base;
   const uint32_t wsm = ring + SR_STAGES * SR_STAGE_BYTES + 256;
-  const uint32_t rows3 = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // three stem rows [128 px][128 B], chunk-swizzled
+  const uint32_t rows = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // SP_RING stem rows [128 px][128 B], chunk-swizzled
   const int per_cta = (p.total_units + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
   const int unit0 = static_cast<int>(blockIdx.x) * per_cta;
   const int my_units = max(0, min(per_cta, p.total_units - unit0));
   const int Hp = p.Ho >> 1, Wp = p.Wo >> 1;
 
-  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SR_THREADS) {
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SP_THREADS) {
     const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
@@ -242,6 +254,10 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bar_t_full[b]), 1);
       mbar_init(smem_u32(&bar_t_empty[b]), 128);
+    }
+    for (int r = 0; r < SP_RING; ++r) {
+      mbar_init(smem_u32(&bar_row_ready[r]), 128);
+      mbar_init(smem_u32(&bar_row_free[r]), 128);
     }
     fence_barrier_init();
   } else if (warp == 1) {
@@ -273,7 +289,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
           mbar_expect_tx(full, 7 * SR_ROW_BYTES);
-          tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -2, 2 * y - 3, n);
+          tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - 3, n);
         }
       }
     }
@@ -295,7 +311,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           for (int r = 0; r < 7; ++r) {
 #pragma unroll
             for (int kk = 0; kk < 2; ++kk) {
-              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + kk * 32, 16, 128);
+              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
               const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
               umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
             }
@@ -306,20 +322,21 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
-    const int epi_tid = threadIdx.x - 128;
+  } else if (warp >= 4 && warp < 8) {
+    // =========================== accumulator drain: TMEM -> +bias -> ReLU -> bf16 -> row ring ===========================
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;     // stem pixel (ow) owned by this thread
     const int sw = row & 7;
-    int it = 0;
+    int it = 0;                               // stem rows processed by this CTA (ring slot = it % SP_RING)
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
-        const int b = it & 1;
+        const int b = it & 1, slot = it % SP_RING;
+        mbar_wait(smem_u32(&bar_row_free[slot]), ((it / SP_RING) & 1) ^ 1);   // pooling is done with the row that lived here
         mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
         tc_fence_after();
-        const uint32_t dst_row = rows3 + (y % 3) * SR_OUT_BYTES + row * 128;
+        const uint32_t dst_row = rows + slot * SR_OUT_BYTES + row * 128;
         const uint32_t acc = tmem_base + b * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
@@ -341,19 +358,31 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         }
         tc_fence_before();
         mbar_arrive(smem_u32(&bar_t_empty[b]));
-        named_bar_sync(1, 128);                       // stem row y is complete in shared memory
-        if ((y & 1) && (y >> 1) >= ph0) {              // y = 2*ph + 1: pooled row ph over stem rows y-2, y-1, y (the band's
-                                                       // first row 2*ph0-1 is only the top halo of pooled row ph0)
+        mbar_arrive(smem_u32(&bar_row_ready[slot]));
+      }
+    }
+  } else if (warp >= 8) {
+    // =========================== pooling warps: 3x3 / stride 2 max over the row ring, coalesced stores ===========================
+    const int ptid = threadIdx.x - 256;       // 0..127
+    int it = 0;
+    for (int u = unit0; u < unit0 + my_units; ++u) {
+      int n, ph0, ph1, y_lo, y_hi;
+      unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+      for (int y = y_lo; y <= y_hi; ++y, ++it) {
+        const int slot = it % SP_RING;
+        mbar_wait(smem_u32(&bar_row_ready[slot]), (it / SP_RING) & 1);
+        const bool pool = (y & 1) && (y >> 1) >= ph0;     // y = 2*ph + 1 completes pooled row ph (rows y-2, y-1, y)
+        if (pool) {
           const int ph = y >> 1;
           uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
-          for (int item = epi_tid; item < Wp * 8; item += 128) {
+          for (int item = ptid; item < Wp * 8; item += 128) {
             const int pw = item >> 3, chunk = item & 7;
             uint4 m = make_uint4(0, 0, 0, 0);          // post-ReLU values are >= 0, so 0 is the identity of max
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy) {
               const int yy = y - 2 + dy;
-              if (yy < 0) continue;
-              const uint32_t rbase = rows3 + (yy % 3) * SR_OUT_BYTES;
+              if (yy < y_lo) continue;                 // above the image (or above the band's halo row: never happens)
+              const uint32_t rbase = rows + ((it - 2 + dy) % SP_RING) * SR_OUT_BYTES;
 #pragma unroll
               for (int dx = 0; dx < 3; ++dx) {
                 const int xx = 2 * pw - 1 + dx;
@@ -368,8 +397,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
             }
             *reinterpret_cast<uint4*>(orow + static_cast<size_t>(pw) * p.out_ps + chunk * 8) = m;
           }
+          // rows y-2 (top, second and last use) and y-1 (middle, only use) are no longer needed
+          if (y - 2 >= y_lo) mbar_arrive(smem_u32(&bar_row_free[(it - 2) % SP_RING]));
+          mbar_arrive(smem_u32(&bar_row_free[(it - 1) % SP_RING]));
         }
-        named_bar_sync(2, 128);                       // pooling reads are done before the oldest row is overwritten
+        if (y == y_hi) mbar_arrive(smem_u32(&bar_row_free[slot]));   // last row of the band: nobody below will need it
       }
     }
   }
@@ -383,16 +415,16 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
 
 // Fused conv1 + bn1 + relu + maxpool(3,2,1).  `out` is the pooled tensor [N][Ho/2][Wo/2][64].
 int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
-  if (in.C != 4 || in.pix_stride != 4 || in.W % 2) return fail(B200_ERR_INVALID, "stem_pool: input must be NHWC4 with even width");
+  if (in.C != 4 || in.pix_stride != 4 || in.W % 16) return fail(B200_ERR_INVALID, "stem_pool: input must be NHWC4 with width a multiple of 16");
   const int Ho = (in.H + 6 - 7) / 2 + 1, Wo = (in.W + 6 - 7) / 2 + 1;
   if (Wo > 128 || (Ho & 1) || (Wo & 1)) return fail(B200_ERR_INVALID, "stem_pool: needs stem width <= 128 and even stem size");
   if (out.C != 64 || out.pix_stride % 8 || out.H != Ho / 2 || out.W != Wo / 2 || out.N != in.N)
     return fail(B200_ERR_INVALID, "stem_pool: output geometry mismatch");
   CUtensorMap in_map;
   {
-    const uint64_t dims[4] = {8, uint64_t(in.W / 2), uint64_t(in.H), uint64_t(in.N)};
-    const uint64_t str[3] = {16, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
-    const uint32_t box[4] = {8, uint32_t(SR_PAIRS), 7, 1};
+    const uint64_t dims[4] = {64, uint64_t(in.W / 16), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
+    const uint32_t box[4] = {64, uint32_t(SR_GROUPS), 7, 1};
     B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
   }
   StemPoolParams p;
@@ -403,7 +435,7 @@ int stem_pool_launch(const View& in, const View& out, const void* w, const float
   p.Ho = Ho; p.Wo = Wo;
   p.bands = (Ho / 2 + SP_BAND - 1) / SP_BAND;
   p.total_units = in.N * p.bands;
-  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + 3 * SR_OUT_BYTES + 1024;
+  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -412,7 +444,7 @@ int stem_pool_launch(const View& in, const View& out, const void* w, const float
     configured[dev & 63] = true;
   }
   const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
-  stem_pool_kernel<<<ctas, SR_THREADS, smem, stream>>>(in_map, p);
+  stem_pool_kernel<<<ctas, SP_THREADS, smem, stream>>>(in_map, p);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }
@@ -422,15 +454,15 @@ int stem_row_weight_bytes() { return SR_W_BYTES; }
 // weights: bf16 smem image [kernel row 7][k chunk 4][cout 64][8]: element e of chunk k = window pixel 2k + e/4 (= kernel
 // column + 1), channel e%4; zero for window pixel 0 and channel 3.  bias fp32 [64].
 int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
-  if (in.C != 4 || in.pix_stride != 4 || in.W % 2) return fail(B200_ERR_INVALID, "stem_row: input must be NHWC4 with even width");
+  if (in.C != 4 || in.pix_stride != 4 || in.W % 16) return fail(B200_ERR_INVALID, "stem_row: input must be NHWC4 with width a multiple of 16");
   if (out.C != 64 || out.pix_stride % 8) return fail(B200_ERR_INVALID, "stem_row: cout must be 64");
   if ((in.H + 6 - 7) / 2 + 1 != out.H || (in.W + 6 - 7) / 2 + 1 != out.W || in.N != out.N)
     return fail(B200_ERR_INVALID, "stem_row: output geometry mismatch");
   CUtensorMap in_map, out_map;
   {
-    const uint64_t dims[4] = {8, uint64_t(in.W / 2), uint64_t(in.H), uint64_t(in.N)};
-    const uint64_t str[3] = {16, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
-    const uint32_t box[4] = {8, uint32_t(SR_PAIRS), 7, 1};
+    const uint64_t dims[4] = {64, uint64_t(in.W / 16), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
+    const uint32_t box[4] = {64, uint32_t(SR_GROUPS), 7, 1};
     B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
   }
   {
@@ -455,7 +487,7 @@ int stem_row_launch(const View& in, const View& out, const void* w, const float*
     configured[dev & 63] = true;
   }
   const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
-  stem_row_kernel<<<ctas, SR_THREADS, smem, stream>>>(in_map, out_map, p);
+  stem_row_kernel<<<ctas, SR2_THREADS, smem, stream>>>(in_map, out_map, p);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }

@@ -212,7 +212,7 @@ class PlanBuilder:
         assert cin == 3 and x.buf == self.in_buf
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
         out = self.new_act(ho, wo, cout)
-        if self.toeplitz_stem and (k, stride, pad, cout, act) == (7, 2, 3, 64, ACT_RELU) and x.w % 2 == 0:
+        if self.toeplitz_stem and (k, stride, pad, cout, act) == (7, 2, 3, 64, ACT_RELU) and x.w % 16 == 0:
             wb, bb = stem_row_weights(weight, bias)
             w_off = self.add_weights(wb)
             b_off = self.add_weights(bb)
@@ -399,7 +399,7 @@ def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
     pb = PlanBuilder("resnet50", in_hw[0], in_hw[1])
     w, b = fold_bn(model.conv1, model.bn1)
     hs, ws = (in_hw[0] - 1) // 2 + 1, (in_hw[1] - 1) // 2 + 1
-    if pb.fuse_stem_pool and ws <= 128 and hs % 2 == 0 and ws % 2 == 0 and in_hw[1] % 2 == 0:
+    if pb.fuse_stem_pool and ws <= 128 and hs % 2 == 0 and ws % 2 == 0 and in_hw[1] % 16 == 0:
         x = pb.stem_pool(pb.input(), w, b, name="conv1+maxpool")
     else:
         x = pb.stem(pb.input(), w, b, 2, 3, ACT_RELU, name="conv1")
