@@ -721,6 +721,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
 // `full` barrier; tcgen05.commit multicasts `empty` / `tmem_full` arrivals to both CTAs; both epilogues release the
 // accumulator on the leader's `tmem_empty` barrier (count 256).
 // ================================================================================================================
+static constexpr int P2CONV_THREADS = 384;   // warps 0-2: TMA / MMA / DMA, 4-7 and 8-11: one epilogue warpgroup per 128 columns
+
 template <int BLOCK_N, int RES>
 struct P2ConvCfg {
   static constexpr int STAGES = RES ? (BLOCK_N == 256 ? 3 : 4) : (BLOCK_N == 256 ? 5 : 6);
@@ -737,7 +739,7 @@ struct P2ConvCfg {
 };
 
 template <int BLOCK_N, int RES, int ACT>
-__global__ void __launch_bounds__(PCONV_THREADS, 1)
+__global__ void __launch_bounds__(P2CONV_THREADS, 1)
 conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
                       const int total_pair_tiles, const int m_tiles) {
   using Cfg = P2ConvCfg<BLOCK_N, RES>;
@@ -792,7 +794,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bar_tmem_full[b]), 1);
-      mbar_init(smem_u32(&bar_tmem_empty[b]), 256);   // 128 epilogue threads of each CTA (used on the leader only)
+      mbar_init(smem_u32(&bar_tmem_empty[b]), 2 * 128 * Cfg::SUBS);   // every epilogue thread of both CTAs (leader's copy is used)
     }
     for (int b = 0; b < NB; ++b) {
       mbar_init(smem_u32(&bar_stage_ready[b]), 1);
@@ -906,26 +908,28 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     __syncwarp();
   } else if (warp >= 4) {
     // =========================== epilogue (per CTA, its own 128 rows) ===========================
+    // One warpgroup per 128-column unit: with N = 256 the two halves of a tile are drained concurrently (warps 4-7 and
+    // 8-11 both cover TMEM lane quarters 0-3), which keeps short-K layers MMA-bound instead of epilogue-bound.
     constexpr int SUBS = Cfg::SUBS, SUB_N = Cfg::SUB_N;
-    const int epi_tid = threadIdx.x - 128;
+    const int h = (warp - 4) >> 2;
+    const int epi_tid = (threadIdx.x - 128) & 127;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t row_off = row * 128;
     const int sw = row & 7;
-    for (int it = 0; it < my_tiles; ++it) {
+    for (int it = 0; it < my_tiles && h < SUBS; ++it) {
       const int b = it & 1;
       const int pt0_ = pair + it * num_pairs;
       const int n0 = (((p.reverse & 1) ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
-      for (int i = epi_tid; i < BLOCK_N; i += 128) {
-        const int c = n0 + i;
-        bias_s[b % NBIAS][i] = (c < p.cout) ? p.bias[c] : 0.f;
+      for (int i = epi_tid; i < SUB_N; i += 128) {
+        const int c = n0 + h * SUB_N + i;
+        bias_s[b % NBIAS][h * SUB_N + i] = (c < p.cout) ? p.bias[c] : 0.f;
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1 + h, 128);
       mbar_wait_cluster(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
-#pragma unroll 1
-      for (int h = 0; h < SUBS; ++h) {
+      {
         const int u = it * SUBS + h;
         const int ob = u % NB;
         mbar_wait(smem_u32(&bar_stage_ready[ob]), (u / NB) & 1);
@@ -970,7 +974,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
       }
       tc_fence_before();
       mbar_arrive_leader(smem_u32(&bar_tmem_empty[b]));   // release the accumulator to the leader's MMA issuer
-      if (NBIAS == 1) named_bar_sync(1, 128);             // everyone is done reading the single bias buffer
+      if (NBIAS == 1) named_bar_sync(1 + h, 128);         // this group is done reading its half of the single bias buffer
     }
   }
 
@@ -1043,12 +1047,13 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   static int res_mode = -1;   // residual layers: 0 single CTA, 1 CTA pair N=128 (deep residual prefetch), 2 CTA pair N=256
   if (res_mode < 0) {
     const char* e = getenv("B200_2CTA_RES_MODE");
-    res_mode = e ? atoi(e) : 0;
+    res_mode = e ? atoi(e) : 2;
   }
   bool two_cta = use_2cta() && out.C >= 256 && k_total >= 256;
   int block_n = two_cta ? 256 : (out.C <= 64 ? 64 : 128);
   if (two_cta && has_res) {
-    if (res_mode == 0) { two_cta = false; block_n = 128; }
+    // residual layers: CTA pairs pay off only with enough K per tile to hide the residual prefetch (layer4 conv3: K = 512)
+    if (res_mode == 0 || (res_mode == 2 && k_total < 512)) { two_cta = false; block_n = 128; }
     else if (res_mode == 1) block_n = 128;
   }
   static int use_halo = -1;
@@ -1207,7 +1212,7 @@ static int launch_2cta_t(const ConvLaunch& l, cudaStream_t stream) {
   const int pairs = pair_tiles < max_pairs ? pair_tiles : max_pairs;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * pairs);
-  cfg.blockDim = dim3(PCONV_THREADS);
+  cfg.blockDim = dim3(P2CONV_THREADS);
   cfg.dynamicSmemBytes = P2ConvCfg<BLOCK_N, RES>::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
