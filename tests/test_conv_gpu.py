@@ -54,6 +54,11 @@ CASES = [
     (1, 7, 7, 512, 512, 1, 1, 0, "relu", False),     # CTA-pair kernel with a single (odd) m-tile: phantom peer tile
     (5, 14, 14, 1024, 256, 1, 1, 0, "relu", False),  # CTA-pair, 16 k-blocks, odd number of m-tiles (980 px -> 8 tiles) 
     (3, 28, 28, 128, 128, 3, 1, 1, "silu", True),    # CTA-pair N=128 with post-activation residual geometry (3x3)
+    (2, 7, 7, 512, 2048, 1, 1, 0, "relu", True),     # CTA pair + residual, K = 512 (layer4 conv3): two epilogue warpgroups
+    (3, 64, 64, 64, 64, 3, 1, 1, "silu", True),      # halo-tile 3x3 kernel with residual, H a multiple of 16
+    (1, 16, 24, 64, 64, 3, 1, 1, "none", False),     # halo-tile kernel, one tile high, three wide
+    (5, 56, 56, 64, 64, 3, 1, 1, "relu", False),     # halo-tile kernel, odd batch (tile count not a multiple of anything)
+    (2, 20, 20, 64, 64, 3, 1, 1, "relu", False),     # W not a multiple of 8 / H waste too high: generic kernel
 ]
 
 
