@@ -1049,8 +1049,14 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const char* e = getenv("B200_2CTA_RES_MODE");
     res_mode = e ? atoi(e) : 2;
   }
-  bool two_cta = use_2cta() && out.C >= 256 && k_total >= 256;
-  int block_n = two_cta ? 256 : (out.C <= 64 ? 64 : 128);
+  static int pair128_min_k = -1;   // Cout in [128, 256): CTA pairs with N = 128 from this K on (0 = never)
+  if (pair128_min_k < 0) {
+    const char* e = getenv("B200_PAIR128_MIN_K");
+    pair128_min_k = e ? atoi(e) : 0;
+  }
+  bool two_cta = use_2cta() && ((out.C >= 256 && k_total >= 256) ||
+                                (out.C >= 128 && pair128_min_k > 0 && k_total >= pair128_min_k));
+  int block_n = two_cta ? (out.C >= 256 ? 256 : 128) : (out.C <= 64 ? 64 : 128);
   if (two_cta && has_res) {
     // residual layers: CTA pairs pay off only with enough K per tile to hide the residual prefetch (layer4 conv3: K = 512)
     if (res_mode == 0 || (res_mode == 2 && k_total < 512)) { two_cta = false; block_n = 128; }
