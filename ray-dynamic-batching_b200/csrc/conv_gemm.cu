@@ -232,8 +232,8 @@ __device__ __forceinline__ void tile_coords(const ConvParams& p, int tile, int& 
 template <int ACT>
 __device__ __forceinline__ float act_t(float x) {
   if (ACT == ACT_RELU) return fmaxf(x, 0.f);
-  if (ACT == ACT_SILU) return x / (1.f + __expf(-x));
-  if (ACT == ACT_SIGMOID) return 1.f / (1.f + __expf(-x));
+  if (ACT == ACT_SILU) return silu_f(x);
+  if (ACT == ACT_SIGMOID) return sigmoid_f(x);
   return x;
 }
 
