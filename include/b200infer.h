@@ -98,6 +98,22 @@ B200_API int b200_stem_pool_nhwc(const void* in, int n, int h, int w, const void
 B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
                                  const float* bias, void* out, int out_pix_stride, int stride, int act, void* stream);
 
+/* The same depthwise convolution with the squeeze of the SqueezeExcitation block that follows it in MBConv fused in
+ * (tv efficientnet.py:153-155 -> tv ops/misc.py:249-250, AdaptiveAvgPool2d(1)): besides `out`, writes fp32
+ * strip_sums[n][strips][c], the channel sums of the stored outputs of each strip of the image, strips =
+ * b200_dwconv3x3_strips(ho, wo, stride) (0: this output geometry has no strip kernel and the call is rejected; widths
+ * that are a multiple of 7 have one). b200_se_gate adds the strips in index order, so the result is deterministic. */
+B200_API int b200_dwconv3x3_strips(int ho, int wo, int stride);
+B200_API int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride,
+                                         const float* weight, const float* bias, void* out, int out_pix_stride,
+                                         int stride, int act, float* strip_sums, void* stream);
+
+/* Squeeze-excitation gate, one launch: gate[n][c] = sigmoid(fc2(silu(fc1(sum(strip_sums[n]) * inv_hw)))). Replaces
+ * SqueezeExcitation._scale (tv ops/misc.py:249-254). w1 fp32 [squeeze][c] (fc1 weight), b1 [squeeze], w2t fp32
+ * [squeeze][c] (fc2 weight TRANSPOSED), b2 [c]; gate fp32 [n][c] feeds b200_channel_scale_nhwc. */
+B200_API int b200_se_gate(const float* strip_sums, int n, int strips, int c, float inv_hw, const float* w1,
+                          const float* b1, const float* w2t, const float* b2, int squeeze, float* gate, void* stream);
+
 /* Max pooling (k, stride, pad). Replaces nn.MaxPool2d(3,2,1) (tv resnet.py:271, shufflenetv2.py:118) and SPPF's 5x5/1/2. */
 B200_API int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,
                                int out_pix_stride, int ksize, int stride, int pad, void* stream);

@@ -14,7 +14,7 @@ import torch
 import torch.nn.functional as F
 
 OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
-    OP_YOLO_DECODE, OP_GATHER_CONV = range(1, 13)
+    OP_YOLO_DECODE, OP_GATHER_CONV, OP_SE_GATE = range(1, 14)
 
 
 def _bf16(x):
@@ -118,7 +118,21 @@ class PlanInterpreter:
                 w = self._f32(op["w_off"], 9 * c).view(3, 3, c).permute(2, 0, 1).unsqueeze(1)
                 b = self._f32(op["b_off"], c)
                 y = F.conv2d(x, w, b, stride=s, padding=1, groups=c)
-                B[p[3]][..., p[4]:p[4] + c] = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+                y = _bf16(_act(y, act)).permute(0, 2, 3, 1)
+                B[p[3]][..., p[4]:p[4] + c] = y
+                if p[12] > 0:      # fused squeeze: per-strip channel sums of the stored outputs; the gate only uses their
+                    B[p[12]].zero_()   # total, so the restatement puts the whole image in strip 0
+                    B[p[12]].view(n, -1)[:, :c] = y.sum(dim=(1, 2))
+            elif t == OP_SE_GATE:
+                strips, c, sq = p[1], p[2], p[8]
+                inv_hw = struct.unpack("<f", struct.pack("<i", p[12]))[0]
+                mean = B[p[0]].view(n, -1)[:, :strips * c].view(n, strips, c).sum(dim=1) * inv_hw
+                w1 = self._f32(op["w_off"], sq * c).view(sq, c)
+                b1 = self._f32(op["b_off"], sq)
+                w2t = self._f32(op["w2_off"], sq * c).view(sq, c)
+                b2 = self._f32(op["b2_off"], c)
+                hid = F.silu(mean @ w1.t() + b1)
+                B[p[3]] = torch.sigmoid(hid @ w2t + b2).view(n, 1, 1, c)
             elif t == OP_MAXPOOL:
                 c, k, s, pad = p[2], p[8], p[9], p[10]
                 x = B[p[0]][..., p[1]:p[1] + c].permute(0, 3, 1, 2)

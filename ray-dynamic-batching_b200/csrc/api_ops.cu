@@ -90,6 +90,25 @@ int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_s
                           static_cast<cudaStream_t>(stream));
 }
 
+int b200_dwconv3x3_strips(int ho, int wo, int stride) { return dwconv3x3_strips(ho, wo, stride); }
+
+int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
+                                const float* bias, void* out, int out_pix_stride, int stride, int act,
+                                float* strip_sums, void* stream) {
+  if (!strip_sums) return fail(B200_ERR_INVALID, "dwconv3x3_squeeze: strip_sums is null");
+  if (stride != 1 && stride != 2) return fail(B200_ERR_INVALID, "dwconv3x3_squeeze: stride must be 1 or 2");
+  const int ho = (h - 1) / stride + 1, wo = (w - 1) / stride + 1;
+  return dwconv3x3_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                          make_view(out, n, ho, wo, c, out_pix_stride), weight, bias, stride, act, strip_sums,
+                          static_cast<cudaStream_t>(stream));
+}
+
+int b200_se_gate(const float* strip_sums, int n, int strips, int c, float inv_hw, const float* w1, const float* b1,
+                 const float* w2t, const float* b2, int squeeze, float* gate, void* stream) {
+  return se_gate_launch(strip_sums, n, strips, c, inv_hw, w1, b1, w2t, b2, squeeze, gate,
+                        static_cast<cudaStream_t>(stream));
+}
+
 int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out, int out_pix_stride,
                       int ksize, int stride, int pad, void* stream) {
   const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;

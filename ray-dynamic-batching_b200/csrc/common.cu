@@ -50,7 +50,9 @@ int encode_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* di
     if (gstr[i] % 16 != 0) return fail(B200_ERR_INVALID, "tensor map stride not a multiple of 16 bytes");
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdim,
                   gstr, bx, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  swz == SWZ_128B ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  swz == SWZ_128B ? CU_TENSOR_MAP_SWIZZLE_128B
+                  : swz == SWZ_64B ? CU_TENSOR_MAP_SWIZZLE_64B
+                  : swz == SWZ_32B ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     std::string m = "cuTensorMapEncodeTiled failed rc=" + std::to_string(static_cast<int>(r)) + " rank=" +

@@ -45,7 +45,7 @@ inline View make_view(void* base, int N, int H, int W, int C, int pix_stride = 0
 }
 
 // ---- TMA descriptors (driver entry point fetched at run time; no link-time libcuda dependency) ----
-enum Swizzle : int { SWZ_NONE = 0, SWZ_128B = 3 };
+enum Swizzle : int { SWZ_NONE = 0, SWZ_32B = 1, SWZ_64B = 2, SWZ_128B = 3 };
 // rank-4 tiled map over bf16: dims[0] is innermost (contiguous); strides_bytes[i] is the stride of dims[i+1].
 int encode_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                 const uint32_t* box, Swizzle swz);

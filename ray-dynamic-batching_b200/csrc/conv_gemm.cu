@@ -292,7 +292,9 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
-    if (lane == 0) {
+    // Every single-thread role below runs its loops with the WHOLE warp (uniform control flow) and issues under
+    // elect_one(): see ptx.cuh.
+    {
       uint32_t g = 0;  // k-block counter across all tiles of this CTA
       for (int it = 0; it < my_tiles; ++it) {
         const int tile0_ = blockIdx.x + it * gridDim.x;
@@ -305,19 +307,21 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const uint32_t ph = (g / STAGES) & 1;
           mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
-          mbar_expect_tx(full, Cfg::STAGE_BYTES);
           const int t = kb / p.kb_per_tap;
           const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
           const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
-          tma_load_4d(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
-          tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0);
+          if (elect_one()) {
+            mbar_expect_tx(full, Cfg::STAGE_BYTES);
+            tma_load_4d(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
+            tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0);
+          }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, BLOCK_N);
       uint32_t g = 0;
       for (int it = 0; it < my_tiles; ++it) {
@@ -333,18 +337,22 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const uint32_t a_src = ring + s * Cfg::STAGE_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_src);
           const uint64_t bdesc = umma_desc_sw128(a_src + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(smem_u32(&bar_empty[s]));
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit(smem_u32(&bar_empty[s]));
+            if (kb == num_kb - 1) umma_commit(smem_u32(&bar_tmem_full[b]));
+          }
         }
-        umma_commit(smem_u32(&bar_tmem_full[b]));
       }
     }
     __syncwarp();
   } else if (warp == 2) {
     // =========================== DMA: residual prefetch (LA tiles ahead) + output stores ===========================
-    if (lane == 0) {
+    {
+      // whole warp in the loops, single-thread work under elect_one() (always the same lane, so the bulk-group
+      // bookkeeping of the TMA stores stays with one thread)
       auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
         const int tile0_ = blockIdx.x + j * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
@@ -352,20 +360,22 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         if (RES) {
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
-          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+          if (elect_one()) {
+            mbar_expect_tx(rdy, Cfg::OUT_BYTES);
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
-            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * BLOCK_N + q * 64,
-                        w0, h0, nb0);
+            for (int q = 0; q < BLOCK_N / 64; ++q)
+              tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * BLOCK_N + q * 64,
+                          w0, h0, nb0);
+          }
         } else {
-          mbar_arrive(rdy);
+          if (elect_one()) mbar_arrive(rdy);
         }
       };
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
         if (LA == 0) {
           // no prefetch distance: staging[it % NB] was last read by the store of tile it - NB; stores issued so far: <= it - 1
-          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
           acquire_staging(it);
         }
         // store of tile it, once its epilogue is done
@@ -377,21 +387,23 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const int n0 = n_tile * BLOCK_N;
           const int ob = it % NB;
           mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+          if (elect_one()) {
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
-            if (n0 + q * 64 < p.cout)
-              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
-          tma_store_commit();
+            for (int q = 0; q < BLOCK_N / 64; ++q)
+              if (n0 + q * 64 < p.cout)
+                tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+            tma_store_commit();
+          }
         }
         // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
         // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
         const int j = it + LA;
         if (LA > 0 && j < my_tiles) {
-          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
       }
-      tma_store_wait_all();
+      if (elect_one()) tma_store_wait_all();
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -466,28 +478,36 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
 }
 
 // ================================================================================================================
-// 3x3 / stride 1 / pad 1 convolution with Cin = Cout = 64 (ResNet layer1 conv2) from a halo tile.
+// 3x3 / stride 1 / pad 1 convolution with few input channels (Cin <= 64) from a halo tile.
 // The generic kernel loads the 128-pixel input tile nine times (once per tap) and the weights once per tile, which makes a
-// 64-wide layer shared-memory-bandwidth bound at ~31 % of the tensor peak.  Here a tile is 8 x 16 pixels of one image; ONE TMA
-// box brings its 18-row x 16-pixel halo (64 channels, 128-byte swizzle, 2 KB per row) and the nine taps are nine shifted
-// *views* of it: descriptor start = halo + (dy*16 + dx)*128 B, SBO = 2048 B (one halo row per 8-pixel group), base_offset 0
-// (the hardware swizzles on absolute address bits, so shifted starts stay consistent with what TMA wrote).  The 9 x 64 x 64 weights stay resident in shared memory.
+// narrow layer shared-memory-bandwidth bound (~31 % of the tensor peak at 64 channels, far less below).  Here a tile is
+// 16 rows x 8 pixels of one image; ONE TMA box brings its 18-row x 16-pixel halo and the nine taps are nine shifted *views*
+// of it: descriptor start = halo + (dy*16 + dx) * PB, SBO = 16 * PB (one halo row per 8-pixel group), base_offset 0 (the
+// hardware swizzles on absolute address bits, so shifted starts stay consistent with what TMA wrote).
+// PB = bytes per staged pixel = the swizzle span: 128 B (33..64 channels), 64 B (17..32) or 32 B (<= 16); channels between
+// Cin and PB/2 are out of bounds of the tensor map and arrive as zeros, so HBM keeps the compact layout.  GEMM-K per tap is
+// PB/2.  The 9 x N x PB/2 weights of the CTA's output-channel tile (N = 32 or 64) stay resident in shared memory; with
+// Cout > 64 the grid is a multiple of the channel tiles so that a CTA always works on the same one.
 // ================================================================================================================
 static constexpr int HALO_ROWS = 18, HALO_PITCH_PX = 16;
-static constexpr int HALO_BYTES = HALO_ROWS * HALO_PITCH_PX * 128;   // 36864
-static constexpr int HALO_W_BYTES = 9 * 64 * 128;                    // 73728: nine taps of [64 cout][64 cin] bf16
+static constexpr int HALO_MAX_STAGES = 4;
 
 struct HaloCfg {
   static constexpr int OUT_BUFS = 4;
   static constexpr int LOOKAHEAD = 2;
   static constexpr int OUT_BYTES = BLOCK_M * 64 * 2;
-  static constexpr int SMEM_BYTES = HALO_W_BYTES + 2 * HALO_BYTES + OUT_BUFS * OUT_BYTES + 1024;
+  static constexpr int halo_bytes(int pb) { return HALO_ROWS * HALO_PITCH_PX * pb; }
+  static constexpr int w_bytes(int pb, int n) { return 9 * n * pb; }
+  static constexpr int smem_bytes(int pb, int n, int stages) {
+    return w_bytes(pb, n) + stages * halo_bytes(pb) + OUT_BUFS * OUT_BYTES + 1024;
+  }
 };
 
-// K-major SWIZZLE_128B descriptor with explicit 8-row-group stride and base offset (start not 1024-byte aligned)
-__device__ __forceinline__ uint64_t umma_desc_sw128_ex(uint32_t smem_addr, uint32_t sbo_bytes, uint32_t base_offset) {
+// K-major swizzled descriptor (span = pb bytes) with explicit 8-row-group stride; start need not be atom aligned
+__device__ __forceinline__ uint64_t umma_desc_swz(uint32_t smem_addr, uint32_t sbo_bytes, int pb) {
+  const uint32_t layout = pb == 128 ? 2u : (pb == 64 ? 4u : 6u);
   const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | (1u << 16);
-  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) | (base_offset << 17) | (2u << 29);
+  const uint32_t hi = (sbo_bytes >> 4) | (1u << 14) | (layout << 29);
   return (static_cast<uint64_t>(hi) << 32) | lo;
 }
 
@@ -495,13 +515,15 @@ template <int RES, int ACT>
 __global__ void __launch_bounds__(PCONV_THREADS, 1)
 conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p, const int total_tiles) {
   using Cfg = HaloCfg;
-  constexpr int BLOCK_N = 64;
+  constexpr int BLOCK_N = 64;          // accumulator stride in TMEM and bias buffer size; the tile's width is p.block_n
   constexpr int NB = Cfg::OUT_BUFS;
   constexpr int LA = Cfg::LOOKAHEAD;
+  const int PB = p.pb, N = p.block_n, HS = p.halo_stages;
+  const int halo_bytes = Cfg::halo_bytes(PB), tap_bytes = N * PB;
 
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_halo_full[2];
-  __shared__ __align__(8) uint64_t bar_halo_empty[2];
+  __shared__ __align__(8) uint64_t bar_halo_full[HALO_MAX_STAGES];
+  __shared__ __align__(8) uint64_t bar_halo_empty[HALO_MAX_STAGES];
   __shared__ __align__(8) uint64_t bar_w_full;
   __shared__ __align__(8) uint64_t bar_tmem_full[2];
   __shared__ __align__(8) uint64_t bar_tmem_empty[2];
@@ -513,8 +535,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t wres = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t halo = wres + HALO_W_BYTES;
-  const uint32_t staging = halo + 2 * HALO_BYTES;
+  const uint32_t halo = wres + 9 * tap_bytes;
+  const uint32_t staging = halo + HS * halo_bytes;
   const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
@@ -522,9 +544,11 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
     tma_prefetch_desc(&maps.b);
     tma_prefetch_desc(&maps.d);
     if (RES) tma_prefetch_desc(&maps.r);
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < HALO_MAX_STAGES; ++b) {
       mbar_init(smem_u32(&bar_halo_full[b]), 1);
       mbar_init(smem_u32(&bar_halo_empty[b]), 1);
+    }
+    for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bar_tmem_full[b]), 1);
       mbar_init(smem_u32(&bar_tmem_empty[b]), 128);
     }
@@ -544,53 +568,76 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
 
   if (warp == 0) {
     // =========================== TMA producer: weights once, one halo box per tile ===========================
-    if (lane == 0) {
-      mbar_expect_tx(smem_u32(&bar_w_full), HALO_W_BYTES);
-      for (int t = 0; t < 9; ++t) tma_load_3d(&maps.b, smem_u32(&bar_w_full), wres + t * (64 * 128), 0, t, 0);
+    if (my_tiles > 0) {
+      {
+        // the grid is a multiple of n_tiles, so every tile of this CTA has the channel tile of its first one
+        const int first = (p.reverse & 1) ? total_tiles - 1 - static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x);
+        const int n0 = (first % p.n_tiles) * N;
+        if (elect_one()) {
+          mbar_expect_tx(smem_u32(&bar_w_full), 9 * tap_bytes);
+          for (int t = 0; t < 9; ++t) tma_load_3d(&maps.b, smem_u32(&bar_w_full), wres + t * tap_bytes, 0, t, n0);
+        }
+      }
       for (int it = 0; it < my_tiles; ++it) {
         const int tile0_ = blockIdx.x + it * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
         int n_tile, w0, h0, nb0;
         tile_coords(p, tile, n_tile, w0, h0, nb0);
-        const int hb = it & 1;
-        mbar_wait(smem_u32(&bar_halo_empty[hb]), ((it >> 1) & 1) ^ 1);
+        const int hb = it % HS;
+        mbar_wait(smem_u32(&bar_halo_empty[hb]), ((it / HS) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_halo_full[hb]);
-        mbar_expect_tx(full, HALO_BYTES);
-        tma_load_4d(&maps.a[0], full, halo + hb * HALO_BYTES, 0, w0 - 1, h0 - 1, nb0);   // box [64, 16, 18, 1]
+        if (elect_one()) {
+          mbar_expect_tx(full, halo_bytes);
+          tma_load_4d(&maps.a[0], full, halo + hb * halo_bytes, 0, w0 - 1, h0 - 1, nb0);   // box [PB/2, 16, 18, 1]
+        }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer: nine shifted views of the halo ===========================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, BLOCK_N);
+    // The whole warp walks the tile loop (uniform control flow); one elected lane issues the MMAs.
+    if (my_tiles > 0) {
+      const uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, N);
+      const int ksteps = PB >> 5;      // K = 16 (32 bytes) per MMA
+      // Everything that does not depend on the tile is hoisted.  base_offset stays 0: measured on B200, the swizzle is
+      // applied to the absolute shared-memory address bits, so a start shifted by dx pixels sees exactly the pattern TMA
+      // wrote (base_offset = dx gives garbage).
+      uint64_t bdesc[9];
+      uint32_t aoff[9];                // tap offset inside the halo, in the descriptor's 16-byte units
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        bdesc[t] = umma_desc_swz(wres + t * tap_bytes, 8 * PB, PB);
+        aoff[t] = static_cast<uint32_t>(((t / 3) * HALO_PITCH_PX + (t % 3)) * PB) >> 4;
+      }
+      const uint64_t adesc0 = umma_desc_swz(halo, HALO_PITCH_PX * PB, PB);
+      const uint32_t halo_step = static_cast<uint32_t>(halo_bytes) >> 4;
       mbar_wait(smem_u32(&bar_w_full), 0);
       for (int it = 0; it < my_tiles; ++it) {
-        const int b = it & 1, hb = it & 1;
+        const int b = it & 1, hb = it % HS;
         mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it >> 1) & 1) ^ 1);
-        mbar_wait(smem_u32(&bar_halo_full[hb]), (it >> 1) & 1);
+        mbar_wait(smem_u32(&bar_halo_full[hb]), (it / HS) & 1);
         tc_fence_after();
         const uint32_t acc = tmem_base + b * BLOCK_N;
-        const uint32_t hbase = halo + hb * HALO_BYTES;
+        const uint64_t abase = adesc0 + hb * halo_step;     // start-address field: (halo + hb * halo_bytes) >> 4, no carry out of 14 bits
+        if (elect_one()) {
 #pragma unroll
-        for (int t = 0; t < 9; ++t) {
-          const int dy = t / 3, dx = t % 3;
-          // base_offset stays 0: measured on B200, the 128-byte swizzle is applied to the absolute shared-memory address
-          // bits, so a start shifted by dx * 128 B sees exactly the pattern TMA wrote (base_offset = dx gives garbage).
-          const uint64_t adesc = umma_desc_sw128_ex(hbase + (dy * HALO_PITCH_PX + dx) * 128, HALO_PITCH_PX * 128, 0);
-          const uint64_t bdesc = umma_desc_sw128(wres + t * (64 * 128));
+          for (int t = 0; t < 9; ++t) {
+            const uint64_t ad = abase + aoff[t];
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (t | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < 4; ++k)
+              if (k < ksteps) umma_bf16(acc, ad + 2 * k, bdesc[t] + 2 * k, idesc, (t | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(smem_u32(&bar_halo_empty[hb]));
+          umma_commit(smem_u32(&bar_tmem_full[b]));
         }
-        umma_commit(smem_u32(&bar_halo_empty[hb]));
-        umma_commit(smem_u32(&bar_tmem_full[b]));
+        __syncwarp();
       }
     }
-    __syncwarp();
   } else if (warp == 2) {
     // =========================== DMA: residual prefetch (LA tiles ahead) + output stores ===========================
-    if (lane == 0) {
+    {
+      // whole warp in the loops, single-thread work under elect_one() (always the same lane, so the bulk-group
+      // bookkeeping of the TMA stores stays with one thread)
       auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
         const int tile0_ = blockIdx.x + j * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
@@ -598,20 +645,22 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         if (RES) {
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
-          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+          if (elect_one()) {
+            mbar_expect_tx(rdy, Cfg::OUT_BYTES);
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
-            tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * BLOCK_N + q * 64,
-                        w0, h0, nb0);
+            for (int q = 0; q < BLOCK_N / 64; ++q)
+              tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * N + q * 64,
+                          w0, h0, nb0);
+          }
         } else {
-          mbar_arrive(rdy);
+          if (elect_one()) mbar_arrive(rdy);
         }
       };
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
         if (LA == 0) {
           // no prefetch distance: staging[it % NB] was last read by the store of tile it - NB; stores issued so far: <= it - 1
-          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
           acquire_staging(it);
         }
         // store of tile it, once its epilogue is done
@@ -620,24 +669,26 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
           const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
-          const int n0 = n_tile * BLOCK_N;
+          const int n0 = n_tile * N;
           const int ob = it % NB;
           mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+          if (elect_one()) {
 #pragma unroll
-          for (int q = 0; q < BLOCK_N / 64; ++q)
-            if (n0 + q * 64 < p.cout)
-              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
-          tma_store_commit();
+            for (int q = 0; q < BLOCK_N / 64; ++q)
+              if (n0 + q * 64 < p.cout)
+                tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+            tma_store_commit();
+          }
         }
         // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
         // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
         const int j = it + LA;
         if (LA > 0 && j < my_tiles) {
-          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
       }
-      tma_store_wait_all();
+      if (elect_one()) tma_store_wait_all();
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -652,8 +703,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
       const int b = it & 1;
       const int ob = it % NB;
-      const int n0 = (tile % p.n_tiles) * BLOCK_N;
-      for (int i = epi_tid; i < BLOCK_N; i += 128) {
+      const int n0 = (tile % p.n_tiles) * N;
+      for (int i = epi_tid; i < N; i += 128) {
         const int c = n0 + i;
         bias_s[b][i] = (c < p.cout) ? p.bias[c] : 0.f;
       }
@@ -664,7 +715,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
       const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
-      for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
+      for (int cc = 0; cc < N / 32; ++cc) {
         uint32_t v[32];
         tmem_ld_32x32(acc + cc * 32, v);
         tmem_ld_wait();
@@ -811,7 +862,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
 
   if (warp == 0) {
     // =========================== TMA producer (both CTAs) ===========================
-    if (lane == 0) {
+    {
       uint32_t g = 0;
       for (int it = 0; it < my_tiles; ++it) {
         int n0, w0, h0, nb0;
@@ -821,19 +872,21 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
           const uint32_t ph = (g / STAGES) & 1;
           mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
-          if (rank == 0) mbar_expect_tx(full, 2 * Cfg::STAGE_BYTES);   // both CTAs' bytes land on the leader's barrier
           const int t = kb / p.kb_per_tap;
           const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
           const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
-          tma_load_4d_2cta(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
-          tma_load_3d_2cta(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0 + static_cast<int>(rank) * (BLOCK_N / 2));
+          if (elect_one()) {
+            if (rank == 0) mbar_expect_tx(full, 2 * Cfg::STAGE_BYTES);   // both CTAs' bytes land on the leader's barrier
+            tma_load_4d_2cta(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
+            tma_load_3d_2cta(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0 + static_cast<int>(rank) * (BLOCK_N / 2));
+          }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer (leader CTA only) ===========================
-    if (rank == 0 && lane == 0) {
+    if (rank == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(2 * BLOCK_M, BLOCK_N);
       uint32_t g = 0;
       for (int it = 0; it < my_tiles; ++it) {
@@ -849,18 +902,20 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
           const uint32_t a_src = ring + s * Cfg::STAGE_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_src);
           const uint64_t bdesc = umma_desc_sw128(a_src + A_STAGE_BYTES);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BLOCK_K / 16; ++k)
-            umma_bf16_2cta(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit_2cta(smem_u32(&bar_empty[s]));       // frees the slot in both CTAs
+            for (int k = 0; k < BLOCK_K / 16; ++k)
+              umma_bf16_2cta(acc, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit_2cta(smem_u32(&bar_empty[s]));       // frees the slot in both CTAs
+            if (kb == num_kb - 1) umma_commit_2cta(smem_u32(&bar_tmem_full[b]));     // accumulator ready in both CTAs
+          }
         }
-        umma_commit_2cta(smem_u32(&bar_tmem_full[b]));     // accumulator ready in both CTAs
       }
     }
     __syncwarp();
   } else if (warp == 2) {
     // =========================== DMA: residual prefetch + output stores (per CTA, 128-column units) ===========================
-    if (lane == 0) {
+    {
       constexpr int SUBS = Cfg::SUBS, SUB_N = Cfg::SUB_N;
       const int total_units = my_tiles * SUBS;
       auto unit_coords = [&](int u, int& n0, int& w0, int& h0, int& nb0) {
@@ -872,18 +927,20 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
         if (RES) {
           int n0, w0, h0, nb0;
           unit_coords(u, n0, w0, h0, nb0);
-          mbar_expect_tx(rdy, Cfg::OUT_BYTES);
+          if (elect_one()) {
+            mbar_expect_tx(rdy, Cfg::OUT_BYTES);
 #pragma unroll
-          for (int q = 0; q < SUB_N / 64; ++q)
-            tma_load_4d(&maps.r, rdy, staging + (u % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+            for (int q = 0; q < SUB_N / 64; ++q)
+              tma_load_4d(&maps.r, rdy, staging + (u % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+          }
         } else {
-          mbar_arrive(rdy);
+          if (elect_one()) mbar_arrive(rdy);
         }
       };
       for (int u = 0; u < LA && u < total_units; ++u) acquire_staging(u);
       for (int u = 0; u < total_units; ++u) {
         if (LA == 0) {
-          asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
           acquire_staging(u);
         }
         {
@@ -891,19 +948,21 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
           unit_coords(u, n0, w0, h0, nb0);
           const int ob = u % NB;
           mbar_wait(smem_u32(&bar_out_ready[ob]), (u / NB) & 1);
+          if (elect_one()) {
 #pragma unroll
-          for (int q = 0; q < SUB_N / 64; ++q)
-            if (n0 + q * 64 < p.cout)
-              tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
-          tma_store_commit();
+            for (int q = 0; q < SUB_N / 64; ++q)
+              if (n0 + q * 64 < p.cout)
+                tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+            tma_store_commit();
+          }
         }
         const int j = u + LA;   // its buffer was last read by the store of unit j - NB = u - 2; stores issued so far: <= u
         if (LA > 0 && j < total_units) {
-          asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
           acquire_staging(j);
         }
       }
-      tma_store_wait_all();
+      if (elect_one()) tma_store_wait_all();
     }
     __syncwarp();
   } else if (warp >= 4) {
@@ -1067,10 +1126,19 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const char* e = getenv("B200_CONV_HALO");
     use_halo = (e && e[0] == '0') ? 0 : 1;
   }
-  // halo kernel: 3x3/s1/p1, Cin = Cout = 64, 8x16-pixel tiles with little padding waste
-  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C == 64 && out.C == 64 &&
-                    in.W % 8 == 0 && ((in.H + 15) / 16 * 16) * 100 <= in.H * 115;
-  if (halo) { two_cta = false; block_n = 64; }
+  // halo kernel: 3x3/s1/p1, Cin <= 64, 16x8-pixel tiles with little padding waste; Cout <= 64, or wider while the layer
+  // is too thin in K for the generic kernel (Cin < 64: each of its k-blocks would be mostly padding)
+  const long long halo_cover = (long long)((in.W + 7) / 8 * 8) * ((in.H + 15) / 16 * 16);
+  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 &&
+                    (out.C <= 64 || (in.C < 64 && out.C <= 256)) && halo_cover * 100 <= (long long)in.W * in.H * 135;
+  if (halo) {
+    two_cta = false;
+    block_n = out.C <= 32 ? 32 : 64;
+    p.pb = in.C <= 16 ? 32 : (in.C <= 32 ? 64 : 128);
+    p.block_n = block_n;
+    p.halo_stages = p.pb == 128 ? 2 : 4;
+    L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages);
+  }
   L->halo = halo;
   L->block_n = block_n;
   L->two_cta = two_cta;
@@ -1089,8 +1157,9 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
     const uint64_t dims[4] = {uint64_t(in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
     const uint64_t str[3] = {ips, rowb, imgb};
-    const uint32_t box[4] = {64u, uint32_t(HALO_PITCH_PX), uint32_t(HALO_ROWS), 1u};
-    B200_TRY(encode_tmap(&L->maps.a[0], in.base, 4, dims, str, box, SWZ_128B));
+    const uint32_t box[4] = {uint32_t(p.pb / 2), uint32_t(HALO_PITCH_PX), uint32_t(HALO_ROWS), 1u};
+    B200_TRY(encode_tmap(&L->maps.a[0], in.base, 4, dims, str, box,
+                         p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B)));
   } else {
     pick_tile(oW, oH, oN, &p.tw, &p.th, &p.tn);
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
@@ -1138,8 +1207,9 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   {
     const uint64_t dims[3] = {uint64_t(in.C), uint64_t(taps), uint64_t(out.C)};
     const uint64_t str[2] = {uint64_t(in.C) * 2, uint64_t(in.C) * 2 * taps};
-    const uint32_t box[3] = {64u, 1u, uint32_t(two_cta ? block_n / 2 : block_n)};  // a CTA pair loads half each
-    B200_TRY(encode_tmap(&L->maps.b, s.w, 3, dims, str, box, SWZ_128B));
+    const uint32_t box[3] = {halo ? uint32_t(p.pb / 2) : 64u, 1u, uint32_t(two_cta ? block_n / 2 : block_n)};  // a CTA pair loads half each
+    B200_TRY(encode_tmap(&L->maps.b, s.w, 3, dims, str, box,
+                         !halo || p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B)));
   }
   const long long m_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
   if (m_tiles * p.n_tiles > 0x7fffffffLL) return fail(B200_ERR_INVALID, "conv: grid too large");
@@ -1257,12 +1327,13 @@ static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
     B200_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<RES, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      HaloCfg::SMEM_BYTES));
+                                      HaloCfg::smem_bytes(128, 64, 2)));
     configured[dev & 63] = true;
   }
   const int total = static_cast<int>(l.grid);
-  const int ctas = total < device_sm_count() ? total : device_sm_count();
-  conv3x3_halo_kernel<RES, ACT><<<ctas, PCONV_THREADS, HaloCfg::SMEM_BYTES, stream>>>(l.maps, l.p, total);
+  int ctas = total < device_sm_count() ? total : device_sm_count();
+  ctas -= ctas % l.p.n_tiles;    // a CTA keeps ONE channel tile's weights resident: tile stride must preserve tile % n_tiles
+  conv3x3_halo_kernel<RES, ACT><<<ctas, PCONV_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }

@@ -28,6 +28,9 @@ struct ConvParams {
   int n_tiles;                    // tiles along Cout
   int num_taps, kb_per_tap;
   int cout, act, has_res;  // has_res: 0 none, 1 add before the activation, 2 add after it
+  int pb;                  // halo kernel: bytes per pixel of the staged halo (32 / 64 / 128 = swizzle span), K per tap = pb / 2
+  int block_n;             // halo kernel: accumulator width (32 or 64)
+  int halo_stages;         // halo kernel: halo boxes in flight (2 or 4)
   int reverse;             // walk the tiles last-to-first (alternated layer by layer so a layer starts on what is still in L2)
   signed char tap_map[9], tap_dx[9], tap_dy[9];
   const float* bias;
@@ -39,7 +42,8 @@ struct ConvLaunch {
   unsigned grid = 0;
   int block_n = 0;
   bool two_cta = false;
-  bool halo = false;     // 3x3 halo-tile kernel (Cin = Cout = 64)  // CTA-pair kernel (tcgen05.mma.cta_group::2)
+  bool halo = false;     // 3x3 halo-tile kernel (Cin <= 64, resident weights)
+  int halo_smem = 0;
   double flops = 0;  // 2*M*N*K (useful, un-padded)
 };
 

@@ -1,14 +1,135 @@
-// Depthwise 3x3 convolution (stride 1 / 2, pad 1) + folded BatchNorm bias + optional activation on NHWC bf16.
-// Bandwidth-bound (9 MAC per output element): one thread owns 8 channels (16 B) of one output pixel, so a warp reads
-// 512 contiguous bytes per tap; the 3x3 halo re-reads hit L1/L2.  fp32 weights [9][C] and fp32 accumulation.
+// Depthwise 3x3 convolution (stride 1 / 2, pad 1) + folded BatchNorm bias + optional activation on NHWC bf16, with an
+// optional fused squeeze (per-strip channel sums for the squeeze-excitation block that follows in MBConv).
+//
+// Bandwidth-bound (9 MAC per output element).  Strip kernel: one thread owns 4 channels (8 B) of a strip of DW_TW
+// output columns x R output rows (R = 2 at stride 1, 1 at stride 2), keeps its 36 weights in registers and slides a
+// 3-column register window along the strip, so every input element is loaded once per strip (+ the 2-column halo)
+// instead of once per tap: L1 wavefronts per output drop ~10x against the per-pixel kernel below, which is L1-bound.
+// A warp covers 128 contiguous channels of one pixel per load (256 B).  fp32 weights [9][C], fp32 accumulation, taps
+// accumulated in (row, column) order on top of the bias -- the same order as the per-pixel kernel, so both agree bit
+// for bit.  Widths that are not a multiple of DW_TW fall back to the per-pixel kernel.
 //
 // Replaces the grouped nn.Conv2d(groups=C)+BatchNorm2d of tv shufflenetv2.py:62-76,86-96 (`depthwise_conv`) and the
-// depthwise stage of MBConv (tv efficientnet.py:140-151).
+// depthwise stage of MBConv (tv efficientnet.py:140-151); the fused sums replace the AdaptiveAvgPool2d(1) that opens
+// SqueezeExcitation (tv ops/misc.py:244-254).
 #include "kernels.cuh"
 #include "ptx.cuh"
 
 namespace b200 {
 
+constexpr int DW_STRIP_THREADS = 128;
+constexpr int DW_TW = 7;   // strip width: every spatial size of the served classifiers (224 / 2^k) is a multiple of 7
+
+__device__ __forceinline__ uint2 dw_load(const uint16_t* __restrict__ p, bool ok) {
+  uint2 r = make_uint2(0u, 0u);
+  if (ok) r = *reinterpret_cast<const uint2*>(p);
+  return r;
+}
+__device__ __forceinline__ void dw_unpack(const uint2 r, float (&v)[4]) {
+  v[0] = bf16_lo(r.x); v[1] = bf16_hi(r.x); v[2] = bf16_lo(r.y); v[3] = bf16_hi(r.y);
+}
+
+// se_partial: null, or fp32 [N][strips_h * strips_w][C]: sums of the STORED (bf16-rounded, activated) outputs of each
+// strip; the gate kernel adds the strips of an image in index order, so the squeeze is deterministic.
+// All loads of a strip (ROWS x NCOL 8-byte words, still packed) are issued before the first FMA: the kernel is
+// latency-bound otherwise (4 loads in flight per thread gave ~2.4 TB/s).
+template <int STRIDE, int ACT>
+__global__ void __launch_bounds__(DW_STRIP_THREADS, 3)
+dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho,
+                       int Wo, int out_ps, int C4, int strips_h, int strips_w, const float* __restrict__ w,
+                       const float* __restrict__ bias, float* __restrict__ se_partial, long long total) {
+  constexpr int R = STRIDE == 1 ? 2 : 1;                        // output rows per thread
+  constexpr int ROWS = STRIDE == 1 ? 4 : 3;                     // input rows per thread
+  constexpr int NCOL = STRIDE == 1 ? DW_TW + 2 : 2 * DW_TW + 1;   // input columns per thread, first one = halo
+  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (idx >= total) return;
+  const int c4 = static_cast<int>(idx % C4);
+  long long t = idx / C4;
+  const int sx = static_cast<int>(t % strips_w);
+  t /= strips_w;
+  const int sy = static_cast<int>(t % strips_h);
+  const int n = static_cast<int>(t / strips_h);
+  const int C = C4 * 4;
+  const int oy0 = sy * R, ox0 = sx * DW_TW;
+  const int iy0 = oy0 * STRIDE - 1, ix0 = ox0 * STRIDE - 1;
+
+  uint2 raw[ROWS][NCOL];
+#pragma unroll
+  for (int i = 0; i < ROWS; ++i) {
+    const int y = iy0 + i;
+    const bool rowok = y >= 0 && y < H;
+    const uint16_t* rowp = in + ((static_cast<size_t>(n) * H + (rowok ? y : 0)) * W) * in_ps + c4 * 4;
+#pragma unroll
+    for (int k = 0; k < NCOL; ++k) {
+      const int x = ix0 + k;
+      raw[i][k] = dw_load(rowp + static_cast<ptrdiff_t>(x) * in_ps, rowok && x >= 0 && x < W);
+    }
+  }
+  float wt[9][4], b[4];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const float4 v = *reinterpret_cast<const float4*>(w + k * C + c4 * 4);
+    wt[k][0] = v.x; wt[k][1] = v.y; wt[k][2] = v.z; wt[k][3] = v.w;
+  }
+  {
+    const float4 v = *reinterpret_cast<const float4*>(bias + c4 * 4);
+    b[0] = v.x; b[1] = v.y; b[2] = v.z; b[3] = v.w;
+  }
+  float win[ROWS][3][4];
+  float sum[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < ROWS; ++i) {
+    if (STRIDE == 1) {
+      dw_unpack(raw[i][0], win[i][1]);
+      dw_unpack(raw[i][1], win[i][2]);
+    } else {
+      dw_unpack(raw[i][0], win[i][2]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < DW_TW; ++j) {
+    const int ox = ox0 + j;
+#pragma unroll
+    for (int i = 0; i < ROWS; ++i) {
+      if (STRIDE == 1) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { win[i][0][c] = win[i][1][c]; win[i][1][c] = win[i][2][c]; }
+        dw_unpack(raw[i][j + 2], win[i][2]);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) win[i][0][c] = win[i][2][c];
+        dw_unpack(raw[i][2 * j + 1], win[i][1]);
+        dw_unpack(raw[i][2 * j + 2], win[i][2]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (oy0 + r >= Ho) continue;
+      float acc[4] = {b[0], b[1], b[2], b[3]};
+#pragma unroll
+      for (int dr = 0; dr < 3; ++dr) {
+        // a tap outside the image is skipped by the per-pixel kernel; here it multiplies an exact zero: same result
+        // unless a weight is inf/nan, which a folded BatchNorm never produces
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[c] = fmaf(win[r + dr][q][c], wt[dr * 3 + q][c], acc[c]);
+        }
+      }
+      uint2 o;
+      o.x = pack_bf16x2(apply_act(acc[0], ACT), apply_act(acc[1], ACT));
+      o.y = pack_bf16x2(apply_act(acc[2], ACT), apply_act(acc[3], ACT));
+      *reinterpret_cast<uint2*>(out + ((static_cast<size_t>(n) * Ho + oy0 + r) * Wo + ox) * out_ps + c4 * 4) = o;
+      sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y);
+    }
+  }
+  if (se_partial) {
+    const size_t strip = (static_cast<size_t>(n) * strips_h + sy) * strips_w + sx;
+    *reinterpret_cast<float4*>(se_partial + strip * C + c4 * 4) = make_float4(sum[0], sum[1], sum[2], sum[3]);
+  }
+}
+
+// Per-pixel fallback: one thread owns 8 channels (16 B) of one output pixel.
 __global__ void __launch_bounds__(256)
 dwconv3x3_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho, int Wo,
                  int out_ps, int C8, int stride, const float* __restrict__ w, const float* __restrict__ bias, int act,
@@ -55,13 +176,52 @@ dwconv3x3_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint1
   *reinterpret_cast<uint4*>(out + ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * out_ps + c8 * 8) = o;
 }
 
+int dwconv3x3_strips(int Ho, int Wo, int stride) {
+  if (Wo % DW_TW) return 0;
+  const int r = stride == 1 ? 2 : 1;
+  return ((Ho + r - 1) / r) * (Wo / DW_TW);
+}
+
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
-                     float* se_sum, cudaStream_t stream) {
-  if (se_sum) return fail(B200_ERR_INVALID, "dwconv: fused SE squeeze not implemented");
+                     float* se_partial, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.pix_stride % 8 || out.pix_stride % 8)
     return fail(B200_ERR_INVALID, "dwconv: channels must match and be multiples of 8");
+  if (stride != 1 && stride != 2) return fail(B200_ERR_INVALID, "dwconv: stride must be 1 or 2");
   if ((in.H + 2 - 3) / stride + 1 != out.H || (in.W + 2 - 3) / stride + 1 != out.W || in.N != out.N)
     return fail(B200_ERR_INVALID, "dwconv: output geometry mismatch");
+  static int use_strips = -1;
+  if (use_strips < 0) {
+    const char* e = getenv("B200_DW_STRIPS");
+    use_strips = (e && e[0] == '0') ? 0 : 1;
+  }
+  const int strips = dwconv3x3_strips(out.H, out.W, stride);
+  if (strips > 0 && (use_strips || se_partial)) {
+    const int r = stride == 1 ? 2 : 1;
+    const int strips_h = (out.H + r - 1) / r, strips_w = out.W / DW_TW;
+    const long long total = static_cast<long long>(out.N) * strips * (out.C / 4);
+    const unsigned grid = static_cast<unsigned>((total + DW_STRIP_THREADS - 1) / DW_STRIP_THREADS);
+    const uint16_t* ip = static_cast<const uint16_t*>(in.base);
+    uint16_t* op = static_cast<uint16_t*>(out.base);
+#define B200_DW_LAUNCH(S, A)                                                                                          \
+  dwconv3x3_strip_kernel<S, A><<<grid, DW_STRIP_THREADS, 0, stream>>>(ip, in.H, in.W, in.pix_stride, op, out.H, out.W, \
+                                                                      out.pix_stride, out.C / 4, strips_h, strips_w, w, \
+                                                                      bias, se_partial, total)
+    if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU)
+      return fail(B200_ERR_INVALID, "dwconv: activation must be none, relu or silu");
+    if (stride == 1) {
+      if (act == ACT_NONE) B200_DW_LAUNCH(1, ACT_NONE);
+      else if (act == ACT_RELU) B200_DW_LAUNCH(1, ACT_RELU);
+      else B200_DW_LAUNCH(1, ACT_SILU);
+    } else {
+      if (act == ACT_NONE) B200_DW_LAUNCH(2, ACT_NONE);
+      else if (act == ACT_RELU) B200_DW_LAUNCH(2, ACT_RELU);
+      else B200_DW_LAUNCH(2, ACT_SILU);
+    }
+#undef B200_DW_LAUNCH
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+  }
+  if (se_partial) return fail(B200_ERR_INVALID, "dwconv: fused squeeze needs an output width that is a multiple of 7");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
   dwconv3x3_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
       static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.H, out.W,

@@ -55,6 +55,22 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     const int ids[3] = {o.p[0], o.p[3], o.p[6]};
     for (int k = 0; k < 3; ++k)
       if (ids[k] >= int(hdr.n_bufs) || (k < 2 && ids[k] < 0)) return fail(B200_ERR_BLOB, "engine: op references unknown buffer");
+    if ((o.type == OP_DWCONV || o.type == OP_SCALE) && (o.p[12] < 0 || o.p[12] >= int(hdr.n_bufs)))
+      return fail(B200_ERR_BLOB, "engine: op references unknown side buffer");
+    if (o.type == OP_DWCONV && o.p[12] > 0) {   // fused squeeze: the side buffer must hold every strip's channel sums
+      const BufRec& sb = bufs[o.p[12]];
+      const BufRec& ob = bufs[o.p[3]];
+      const int strips = dwconv3x3_strips(ob.h, ob.w, o.p[9]);
+      if (strips <= 0 || sb.dtype != 1 || int64_t(sb.h) * sb.w * sb.c < int64_t(strips) * o.p[5])
+        return fail(B200_ERR_BLOB, "engine: depthwise squeeze buffer too small for this geometry");
+    }
+    if (o.type == OP_SE_GATE) {
+      const BufRec& sb = bufs[o.p[0]];
+      const BufRec& gb = bufs[o.p[3]];
+      if (o.p[1] <= 0 || o.p[2] <= 0 || o.p[8] <= 0 || sb.dtype != 1 || gb.dtype != 1 ||
+          int64_t(sb.h) * sb.w * sb.c < int64_t(o.p[1]) * o.p[2] || int64_t(gb.h) * gb.w * gb.c < o.p[2])
+        return fail(B200_ERR_BLOB, "engine: squeeze-excitation gate buffers do not match its shape");
+    }
     const int64_t offs[4] = {o.w_off, o.b_off, o.w2_off, o.b2_off};
     for (int64_t off : offs)
       if (off >= int64_t(hdr.weights_bytes)) return fail(B200_ERR_BLOB, "engine: weight offset out of range");
@@ -170,8 +186,20 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
       case OP_DWCONV:
         rc = dwconv3x3_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
                               reinterpret_cast<const float*>(W + po.rec.w_off),
-                              reinterpret_cast<const float*>(W + po.rec.b_off), p[9], p[11], nullptr, stream);
+                              reinterpret_cast<const float*>(W + po.rec.b_off), p[9], p[11],
+                              p[12] > 0 ? reinterpret_cast<float*>(buf_dev[p[12]]) : nullptr, stream);
         break;
+      case OP_SE_GATE: {
+        float inv_hw;
+        memcpy(&inv_hw, &p[12], 4);
+        rc = se_gate_launch(reinterpret_cast<const float*>(buf_dev[p[0]]), batch, p[1], p[2], inv_hw,
+                            reinterpret_cast<const float*>(W + po.rec.w_off),
+                            reinterpret_cast<const float*>(W + po.rec.b_off),
+                            reinterpret_cast<const float*>(W + po.rec.w2_off),
+                            reinterpret_cast<const float*>(W + po.rec.b2_off), p[8],
+                            reinterpret_cast<float*>(buf_dev[p[3]]), stream);
+        break;
+      }
       case OP_SCALE:
         rc = channel_scale_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
                                   reinterpret_cast<const float*>(buf_dev[p[12]]), stream);

@@ -92,6 +92,84 @@ int fc_launch(const float* x, const float* w, const float* b, float* out, int n,
   return B200_OK;
 }
 
+// Squeeze-excitation gate in one launch: mean over the strips the depthwise kernel summed -> fc1 + SiLU -> fc2 +
+// sigmoid.  One 1024-thread block per image; the two matrices are tiny (C x C/4 .. C/24) and every block reads them
+// from L2, so the kernel is three dependent rounds of L2 latency: all loads are 16-byte and issued in unrolled batches.
+// w1 fp32 [S][C] (row per squeeze unit), w2t fp32 [S][C] (fc2 TRANSPOSED so a warp reads consecutive channels).
+// Replaces SqueezeExcitation._scale (tv ops/misc.py:249-254): avgpool, fc1, activation, fc2, scale_activation.
+constexpr int SE_THREADS = 1024;
+__global__ void __launch_bounds__(SE_THREADS)
+se_gate_kernel(const float* __restrict__ partial, int P, int C, float inv_hw, const float* __restrict__ w1,
+               const float* __restrict__ b1, const float* __restrict__ w2t, const float* __restrict__ b2, int S, int JS,
+               float* __restrict__ gate) {
+  extern __shared__ __align__(16) float se_smem[];   // mean[C], hid[S], part[JS][C]
+  float* mean = se_smem;
+  float* hid = se_smem + C;
+  float* part = hid + S;
+  const int n = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Q = C >> 2;
+  for (int q = threadIdx.x; q < Q; q += SE_THREADS) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int p = 0; p < P; ++p) {      // fixed order: deterministic
+      const float4 v = *reinterpret_cast<const float4*>(partial + (static_cast<size_t>(n) * P + p) * C + q * 4);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    *reinterpret_cast<float4*>(mean + q * 4) = make_float4(s.x * inv_hw, s.y * inv_hw, s.z * inv_hw, s.w * inv_hw);
+  }
+  __syncthreads();
+  for (int j = warp; j < S; j += SE_THREADS / 32) {
+    float acc = 0.f;
+    const float* wr = w1 + static_cast<size_t>(j) * C;
+#pragma unroll 4
+    for (int q = lane; q < Q; q += 32) {
+      const float4 wv = *reinterpret_cast<const float4*>(wr + q * 4);
+      const float4 mv = *reinterpret_cast<const float4*>(mean + q * 4);
+      acc = fmaf(mv.x, wv.x, acc); acc = fmaf(mv.y, wv.y, acc); acc = fmaf(mv.z, wv.z, acc); acc = fmaf(mv.w, wv.w, acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      const float z = acc + b1[j];
+      hid[j] = z / (1.f + expf(-z));
+    }
+  }
+  __syncthreads();
+  // fc2: thread = (channel quad, j-slice js); slices are combined through shared memory in slice order
+  for (int item = threadIdx.x; item < Q * JS; item += SE_THREADS) {
+    const int q = item % Q, js = item / Q;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+    for (int j = js; j < S; j += JS) {
+      const float4 wv = *reinterpret_cast<const float4*>(w2t + static_cast<size_t>(j) * C + q * 4);
+      const float h = hid[j];
+      acc.x = fmaf(h, wv.x, acc.x); acc.y = fmaf(h, wv.y, acc.y); acc.z = fmaf(h, wv.z, acc.z); acc.w = fmaf(h, wv.w, acc.w);
+    }
+    *reinterpret_cast<float4*>(part + static_cast<size_t>(js) * C + q * 4) = acc;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += SE_THREADS) {
+    float acc = b2[c];
+    for (int js = 0; js < JS; ++js) acc += part[static_cast<size_t>(js) * C + c];
+    gate[static_cast<size_t>(n) * C + c] = 1.f / (1.f + expf(-acc));
+  }
+}
+
+int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw, const float* w1, const float* b1,
+                   const float* w2t, const float* b2, int s, float* gate, cudaStream_t stream) {
+  if (n <= 0 || strips <= 0 || c <= 0 || s <= 0) return fail(B200_ERR_INVALID, "se_gate: empty shape");
+  if (c % 4) return fail(B200_ERR_INVALID, "se_gate: channels must be a multiple of 4");
+  int js = SE_THREADS / (c / 4);
+  js = js < 1 ? 1 : (js > 8 ? 8 : js);
+  if (js > s) js = s;
+  const size_t smem = sizeof(float) * (static_cast<size_t>(c) * (1 + js) + s);
+  if (smem > 48 * 1024) return fail(B200_ERR_INVALID, "se_gate: more than ~6k channels unsupported");
+  se_gate_kernel<<<n, SE_THREADS, smem, stream>>>(partial, strips, c, inv_hw, w1, b1, w2t, b2, s, js, gate);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
 // y[n,h,w,c] = x[n,h,w,c] * gate[n][c]
 __global__ void __launch_bounds__(256)
 channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C8,

@@ -40,9 +40,11 @@ int gather_conv_kpad(int cin_p, int ksize);
 int gather_conv_launch(const View& in, const View& out, const View& res, const void* w, const float* bias, int ksize,
                        int stride, int pad, int act, bool res_after_act, cudaStream_t stream);
 
-// ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional per-(n,c) fp32 sum output for SE squeeze ----
+// ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional fused squeeze: per-strip fp32 channel sums of
+// the stored outputs, [N][dwconv3x3_strips()][C] (0 strips = this geometry has no strip kernel) ----
+int dwconv3x3_strips(int Ho, int Wo, int stride);
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
-                     float* se_sum /* [N][C] or null, must be zeroed */, cudaStream_t stream);
+                     float* se_partial /* or null */, cudaStream_t stream);
 
 // ---- pooling (pool.cu) ----
 int maxpool_launch(const View& in, const View& out, int ksize, int stride, int pad, cudaStream_t stream);
@@ -52,6 +54,9 @@ int global_avgpool_launch(const View& in, float* out /* [N][C] fp32 */, cudaStre
 // out[n][j] = act(sum_k x[n][k] * w[j][k] + b[j]);  x fp32 [N][K] (optionally pre-scaled), w fp32 [J][K]
 int fc_launch(const float* x, const float* w, const float* b, float* out, int n, int k, int j, float x_scale, int act,
               cudaStream_t stream);
+// gate[n][c] = sigmoid(fc2(silu(fc1(mean)))) from the depthwise kernel's strip sums; w1 [S][C], w2t [S][C] (fc2 transposed)
+int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw, const float* w1, const float* b1,
+                   const float* w2t, const float* b2, int s, float* gate, cudaStream_t stream);
 // y = x * gate[n][c]  (SE excitation), gate fp32 already passed through sigmoid
 int channel_scale_launch(const View& in, const View& out, const float* gate, cudaStream_t stream);
 

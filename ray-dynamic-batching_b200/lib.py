@@ -38,6 +38,11 @@ SIGNATURES = {
                                        c_int, c_int, c_int, c_void_p]),
     "b200_dwconv3x3_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                     c_int, c_int, c_void_p]),
+    "b200_dwconv3x3_strips": (c_int, [c_int, c_int, c_int]),
+    "b200_dwconv3x3_squeeze_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                            c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b200_se_gate": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                             c_void_p, c_void_p]),
     "b200_maxpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int,
                                   c_void_p]),
     "b200_global_avgpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -8,6 +8,7 @@ Blob layout (little endian): BlobHeader | BufRec[n_bufs] | OpRec[n_ops] | pad to
 See csrc/engine.h for the record definitions; `parse_blob` below is the inverse (used by the CPU plan interpreter in
 oracle/ to check the lowering without a GPU).
 """
+import os
 import struct
 from dataclasses import dataclass
 from typing import List, Optional
@@ -17,7 +18,7 @@ import torch
 import torch.nn as nn
 
 OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
-    OP_YOLO_DECODE, OP_GATHER_CONV = range(1, 13)
+    OP_YOLO_DECODE, OP_GATHER_CONV, OP_SE_GATE = range(1, 14)
 ACT_NONE, ACT_RELU, ACT_SILU, ACT_SIGMOID = 0, 1, 2, 3
 HEADER_FMT = "<8sIIII32siiiiii3f3fQQ"
 HEADER_SIZE = struct.calcsize(HEADER_FMT)
@@ -128,6 +129,7 @@ class PlanBuilder:
         self.toeplitz_stem = True
         self.fuse_stem_pool = __import__('os').environ.get('B200_FUSE_STEM_POOL', '0') == '1'
         self.gather_small_cin = True
+        self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
     # ---- buffers / weights ----
@@ -168,7 +170,9 @@ class PlanBuilder:
             out = self.new_act(ho, wo, cout)
         assert (out.h, out.w, out.c) == (ho, wo, cout)
         cin_p, cout_p = x.cphys, out.cphys
-        if self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
+        halo = (self.halo_small_cin and k == 3 and stride == 1 and pad == 1 and cin_p <= 64 and cout_p <= 256 and
+                ((x.w + 7) // 8 * 8) * ((x.h + 15) // 16 * 16) * 100 <= x.w * x.h * 135)   # conv_prepare's halo rule
+        if not halo and self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
                                                        (k == 1 and cin_p % 64 != 0 and cin_p <= self.gather_1x1_max_cin)):
             return self._gather_conv(x, weight, bias, stride, pad, act, res, out, name, res_after_act)
         wp = torch.zeros(cout_p, k * k, cin_p)
@@ -250,7 +254,16 @@ class PlanBuilder:
         self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, 64, -1, 0, 7, 2, 3, ACT_RELU, 3], w_off, b_off, name=name)
         return out
 
-    def dwconv(self, x: T, weight, bias, stride, act, out: Optional[T] = None, name=""):
+    @staticmethod
+    def dw_strips(ho, wo, stride):
+        """Strips per image of the depthwise strip kernel (csrc/dwconv.cu dwconv3x3_strips); 0 = no strip kernel."""
+        if wo % 7:
+            return 0
+        r = 2 if stride == 1 else 1
+        return ((ho + r - 1) // r) * (wo // 7)
+
+    def dwconv(self, x: T, weight, bias, stride, act, out: Optional[T] = None, name="", squeeze=False):
+        """squeeze=True: also returns the fp32 strip-sum buffer [strips][cphys] feeding se_gate (fused SE squeeze)."""
         c = weight.shape[0]
         assert weight.shape[1] == 1 and weight.shape[2] == 3 and c == x.c
         ho, wo = (x.h - 1) // stride + 1, (x.w - 1) // stride + 1
@@ -265,8 +278,37 @@ class PlanBuilder:
         bp[torch.as_tensor(x.cmap)] = bias
         w_off = self.add_weights(wp.numpy().astype(np.float32))
         b_off = self.add_weights(bp.numpy().astype(np.float32))
+        if squeeze:
+            strips = self.dw_strips(ho, wo, stride)
+            assert strips > 0
+            sums = self.new_buf(1, strips, cp, dtype=1)
+            self._op(OP_DWCONV, [x.buf, x.coff, cp, out.buf, out.coff, cp, -1, 0, 3, stride, 1, act, sums], w_off, b_off,
+                     name=name)
+            return out, (sums, strips)
         self._op(OP_DWCONV, [x.buf, x.coff, cp, out.buf, out.coff, cp, -1, 0, 3, stride, 1, act], w_off, b_off, name=name)
         return out
+
+    def se_gate(self, x: T, sums, w1, b1, w2, b2, name=""):
+        """Fused SE gate from the depthwise strip sums of x: sigmoid(fc2(silu(fc1(mean)))) -> fp32 vector buffer [cphys].
+        w1 fp32 [S, C], w2 fp32 [C, S] (torchvision's fc1 / fc2 1x1 conv weights, flattened)."""
+        sums_buf, strips = sums
+        sq, c = w1.shape
+        assert c == x.c and tuple(w2.shape) == (c, sq)
+        cp, sp = x.cphys, pad8(sq)
+        cm = torch.as_tensor(x.cmap)
+        w1p = torch.zeros(sp, cp)
+        w1p[:sq, cm] = w1
+        b1p = torch.zeros(sp)
+        b1p[:sq] = b1
+        w2t = torch.zeros(sp, cp)
+        w2t[:sq, cm] = w2.t()
+        b2p = torch.zeros(cp)
+        b2p[cm] = b2
+        out_buf = self.new_buf(1, 1, cp, dtype=1)
+        offs = [self.add_weights(a.numpy().astype(np.float32)) for a in (w1p, b1p, w2t, b2p)]
+        inv = struct.unpack("<i", struct.pack("<f", 1.0 / (x.h * x.w)))[0]
+        self._op(OP_SE_GATE, [sums_buf, strips, cp, out_buf, 0, cp, -1, 0, sp, 0, 0, 0, inv], *offs, name=name)
+        return T(out_buf, 0, x.c, 1, 1, cp, x.cmap)
 
     def maxpool(self, x: T, k, stride, pad, out: Optional[T] = None, name=""):
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
@@ -459,11 +501,13 @@ def lower_shufflenet(model, in_hw=(224, 224)) -> PlanBuilder:
     return pb
 
 
-def lower_efficientnet_v2(model, in_hw=(224, 224)) -> PlanBuilder:
+def lower_efficientnet_v2(model, in_hw=(224, 224), fuse_se=None) -> PlanBuilder:
     """torchvision EfficientNetV2-S: tv models/efficientnet.py:105-170 (MBConv), 172-231 (FusedMBConv), 333-345;
     SqueezeExcitation: tv ops/misc.py. stochastic_depth is the identity in eval mode."""
     from torchvision.models.efficientnet import FusedMBConv, MBConv
     pb = PlanBuilder("efficientnet_v2_s", in_hw[0], in_hw[1])
+    if fuse_se is None:      # depthwise conv writes the squeeze sums; one gate kernel replaces avgpool + fc1 + fc2
+        fuse_se = os.environ.get("B200_FUSE_SE", "1") != "0"
     feats = model.features
     w, b = fold_bn(feats[0][0], feats[0][1])
     x = pb.stem(pb.input(), w, b, 2, 1, ACT_SILU, name="features.0")
@@ -489,12 +533,19 @@ def lower_efficientnet_v2(model, in_hw=(224, 224)) -> PlanBuilder:
                 w, b = fold_bn(exp[0], exp[1])
                 t = pb.conv(x, w, b, 1, 0, ACT_SILU, name=nm + "expand")
                 w, b = fold_bn(dw[0], dw[1])
-                t = pb.dwconv(t, w, b, dw[0].stride[0], ACT_SILU, name=nm + "dw")
-                s = pb.avgpool(t, name=nm + "se.squeeze")
-                s = pb.fc(s, se.fc1.weight.detach().float().flatten(1), se.fc1.bias.detach().float(), ACT_SILU,
-                          name=nm + "se.fc1")
-                s = pb.fc(s, se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float(), ACT_SIGMOID,
-                          name=nm + "se.fc2")
+                st = dw[0].stride[0]
+                if fuse_se and pb.dw_strips((t.h - 1) // st + 1, (t.w - 1) // st + 1, st) > 0:
+                    t, sums = pb.dwconv(t, w, b, st, ACT_SILU, name=nm + "dw", squeeze=True)
+                    s = pb.se_gate(t, sums, se.fc1.weight.detach().float().flatten(1), se.fc1.bias.detach().float(),
+                                   se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float(),
+                                   name=nm + "se.gate")
+                else:
+                    t = pb.dwconv(t, w, b, st, ACT_SILU, name=nm + "dw")
+                    s = pb.avgpool(t, name=nm + "se.squeeze")
+                    s = pb.fc(s, se.fc1.weight.detach().float().flatten(1), se.fc1.bias.detach().float(), ACT_SILU,
+                              name=nm + "se.fc1")
+                    s = pb.fc(s, se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float(), ACT_SIGMOID,
+                              name=nm + "se.fc2")
                 t = pb.scale(t, s, name=nm + "se.scale")
                 w, b = fold_bn(proj[0], proj[1])
                 x = pb.conv(t, w, b, 1, 0, ACT_NONE, res=res, name=nm + "project")

@@ -59,6 +59,13 @@ CASES = [
     (1, 16, 24, 64, 64, 3, 1, 1, "none", False),     # halo-tile kernel, one tile high, three wide
     (5, 56, 56, 64, 64, 3, 1, 1, "relu", False),     # halo-tile kernel, odd batch (tile count not a multiple of anything)
     (2, 20, 20, 64, 64, 3, 1, 1, "relu", False),     # W not a multiple of 8 / H waste too high: generic kernel
+    (2, 112, 112, 24, 24, 3, 1, 1, "silu", True),    # halo kernel, 64-byte pixels (24 -> 32 channels zero-filled by TMA), N = 32
+    (1, 56, 56, 48, 192, 3, 1, 1, "silu", False),    # halo kernel, 128-byte pixels, three resident channel tiles
+    (2, 160, 160, 16, 16, 3, 1, 1, "silu", False),   # halo kernel, 32-byte pixels (YOLOv8n c2f bottleneck at 160x160)
+    (3, 80, 80, 32, 32, 3, 1, 1, "silu", True),      # halo kernel, 64-byte pixels, residual
+    (2, 30, 30, 8, 40, 3, 1, 1, "relu", False),      # halo kernel, Cin = 8, W not a multiple of 8, Cout 40 -> N = 64
+    (5, 48, 40, 48, 136, 3, 1, 1, "none", True),     # halo kernel, odd batch, three channel tiles, last one ragged (136 = 2*64 + 8)
+    (1, 17, 9, 16, 200, 3, 1, 1, "relu", False),     # too much tile padding for the halo kernel: generic kernel, thin K
 ]
 
 

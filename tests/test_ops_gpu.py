@@ -135,6 +135,62 @@ def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
     assert ok, e
 
 
+@pytest.mark.parametrize("n,h,w,c,stride,act", [(3, 14, 14, 960, 1, 2), (2, 7, 7, 1536, 1, 2), (2, 28, 28, 256, 2, 2),
+                                                (5, 14, 14, 960, 2, 2), (1, 21, 7, 8, 1, 0), (2, 13, 14, 16, 2, 1)])
+def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, act):
+    """Strip kernel with the SE squeeze fused in (odd row counts, both strides), then the one-launch gate; against
+    torch: AdaptiveAvgPool2d(1) of the STORED output, fc1 + SiLU, fc2 + sigmoid (tv ops/misc.py:249-254)."""
+    x = rnd((n, h, w, c), 11, cuda)
+    wt = rnd((c, 1, 3, 3), 12, cuda, torch.float32) / 3
+    b = rnd((c,), 13, cuda, torch.float32)
+    ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
+    strips = b200lib.b200_dwconv3x3_strips(ho, wo, stride)
+    assert strips == ((ho + 1) // 2 if stride == 1 else ho) * (wo // 7)
+    out = torch.full((n, ho, wo, c), float("nan"), device=cuda, dtype=torch.bfloat16)
+    sums = torch.full((n, strips, c), float("nan"), device=cuda)
+    w9 = wt.reshape(c, 9).t().contiguous()
+    check(b200lib.b200_dwconv3x3_squeeze_nhwc(ptr(x), n, h, w, c, 0, ptr(w9), ptr(b), ptr(out), 0, stride, act,
+                                              ptr(sums), stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt, b, stride=stride, padding=1, groups=c)
+    ref = (F.silu(ref) if act == 2 else F.relu(ref) if act == 1 else ref).permute(0, 2, 3, 1)
+    ok, e = close_bf16(out, ref)
+    assert ok, e
+    want_sum = out.float().sum(dim=(1, 2))
+    assert torch.allclose(sums.sum(dim=1), want_sum, rtol=1e-5, atol=1e-4)
+    # same output as the plain entry point, bit for bit
+    out2 = torch.empty_like(out)
+    check(b200lib.b200_dwconv3x3_nhwc(ptr(x), n, h, w, c, 0, ptr(w9), ptr(b), ptr(out2), 0, stride, act, stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(out.view(torch.int16), out2.view(torch.int16))
+
+    sq = max(8, c // 24 // 8 * 8)
+    w1 = rnd((sq, c), 14, cuda, torch.float32) / c ** 0.5
+    b1 = rnd((sq,), 15, cuda, torch.float32)
+    w2 = rnd((c, sq), 16, cuda, torch.float32) / sq ** 0.5
+    b2 = rnd((c,), 17, cuda, torch.float32)
+    w2t = w2.t().contiguous()
+    gate = torch.full((n, c), float("nan"), device=cuda)
+    check(b200lib.b200_se_gate(ptr(sums), n, strips, c, 1.0 / (ho * wo), ptr(w1), ptr(b1), ptr(w2t), ptr(b2), sq, ptr(gate),
+                               stream_ptr()))
+    torch.cuda.synchronize()
+    mean = out.float().mean(dim=(1, 2))
+    want = torch.sigmoid(F.silu(mean @ w1.t() + b1) @ w2.t() + b2)
+    assert torch.allclose(gate, want, rtol=1e-4, atol=1e-5), (gate - want).abs().max().item()
+
+
+def test_dwconv3x3_squeeze_rejects_widths_without_strips(b200lib, cuda):
+    x = rnd((1, 10, 10, 8), 1, cuda)
+    w9 = torch.zeros(9, 8, device=cuda)
+    b = torch.zeros(8, device=cuda)
+    out = torch.empty(1, 10, 10, 8, device=cuda, dtype=torch.bfloat16)
+    sums = torch.empty(1, 16, 8, device=cuda)
+    assert b200lib.b200_dwconv3x3_strips(10, 10, 1) == 0
+    rc = b200lib.b200_dwconv3x3_squeeze_nhwc(ptr(x), 1, 10, 10, 8, 0, ptr(w9), ptr(b), ptr(out), 0, 1, 0, ptr(sums),
+                                             stream_ptr())
+    assert rc != 0
+
+
 @pytest.mark.parametrize("n,h,w,c,k,s,p", [(2, 112, 112, 64, 3, 2, 1), (1, 20, 20, 128, 5, 1, 2), (3, 7, 9, 24, 3, 2, 1)])
 def test_maxpool_bit_exact(b200lib, cuda, n, h, w, c, k, s, p):
     x = rnd((n, h, w, c), 4, cuda)

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Per-op gap to the roofline: measured us vs max(bytes / HBM peak, flops / tensor peak), sorted by absolute gap."""
-import json, os, sys
+import json, os, re, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import numpy as np, torch
@@ -32,4 +32,17 @@ tot, totb = sum(r[2] for r in rows), sum(r[3] for r in rows)
 print("%-28s %8s %8s %8s" % ("op", "us", "bound", "gap"))
 for g, n, u, b, k in rows[:24]:
     print("%-28s %8.1f %8.1f %8.1f  %s" % (n, u, b, g, k))
+if os.environ.get("GAP_ALL"):
+    import collections
+    agg = collections.defaultdict(lambda: [0, 0.0, 0.0])
+    for g, n, u, b, k in rows:
+        key = re.sub(r"\d+", "#", n)
+        agg[key][0] += 1; agg[key][1] += u; agg[key][2] += b
+    print("--- by op family")
+    for key, (c, u, b) in sorted(agg.items(), key=lambda kv: -(kv[1][1] - kv[1][2])):
+        print("%-28s x%-3d %8.1f %8.1f %8.1f" % (key, c, u, b, u - b))
 print("TOTAL measured %.0f us, sum of per-op bounds %.0f us (%.0f%%)" % (tot, totb, 100 * totb / tot))
+if os.environ.get("GAP_GREP"):
+    for g, n, u, b, k in sorted(rows, key=lambda r: r[1]):
+        if re.search(os.environ["GAP_GREP"], n):
+            print("%-28s %8.1f %8.1f %8.1f  %s" % (n, u, b, g, k))
