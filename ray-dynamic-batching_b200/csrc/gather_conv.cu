@@ -175,7 +175,8 @@ gather_conv_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_consta
     }
   } else {
     // =========================== weight TMA + MMA issuer ===========================
-    if (lane == 0) {
+    // whole warp in the loops, one elected lane issues (see elect_one in ptx.cuh)
+    {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NPAD);
       const uint32_t total_kb = static_cast<uint32_t>(my_tiles) * p.kb;
       uint32_t wl = 0;  // weight k-blocks requested
@@ -183,8 +184,10 @@ gather_conv_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_consta
         const int s = wl % GC_STAGES;
         mbar_wait(smem_u32(&bar_empty[s]), ((wl / GC_STAGES) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_full[s]);
-        mbar_expect_tx(full, NPAD * 128);
-        tma_load_2d(&wmap, full, ring + s * STAGE_BYTES + 128 * 128, static_cast<int>(wl % p.kb) * 64, 0);
+        if (elect_one()) {
+          mbar_expect_tx(full, NPAD * 128);
+          tma_load_2d(&wmap, full, ring + s * STAGE_BYTES + 128 * 128, static_cast<int>(wl % p.kb) * 64, 0);
+        }
         ++wl;
       };
       for (int i = 0; i < GC_STAGES - 1 && wl < total_kb; ++i) request_weights();
@@ -200,12 +203,14 @@ gather_conv_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_consta
           const uint32_t a_src = ring + s * STAGE_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_src);
           const uint64_t bdesc = umma_desc_sw128(a_src + 128 * 128);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + b * NPAD, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
-          umma_commit(smem_u32(&bar_empty[s]));
+            for (int k = 0; k < 4; ++k) umma_bf16(tmem_base + b * NPAD, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_commit(smem_u32(&bar_empty[s]));
+            if (kb == p.kb - 1) umma_commit(smem_u32(&bar_t_full[b]));
+          }
           if (wl < total_kb) request_weights();   // refill the ring (waits for the slot freed GC_STAGES-1 blocks ago)
         }
-        umma_commit(smem_u32(&bar_t_full[b]));
       }
     }
     __syncwarp();

@@ -99,13 +99,14 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   };
 
   if (warp == 0) {
-    if (lane == 0) {
-      for (int it = 0; it < my_tiles; ++it) {
-        int n_oh, oh, ow0;
-        tile_coords(it, n_oh, oh, ow0);
-        const int s = it % SR_STAGES;
-        mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
-        const uint32_t full = smem_u32(&bar_full[s]);
+    // whole warp in the loop, one elected lane issues (see elect_one in ptx.cuh)
+    for (int it = 0; it < my_tiles; ++it) {
+      int n_oh, oh, ow0;
+      tile_coords(it, n_oh, oh, ow0);
+      const int s = it % SR_STAGES;
+      mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
+      const uint32_t full = smem_u32(&bar_full[s]);
+      if (elect_one()) {
         mbar_expect_tx(full, 7 * SR_ROW_BYTES);
         // box [64 (16 pixels), 18 groups, 7 rows, 1 image] at (0, ow0/8 - 1, 2*oh - 3, n); outside the image -> zeros
         tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - 3, n_oh / p.Ho);
@@ -113,7 +114,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
       for (int it = 0; it < my_tiles; ++it) {
         const int b = it & 1, s = it % SR_STAGES;
@@ -121,18 +122,20 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
         mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
         tc_fence_after();
         const uint32_t a0 = ring + s * SR_STAGE_BYTES;
+        if (elect_one()) {
 #pragma unroll
-        for (int r = 0; r < 7; ++r) {
+          for (int r = 0; r < 7; ++r) {
 #pragma unroll
-          for (int kk = 0; kk < 2; ++kk) {
-            // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride 1024, 8-row stride 128
-            const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
-            const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
-            umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+            for (int kk = 0; kk < 2; ++kk) {
+              // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride 1024, 8-row stride 128
+              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
+              const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
+              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+            }
           }
+          umma_commit(smem_u32(&bar_empty[s]));
+          umma_commit(smem_u32(&bar_t_full[b]));
         }
-        umma_commit(smem_u32(&bar_empty[s]));
-        umma_commit(smem_u32(&bar_t_full[b]));
       }
     }
     __syncwarp();
@@ -279,7 +282,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   };
 
   if (warp == 0) {
-    if (lane == 0) {
+    {
       int it = 0;
       for (int u = unit0; u < unit0 + my_units; ++u) {
         int n, ph0, ph1, y_lo, y_hi;
@@ -288,14 +291,16 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           const int s = it % SR_STAGES;
           mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
-          mbar_expect_tx(full, 7 * SR_ROW_BYTES);
-          tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - 3, n);
+          if (elect_one()) {
+            mbar_expect_tx(full, 7 * SR_ROW_BYTES);
+            tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - 3, n);
+          }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
+    {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
       int it = 0;
       for (int u = unit0; u < unit0 + my_units; ++u) {
@@ -307,17 +312,19 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
           tc_fence_after();
           const uint32_t a0 = ring + s * SR_STAGE_BYTES;
+          if (elect_one()) {
 #pragma unroll
-          for (int r = 0; r < 7; ++r) {
+            for (int r = 0; r < 7; ++r) {
 #pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {
-              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
-              const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
-              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+              for (int kk = 0; kk < 2; ++kk) {
+                const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
+                const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
+                umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+              }
             }
+            umma_commit(smem_u32(&bar_empty[s]));
+            umma_commit(smem_u32(&bar_t_full[b]));
           }
-          umma_commit(smem_u32(&bar_empty[s]));
-          umma_commit(smem_u32(&bar_t_full[b]));
         }
       }
     }

@@ -172,16 +172,19 @@ stem_tc_kernel(const __grid_constant__ CUtensorMap wmap, const uint16_t* __restr
     }
   } else {
     // =========================== weights + MMA issuer ===========================
-    if (lane == 0) {
+    // whole warp in the loop, one elected lane issues (see elect_one in ptx.cuh)
+    if (elect_one()) {
       mbar_expect_tx(smem_u32(&bar_w), G::KB * NOUT * 128);
       for (int kb = 0; kb < G::KB; ++kb) tma_load_2d(&wmap, smem_u32(&bar_w), w_buf + kb * (NOUT * 128), kb * 64, 0);
-      mbar_wait(smem_u32(&bar_w), 0);
-      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
-      for (int it = 0; it < my_tiles; ++it) {
-        const int b = it & 1;
-        mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
-        mbar_wait(smem_u32(&bar_a_full[b]), (it >> 1) & 1);
-        tc_fence_after();
+    }
+    mbar_wait(smem_u32(&bar_w), 0);
+    constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
+    for (int it = 0; it < my_tiles; ++it) {
+      const int b = it & 1;
+      mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
+      mbar_wait(smem_u32(&bar_a_full[b]), (it >> 1) & 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kb = 0; kb < G::KB; ++kb) {
           const uint64_t adesc = umma_desc_sw128(a_buf[b] + kb * (128 * 128));
