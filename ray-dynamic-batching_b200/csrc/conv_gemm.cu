@@ -201,16 +201,19 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 // overlap (smem ring continues across tiles, two TMEM accumulators, three output-staging buffers).
 //   warp 0 : TMA producer (A/B ring)              warp 1 : MMA issuer (TMEM accumulator it & 1)
 //   warp 2 : "DMA" thread: prefetches the residual tile into staging[it % 3] and issues the TMA store of tile it-1
-//   warps 4-7 : epilogue (TMEM -> +bias/+res/act -> bf16 -> staging, in place over the residual)
+//   warps 4-7, 8-11 : two epilogue warpgroups (TMEM -> +bias/+res/act -> bf16 -> staging, in place over the residual);
+//                     group g drains accumulator g of every second tile, so thin-K layers, whose tile time IS the
+//                     epilogue (~0.6 us with SiLU), overlap two of them
 // ================================================================================================================
-static constexpr int PCONV_THREADS = 256;
+static constexpr int PCONV_THREADS = 384;
+static constexpr int HALO_THREADS = 256;
 
 // Without a residual the staging ring only has to cover the store of the previous tile (2 buffers); the shared memory that
 // frees goes into a deeper A/B ring, which is what the HBM-bound layers need (bytes in flight per SM ~ latency x bandwidth).
 template <int BLOCK_N, int RES>
 struct PConvCfg {
-  static constexpr int STAGES = RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 8 : 5);      // A/B ring
-  static constexpr int OUT_BUFS = RES ? (BLOCK_N == 64 ? 6 : 4) : 2;                           // output / residual staging ring
+  static constexpr int STAGES = RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4);      // A/B ring
+  static constexpr int OUT_BUFS = RES ? (BLOCK_N == 64 ? 6 : 4) : 3;                           // output / residual staging ring
   static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -255,7 +258,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   __shared__ __align__(8) uint64_t bar_stage_ready[NB];  // staging buffer free (and residual landed, if any)
   __shared__ __align__(8) uint64_t bar_out_ready[NB];    // epilogue finished writing the staging buffer
   __shared__ uint32_t tmem_base_s;
-  __shared__ __align__(16) float bias_s[2][BLOCK_N];
+  __shared__ __align__(16) float bias_s[2][BLOCK_N];   // one per epilogue warpgroup
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -408,22 +411,25 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     __syncwarp();
   } else if (warp >= 4) {
     // =========================== epilogue ===========================
-    const int epi_tid = threadIdx.x - 128;  // 0..127
+    const int wg = (warp - 4) >> 2;                  // epilogue warpgroup 0 / 1 <-> accumulator 0 / 1
+    const int epi_tid = (threadIdx.x - 128) & 127;   // 0..127 within the group
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t row_off = row * 128;
     const int sw = row & 7;
-    for (int it = 0; it < my_tiles; ++it) {
+    for (int it = wg; it < my_tiles; it += 2) {
       const int tile0_ = blockIdx.x + it * gridDim.x;
       const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
       const int b = it & 1;
+      const int bb = wg;
       const int ob = it % NB;
       const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      named_bar_sync(1 + wg, 128);               // every thread of the group is done reading the previous tile's bias
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
         const int c = n0 + i;
-        bias_s[b][i] = (c < p.cout) ? p.bias[c] : 0.f;
+        bias_s[bb][i] = (c < p.cout) ? p.bias[c] : 0.f;
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1 + wg, 128);
       mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
       tc_fence_after();
       mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
@@ -439,8 +445,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         for (int g = 0; g < 4; ++g) {
           const int chunk = (cc & 1) * 4 + g;
           const uint32_t addr = sub + ((chunk ^ sw) << 4);
-          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8]);
-          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[b][cc * 32 + g * 8 + 4]);
+          const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[bb][cc * 32 + g * 8]);
+          const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[bb][cc * 32 + g * 8 + 4]);
           float f[8];
           f[0] = __uint_as_float(v[g * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[g * 8 + 1]) + b0.y;
           f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
@@ -512,7 +518,7 @@ __device__ __forceinline__ uint64_t umma_desc_swz(uint32_t smem_addr, uint32_t s
 }
 
 template <int RES, int ACT>
-__global__ void __launch_bounds__(PCONV_THREADS, 1)
+__global__ void __launch_bounds__(HALO_THREADS, 1)
 conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p, const int total_tiles) {
   using Cfg = HaloCfg;
   constexpr int BLOCK_N = 64;          // accumulator stride in TMEM and bias buffer size; the tile's width is p.block_n
@@ -1333,7 +1339,7 @@ static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
   const int total = static_cast<int>(l.grid);
   int ctas = total < device_sm_count() ? total : device_sm_count();
   ctas -= ctas % l.p.n_tiles;    // a CTA keeps ONE channel tile's weights resident: tile stride must preserve tile % n_tiles
-  conv3x3_halo_kernel<RES, ACT><<<ctas, PCONV_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
+  conv3x3_halo_kernel<RES, ACT><<<ctas, HALO_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }
