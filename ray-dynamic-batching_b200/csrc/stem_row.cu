@@ -222,7 +222,7 @@ __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
   return *reinterpret_cast<uint32_t*>(&m);
 }
 
-static constexpr int SP_THREADS = 384;   // warps 0: TMA, 1: MMA, 4-7: accumulator drain, 8-11: pooling
+static constexpr int SP_THREADS = 512;   // warps 0: TMA, 1: MMA, 4-7 / 8-11: drain of accumulator 0 / 1, 12-15: pooling
 static constexpr int SP_RING = 4;        // stem rows kept in shared memory
 
 __global__ void __launch_bounds__(SP_THREADS, 1)
@@ -329,8 +329,11 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       }
     }
     __syncwarp();
-  } else if (warp >= 4 && warp < 8) {
+  } else if (warp >= 4 && warp < 12) {
     // =========================== accumulator drain: TMEM -> +bias -> ReLU -> bf16 -> row ring ===========================
+    // Two warpgroups, one per accumulator: group g drains every second stem row, so the drain (~1000 cycles per row:
+    // two dependent TMEM loads, bias, ReLU, pack, 8 stores) keeps up with the ~450-cycle MMA of a row.
+    const int dwg = (warp - 4) >> 2;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;     // stem pixel (ow) owned by this thread
     const int sw = row & 7;
@@ -340,6 +343,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
         const int b = it & 1, slot = it % SP_RING;
+        if (b != dwg) continue;
         mbar_wait(smem_u32(&bar_row_free[slot]), ((it / SP_RING) & 1) ^ 1);   // pooling is done with the row that lived here
         mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
         tc_fence_after();
@@ -353,9 +357,13 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             const int chunk = cc * 4 + g;
+            const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[chunk * 8]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[chunk * 8 + 4]);
             float f[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) f[i] = fmaxf(__uint_as_float(v[g * 8 + i]) + bias_s[chunk * 8 + i], 0.f);
+            f[0] = fmaxf(__uint_as_float(v[g * 8 + 0]) + b0.x, 0.f); f[1] = fmaxf(__uint_as_float(v[g * 8 + 1]) + b0.y, 0.f);
+            f[2] = fmaxf(__uint_as_float(v[g * 8 + 2]) + b0.z, 0.f); f[3] = fmaxf(__uint_as_float(v[g * 8 + 3]) + b0.w, 0.f);
+            f[4] = fmaxf(__uint_as_float(v[g * 8 + 4]) + b1.x, 0.f); f[5] = fmaxf(__uint_as_float(v[g * 8 + 5]) + b1.y, 0.f);
+            f[6] = fmaxf(__uint_as_float(v[g * 8 + 6]) + b1.z, 0.f); f[7] = fmaxf(__uint_as_float(v[g * 8 + 7]) + b1.w, 0.f);
             const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
             const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((chunk ^ sw) << 4)), "r"(o0), "r"(o1),
@@ -368,9 +376,9 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         mbar_arrive(smem_u32(&bar_row_ready[slot]));
       }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 12) {
     // =========================== pooling warps: 3x3 / stride 2 max over the row ring, coalesced stores ===========================
-    const int ptid = threadIdx.x - 256;       // 0..127
+    const int ptid = threadIdx.x - 384;       // 0..127
     int it = 0;
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
@@ -384,23 +392,28 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
           for (int item = ptid; item < Wp * 8; item += 128) {
             const int pw = item >> 3, chunk = item & 7;
-            uint4 m = make_uint4(0, 0, 0, 0);          // post-ReLU values are >= 0, so 0 is the identity of max
+            // Branch-free window: a tap outside the image is replaced by its in-window neighbour (max is idempotent), so
+            // the nine 16-byte loads are independent and issue back to back; with a branch per tap this loop was
+            // latency-bound and the pooling warps were the kernel's bottleneck.  Only the left column (pw = 0) and the top
+            // row of the image (y = 1) ever clamp: Wo and Ho are even.
+            uint4 v[9];
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy) {
-              const int yy = y - 2 + dy;
-              if (yy < y_lo) continue;                 // above the image (or above the band's halo row: never happens)
-              const uint32_t rbase = rows + ((it - 2 + dy) % SP_RING) * SR_OUT_BYTES;
+              const int back = (y - 2 + dy < y_lo) ? 1 : 2 - dy;      // rows y-2, y-1, y live in slots it-2, it-1, it
+              const uint32_t rbase = rows + ((it - back) % SP_RING) * SR_OUT_BYTES;
 #pragma unroll
               for (int dx = 0; dx < 3; ++dx) {
-                const int xx = 2 * pw - 1 + dx;
-                if (xx < 0 || xx >= p.Wo) continue;
-                uint32_t a0, a1, a2, a3;
+                const int xx = max(2 * pw - 1 + dx, 0);
                 asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];"
-                             : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3)
+                             : "=r"(v[dy * 3 + dx].x), "=r"(v[dy * 3 + dx].y), "=r"(v[dy * 3 + dx].z), "=r"(v[dy * 3 + dx].w)
                              : "r"(rbase + xx * 128 + ((chunk ^ (xx & 7)) << 4)));
-                m.x = bf16x2_max_u32(m.x, a0); m.y = bf16x2_max_u32(m.y, a1);
-                m.z = bf16x2_max_u32(m.z, a2); m.w = bf16x2_max_u32(m.w, a3);
               }
+            }
+            uint4 m = v[0];
+#pragma unroll
+            for (int t = 1; t < 9; ++t) {
+              m.x = bf16x2_max_u32(m.x, v[t].x); m.y = bf16x2_max_u32(m.y, v[t].y);
+              m.z = bf16x2_max_u32(m.z, v[t].z); m.w = bf16x2_max_u32(m.w, v[t].w);
             }
             *reinterpret_cast<uint4*>(orow + static_cast<size_t>(pw) * p.out_ps + chunk * 8) = m;
           }

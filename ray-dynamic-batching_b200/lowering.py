@@ -127,7 +127,7 @@ class PlanBuilder:
         self.names = []     # op index -> human readable name (kept out of the blob)
         self.tensor_core_stem = True
         self.toeplitz_stem = True
-        self.fuse_stem_pool = __import__('os').environ.get('B200_FUSE_STEM_POOL', '0') == '1'
+        self.fuse_stem_pool = os.environ.get('B200_FUSE_STEM_POOL', '1') != '0'   # conv1 + bn1 + relu + maxpool in one kernel
         self.gather_small_cin = True
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
