@@ -206,7 +206,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 //                     epilogue (~0.6 us with SiLU), overlap two of them
 // ================================================================================================================
 static constexpr int PCONV_THREADS = 384;
-static constexpr int HALO_THREADS = 256;
+static constexpr int HALO_THREADS = 384;   // warps 0-2: TMA / MMA / DMA, 4-7 and 8-11: two epilogue warpgroups
 
 // Without a residual the staging ring only has to cover the store of the previous tile (2 buffers); the shared memory that
 // frees goes into a deeper A/B ring, which is what the HBM-bound layers need (bytes in flight per SM ~ latency x bandwidth).
@@ -487,27 +487,38 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
 // 3x3 / stride 1 / pad 1 convolution with few input channels (Cin <= 64) from a halo tile.
 // The generic kernel loads the 128-pixel input tile nine times (once per tap) and the weights once per tile, which makes a
 // narrow layer shared-memory-bandwidth bound (~31 % of the tensor peak at 64 channels, far less below).  Here a tile is
-// 16 rows x 8 pixels of one image; ONE TMA box brings its 18-row x 16-pixel halo and the nine taps are nine shifted *views*
-// of it: descriptor start = halo + (dy*16 + dx) * PB, SBO = 16 * PB (one halo row per 8-pixel group), base_offset 0 (the
+// 16 rows x 8 pixels of one image; ONE TMA box brings its 18-row x 10-pixel halo and the nine taps are nine shifted *views*
+// of it: descriptor start = halo + (dy*10 + dx) * PB, SBO = 10 * PB (one halo row per 8-pixel group), base_offset 0 (the
 // hardware swizzles on absolute address bits, so shifted starts stay consistent with what TMA wrote).
 // PB = bytes per staged pixel = the swizzle span: 128 B (33..64 channels), 64 B (17..32) or 32 B (<= 16); channels between
 // Cin and PB/2 are out of bounds of the tensor map and arrive as zeros, so HBM keeps the compact layout.  GEMM-K per tap is
 // PB/2.  The 9 x N x PB/2 weights of the CTA's output-channel tile (N = 32 or 64) stay resident in shared memory; with
 // Cout > 64 the grid is a multiple of the channel tiles so that a CTA always works on the same one.
+// Measured floor (ablation on B200, 256 x 56 x 56 x 64 -> 64): with loads, stores and the epilogue all disabled the 36
+// M128 x N64 x K16 MMAs of a tile still take ~1.7 us (~90 cycles each, aligned or shifted views alike): operands stream
+// from shared memory at ~64 B/clk/SM (A 4 KB + B 2 KB per MMA), so 64-wide layers are operand-bandwidth bound at ~45 %
+// of the tensor peak whatever the pipelining; the same law gives 128 cycles for N = 128 and peak only for CTA pairs.
 // ================================================================================================================
-static constexpr int HALO_ROWS = 18, HALO_PITCH_PX = 16;
+static constexpr int HALO_ROWS = 18, HALO_PITCH_PX = 10;   // exactly the 18 x 10 pixels a 16 x 8 tile needs
 static constexpr int HALO_MAX_STAGES = 4;
 
 struct HaloCfg {
   static constexpr int OUT_BUFS = 4;
   static constexpr int LOOKAHEAD = 2;
   static constexpr int OUT_BYTES = BLOCK_M * 64 * 2;
-  static constexpr int halo_bytes(int pb) { return HALO_ROWS * HALO_PITCH_PX * pb; }
+  static constexpr int halo_bytes(int pb) { return HALO_ROWS * HALO_PITCH_PX * pb; }               // what TMA delivers
+  static constexpr int halo_stride(int pb) { return (halo_bytes(pb) + 1023) / 1024 * 1024; }       // stage pitch
   static constexpr int w_bytes(int pb, int n) { return 9 * n * pb; }
   static constexpr int smem_bytes(int pb, int n, int stages) {
-    return w_bytes(pb, n) + stages * halo_bytes(pb) + OUT_BUFS * OUT_BYTES + 1024;
+    return w_bytes(pb, n) + stages * halo_stride(pb) + OUT_BUFS * OUT_BYTES + 1024;
   }
 };
+
+__device__ __forceinline__ uint64_t make_u64(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
 
 // K-major swizzled descriptor (span = pb bytes) with explicit 8-row-group stride; start need not be atom aligned
 __device__ __forceinline__ uint64_t umma_desc_swz(uint32_t smem_addr, uint32_t sbo_bytes, int pb) {
@@ -517,15 +528,16 @@ __device__ __forceinline__ uint64_t umma_desc_swz(uint32_t smem_addr, uint32_t s
   return (static_cast<uint64_t>(hi) << 32) | lo;
 }
 
-template <int RES, int ACT>
+template <int PB, int RES, int ACT>
 __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p, const int total_tiles) {
   using Cfg = HaloCfg;
   constexpr int BLOCK_N = 64;          // accumulator stride in TMEM and bias buffer size; the tile's width is p.block_n
   constexpr int NB = Cfg::OUT_BUFS;
   constexpr int LA = Cfg::LOOKAHEAD;
-  const int PB = p.pb, N = p.block_n, HS = p.halo_stages;
-  const int halo_bytes = Cfg::halo_bytes(PB), tap_bytes = N * PB;
+  const int N = p.block_n, HS = p.halo_stages;
+  constexpr int halo_bytes = Cfg::halo_bytes(PB), halo_stride = Cfg::halo_stride(PB);
+  const int tap_bytes = N * PB;
 
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_halo_full[HALO_MAX_STAGES];
@@ -542,7 +554,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   const int lane = threadIdx.x & 31;
   const uint32_t wres = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t halo = wres + 9 * tap_bytes;
-  const uint32_t staging = halo + HS * halo_bytes;
+  const uint32_t staging = halo + HS * halo_stride;
   const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
@@ -594,29 +606,26 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         const uint32_t full = smem_u32(&bar_halo_full[hb]);
         if (elect_one()) {
           mbar_expect_tx(full, halo_bytes);
-          tma_load_4d(&maps.a[0], full, halo + hb * halo_bytes, 0, w0 - 1, h0 - 1, nb0);   // box [PB/2, 16, 18, 1]
+          tma_load_4d(&maps.a[0], full, halo + hb * halo_stride, 0, w0 - 1, h0 - 1, nb0);   // box [PB/2, 10, 18, 1]
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     // =========================== MMA issuer: nine shifted views of the halo ===========================
-    // The whole warp walks the tile loop (uniform control flow); one elected lane issues the MMAs.
+    // The whole warp walks the tile loop (uniform control flow); one elected lane issues the MMAs.  This one thread
+    // issues every MMA of the CTA, so the issue sequence is kept to ~3 uniform-datapath instructions per MMA: the
+    // descriptors' high words are loop constants, the low words (start address >> 4) are a per-tile base plus
+    // compile-time tap / k offsets.  base_offset stays 0: measured on B200, the swizzle is applied to the absolute
+    // shared-memory address bits, so a start shifted by dx pixels sees exactly the pattern TMA wrote.
     if (my_tiles > 0) {
       const uint32_t idesc = umma_idesc_bf16_f32(BLOCK_M, N);
-      const int ksteps = PB >> 5;      // K = 16 (32 bytes) per MMA
-      // Everything that does not depend on the tile is hoisted.  base_offset stays 0: measured on B200, the swizzle is
-      // applied to the absolute shared-memory address bits, so a start shifted by dx pixels sees exactly the pattern TMA
-      // wrote (base_offset = dx gives garbage).
-      uint64_t bdesc[9];
-      uint32_t aoff[9];                // tap offset inside the halo, in the descriptor's 16-byte units
-#pragma unroll
-      for (int t = 0; t < 9; ++t) {
-        bdesc[t] = umma_desc_swz(wres + t * tap_bytes, 8 * PB, PB);
-        aoff[t] = static_cast<uint32_t>(((t / 3) * HALO_PITCH_PX + (t % 3)) * PB) >> 4;
-      }
+      constexpr int KSTEPS = PB / 32;     // K = 16 (32 bytes) per MMA
       const uint64_t adesc0 = umma_desc_swz(halo, HALO_PITCH_PX * PB, PB);
-      const uint32_t halo_step = static_cast<uint32_t>(halo_bytes) >> 4;
+      const uint64_t bdesc0 = umma_desc_swz(wres, 8 * PB, PB);
+      const uint32_t a_hi = static_cast<uint32_t>(adesc0 >> 32), b_hi = static_cast<uint32_t>(bdesc0 >> 32);
+      const uint32_t a_lo0 = static_cast<uint32_t>(adesc0), b_lo0 = static_cast<uint32_t>(bdesc0);
+      const uint32_t wtap = static_cast<uint32_t>(tap_bytes) >> 4;
       mbar_wait(smem_u32(&bar_w_full), 0);
       for (int it = 0; it < my_tiles; ++it) {
         const int b = it & 1, hb = it % HS;
@@ -624,14 +633,15 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         mbar_wait(smem_u32(&bar_halo_full[hb]), (it / HS) & 1);
         tc_fence_after();
         const uint32_t acc = tmem_base + b * BLOCK_N;
-        const uint64_t abase = adesc0 + hb * halo_step;     // start-address field: (halo + hb * halo_bytes) >> 4, no carry out of 14 bits
+        const uint32_t a_lo = a_lo0 + hb * (halo_stride >> 4);   // no carry out of the 14-bit address field: smem < 256 KB
         if (elect_one()) {
 #pragma unroll
           for (int t = 0; t < 9; ++t) {
-            const uint64_t ad = abase + aoff[t];
+            const uint32_t a_t = a_lo + ((((t / 3) * HALO_PITCH_PX + (t % 3)) * PB) >> 4);
+            const uint32_t b_t = b_lo0 + t * wtap;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              if (k < ksteps) umma_bf16(acc, ad + 2 * k, bdesc[t] + 2 * k, idesc, (t | k) != 0 ? 1u : 0u);
+            for (int k = 0; k < KSTEPS; ++k)
+              umma_bf16(acc, make_u64(a_t + 2 * k, a_hi), make_u64(b_t + 2 * k, b_hi), idesc, (t | k) != 0 ? 1u : 0u);
           }
           umma_commit(smem_u32(&bar_halo_empty[hb]));
           umma_commit(smem_u32(&bar_tmem_full[b]));
@@ -699,22 +709,27 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
     __syncwarp();
   } else if (warp >= 4) {
     // =========================== epilogue ===========================
-    const int epi_tid = threadIdx.x - 128;  // 0..127
+    // Two warpgroups, one per accumulator: group g drains every second tile.  With N <= 64 the per-tile epilogue
+    // (TMEM load -> bias/residual/activation -> staging, ~2700 cycles of mostly latency) is longer than the tile's MMAs.
+    const int wg = (warp - 4) >> 2;
+    const int epi_tid = (threadIdx.x - 128) & 127;  // 0..127 within the group
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t row_off = row * 128;
     const int sw = row & 7;
-    for (int it = 0; it < my_tiles; ++it) {
-      const int tile0_ = blockIdx.x + it * gridDim.x;
-      const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
-      const int b = it & 1;
-      const int ob = it % NB;
-      const int n0 = (tile % p.n_tiles) * N;
+    {
+      // the channel tile is the same for every tile of this CTA: the bias is staged once per group
+      const int first = (p.reverse & 1) ? total_tiles - 1 - static_cast<int>(blockIdx.x) : static_cast<int>(blockIdx.x);
+      const int n0 = (first % p.n_tiles) * N;
       for (int i = epi_tid; i < N; i += 128) {
         const int c = n0 + i;
-        bias_s[b][i] = (c < p.cout) ? p.bias[c] : 0.f;
+        bias_s[wg][i] = (c < p.cout) ? p.bias[c] : 0.f;
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1 + wg, 128);
+    }
+    for (int it = wg; it < my_tiles; it += 2) {
+      const int b = wg;
+      const int ob = it % NB;
       mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
       tc_fence_after();
       mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
@@ -1135,14 +1150,14 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   // halo kernel: 3x3/s1/p1, Cin <= 64, 16x8-pixel tiles with little padding waste; Cout <= 64, or wider while the layer
   // is too thin in K for the generic kernel (Cin < 64: each of its k-blocks would be mostly padding)
   const long long halo_cover = (long long)((in.W + 7) / 8 * 8) * ((in.H + 15) / 16 * 16);
-  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 &&
+  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 && s.act != ACT_SIGMOID &&
                     (out.C <= 64 || (in.C < 64 && out.C <= 256)) && halo_cover * 100 <= (long long)in.W * in.H * 135;
   if (halo) {
     two_cta = false;
     block_n = out.C <= 32 ? 32 : 64;
     p.pb = in.C <= 16 ? 32 : (in.C <= 32 ? 64 : 128);
     p.block_n = block_n;
-    p.halo_stages = p.pb == 128 ? 2 : 4;
+    p.halo_stages = p.pb == 128 ? 3 : 4;
     L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages);
   }
   L->halo = halo;
@@ -1326,33 +1341,39 @@ static int launch_2cta_res(const ConvLaunch& l, cudaStream_t stream) {
   return launch_2cta_act<BLOCK_N, 2>(l, stream);
 }
 
-template <int RES, int ACT>
+template <int PB, int RES, int ACT>
 static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<RES, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      HaloCfg::smem_bytes(128, 64, 2)));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<PB, RES, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      HaloCfg::smem_bytes(PB, 64, PB == 128 ? 3 : 4)));
     configured[dev & 63] = true;
   }
   const int total = static_cast<int>(l.grid);
   int ctas = total < device_sm_count() ? total : device_sm_count();
   ctas -= ctas % l.p.n_tiles;    // a CTA keeps ONE channel tile's weights resident: tile stride must preserve tile % n_tiles
-  conv3x3_halo_kernel<RES, ACT><<<ctas, HALO_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
+  conv3x3_halo_kernel<PB, RES, ACT><<<ctas, HALO_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }
 
-template <int RES>
+template <int PB, int RES>
 static int launch_halo_act(const ConvLaunch& l, cudaStream_t stream) {
   switch (l.p.act) {
-    case ACT_NONE: return launch_halo_t<RES, ACT_NONE>(l, stream);
-    case ACT_RELU: return launch_halo_t<RES, ACT_RELU>(l, stream);
-    case ACT_SILU: return launch_halo_t<RES, ACT_SILU>(l, stream);
-    case ACT_SIGMOID: return launch_halo_t<RES, ACT_SIGMOID>(l, stream);
+    case ACT_NONE: return launch_halo_t<PB, RES, ACT_NONE>(l, stream);
+    case ACT_RELU: return launch_halo_t<PB, RES, ACT_RELU>(l, stream);
+    case ACT_SILU: return launch_halo_t<PB, RES, ACT_SILU>(l, stream);
   }
-  return fail(B200_ERR_INVALID, "conv: unknown activation");
+  return fail(B200_ERR_INVALID, "conv: activation not supported by the halo kernel");
+}
+
+template <int PB>
+static int launch_halo_res(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.p.has_res == 0) return launch_halo_act<PB, 0>(l, stream);
+  if (l.p.has_res == 1) return launch_halo_act<PB, 1>(l, stream);
+  return launch_halo_act<PB, 2>(l, stream);
 }
 
 template <int BLOCK_N>
@@ -1372,9 +1393,9 @@ static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
 
 int conv_launch(const ConvLaunch& l, cudaStream_t stream) {
   if (l.halo) {
-    if (l.p.has_res == 0) return launch_halo_act<0>(l, stream);
-    if (l.p.has_res == 1) return launch_halo_act<1>(l, stream);
-    return launch_halo_act<2>(l, stream);
+    if (l.p.pb == 128) return launch_halo_res<128>(l, stream);
+    if (l.p.pb == 64) return launch_halo_res<64>(l, stream);
+    return launch_halo_res<32>(l, stream);
   }
   if (l.two_cta) {
     if (l.block_n == 256) return launch_2cta_res<256>(l, stream);
