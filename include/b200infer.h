@@ -100,9 +100,10 @@ B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int
 
 /* The same depthwise convolution with the squeeze of the SqueezeExcitation block that follows it in MBConv fused in
  * (tv efficientnet.py:153-155 -> tv ops/misc.py:249-250, AdaptiveAvgPool2d(1)): besides `out`, writes fp32
- * strip_sums[n][strips][c], the channel sums of the stored outputs of each strip of the image, strips =
- * b200_dwconv3x3_strips(ho, wo, stride) (0: this output geometry has no strip kernel and the call is rejected; widths
- * that are a multiple of 7 have one). b200_se_gate adds the strips in index order, so the result is deterministic. */
+ * strip_sums[n][rows][c], channel sums of the stored outputs of each strip of the image, rows =
+ * b200_dwconv3x3_strips(ho, wo, stride) (1 with B200_DW_SQ=1 when an image's strips fit one thread block, which then
+ * adds them itself; 0: this output geometry has no strip kernel and the call is rejected -- widths that are a multiple
+ * of 7 have one). b200_se_gate / b200_se_hidden add the rows in index order, so the result is deterministic. */
 B200_API int b200_dwconv3x3_strips(int ho, int wo, int stride);
 B200_API int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride,
                                          const float* weight, const float* bias, void* out, int out_pix_stride,
@@ -113,6 +114,16 @@ B200_API int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, in
  * [squeeze][c] (fc2 weight TRANSPOSED), b2 [c]; gate fp32 [n][c] feeds b200_channel_scale_nhwc. */
 B200_API int b200_se_gate(const float* strip_sums, int n, int strips, int c, float inv_hw, const float* w1,
                           const float* b1, const float* w2t, const float* b2, int squeeze, float* gate, void* stream);
+
+/* The same block in two launches, so that no thread block streams a whole fc matrix (the form the engine uses):
+ * b200_se_hidden: hidden[n][j] = silu(b1[j] + inv_hw * sum_c rows(strip_sums[n])[c] * w1[j][c]), fp32 [n][squeeze];
+ * b200_se_scale_nhwc: out = in * sigmoid(b2[c] + sum_j hidden[n][j] * w2t[j][c]) -- fc2, scale_activation and the
+ * `scale * input` of SqueezeExcitation.forward (tv ops/misc.py:252-258) in one pass over the activation. squeeze <= 256. */
+B200_API int b200_se_hidden(const float* strip_sums, int n, int rows, int c, float inv_hw, const float* w1, const float* b1,
+                            int squeeze, float* hidden, void* stream);
+B200_API int b200_se_scale_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* hidden,
+                                const float* w2t, const float* b2, int squeeze, void* out, int out_pix_stride,
+                                void* stream);
 
 /* Max pooling (k, stride, pad). Replaces nn.MaxPool2d(3,2,1) (tv resnet.py:271, shufflenetv2.py:118) and SPPF's 5x5/1/2. */
 B200_API int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out,

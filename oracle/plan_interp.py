@@ -14,7 +14,7 @@ import torch
 import torch.nn.functional as F
 
 OP_CONV, OP_STEM, OP_MAXPOOL, OP_AVGPOOL, OP_FC, OP_DWCONV, OP_SCALE, OP_COPY, OP_UPSAMPLE, OP_SHUFFLE, \
-    OP_YOLO_DECODE, OP_GATHER_CONV, OP_SE_GATE = range(1, 14)
+    OP_YOLO_DECODE, OP_GATHER_CONV, OP_SE_GATE, OP_SE_HIDDEN, OP_SE_SCALE = range(1, 16)
 
 
 def _bf16(x):
@@ -133,6 +133,19 @@ class PlanInterpreter:
                 b2 = self._f32(op["b2_off"], c)
                 hid = F.silu(mean @ w1.t() + b1)
                 B[p[3]] = torch.sigmoid(hid @ w2t + b2).view(n, 1, 1, c)
+            elif t == OP_SE_HIDDEN:
+                rows, c, sq = p[1], p[2], p[8]
+                inv_hw = struct.unpack("<f", struct.pack("<i", p[12]))[0]
+                mean = B[p[0]].view(n, -1)[:, :rows * c].view(n, rows, c).sum(dim=1) * inv_hw
+                w1 = self._f32(op["w_off"], sq * c).view(sq, c)
+                b1 = self._f32(op["b_off"], sq)
+                B[p[3]] = F.silu(mean @ w1.t() + b1).view(n, 1, 1, sq)
+            elif t == OP_SE_SCALE:
+                c, sq = p[2], p[8]
+                w2t = self._f32(op["w_off"], sq * c).view(sq, c)
+                b2 = self._f32(op["b_off"], c)
+                g = torch.sigmoid(B[p[12]].view(n, -1)[:, :sq] @ w2t + b2).view(n, 1, 1, c)
+                B[p[3]][..., p[4]:p[4] + c] = _bf16(B[p[0]][..., p[1]:p[1] + c] * g)
             elif t == OP_MAXPOOL:
                 c, k, s, pad = p[2], p[8], p[9], p[10]
                 x = B[p[0]][..., p[1]:p[1] + c].permute(0, 3, 1, 2)

@@ -109,6 +109,18 @@ int b200_se_gate(const float* strip_sums, int n, int strips, int c, float inv_hw
                         static_cast<cudaStream_t>(stream));
 }
 
+int b200_se_hidden(const float* strip_sums, int n, int rows, int c, float inv_hw, const float* w1, const float* b1,
+                   int squeeze, float* hidden, void* stream) {
+  return se_hidden_launch(strip_sums, n, rows, c, inv_hw, w1, b1, squeeze, hidden, static_cast<cudaStream_t>(stream));
+}
+
+int b200_se_scale_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* hidden,
+                       const float* w2t, const float* b2, int squeeze, void* out, int out_pix_stride, void* stream) {
+  return se_scale_launch(make_view(const_cast<void*>(in), n, h, w, c, in_pix_stride),
+                         make_view(out, n, h, w, c, out_pix_stride), hidden, w2t, b2, squeeze,
+                         static_cast<cudaStream_t>(stream));
+}
+
 int b200_maxpool_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, void* out, int out_pix_stride,
                       int ksize, int stride, int pad, void* stream) {
   const int ho = (h + 2 * pad - ksize) / stride + 1, wo = (w + 2 * pad - ksize) / stride + 1;

@@ -1129,6 +1129,11 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const char* e = getenv("B200_2CTA_RES_MODE");
     res_mode = e ? atoi(e) : 2;
   }
+  static int res_min_k = -1;       // residual layers go to CTA pairs from this K on
+  if (res_min_k < 0) {
+    const char* e = getenv("B200_2CTA_RES_MIN_K");
+    res_min_k = e ? atoi(e) : 512;
+  }
   static int pair128_min_k = -1;   // Cout in [128, 256): CTA pairs with N = 128 from this K on (0 = never)
   if (pair128_min_k < 0) {
     const char* e = getenv("B200_PAIR128_MIN_K");
@@ -1139,7 +1144,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   int block_n = two_cta ? (out.C >= 256 ? 256 : 128) : (out.C <= 64 ? 64 : 128);
   if (two_cta && has_res) {
     // residual layers: CTA pairs pay off only with enough K per tile to hide the residual prefetch (layer4 conv3: K = 512)
-    if (res_mode == 0 || (res_mode == 2 && k_total < 512)) { two_cta = false; block_n = 128; }
+    if (res_mode == 0 || (res_mode == 2 && k_total < res_min_k)) { two_cta = false; block_n = 128; }
     else if (res_mode == 1) block_n = 128;
   }
   static int use_halo = -1;

@@ -33,22 +33,42 @@ __device__ __forceinline__ void dw_unpack(const uint2 r, float (&v)[4]) {
 // strip; the gate kernel adds the strips of an image in index order, so the squeeze is deterministic.
 // All loads of a strip (ROWS x NCOL 8-byte words, still packed) are issued before the first FMA: the kernel is
 // latency-bound otherwise (4 loads in flight per thread gave ~2.4 TB/s).
-template <int STRIDE, int ACT>
+// SQ (fused squeeze, an image has at most 32 strips): a block is (slots = strips rounded up to a power of two) x
+// (128 / slots channel quads) of ONE image, so the strips of a channel meet in shared memory and the block writes the
+// image's channel sums [N][C] directly, added in strip order (deterministic).  Otherwise threads are laid out channel
+// quad fastest over (image, strip) and, if se_partial is given, every strip writes its own partial row.
+template <int STRIDE, int ACT, bool SQ>
 __global__ void __launch_bounds__(DW_STRIP_THREADS, 3)
 dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho,
                        int Wo, int out_ps, int C4, int strips_h, int strips_w, const float* __restrict__ w,
-                       const float* __restrict__ bias, float* __restrict__ se_partial, long long total) {
+                       const float* __restrict__ bias, float* __restrict__ se_partial, long long total, int slots) {
   constexpr int R = STRIDE == 1 ? 2 : 1;                        // output rows per thread
   constexpr int ROWS = STRIDE == 1 ? 4 : 3;                     // input rows per thread
   constexpr int NCOL = STRIDE == 1 ? DW_TW + 2 : 2 * DW_TW + 1;   // input columns per thread, first one = halo
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int c4 = static_cast<int>(idx % C4);
-  long long t = idx / C4;
-  const int sx = static_cast<int>(t % strips_w);
-  t /= strips_w;
-  const int sy = static_cast<int>(t % strips_h);
-  const int n = static_cast<int>(t / strips_h);
+  __shared__ float4 red[SQ ? DW_STRIP_THREADS : 1];
+  int c4, sx, sy, n;
+  bool active;
+  if (SQ) {
+    const int qn = DW_STRIP_THREADS / slots;                    // channel quads per block
+    const int qblocks = (C4 + qn - 1) / qn;
+    const int slot = threadIdx.x / qn;
+    c4 = (blockIdx.x % qblocks) * qn + threadIdx.x % qn;
+    n = blockIdx.x / qblocks;
+    sy = slot / strips_w;
+    sx = slot - sy * strips_w;
+    active = slot < strips_h * strips_w && c4 < C4;
+    if (!active) { c4 = 0; sx = 0; sy = 0; }                    // idle lanes still reach the barrier below
+  } else {
+    const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    c4 = static_cast<int>(idx % C4);
+    long long t = idx / C4;
+    sx = static_cast<int>(t % strips_w);
+    t /= strips_w;
+    sy = static_cast<int>(t % strips_h);
+    n = static_cast<int>(t / strips_h);
+    active = true;
+  }
   const int C = C4 * 4;
   const int oy0 = sy * R, ox0 = sx * DW_TW;
   const int iy0 = oy0 * STRIDE - 1, ix0 = ox0 * STRIDE - 1;
@@ -62,7 +82,7 @@ dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps,
 #pragma unroll
     for (int k = 0; k < NCOL; ++k) {
       const int x = ix0 + k;
-      raw[i][k] = dw_load(rowp + static_cast<ptrdiff_t>(x) * in_ps, rowok && x >= 0 && x < W);
+      raw[i][k] = dw_load(rowp + static_cast<ptrdiff_t>(x) * in_ps, active && rowok && x >= 0 && x < W);
     }
   }
   float wt[9][4], b[4];
@@ -104,7 +124,7 @@ dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps,
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-      if (oy0 + r >= Ho) continue;
+      if (oy0 + r >= Ho || !active) continue;
       float acc[4] = {b[0], b[1], b[2], b[3]};
 #pragma unroll
       for (int dr = 0; dr < 3; ++dr) {
@@ -123,7 +143,20 @@ dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps,
       sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y);
     }
   }
-  if (se_partial) {
+  if (SQ) {
+    const int qn = DW_STRIP_THREADS / slots;
+    red[threadIdx.x] = active ? make_float4(sum[0], sum[1], sum[2], sum[3]) : make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    if (threadIdx.x < qn && active) {
+      float4 s4 = red[threadIdx.x];
+      const int strips = strips_h * strips_w;
+      for (int j = 1; j < strips; ++j) {            // fixed order
+        const float4 v = red[j * qn + threadIdx.x];
+        s4.x += v.x; s4.y += v.y; s4.z += v.z; s4.w += v.w;
+      }
+      *reinterpret_cast<float4*>(se_partial + static_cast<size_t>(n) * C + c4 * 4) = s4;
+    }
+  } else if (se_partial) {
     const size_t strip = (static_cast<size_t>(n) * strips_h + sy) * strips_w + sx;
     *reinterpret_cast<float4*>(se_partial + strip * C + c4 * 4) = make_float4(sum[0], sum[1], sum[2], sum[3]);
   }
@@ -176,10 +209,26 @@ dwconv3x3_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint1
   *reinterpret_cast<uint4*>(out + ((static_cast<size_t>(n) * Ho + oh) * Wo + ow) * out_ps + c8 * 8) = o;
 }
 
-int dwconv3x3_strips(int Ho, int Wo, int stride) {
+static int dw_strip_count(int Ho, int Wo, int stride) {
   if (Wo % DW_TW) return 0;
   const int r = stride == 1 ? 2 : 1;
   return ((Ho + r - 1) / r) * (Wo / DW_TW);
+}
+
+// rows of channel sums the fused squeeze writes per image: one per strip (or 1 with B200_DW_SQ=1 when the strips of an
+// image fit one block); 0 = this geometry has no strip kernel
+static bool dw_block_reduce() {      // B200_DW_SQ=1: reduce an image's strips inside the kernel (one row of sums per image)
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_DW_SQ");
+    v = (e && e[0] == '1') ? 1 : 0;    // measured on EfficientNetV2-S @128: the strip-major layout it needs costs more
+  }                                    // in the depthwise kernel (+1.5 us a layer) than the gate saves
+  return v == 1;
+}
+
+int dwconv3x3_strips(int Ho, int Wo, int stride) {
+  const int s = dw_strip_count(Ho, Wo, stride);
+  return (dw_block_reduce() && s <= 32) ? (s > 0 ? 1 : 0) : s;
 }
 
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
@@ -194,18 +243,24 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
     const char* e = getenv("B200_DW_STRIPS");
     use_strips = (e && e[0] == '0') ? 0 : 1;
   }
-  const int strips = dwconv3x3_strips(out.H, out.W, stride);
+  const int strips = dw_strip_count(out.H, out.W, stride);
   if (strips > 0 && (use_strips || se_partial)) {
     const int r = stride == 1 ? 2 : 1;
     const int strips_h = (out.H + r - 1) / r, strips_w = out.W / DW_TW;
+    const bool sq = se_partial != nullptr && strips <= 32 && dw_block_reduce();
+    int slots = 1;
+    while (slots < strips) slots <<= 1;
+    const int qn = DW_STRIP_THREADS / slots;
     const long long total = static_cast<long long>(out.N) * strips * (out.C / 4);
-    const unsigned grid = static_cast<unsigned>((total + DW_STRIP_THREADS - 1) / DW_STRIP_THREADS);
+    const unsigned grid = sq ? static_cast<unsigned>(out.N) * static_cast<unsigned>((out.C / 4 + qn - 1) / qn)
+                             : static_cast<unsigned>((total + DW_STRIP_THREADS - 1) / DW_STRIP_THREADS);
     const uint16_t* ip = static_cast<const uint16_t*>(in.base);
     uint16_t* op = static_cast<uint16_t*>(out.base);
-#define B200_DW_LAUNCH(S, A)                                                                                          \
-  dwconv3x3_strip_kernel<S, A><<<grid, DW_STRIP_THREADS, 0, stream>>>(ip, in.H, in.W, in.pix_stride, op, out.H, out.W, \
-                                                                      out.pix_stride, out.C / 4, strips_h, strips_w, w, \
-                                                                      bias, se_partial, total)
+#define B200_DW_LAUNCH2(S, A, Q)                                                                                       \
+  dwconv3x3_strip_kernel<S, A, Q><<<grid, DW_STRIP_THREADS, 0, stream>>>(ip, in.H, in.W, in.pix_stride, op, out.H,      \
+                                                                         out.W, out.pix_stride, out.C / 4, strips_h,    \
+                                                                         strips_w, w, bias, se_partial, total, slots)
+#define B200_DW_LAUNCH(S, A) do { if (sq) B200_DW_LAUNCH2(S, A, true); else B200_DW_LAUNCH2(S, A, false); } while (0)
     if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU)
       return fail(B200_ERR_INVALID, "dwconv: activation must be none, relu or silu");
     if (stride == 1) {
@@ -217,6 +272,7 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
       else if (act == ACT_RELU) B200_DW_LAUNCH(2, ACT_RELU);
       else B200_DW_LAUNCH(2, ACT_SILU);
     }
+#undef B200_DW_LAUNCH2
 #undef B200_DW_LAUNCH
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;

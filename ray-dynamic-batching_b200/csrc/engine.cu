@@ -55,7 +55,7 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     const int ids[3] = {o.p[0], o.p[3], o.p[6]};
     for (int k = 0; k < 3; ++k)
       if (ids[k] >= int(hdr.n_bufs) || (k < 2 && ids[k] < 0)) return fail(B200_ERR_BLOB, "engine: op references unknown buffer");
-    if ((o.type == OP_DWCONV || o.type == OP_SCALE) && (o.p[12] < 0 || o.p[12] >= int(hdr.n_bufs)))
+    if ((o.type == OP_DWCONV || o.type == OP_SCALE || o.type == OP_SE_SCALE) && (o.p[12] < 0 || o.p[12] >= int(hdr.n_bufs)))
       return fail(B200_ERR_BLOB, "engine: op references unknown side buffer");
     if (o.type == OP_DWCONV && o.p[12] > 0) {   // fused squeeze: the side buffer must hold every strip's channel sums
       const BufRec& sb = bufs[o.p[12]];
@@ -63,6 +63,18 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
       const int strips = dwconv3x3_strips(ob.h, ob.w, o.p[9]);
       if (strips <= 0 || sb.dtype != 1 || int64_t(sb.h) * sb.w * sb.c < int64_t(strips) * o.p[5])
         return fail(B200_ERR_BLOB, "engine: depthwise squeeze buffer too small for this geometry");
+    }
+    if (o.type == OP_SE_HIDDEN) {
+      const BufRec& sb = bufs[o.p[0]];
+      const BufRec& hb = bufs[o.p[3]];
+      if (o.p[1] <= 0 || o.p[2] <= 0 || o.p[8] <= 0 || sb.dtype != 1 || hb.dtype != 1 ||
+          int64_t(sb.h) * sb.w * sb.c < int64_t(o.p[1]) * o.p[2] || int64_t(hb.h) * hb.w * hb.c < o.p[8])
+        return fail(B200_ERR_BLOB, "engine: squeeze-excitation hidden buffers do not match its shape");
+    }
+    if (o.type == OP_SE_SCALE) {
+      const BufRec& hb = bufs[o.p[12]];
+      if (o.p[8] <= 0 || o.p[8] > 256 || hb.dtype != 1 || int64_t(hb.h) * hb.w * hb.c < o.p[8])
+        return fail(B200_ERR_BLOB, "engine: squeeze-excitation scale does not match its hidden buffer");
     }
     if (o.type == OP_SE_GATE) {
       const BufRec& sb = bufs[o.p[0]];
@@ -200,6 +212,21 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
                             reinterpret_cast<float*>(buf_dev[p[3]]), stream);
         break;
       }
+      case OP_SE_HIDDEN: {
+        float inv_hw;
+        memcpy(&inv_hw, &p[12], 4);
+        rc = se_hidden_launch(reinterpret_cast<const float*>(buf_dev[p[0]]), batch, p[1], p[2], inv_hw,
+                              reinterpret_cast<const float*>(W + po.rec.w_off),
+                              reinterpret_cast<const float*>(W + po.rec.b_off), p[8],
+                              reinterpret_cast<float*>(buf_dev[p[3]]), stream);
+        break;
+      }
+      case OP_SE_SCALE:
+        rc = se_scale_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
+                             reinterpret_cast<const float*>(buf_dev[p[12]]),
+                             reinterpret_cast<const float*>(W + po.rec.w_off),
+                             reinterpret_cast<const float*>(W + po.rec.b_off), p[8], stream);
+        break;
       case OP_SCALE:
         rc = channel_scale_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch),
                                   reinterpret_cast<const float*>(buf_dev[p[12]]), stream);
@@ -334,6 +361,37 @@ int b200_engine_profile(b200_engine* h, int batch, float* ms_per_op, double* flo
   B200_TRY(e.plan_for(batch, &plan));
   std::vector<cudaEvent_t> ev(n_ops + 1);
   for (auto& x : ev) B200_CUDA_OK(cudaEventCreate(&x));
+  // The launches and the event records between them are captured into one graph, so the gaps between events are kernel
+  // time and not the host's launch rate (eager launches put a ~10-15 us floor under every small op).
+  static int graph_profile = -1;
+  if (graph_profile < 0) {
+    const char* g = getenv("B200_PROFILE_GRAPH");
+    graph_profile = (g && g[0] == '0') ? 0 : 1;
+  }
+  if (graph_profile) {
+    cudaStream_t cs = e.capture_stream;
+    B200_CUDA_OK(cudaStreamSynchronize(stream));
+    B200_CUDA_OK(cudaStreamBeginCapture(cs, cudaStreamCaptureModeThreadLocal));
+    int rc = B200_OK;
+    cudaError_t ce = cudaEventRecordWithFlags(ev[0], cs, cudaEventRecordExternal);   // a real event-record node
+    for (int i = 0; i < n_ops && rc == B200_OK && ce == cudaSuccess; ++i) {
+      rc = e.run_ops(*plan, cs, i, i);
+      if (rc == B200_OK) ce = cudaEventRecordWithFlags(ev[i + 1], cs, cudaEventRecordExternal);
+    }
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ee = cudaStreamEndCapture(cs, &graph);
+    if (rc != B200_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+    B200_CUDA_OK(ce);
+    B200_CUDA_OK(ee);
+    cudaGraphExec_t exec = nullptr;
+    B200_CUDA_OK(cudaGraphInstantiate(&exec, graph, 0));
+    B200_CUDA_OK(cudaGraphLaunch(exec, cs));     // warm-up replay
+    B200_CUDA_OK(cudaGraphLaunch(exec, cs));
+    B200_CUDA_OK(cudaStreamSynchronize(cs));
+    cudaGraphExecDestroy(exec);
+    cudaGraphDestroy(graph);
+    e.launches += 2 * n_ops;
+  } else {
   B200_CUDA_OK(cudaEventRecord(ev[0], stream));
   for (int i = 0; i < n_ops; ++i) {
     int rc = e.run_ops(*plan, stream, i, i);
@@ -342,6 +400,7 @@ int b200_engine_profile(b200_engine* h, int batch, float* ms_per_op, double* flo
   }
   B200_CUDA_OK(cudaStreamSynchronize(stream));
   e.launches += n_ops;
+  }
   for (int i = 0; i < n_ops; ++i) {
     B200_CUDA_OK(cudaEventElapsedTime(&ms_per_op[i], ev[i], ev[i + 1]));
     if (flops_per_op) flops_per_op[i] = plan->ops[i].rec.type == OP_CONV ? plan->ops[i].conv.flops : 0.0;

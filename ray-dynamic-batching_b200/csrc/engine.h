@@ -41,7 +41,8 @@ static_assert(sizeof(OpRec) == 128, "OpRec layout");
 
 enum OpType : int {
   OP_CONV = 1, OP_STEM = 2, OP_MAXPOOL = 3, OP_AVGPOOL = 4, OP_FC = 5, OP_DWCONV = 6, OP_SCALE = 7, OP_COPY = 8,
-  OP_UPSAMPLE = 9, OP_SHUFFLE = 10, OP_YOLO_DECODE = 11, OP_GATHER_CONV = 12, OP_SE_GATE = 13
+  OP_UPSAMPLE = 9, OP_SHUFFLE = 10, OP_YOLO_DECODE = 11, OP_GATHER_CONV = 12, OP_SE_GATE = 13,
+  OP_SE_HIDDEN = 14, OP_SE_SCALE = 15
 };
 
 struct PreparedOp {

@@ -170,6 +170,178 @@ int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw,
   return B200_OK;
 }
 
+// Squeeze-excitation split so that no block drags a whole weight matrix through its SM (the one-launch gate reads
+// 2 * S * C * 4 bytes per image: up to 786 KB per block at ~100 GB/s per SM):
+//   se_hidden : block = 16 images x 16 squeeze units; hid[n][j] = silu(b1[j] + inv_hw * sum_c sums[n][c] * w1[j][c])
+//   se_scale  : block = one image x 64 channels; gate = sigmoid(b2 + hid[n] . w2t[:, c]) computed on the fly, then
+//               y = x * gate over the image's pixels (replaces channel_scale + the fc2 half of the gate)
+constexpr int SEH_G = 16, SEH_J = 16, SEH_THREADS = 512, SEH_PAD = 4;
+// block = 16 images x 16 squeeze units: their 32 rows (C floats each) are staged in shared memory in one burst of
+// independent 16-byte copies, then 8 k-slices x 64 register-tiled (2 x 2) threads reduce them from shared memory.
+__global__ void __launch_bounds__(SEH_THREADS)
+se_hidden_kernel(const float* __restrict__ sums, int N, int P, int C, float inv_hw, const float* __restrict__ w1,
+                 const float* __restrict__ b1, int S, float* __restrict__ hid) {
+  extern __shared__ __align__(16) float seh_smem[];   // x[16][C + PAD], w[16][C + PAD], part[8 * 64 * 4]
+  const int ld = C + SEH_PAD;
+  float* xs = seh_smem;
+  float* ws = seh_smem + SEH_G * ld;
+  float* part = ws + SEH_J * ld;
+  const int g0 = blockIdx.x * SEH_G, j0 = blockIdx.y * SEH_J;
+  const int Q = C >> 2;
+  // Both tiles go global -> shared with cp.async (zero-filled past the last image / unit): every 16-byte copy is in
+  // flight at once, where a load + store loop waits one L2 round trip per iteration.
+  for (int i = threadIdx.x; i < (SEH_G + SEH_J) * Q; i += SEH_THREADS) {
+    const int r = i / Q, q = i - r * Q;
+    const bool is_w = r >= SEH_G;
+    const int row = is_w ? j0 + r - SEH_G : g0 + r;
+    const bool ok = is_w ? row < S : row < N;
+    const float* src = is_w ? w1 + static_cast<size_t>(ok ? row : 0) * C + q * 4
+                            : sums + static_cast<size_t>(ok ? row : 0) * P * C + q * 4;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(seh_smem + r * ld + q * 4)), "l"(src),
+                 "r"(ok ? 16 : 0)
+                 : "memory");
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  if (P > 1) {                                           // more than 32 strips per image: add the remaining rows in order
+    for (int i = threadIdx.x; i < SEH_G * Q; i += SEH_THREADS) {
+      const int r = i / Q, q = i - r * Q;
+      if (g0 + r >= N) continue;
+      float4 v = *reinterpret_cast<float4*>(xs + r * ld + q * 4);
+      for (int p = 1; p < P; ++p) {
+        const float4 u = *reinterpret_cast<const float4*>(sums + (static_cast<size_t>(g0 + r) * P + p) * C + q * 4);
+        v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
+      }
+      *reinterpret_cast<float4*>(xs + r * ld + q * 4) = v;
+    }
+    __syncthreads();
+  }
+  // thread = (k-slice 0..7, 2 x 2 micro-tile): per 16-byte step 4 shared-memory loads feed 16 FMAs, and a warp's loads
+  // touch 4 image rows / 8 unit rows at a 16-byte bank offset from each other (ld = C + 4): one wavefront each
+  const int ks = threadIdx.x >> 6, tile = threadIdx.x & 63;
+  const int ta = tile >> 3, tj = tile & 7;
+  const float* x0 = xs + (2 * ta) * ld;
+  const float* x1 = x0 + ld;
+  const float* w0 = ws + (2 * tj) * ld;
+  const float* w1r = w0 + ld;
+  const int qs = (Q + 7) >> 3;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};      // (image 2ta, unit 2tj), (2ta, 2tj+1), (2ta+1, 2tj), (2ta+1, 2tj+1)
+  for (int q = ks * qs; q < min(Q, (ks + 1) * qs); ++q) {
+    const float4 a0 = *reinterpret_cast<const float4*>(x0 + q * 4);
+    const float4 a1 = *reinterpret_cast<const float4*>(x1 + q * 4);
+    const float4 u0 = *reinterpret_cast<const float4*>(w0 + q * 4);
+    const float4 u1 = *reinterpret_cast<const float4*>(w1r + q * 4);
+    acc[0] = fmaf(a0.x, u0.x, acc[0]); acc[0] = fmaf(a0.y, u0.y, acc[0]); acc[0] = fmaf(a0.z, u0.z, acc[0]); acc[0] = fmaf(a0.w, u0.w, acc[0]);
+    acc[1] = fmaf(a0.x, u1.x, acc[1]); acc[1] = fmaf(a0.y, u1.y, acc[1]); acc[1] = fmaf(a0.z, u1.z, acc[1]); acc[1] = fmaf(a0.w, u1.w, acc[1]);
+    acc[2] = fmaf(a1.x, u0.x, acc[2]); acc[2] = fmaf(a1.y, u0.y, acc[2]); acc[2] = fmaf(a1.z, u0.z, acc[2]); acc[2] = fmaf(a1.w, u0.w, acc[2]);
+    acc[3] = fmaf(a1.x, u1.x, acc[3]); acc[3] = fmaf(a1.y, u1.y, acc[3]); acc[3] = fmaf(a1.z, u1.z, acc[3]); acc[3] = fmaf(a1.w, u1.w, acc[3]);
+  }
+  *reinterpret_cast<float4*>(part + (ks * 64 + tile) * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  __syncthreads();
+  if (threadIdx.x < 256) {
+    const int tl = threadIdx.x >> 2, e = threadIdx.x & 3;       // micro-tile, element of it
+    const int ia = 2 * (tl >> 3) + (e >> 1), ij = 2 * (tl & 7) + (e & 1);
+    float v = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v += part[(k * 64 + tl) * 4 + e];          // fixed order
+    if (g0 + ia < N && j0 + ij < S) {
+      const float z = v * inv_hw + b1[j0 + ij];
+      hid[static_cast<size_t>(g0 + ia) * S + j0 + ij] = z / (1.f + expf(-z));
+    }
+  }
+}
+
+int se_hidden_launch(const float* sums, int n, int rows, int c, float inv_hw, const float* w1, const float* b1, int s,
+                     float* hid, cudaStream_t stream) {
+  if (n <= 0 || rows <= 0 || c <= 0 || s <= 0 || c % 4) return fail(B200_ERR_INVALID, "se_hidden: bad shape");
+  const size_t smem = sizeof(float) * (static_cast<size_t>(SEH_G + SEH_J) * (c + SEH_PAD) + 8 * 64 * 4);
+  if (smem > 220 * 1024) return fail(B200_ERR_INVALID, "se_hidden: more than ~1700 channels unsupported");
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(se_hidden_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    configured[dev & 63] = true;
+  }
+  const dim3 grid((n + SEH_G - 1) / SEH_G, (s + SEH_J - 1) / SEH_J);
+  se_hidden_kernel<<<grid, SEH_THREADS, smem, stream>>>(sums, n, rows, c, inv_hw, w1, b1, s, hid);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+constexpr int SES_C = 64, SES_THREADS = 256;
+__global__ void __launch_bounds__(SES_THREADS)
+se_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C,
+                const float* __restrict__ hid, const float* __restrict__ w2t, const float* __restrict__ b2, int S) {
+  __shared__ __align__(16) float hid_s[256];
+  __shared__ __align__(16) float w_s[256 / 4][SES_C];   // up to 64 squeeze units at a time
+  __shared__ float part[4][SES_C];
+  __shared__ __align__(16) float gate_s[SES_C];
+  const int n = blockIdx.y;
+  const int c0 = blockIdx.x * SES_C;
+  const int cw = min(SES_C, C - c0);                    // channels of this slice (multiple of 8)
+  const int c = threadIdx.x & (SES_C - 1), jg = threadIdx.x >> 6;        // 64 channels x 4 slices of the squeeze units
+  float acc = 0.f;
+  for (int s0 = 0; s0 < S; s0 += 64) {                  // one pass for every served model (S <= 64)
+    const int sn = min(64, S - s0);
+    __syncthreads();
+    // hidden units and the [sn][cw] slice of fc2^T go to shared memory with cp.async: all copies in flight at once
+    for (int i = threadIdx.x; i < sn * (cw >> 2); i += SES_THREADS) {
+      const int j = i / (cw >> 2), q = i - j * (cw >> 2);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(&w_s[j][q * 4])),
+                   "l"(w2t + static_cast<size_t>(s0 + j) * C + c0 + q * 4)
+                   : "memory");
+    }
+    for (int j = threadIdx.x; j < sn; j += SES_THREADS)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(&hid_s[j])),
+                   "l"(hid + static_cast<size_t>(n) * S + s0 + j)
+                   : "memory");
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (c < cw)
+      for (int j = jg; j < sn; j += 4) acc = fmaf(hid_s[j], w_s[j][c], acc);
+  }
+  part[jg][c] = acc;
+  __syncthreads();
+  if (threadIdx.x < SES_C) {
+    float z = (c < cw) ? b2[c0 + c] : 0.f;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) z += part[g][c];                          // fixed order
+    gate_s[c] = 1.f / (1.f + expf(-z));
+  }
+  __syncthreads();
+  const int chunks = min(SES_C, C - c0) >> 3;                             // 16-byte chunks of this slice
+  const uint16_t* ib = in + static_cast<size_t>(n) * HW * in_ps + c0;
+  uint16_t* ob = out + static_cast<size_t>(n) * HW * out_ps + c0;
+  for (int item = threadIdx.x; item < HW * chunks; item += SES_THREADS) {
+    const int px = item / chunks, ch = item - px * chunks;
+    const uint4 v = *reinterpret_cast<const uint4*>(ib + static_cast<size_t>(px) * in_ps + ch * 8);
+    const float4 g0 = *reinterpret_cast<const float4*>(&gate_s[ch * 8]);
+    const float4 g1 = *reinterpret_cast<const float4*>(&gate_s[ch * 8 + 4]);
+    uint4 o;
+    o.x = pack_bf16x2(bf16_lo(v.x) * g0.x, bf16_hi(v.x) * g0.y);
+    o.y = pack_bf16x2(bf16_lo(v.y) * g0.z, bf16_hi(v.y) * g0.w);
+    o.z = pack_bf16x2(bf16_lo(v.z) * g1.x, bf16_hi(v.z) * g1.y);
+    o.w = pack_bf16x2(bf16_lo(v.w) * g1.z, bf16_hi(v.w) * g1.w);
+    *reinterpret_cast<uint4*>(ob + static_cast<size_t>(px) * out_ps + ch * 8) = o;
+  }
+}
+
+int se_scale_launch(const View& in, const View& out, const float* hid, const float* w2t, const float* b2, int s,
+                    cudaStream_t stream) {
+  if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W || in.pix_stride % 8 || out.pix_stride % 8)
+    return fail(B200_ERR_INVALID, "se_scale: shape mismatch");
+  if (s <= 0 || s > 256) return fail(B200_ERR_INVALID, "se_scale: squeeze width must be in [1, 256]");
+  const dim3 grid((in.C + SES_C - 1) / SES_C, in.N);
+  se_scale_kernel<<<grid, SES_THREADS, 0, stream>>>(static_cast<const uint16_t*>(in.base), in.pix_stride,
+                                                    static_cast<uint16_t*>(out.base), out.pix_stride, in.H * in.W, in.C,
+                                                    hid, w2t, b2, s);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
 // y[n,h,w,c] = x[n,h,w,c] * gate[n][c]
 __global__ void __launch_bounds__(256)
 channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C8,

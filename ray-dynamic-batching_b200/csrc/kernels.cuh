@@ -57,6 +57,12 @@ int fc_launch(const float* x, const float* w, const float* b, float* out, int n,
 // gate[n][c] = sigmoid(fc2(silu(fc1(mean)))) from the depthwise kernel's strip sums; w1 [S][C], w2t [S][C] (fc2 transposed)
 int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw, const float* w1, const float* b1,
                    const float* w2t, const float* b2, int s, float* gate, cudaStream_t stream);
+// the same block in two launches that never pull a whole weight matrix through one SM:
+// hid[n][j] = silu(fc1(mean)) fp32 [N][S], then y = x * sigmoid(fc2(hid)) with the gate computed per 64-channel slice
+int se_hidden_launch(const float* sums, int n, int rows, int c, float inv_hw, const float* w1, const float* b1, int s,
+                     float* hid, cudaStream_t stream);
+int se_scale_launch(const View& in, const View& out, const float* hid, const float* w2t, const float* b2, int s,
+                    cudaStream_t stream);
 // y = x * gate[n][c]  (SE excitation), gate fp32 already passed through sigmoid
 int channel_scale_launch(const View& in, const View& out, const float* gate, cudaStream_t stream);
 

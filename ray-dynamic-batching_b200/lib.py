@@ -43,6 +43,9 @@ SIGNATURES = {
                                             c_int, c_int, c_int, c_void_p, c_void_p]),
     "b200_se_gate": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                              c_void_p, c_void_p]),
+    "b200_se_hidden": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "b200_se_scale_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
+                                   c_void_p, c_int, c_void_p]),
     "b200_maxpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int,
                                   c_void_p]),
     "b200_global_avgpool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -136,7 +136,8 @@ def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
 
 
 @pytest.mark.parametrize("n,h,w,c,stride,act", [(3, 14, 14, 960, 1, 2), (2, 7, 7, 1536, 1, 2), (2, 28, 28, 256, 2, 2),
-                                                (5, 14, 14, 960, 2, 2), (1, 21, 7, 8, 1, 0), (2, 13, 14, 16, 2, 1)])
+                                                (5, 14, 14, 960, 2, 2), (1, 21, 7, 8, 1, 0), (2, 13, 14, 16, 2, 1),
+                                                (2, 28, 28, 24, 1, 2), (1, 56, 28, 40, 2, 0)])
 def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, act):
     """Strip kernel with the SE squeeze fused in (odd row counts, both strides), then the one-launch gate; against
     torch: AdaptiveAvgPool2d(1) of the STORED output, fc1 + SiLU, fc2 + sigmoid (tv ops/misc.py:249-254)."""
@@ -145,7 +146,8 @@ def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, 
     b = rnd((c,), 13, cuda, torch.float32)
     ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
     strips = b200lib.b200_dwconv3x3_strips(ho, wo, stride)
-    assert strips == ((ho + 1) // 2 if stride == 1 else ho) * (wo // 7)
+    raw = ((ho + 1) // 2 if stride == 1 else ho) * (wo // 7)
+    assert strips in (raw, 1)      # 1: B200_DW_SQ=1 reduces up to 32 strips inside the kernel
     out = torch.full((n, ho, wo, c), float("nan"), device=cuda, dtype=torch.bfloat16)
     sums = torch.full((n, strips, c), float("nan"), device=cuda)
     w9 = wt.reshape(c, 9).t().contiguous()
@@ -177,6 +179,17 @@ def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, 
     mean = out.float().mean(dim=(1, 2))
     want = torch.sigmoid(F.silu(mean @ w1.t() + b1) @ w2.t() + b2)
     assert torch.allclose(gate, want, rtol=1e-4, atol=1e-5), (gate - want).abs().max().item()
+
+    # the two-launch form the engine uses: hidden units, then fc2 + sigmoid + scale in one pass over the activation
+    hid = torch.full((n, sq), float("nan"), device=cuda)
+    check(b200lib.b200_se_hidden(ptr(sums), n, strips, c, 1.0 / (ho * wo), ptr(w1), ptr(b1), sq, ptr(hid), stream_ptr()))
+    scaled = torch.full((n, ho, wo, c), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_se_scale_nhwc(ptr(out), n, ho, wo, c, 0, ptr(hid), ptr(w2t), ptr(b2), sq, ptr(scaled), 0,
+                                     stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.allclose(hid, F.silu(mean @ w1.t() + b1), rtol=1e-4, atol=1e-5)
+    ok, e = close_bf16(scaled, out.float() * want.view(n, 1, 1, c))
+    assert ok, e
 
 
 def test_dwconv3x3_squeeze_rejects_widths_without_strips(b200lib, cuda):
