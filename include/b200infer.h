@@ -93,6 +93,18 @@ B200_API int b200_stem_row_conv_nhwc(const void* in, int n, int h, int w, const 
 B200_API int b200_stem_pool_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
                                  int out_pix_stride, void* stream);
 
+/* The same two kernels for every stride-2 stem the served models have: ksize 7 (pad 3) or 3 (pad 1), cout a multiple of 8
+ * up to 64, act none / relu / silu (tv shufflenetv2.py:112-118 conv1 + maxpool, efficientnet.py:283-287, YOLOv8 layer 0).
+ * The aligned window of output pixel ow starts at input pixel 2*ow - pad - 1 and spans kc 16-byte chunks (kc = 4 for 7x7,
+ * 2 for 3x3). weight: bf16 image [ksize][kc][cout <= 32 ? 32 : 64][8] (b200_stem_row_weight_bytes_k(ksize, cout) bytes):
+ * element e of chunk k of kernel row r = weight[cout][c = e % 4][r][s = 2k + e / 4 - 1], zero where c == 3, s outside the
+ * kernel, or the row is past cout; bias fp32 padded to the same width. The pooled variant needs w/2 <= 128. */
+B200_API int b200_stem_row_weight_bytes_k(int ksize, int cout);
+B200_API int b200_stem_row_conv_k_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                                       int cout, int out_pix_stride, int ksize, int act, void* stream);
+B200_API int b200_stem_pool_k_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                                   int cout, int out_pix_stride, int ksize, int act, void* stream);
+
 /* Depthwise 3x3 (pad 1) + folded BN + activation. Replaces tv shufflenetv2.py:62-76 `depthwise_conv` and the depthwise
  * stage of MBConv (tv efficientnet.py:140-151). weight: fp32 [9][c]; bias fp32 [c]. */
 B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,

@@ -88,14 +88,16 @@ class PlanInterpreter:
                 ct = stem_cout_tile(cout)
                 cpad = (cout + ct - 1) // ct * ct
                 x = B[p[0]][..., :3].permute(0, 3, 1, 2)
-                if p[12] in (2, 3):      # Toeplitz stem (3: fused with MaxPool2d(3,2,1)): bf16 image [7][4][64][8], element e of chunk k = pixel 2k + e//4, channel e%4
-                    img = self._bf16w(op["w_off"], 7 * 4 * 64 * 8).view(7, 4, 64, 8)
-                    w = torch.zeros(64, 3, 7, 7)
-                    for r in range(7):
-                        for q in range(7):
+                if p[12] in (2, 3):      # Toeplitz stem (3: fused with MaxPool2d(3,2,1)): bf16 image [k][kc][nout][8], element e of chunk c = pixel 2c + e//4, channel e%4
+                    kc = 4 if k == 7 else 2
+                    nout = 32 if cout <= 32 else 64
+                    img = self._bf16w(op["w_off"], k * kc * nout * 8).view(k, kc, nout, 8)
+                    w = torch.zeros(cout, 3, k, k)
+                    for r in range(k):
+                        for q in range(k):
                             wp_ = q + 1
-                            w[:, :, r, q] = img[r, wp_ // 2, :, (wp_ % 2) * 4:(wp_ % 2) * 4 + 3]
-                    b = self._f32(op["b_off"], 64)
+                            w[:, :, r, q] = img[r, wp_ // 2, :cout, (wp_ % 2) * 4:(wp_ % 2) * 4 + 3]
+                    b = self._f32(op["b_off"], nout)[:cout]
                 elif p[12] == 1:      # tensor-core stem layout: bf16 [nout][kpad], K = r*row + (s+1)*4 + c
                     row, kpad = (32, 256) if k == 7 else (16, 64)
                     nout = 16 if cout <= 16 else (32 if cout <= 32 else 64)

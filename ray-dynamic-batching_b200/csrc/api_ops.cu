@@ -72,6 +72,26 @@ int b200_stem_pool_nhwc(const void* in, int n, int h, int w, const void* weight,
                           weight, bias, static_cast<cudaStream_t>(stream));
 }
 
+int b200_stem_row_weight_bytes_k(int ksize, int cout) { return stem_row_weight_bytes_k(ksize, cout); }
+
+int b200_stem_row_conv_k_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                              int cout, int out_pix_stride, int ksize, int act, void* stream) {
+  if (ksize != 7 && ksize != 3) return fail(B200_ERR_INVALID, "stem_row: kernel must be 7x7 or 3x3");
+  const int pad = ksize / 2;
+  const int ho = (h + 2 * pad - ksize) / 2 + 1, wo = (w + 2 * pad - ksize) / 2 + 1;
+  return stem_row_launch_k(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, cout, out_pix_stride),
+                           weight, bias, ksize, act, static_cast<cudaStream_t>(stream));
+}
+
+int b200_stem_pool_k_nhwc(const void* in, int n, int h, int w, const void* weight, const float* bias, void* out,
+                          int cout, int out_pix_stride, int ksize, int act, void* stream) {
+  if (ksize != 7 && ksize != 3) return fail(B200_ERR_INVALID, "stem_pool: kernel must be 7x7 or 3x3");
+  const int pad = ksize / 2;
+  const int ho = ((h + 2 * pad - ksize) / 2 + 1) / 2, wo = ((w + 2 * pad - ksize) / 2 + 1) / 2;
+  return stem_pool_launch_k(make_view(const_cast<void*>(in), n, h, w, 4, 4), make_view(out, n, ho, wo, cout, out_pix_stride),
+                            weight, bias, ksize, act, static_cast<cudaStream_t>(stream));
+}
+
 int b200_stem_tc_kpad(int ksize) { return stem_tc_kpad(ksize); }
 int b200_stem_tc_nout(int cout) { return stem_tc_nout(cout); }
 

@@ -163,13 +163,13 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
         break;
       case OP_STEM:
         if (p[12] == 3) {
-          rc = stem_pool_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
-                                reinterpret_cast<const float*>(W + po.rec.b_off), stream);
+          rc = stem_pool_launch_k(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
+                                  reinterpret_cast<const float*>(W + po.rec.b_off), p[8], p[11], stream);
           break;
         }
         if (p[12] == 2) {
-          rc = stem_row_launch(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
-                               reinterpret_cast<const float*>(W + po.rec.b_off), stream);
+          rc = stem_row_launch_k(view(p[0], p[1], p[2], batch), view(p[3], p[4], p[5], batch), W + po.rec.w_off,
+                                 reinterpret_cast<const float*>(W + po.rec.b_off), p[8], p[11], stream);
           break;
         }
         if (p[12] == 1) {

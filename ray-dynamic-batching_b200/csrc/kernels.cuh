@@ -33,6 +33,13 @@ int stem_row_weight_bytes();
 int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream);
 // fused conv1 + bn1 + relu + maxpool(3,2,1): `out` is the pooled tensor
 int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream);
+// the same two kernels for any served stride-2 stem: ksize 7 (pad 3) or 3 (pad 1), cout <= 64 (multiple of 8),
+// act none / relu / silu; weights = bf16 image [ksize][ksize == 7 ? 4 : 2][cout <= 32 ? 32 : 64][8]
+int stem_row_weight_bytes_k(int ksize, int cout);
+int stem_row_launch_k(const View& in, const View& out, const void* w, const float* bias, int ksize, int act,
+                      cudaStream_t stream);
+int stem_pool_launch_k(const View& in, const View& out, const void* w, const float* bias, int ksize, int act,
+                       cudaStream_t stream);
 
 // ---- packed-K gather convolution for small Cin (gather_conv.cu): bf16 weights [npad][kpad], K index = tap*cin_p + c ----
 int gather_conv_npad(int cout);

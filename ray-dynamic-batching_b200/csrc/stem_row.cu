@@ -26,10 +26,25 @@ static constexpr int SR_STAGES = 4;
 // (96 B) before the first window, so descriptors start at +96.
 static constexpr int SR_GROUPS = 18;
 static constexpr int SR_ROW_BYTES = SR_GROUPS * 128; // 2304
-static constexpr int SR_LEAD_BYTES = 96;
-static constexpr int SR_STAGE_BYTES = 7 * SR_ROW_BYTES;   // 16128 = 126 * 128
-static constexpr int SR_W_BYTES = 7 * 4 * 64 * 16;   // weights: [kernel row][k chunk][cout][8 bf16] = 28672 B
 static constexpr int SR_OUT_BYTES = 128 * 128;       // one staged output tile (128 pixels x 64 channels bf16)
+
+// Geometry of a stride-2 stem with a KS x KS kernel and pad KS / 2 (7x7 pad 3: ResNet; 3x3 pad 1: ShuffleNetV2,
+// EfficientNetV2, YOLOv8), NOUT = accumulator width (cout rounded up to 32 or 64).  The aligned window of output pixel ow
+// starts at input pixel 2*ow - pad - 1 and is KC 16-byte chunks (2 pixels each) long; GEMM-K per kernel row is KC * 8.
+template <int KS, int NOUT_>
+struct StemCfg {
+  static constexpr int KR = KS;                       // kernel rows = input rows per output row
+  static constexpr int PAD = KS / 2;
+  static constexpr int KC = (KS + 2) / 2 & ~1;        // 7 -> 4 chunks (8 pixels), 3 -> 2 chunks (4 pixels)
+  static constexpr int MMAS = KC / 2;                 // K = 16 (two chunks) per MMA
+  static constexpr int NOUT = NOUT_;
+  static constexpr int LEAD_BYTES = (15 - PAD) * 8;   // the box starts 16 pixels left of the tile's first output pixel pair
+  static constexpr int STAGE_BYTES = KR * SR_ROW_BYTES;
+  static constexpr int W_BYTES = KR * KC * NOUT * 16; // weights: [kernel row][k chunk][cout][8 bf16]
+  static constexpr int TMEM_COLS = 2 * NOUT < 32 ? 32 : 2 * NOUT;
+  static_assert(KS == 7 || KS == 3, "stem kernel size");
+  static_assert(NOUT == 32 || NOUT == 64, "stem accumulator width");
+};
 
 // Non-swizzled K-major descriptor: start | LBO (stride between the two 16-byte K chunks of one MMA) | SBO (stride between
 // groups of 8 rows) | version 1 | layout type 0.
@@ -46,9 +61,12 @@ struct StemRowParams {
   int total_tiles;       // N * Ho * segs
 };
 
+template <int KS, int NOUT, int ACT>
 __global__ void __launch_bounds__(SR2_THREADS, 1)
 stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap out_map,
                 const __grid_constant__ StemRowParams p) {
+  using G = StemCfg<KS, NOUT>;
+  constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
   __shared__ uint32_t tmem_base_s;
@@ -68,7 +86,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
-  if (threadIdx.x < 64) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (threadIdx.x < NOUT) bias_s[threadIdx.x] = p.bias[threadIdx.x];
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&in_map);
     tma_prefetch_desc(&out_map);
@@ -82,7 +100,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     }
     fence_barrier_init();
   } else if (warp == 1) {
-    tmem_alloc<128>(smem_u32(&tmem_base_s));
+    tmem_alloc<G::TMEM_COLS>(smem_u32(&tmem_base_s));
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -107,15 +125,15 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
       mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
       const uint32_t full = smem_u32(&bar_full[s]);
       if (elect_one()) {
-        mbar_expect_tx(full, 7 * SR_ROW_BYTES);
+        mbar_expect_tx(full, G::KR * SR_ROW_BYTES);
         // box [64 (16 pixels), 18 groups, 7 rows, 1 image] at (0, ow0/8 - 1, 2*oh - 3, n); outside the image -> zeros
-        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - 3, n_oh / p.Ho);
+        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - G::PAD, n_oh / p.Ho);
       }
     }
     __syncwarp();
   } else if (warp == 1) {
     {
-      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
       for (int it = 0; it < my_tiles; ++it) {
         const int b = it & 1, s = it % SR_STAGES;
         mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
@@ -124,13 +142,13 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
         const uint32_t a0 = ring + s * SR_STAGE_BYTES;
         if (elect_one()) {
 #pragma unroll
-          for (int r = 0; r < 7; ++r) {
+          for (int r = 0; r < G::KR; ++r) {
 #pragma unroll
-            for (int kk = 0; kk < 2; ++kk) {
-              // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride 1024, 8-row stride 128
+            for (int kk = 0; kk < G::MMAS; ++kk) {
+              // A: row m at +m*16, K chunk at +16  (overlapping windows);  B: [k chunk][cout][8]: chunk stride NOUT*16, 8-row stride 128
               const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
-              const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
-              umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+              const uint64_t bdesc = umma_desc_noswz(wsm + (r * G::KC + kk * 2) * (NOUT * 16), NOUT * 16, 128);
+              umma_bf16(tmem_base + b * NOUT, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
             }
           }
           umma_commit(smem_u32(&bar_empty[s]));
@@ -156,9 +174,9 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
       mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
       tc_fence_after();
       const uint32_t dst_row = stage_out + b * SR_OUT_BYTES + row * 128;
-      const uint32_t acc = tmem_base + b * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+      const uint32_t acc = tmem_base + b * NOUT + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll
-      for (int cc = 0; cc < 2; ++cc) {
+      for (int cc = 0; cc < NOUT / 32; ++cc) {
         uint32_t v[32];
         tmem_ld_32x32(acc + cc * 32, v);
         tmem_ld_wait();
@@ -167,7 +185,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
           const int chunk = cc * 4 + g;
           float f[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) f[i] = fmaxf(__uint_as_float(v[g * 8 + i]) + bias_s[chunk * 8 + i], 0.f);
+          for (int i = 0; i < 8; ++i) f[i] = apply_act(__uint_as_float(v[g * 8 + i]) + bias_s[chunk * 8 + i], ACT);
           const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
           const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((chunk ^ sw) << 4)), "r"(o0), "r"(o1),
@@ -193,7 +211,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<128>(tmem_base);
+    tmem_dealloc<G::TMEM_COLS>(tmem_base);
   }
 }
 
@@ -211,6 +229,7 @@ struct StemPoolParams {
   const float* bias;
   uint16_t* out;        // pooled NHWC [N][Ho/2][Wo/2][out_ps]
   int out_ps;
+  int cout;             // stored channels (multiple of 8, <= NOUT)
   int Ho, Wo;           // stem output size
   int bands;            // bands per image = ceil((Ho/2) / SP_BAND)
   int total_units;      // N * bands
@@ -225,8 +244,11 @@ __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
 static constexpr int SP_THREADS = 512;   // warps 0: TMA, 1: MMA, 4-7 / 8-11: drain of accumulator 0 / 1, 12-15: pooling
 static constexpr int SP_RING = 4;        // stem rows kept in shared memory
 
+template <int KS, int NOUT, int ACT>
 __global__ void __launch_bounds__(SP_THREADS, 1)
 stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ StemPoolParams p) {
+  using G = StemCfg<KS, NOUT>;
+  constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
   __shared__ __align__(8) uint64_t bar_row_ready[SP_RING], bar_row_free[SP_RING];
@@ -247,7 +269,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
-  if (threadIdx.x < 64) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (threadIdx.x < NOUT) bias_s[threadIdx.x] = p.bias[threadIdx.x];
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&in_map);
     for (int s = 0; s < SR_STAGES; ++s) {
@@ -264,7 +286,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     }
     fence_barrier_init();
   } else if (warp == 1) {
-    tmem_alloc<128>(smem_u32(&tmem_base_s));
+    tmem_alloc<G::TMEM_COLS>(smem_u32(&tmem_base_s));
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -292,8 +314,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
           if (elect_one()) {
-            mbar_expect_tx(full, 7 * SR_ROW_BYTES);
-            tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - 3, n);
+            mbar_expect_tx(full, G::KR * SR_ROW_BYTES);
+            tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - G::PAD, n);
           }
         }
       }
@@ -301,7 +323,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     __syncwarp();
   } else if (warp == 1) {
     {
-      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, 64);
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
       int it = 0;
       for (int u = unit0; u < unit0 + my_units; ++u) {
         int n, ph0, ph1, y_lo, y_hi;
@@ -314,12 +336,12 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           const uint32_t a0 = ring + s * SR_STAGE_BYTES;
           if (elect_one()) {
 #pragma unroll
-            for (int r = 0; r < 7; ++r) {
+            for (int r = 0; r < G::KR; ++r) {
 #pragma unroll
-              for (int kk = 0; kk < 2; ++kk) {
+              for (int kk = 0; kk < G::MMAS; ++kk) {
                 const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
-                const uint64_t bdesc = umma_desc_noswz(wsm + (r * 4 + kk * 2) * 1024, 1024, 128);
-                umma_bf16(tmem_base + b * 64, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+                const uint64_t bdesc = umma_desc_noswz(wsm + (r * G::KC + kk * 2) * (NOUT * 16), NOUT * 16, 128);
+                umma_bf16(tmem_base + b * NOUT, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
               }
             }
             umma_commit(smem_u32(&bar_empty[s]));
@@ -348,9 +370,9 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
         tc_fence_after();
         const uint32_t dst_row = rows + slot * SR_OUT_BYTES + row * 128;
-        const uint32_t acc = tmem_base + b * 64 + (static_cast<uint32_t>(quarter * 32) << 16);
+        const uint32_t acc = tmem_base + b * NOUT + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
+        for (int cc = 0; cc < NOUT / 32; ++cc) {
           uint32_t v[32];
           tmem_ld_32x32(acc + cc * 32, v);
           tmem_ld_wait();
@@ -360,10 +382,10 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
             const float4 b0 = *reinterpret_cast<const float4*>(&bias_s[chunk * 8]);
             const float4 b1 = *reinterpret_cast<const float4*>(&bias_s[chunk * 8 + 4]);
             float f[8];
-            f[0] = fmaxf(__uint_as_float(v[g * 8 + 0]) + b0.x, 0.f); f[1] = fmaxf(__uint_as_float(v[g * 8 + 1]) + b0.y, 0.f);
-            f[2] = fmaxf(__uint_as_float(v[g * 8 + 2]) + b0.z, 0.f); f[3] = fmaxf(__uint_as_float(v[g * 8 + 3]) + b0.w, 0.f);
-            f[4] = fmaxf(__uint_as_float(v[g * 8 + 4]) + b1.x, 0.f); f[5] = fmaxf(__uint_as_float(v[g * 8 + 5]) + b1.y, 0.f);
-            f[6] = fmaxf(__uint_as_float(v[g * 8 + 6]) + b1.z, 0.f); f[7] = fmaxf(__uint_as_float(v[g * 8 + 7]) + b1.w, 0.f);
+            f[0] = apply_act(__uint_as_float(v[g * 8 + 0]) + b0.x, ACT); f[1] = apply_act(__uint_as_float(v[g * 8 + 1]) + b0.y, ACT);
+            f[2] = apply_act(__uint_as_float(v[g * 8 + 2]) + b0.z, ACT); f[3] = apply_act(__uint_as_float(v[g * 8 + 3]) + b0.w, ACT);
+            f[4] = apply_act(__uint_as_float(v[g * 8 + 4]) + b1.x, ACT); f[5] = apply_act(__uint_as_float(v[g * 8 + 5]) + b1.y, ACT);
+            f[6] = apply_act(__uint_as_float(v[g * 8 + 6]) + b1.z, ACT); f[7] = apply_act(__uint_as_float(v[g * 8 + 7]) + b1.w, ACT);
             const uint32_t o0 = pack_bf16x2(f[0], f[1]), o1 = pack_bf16x2(f[2], f[3]);
             const uint32_t o2 = pack_bf16x2(f[4], f[5]), o3 = pack_bf16x2(f[6], f[7]);
             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst_row + ((chunk ^ sw) << 4)), "r"(o0), "r"(o1),
@@ -390,8 +412,9 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         if (pool) {
           const int ph = y >> 1;
           uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
-          for (int item = ptid; item < Wp * 8; item += 128) {
-            const int pw = item >> 3, chunk = item & 7;
+          const int CH = p.cout >> 3;               // 16-byte chunks per pooled pixel
+          for (int item = ptid; item < Wp * CH; item += 128) {
+            const int pw = item / CH, chunk = item - pw * CH;
             // Branch-free window: a tap outside the image is replaced by its in-window neighbour (max is idempotent), so
             // the nine 16-byte loads are independent and issue back to back; with a branch per tap this loop was
             // latency-bound and the pooling warps were the kernel's bottleneck.  Only the left column (pw = 0) and the top
@@ -429,65 +452,121 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<128>(tmem_base);
+    tmem_dealloc<G::TMEM_COLS>(tmem_base);
   }
 }
 
-// Fused conv1 + bn1 + relu + maxpool(3,2,1).  `out` is the pooled tensor [N][Ho/2][Wo/2][64].
-int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
-  if (in.C != 4 || in.pix_stride != 4 || in.W % 16) return fail(B200_ERR_INVALID, "stem_pool: input must be NHWC4 with width a multiple of 16");
-  const int Ho = (in.H + 6 - 7) / 2 + 1, Wo = (in.W + 6 - 7) / 2 + 1;
-  if (Wo > 128 || (Ho & 1) || (Wo & 1)) return fail(B200_ERR_INVALID, "stem_pool: needs stem width <= 128 and even stem size");
-  if (out.C != 64 || out.pix_stride % 8 || out.H != Ho / 2 || out.W != Wo / 2 || out.N != in.N)
-    return fail(B200_ERR_INVALID, "stem_pool: output geometry mismatch");
-  CUtensorMap in_map;
-  {
-    const uint64_t dims[4] = {64, uint64_t(in.W / 16), uint64_t(in.H), uint64_t(in.N)};
-    const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
-    const uint32_t box[4] = {64, uint32_t(SR_GROUPS), 7, 1};
-    B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
+// ---------------------------------------------------------------------------------------------------------------- host
+static int stem_nout(int cout) { return cout <= 32 ? 32 : 64; }
+
+int stem_row_weight_bytes_k(int ksize, int cout) {
+  if ((ksize != 7 && ksize != 3) || cout <= 0 || cout > 64) return 0;
+  const int kc = ksize == 7 ? 4 : 2;
+  return ksize * kc * stem_nout(cout) * 16;
+}
+int stem_row_weight_bytes() { return stem_row_weight_bytes_k(7, 64); }
+
+static int stem_check(const char* who, const View& in, const View& out, int ksize, int act, int Ho, int Wo) {
+  if (in.C != 4 || in.pix_stride != 4 || in.W % 16)
+    return fail(B200_ERR_INVALID, std::string(who) + ": input must be NHWC4 with width a multiple of 16");
+  if (ksize != 7 && ksize != 3) return fail(B200_ERR_INVALID, std::string(who) + ": kernel must be 7x7 or 3x3 (stride 2, pad k/2)");
+  if (out.C % 8 || out.C > 64 || out.pix_stride % 8) return fail(B200_ERR_INVALID, std::string(who) + ": cout must be a multiple of 8, at most 64");
+  if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU) return fail(B200_ERR_INVALID, std::string(who) + ": activation must be none, relu or silu");
+  if ((in.H + 2 * (ksize / 2) - ksize) / 2 + 1 != Ho || (in.W + 2 * (ksize / 2) - ksize) / 2 + 1 != Wo)
+    return fail(B200_ERR_INVALID, std::string(who) + ": output geometry mismatch");
+  return B200_OK;
+}
+
+static int stem_in_map(CUtensorMap* m, const View& in, int krows) {
+  const uint64_t dims[4] = {64, uint64_t(in.W / 16), uint64_t(in.H), uint64_t(in.N)};
+  const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
+  const uint32_t box[4] = {64, uint32_t(SR_GROUPS), uint32_t(krows), 1};
+  return encode_tmap(m, in.base, 4, dims, str, box, SWZ_NONE);
+}
+
+template <int KS, int NOUT, int ACT>
+static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p, cudaStream_t stream) {
+  using G = StemCfg<KS, NOUT>;
+  const size_t smem = size_t(SR_STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_pool_kernel<KS, NOUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev & 63] = true;
   }
+  const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
+  stem_pool_kernel<KS, NOUT, ACT><<<ctas, SP_THREADS, smem, stream>>>(in_map, p);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+template <int KS, int NOUT, int ACT>
+static int stem_row_launch_t(const CUtensorMap& in_map, const CUtensorMap& out_map, const StemRowParams& p, cudaStream_t stream) {
+  using G = StemCfg<KS, NOUT>;
+  const size_t smem = size_t(SR_STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + 2 * SR_OUT_BYTES + 1024;
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_row_kernel<KS, NOUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev & 63] = true;
+  }
+  const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
+  stem_row_kernel<KS, NOUT, ACT><<<ctas, SR2_THREADS, smem, stream>>>(in_map, out_map, p);
+  B200_CUDA_OK(cudaGetLastError());
+  return B200_OK;
+}
+
+// the served stems: 7x7 -> 64 ReLU (ResNet), 3x3 -> <= 32 with ReLU (ShuffleNetV2) or SiLU (EfficientNetV2, YOLOv8)
+#define B200_STEM_DISPATCH(FN, ...)                                                                       \
+  do {                                                                                                    \
+    if (ksize == 7 && nout == 64 && act == ACT_RELU) return FN<7, 64, ACT_RELU>(__VA_ARGS__);             \
+    if (ksize == 3 && nout == 32 && act == ACT_RELU) return FN<3, 32, ACT_RELU>(__VA_ARGS__);             \
+    if (ksize == 3 && nout == 32 && act == ACT_SILU) return FN<3, 32, ACT_SILU>(__VA_ARGS__);             \
+    if (ksize == 3 && nout == 64 && act == ACT_SILU) return FN<3, 64, ACT_SILU>(__VA_ARGS__);             \
+    if (ksize == 3 && nout == 64 && act == ACT_RELU) return FN<3, 64, ACT_RELU>(__VA_ARGS__);             \
+    return fail(B200_ERR_INVALID, "stem: this (kernel, width, activation) combination is not instantiated"); \
+  } while (0)
+
+// Fused stem conv + bn + act + maxpool(3,2,1).  `out` is the pooled tensor [N][Ho/2][Wo/2][cout].
+int stem_pool_launch_k(const View& in, const View& out, const void* w, const float* bias, int ksize, int act,
+                       cudaStream_t stream) {
+  const int Ho = (in.H + 2 * (ksize / 2) - ksize) / 2 + 1, Wo = (in.W + 2 * (ksize / 2) - ksize) / 2 + 1;
+  B200_TRY(stem_check("stem_pool", in, out, ksize, act, Ho, Wo));
+  if (Wo > 128 || (Ho & 1) || (Wo & 1)) return fail(B200_ERR_INVALID, "stem_pool: needs stem width <= 128 and even stem size");
+  if (out.H != Ho / 2 || out.W != Wo / 2 || out.N != in.N) return fail(B200_ERR_INVALID, "stem_pool: output geometry mismatch");
+  CUtensorMap in_map;
+  B200_TRY(stem_in_map(&in_map, in, ksize));
   StemPoolParams p;
   p.w = static_cast<const uint16_t*>(w);
   p.bias = bias;
   p.out = static_cast<uint16_t*>(out.base);
   p.out_ps = out.pix_stride;
+  p.cout = out.C;
   p.Ho = Ho; p.Wo = Wo;
   p.bands = (Ho / 2 + SP_BAND - 1) / SP_BAND;
   p.total_units = in.N * p.bands;
-  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
-  static bool configured[64] = {};
-  int dev = 0;
-  B200_CUDA_OK(cudaGetDevice(&dev));
-  if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(stem_pool_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    configured[dev & 63] = true;
-  }
-  const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
-  stem_pool_kernel<<<ctas, SP_THREADS, smem, stream>>>(in_map, p);
-  B200_CUDA_OK(cudaGetLastError());
-  return B200_OK;
+  const int nout = stem_nout(out.C);
+  B200_STEM_DISPATCH(stem_pool_launch_t, in_map, p, stream);
 }
 
-int stem_row_weight_bytes() { return SR_W_BYTES; }
+int stem_pool_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
+  if (out.C != 64) return fail(B200_ERR_INVALID, "stem_pool: cout must be 64");
+  return stem_pool_launch_k(in, out, w, bias, 7, ACT_RELU, stream);
+}
 
-// weights: bf16 smem image [kernel row 7][k chunk 4][cout 64][8]: element e of chunk k = window pixel 2k + e/4 (= kernel
-// column + 1), channel e%4; zero for window pixel 0 and channel 3.  bias fp32 [64].
-int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
-  if (in.C != 4 || in.pix_stride != 4 || in.W % 16) return fail(B200_ERR_INVALID, "stem_row: input must be NHWC4 with width a multiple of 16");
-  if (out.C != 64 || out.pix_stride % 8) return fail(B200_ERR_INVALID, "stem_row: cout must be 64");
-  if ((in.H + 6 - 7) / 2 + 1 != out.H || (in.W + 6 - 7) / 2 + 1 != out.W || in.N != out.N)
-    return fail(B200_ERR_INVALID, "stem_row: output geometry mismatch");
+// weights: bf16 smem image [kernel row][k chunk][NOUT][8]: element e of chunk k = window pixel 2k + e/4 (= kernel
+// column + 1), channel e%4; zero for window pixel 0, channel 3 and rows >= cout.  bias fp32 [NOUT].
+int stem_row_launch_k(const View& in, const View& out, const void* w, const float* bias, int ksize, int act,
+                      cudaStream_t stream) {
+  B200_TRY(stem_check("stem_row", in, out, ksize, act, out.H, out.W));
+  if (in.N != out.N) return fail(B200_ERR_INVALID, "stem_row: output geometry mismatch");
   CUtensorMap in_map, out_map;
-  {
-    const uint64_t dims[4] = {64, uint64_t(in.W / 16), uint64_t(in.H), uint64_t(in.N)};
-    const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
-    const uint32_t box[4] = {64, uint32_t(SR_GROUPS), 7, 1};
-    B200_TRY(encode_tmap(&in_map, in.base, 4, dims, str, box, SWZ_NONE));
-  }
+  B200_TRY(stem_in_map(&in_map, in, ksize));
   {
     const uint64_t ops = uint64_t(out.pix_stride) * 2;
-    const uint64_t dims[3] = {64, uint64_t(out.W), uint64_t(out.N) * out.H};
+    const uint64_t dims[3] = {uint64_t(out.C), uint64_t(out.W), uint64_t(out.N) * out.H};   // channels past cout are clipped
     const uint64_t str[2] = {ops, ops * out.W};
     const uint32_t box[3] = {64, 128, 1};
     B200_TRY(encode_tmap(&out_map, out.base, 3, dims, str, box, SWZ_128B));
@@ -498,18 +577,13 @@ int stem_row_launch(const View& in, const View& out, const void* w, const float*
   p.Ho = out.H; p.Wo = out.W;
   p.segs = (out.W + 127) / 128;
   p.total_tiles = out.N * out.H * p.segs;
-  const size_t smem = size_t(SR_STAGES) * SR_STAGE_BYTES + 256 + SR_W_BYTES + 1024 + 2 * SR_OUT_BYTES + 1024;
-  static bool configured[64] = {};
-  int dev = 0;
-  B200_CUDA_OK(cudaGetDevice(&dev));
-  if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(stem_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    configured[dev & 63] = true;
-  }
-  const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
-  stem_row_kernel<<<ctas, SR2_THREADS, smem, stream>>>(in_map, out_map, p);
-  B200_CUDA_OK(cudaGetLastError());
-  return B200_OK;
+  const int nout = stem_nout(out.C);
+  B200_STEM_DISPATCH(stem_row_launch_t, in_map, out_map, p, stream);
+}
+
+int stem_row_launch(const View& in, const View& out, const void* w, const float* bias, cudaStream_t stream) {
+  if (out.C != 64) return fail(B200_ERR_INVALID, "stem_row: cout must be 64");
+  return stem_row_launch_k(in, out, w, bias, 7, ACT_RELU, stream);
 }
 
 }  // namespace b200

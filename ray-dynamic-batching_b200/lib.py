@@ -32,6 +32,11 @@ SIGNATURES = {
     "b200_stem_row_weight_bytes": (c_int, []),
     "b200_stem_row_conv_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "b200_stem_pool_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "b200_stem_row_weight_bytes_k": (c_int, [c_int, c_int]),
+    "b200_stem_row_conv_k_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                          c_int, c_void_p]),
+    "b200_stem_pool_k_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                      c_int, c_void_p]),
     "b200_stem_tc_kpad": (c_int, [c_int]),
     "b200_stem_tc_nout": (c_int, [c_int]),
     "b200_stem_conv_tc_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,

@@ -77,17 +77,22 @@ def stem_tc_weights(weight, bias):
 
 
 def stem_row_weights(weight, bias):
-    """[64,3,7,7] fp32 -> bf16 bits of the shared-memory image of csrc/stem_row.cu: [kernel row 7][K chunk 4][cout 64][8],
-    element e of chunk k = window pixel 2k + e // 4 (= kernel column + 1), channel e % 4."""
-    cout = weight.shape[0]
-    assert weight.shape == (64, 3, 7, 7)
-    img = torch.zeros(7, 4, 64, 8)
-    for r in range(7):
-        for s_ in range(7):
+    """[cout,3,k,k] fp32 (k = 7 or 3, cout <= 64) -> bf16 bits of the shared-memory image of csrc/stem_row.cu:
+    [kernel row k][K chunk kc][nout][8] with kc = 4 (7x7) or 2 (3x3), nout = 32 or 64; element e of chunk c = window pixel
+    2c + e // 4 (= kernel column + 1), channel e % 4. Bias padded to nout."""
+    cout, cin, k, k2 = weight.shape
+    assert cin == 3 and k == k2 and k in (3, 7) and cout <= 64
+    kc = 4 if k == 7 else 2
+    nout = 32 if cout <= 32 else 64
+    img = torch.zeros(k, kc, nout, 8)
+    for r in range(k):
+        for s_ in range(k):
             wp = s_ + 1
-            k, half = wp // 2, wp % 2
-            img[r, k, :, half * 4:half * 4 + 3] = weight[:, :, r, s_]
-    return PlanBuilder.bf16_bits(img), bias.numpy().astype(np.float32)
+            c, half = wp // 2, wp % 2
+            img[r, c, :cout, half * 4:half * 4 + 3] = weight[:, :, r, s_]
+    bp = torch.zeros(nout)
+    bp[:cout] = bias
+    return PlanBuilder.bf16_bits(img), bp.numpy().astype(np.float32)
 
 
 def act_code(m):
@@ -216,11 +221,12 @@ class PlanBuilder:
         assert cin == 3 and x.buf == self.in_buf
         ho, wo = (x.h + 2 * pad - k) // stride + 1, (x.w + 2 * pad - k) // stride + 1
         out = self.new_act(ho, wo, cout)
-        if self.toeplitz_stem and (k, stride, pad, cout, act) == (7, 2, 3, 64, ACT_RELU) and x.w % 16 == 0:
+        if self.toeplitz_stem and self.toeplitz_ok(k, stride, pad, cout, act) and x.w % 16 == 0:
             wb, bb = stem_row_weights(weight, bias)
             w_off = self.add_weights(wb)
             b_off = self.add_weights(bb)
-            self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, 64, -1, 0, k, stride, pad, act, 2], w_off, b_off, name=name)
+            self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, pad8(cout), -1, 0, k, stride, pad, act, 2], w_off, b_off,
+                     name=name)
             return out
         if self.tensor_core_stem and stride == 2 and ((k == 7 and pad == 3) or (k == 3 and pad == 1)) and cout <= 64 \
                 and x.w % 2 == 0:
@@ -242,16 +248,29 @@ class PlanBuilder:
                  name=name)
         return out
 
-    def stem_pool(self, x: T, weight, bias, name=""):
-        """conv 7x7/2 pad 3 (3 -> 64) + bias + ReLU + MaxPool2d(3,2,1) in one kernel (csrc/stem_row.cu stem_pool_kernel)."""
-        assert weight.shape == (64, 3, 7, 7) and x.buf == self.in_buf
+    @staticmethod
+    def toeplitz_ok(k, stride, pad, cout, act):
+        """The (kernel, width, activation) combinations csrc/stem_row.cu instantiates (B200_STEM_DISPATCH)."""
+        if stride != 2 or cout > 64:
+            return False
+        if (k, pad) == (7, 3):
+            return cout > 32 and act == ACT_RELU
+        if (k, pad) == (3, 1):
+            return act in (ACT_RELU, ACT_SILU)
+        return False
+
+    def stem_pool(self, x: T, weight, bias, act=ACT_RELU, name=""):
+        """stride-2 stem conv (7x7 pad 3 or 3x3 pad 1) + bias + act + MaxPool2d(3,2,1) in one kernel
+        (csrc/stem_row.cu stem_pool_kernel): the stem activation never leaves shared memory."""
+        cout, _, k, _ = weight.shape
+        assert x.buf == self.in_buf and self.toeplitz_ok(k, 2, k // 2, cout, act)
         hs, ws = (x.h - 1) // 2 + 1, (x.w - 1) // 2 + 1
         assert ws <= 128 and hs % 2 == 0 and ws % 2 == 0
-        out = self.new_act(hs // 2, ws // 2, 64)
+        out = self.new_act(hs // 2, ws // 2, cout)
         wb, bb = stem_row_weights(weight, bias)
         w_off = self.add_weights(wb)
         b_off = self.add_weights(bb)
-        self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, 64, -1, 0, 7, 2, 3, ACT_RELU, 3], w_off, b_off, name=name)
+        self._op(OP_STEM, [x.buf, 0, 4, out.buf, out.coff, pad8(cout), -1, 0, k, 2, k // 2, act, 3], w_off, b_off, name=name)
         return out
 
     @staticmethod
@@ -468,7 +487,7 @@ def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
     w, b = fold_bn(model.conv1, model.bn1)
     hs, ws = (in_hw[0] - 1) // 2 + 1, (in_hw[1] - 1) // 2 + 1
     if pb.fuse_stem_pool and ws <= 128 and hs % 2 == 0 and ws % 2 == 0 and in_hw[1] % 16 == 0:
-        x = pb.stem_pool(pb.input(), w, b, name="conv1+maxpool")
+        x = pb.stem_pool(pb.input(), w, b, ACT_RELU, name="conv1+maxpool")
     else:
         x = pb.stem(pb.input(), w, b, 2, 3, ACT_RELU, name="conv1")
         x = pb.maxpool(x, 3, 2, 1, name="maxpool")
@@ -495,8 +514,12 @@ def lower_shufflenet(model, in_hw=(224, 224)) -> PlanBuilder:
     """torchvision ShuffleNetV2 x1.0: tv models/shufflenetv2.py:43-104 (InvertedResidual), 149-163 (_forward_impl)."""
     pb = PlanBuilder("shufflenet_v2_x1_0", in_hw[0], in_hw[1])
     w, b = fold_bn(model.conv1[0], model.conv1[1])
-    x = pb.stem(pb.input(), w, b, 2, 1, ACT_RELU, name="conv1")
-    x = pb.maxpool(x, 3, 2, 1, name="maxpool")
+    hs, ws = (in_hw[0] - 1) // 2 + 1, (in_hw[1] - 1) // 2 + 1
+    if pb.fuse_stem_pool and pb.toeplitz_stem and ws <= 128 and hs % 2 == 0 and ws % 2 == 0 and in_hw[1] % 16 == 0:
+        x = pb.stem_pool(pb.input(), w, b, ACT_RELU, name="conv1+maxpool")
+    else:
+        x = pb.stem(pb.input(), w, b, 2, 1, ACT_RELU, name="conv1")
+        x = pb.maxpool(x, 3, 2, 1, name="maxpool")
     for sname in ("stage2", "stage3", "stage4"):
         for ui, unit in enumerate(getattr(model, sname)):
             nm = "%s.%d." % (sname, ui)

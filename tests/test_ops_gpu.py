@@ -93,6 +93,50 @@ def test_stem_pool_fused_bit_exact_vs_unfused_kernels(b200lib, cuda, cfg):
     assert ok, e
 
 
+@pytest.mark.parametrize("k,cout,act,cfg", [(3, 24, 1, (3, 224, 224)), (3, 24, 2, (2, 224, 224)), (3, 16, 2, (1, 640, 640)),
+                                            (3, 32, 2, (2, 64, 96)), (3, 48, 1, (1, 38, 304)), (7, 64, 1, (1, 64, 64))])
+def test_stem_row_toeplitz_general(b200lib, cuda, k, cout, act, cfg):
+    """The Toeplitz stem for every served stride-2 stem (3x3 pad 1 of ShuffleNetV2 / EfficientNetV2 / YOLOv8, 7x7 pad 3),
+    plain and fused with MaxPool2d(3,2,1); channel counts below the accumulator width are clipped by the TMA store."""
+    from rdb_b200.lowering import stem_row_weights
+    n, h, w = cfg
+    pad = k // 2
+    x4 = torch.zeros(n, h, w, 4, device=cuda, dtype=torch.bfloat16)
+    x4[..., :3] = rnd((n, h, w, 3), 1, cuda)
+    wt = (rnd((cout, 3, k, k), 2, cuda, torch.float32) / (3 * k * k) ** 0.5).to(torch.bfloat16).float()
+    b = rnd((cout,), 3, cuda, torch.float32)
+    wb, bb = stem_row_weights(wt.cpu(), b.cpu())
+    assert wb.nbytes == b200lib.b200_stem_row_weight_bytes_k(k, cout)
+    wdev = torch.from_numpy(wb.astype("int16")).to(cuda)
+    bdev = torch.from_numpy(bb).to(cuda)
+    ho, wo = (h + 2 * pad - k) // 2 + 1, (w + 2 * pad - k) // 2 + 1
+    out = torch.full((n, ho, wo, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_stem_row_conv_k_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(out), cout, 0, k, act, stream_ptr()))
+    torch.cuda.synchronize()
+    ref = F.conv2d(x4[..., :3].float().permute(0, 3, 1, 2), wt, b, stride=2, padding=pad)
+    ref = F.relu(ref) if act == 1 else (F.silu(ref) if act == 2 else ref)
+    assert not torch.isnan(out.float()).any()
+    ok, e = close_bf16(out, ref.permute(0, 2, 3, 1))
+    assert ok, e
+    if wo <= 128 and ho % 2 == 0 and wo % 2 == 0:
+        pooled = torch.empty(n, ho // 2, wo // 2, cout, device=cuda, dtype=torch.bfloat16)
+        check(b200lib.b200_maxpool_nhwc(ptr(out), n, ho, wo, cout, 0, ptr(pooled), 0, 3, 2, 1, stream_ptr()))
+        fused = torch.full((n, ho // 2, wo // 2, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+        check(b200lib.b200_stem_pool_k_nhwc(ptr(x4), n, h, w, ptr(wdev), ptr(bdev), ptr(fused), cout, 0, k, act,
+                                            stream_ptr()))
+        torch.cuda.synchronize()
+        assert torch.equal(fused.view(torch.int16), pooled.view(torch.int16))
+
+
+def test_stem_row_rejects_uninstantiated_combination(b200lib, cuda):
+    x4 = torch.zeros(1, 32, 32, 4, device=cuda, dtype=torch.bfloat16)
+    w = torch.zeros(b200lib.b200_stem_row_weight_bytes_k(7, 32) // 2, device=cuda, dtype=torch.int16)
+    b = torch.zeros(64, device=cuda)
+    out = torch.empty(1, 16, 16, 32, device=cuda, dtype=torch.bfloat16)
+    assert b200lib.b200_stem_row_conv_k_nhwc(ptr(x4), 1, 32, 32, ptr(w), ptr(b), ptr(out), 32, 0, 7, 1, stream_ptr()) != 0
+    assert b200lib.b200_stem_row_conv_k_nhwc(ptr(x4), 1, 32, 32, ptr(w), ptr(b), ptr(out), 32, 0, 5, 1, stream_ptr()) != 0
+
+
 @pytest.mark.parametrize("k,p,cout,cfg,act", [(7, 3, 64, (2, 224, 224), 1), (3, 1, 24, (3, 224, 224), 2),
                                               (3, 1, 16, (1, 96, 130), 2), (7, 3, 64, (5, 38, 50), 1),
                                               (3, 1, 32, (2, 64, 64), 0)])
