@@ -108,6 +108,9 @@ def plan_traffic(blob, batch):
             if p[6] >= 0:
                 b += batch * oh * ow * p[5] * 2
             fl = 2.0 * batch * oh * ow * p[5] * p[2] * k * k
+            if t == lowering.OP_CONV and p[13] > 0:      # K-concatenated second input, sampled with stride p[16]
+                b += batch * oh * ow * p[15] * 2 + p[5] * p[15] * 2
+                fl += 2.0 * batch * oh * ow * p[5] * p[15]
         elif t == lowering.OP_STEM:
             k = p[8]
             b += k * k * 3 * p[5] * 4

@@ -54,6 +54,15 @@ B200_API int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int 
                      const float* bias, const void* residual, int res_pix_stride, void* out, int cout,
                      int out_pix_stride, int ksize, int stride, int pad, int act, void* stream);
 
+/* Two 1x1 convolutions that are summed, as ONE GEMM with concatenated K: out = act(W[:, :cin] . in + W[:, cin:] .
+ * in2[::stride2, ::stride2] + bias). Replaces the last conv of a ResNet bottleneck together with its `downsample` branch
+ * (tv resnet.py:155-161: `out = bn3(conv3(out)); identity = downsample(x); out += identity; relu`): the identity tensor
+ * is neither written nor read back. weight: bf16 [cout][cin + cin2], bias fp32 [cout] (= both folded BN biases added);
+ * cin a multiple of 64; in2 is [n][h2][w2][cin2] with (h2 - 1) / stride2 + 1 == h. */
+B200_API int b200_conv1x1_dual_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* in2, int h2,
+                                    int w2, int cin2, int in2_pix_stride, int stride2, const void* weight,
+                                    const float* bias, void* out, int cout, int out_pix_stride, int act, void* stream);
+
 /* Same contract as b200_conv2d_nhwc for layers with few input channels (cin <= 56, cout <= 256): GEMM-K packs the filter
  * taps (k = tap * cin + c), the im2col tile is gathered into shared memory by cp.async producers. Serves the
  * FusedMBConv 3x3 convolutions of EfficientNetV2 (tv efficientnet.py:172-231) and YOLOv8n's early layers.

@@ -59,9 +59,15 @@ class PlanInterpreter:
             if t == OP_CONV:
                 cin, cout, k, s, pad, act = p[2], p[5], p[8], p[9], p[10], p[11]
                 x = B[p[0]][..., p[1]:p[1] + cin].permute(0, 3, 1, 2)
-                w = self._bf16w(op["w_off"], cout * k * k * cin).view(cout, k, k, cin).permute(0, 3, 1, 2)
                 b = self._f32(op["b_off"], cout)
-                y = F.conv2d(x, w, b, stride=s, padding=pad)
+                if p[13] > 0:      # K-concatenated 1x1 conv: W[:, :cin] . x + W[:, cin:] . x2[::s2, ::s2]
+                    cin2, s2 = p[15], p[16]
+                    wk = self._bf16w(op["w_off"], cout * (cin + cin2)).view(cout, cin + cin2)
+                    x2 = B[p[13] - 1][..., p[14]:p[14] + cin2].permute(0, 3, 1, 2)
+                    y = F.conv2d(x, wk[:, :cin, None, None], b) + F.conv2d(x2, wk[:, cin:, None, None], None, stride=s2)
+                else:
+                    w = self._bf16w(op["w_off"], cout * k * k * cin).view(cout, k, k, cin).permute(0, 3, 1, 2)
+                    y = F.conv2d(x, w, b, stride=s, padding=pad)
                 if p[6] >= 0:
                     r = B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
                     y = _act(y, act) + r if p[12] else _act(y + r, act)

@@ -33,6 +33,26 @@ int b200_conv2d_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_st
   return conv_launch(l, static_cast<cudaStream_t>(stream));
 }
 
+int b200_conv1x1_dual_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* in2, int h2, int w2,
+                           int cin2, int in2_pix_stride, int stride2, const void* weight, const float* bias, void* out,
+                           int cout, int out_pix_stride, int act, void* stream) {
+  if (n <= 0 || h <= 0 || w <= 0 || !in2) return fail(B200_ERR_INVALID, "b200_conv1x1_dual_nhwc: empty input");
+  ConvSpec s;
+  s.in = make_view(const_cast<void*>(in), n, h, w, cin, in_pix_stride);
+  s.in2 = make_view(const_cast<void*>(in2), n, h2, w2, cin2, in2_pix_stride);
+  s.stride2 = stride2;
+  s.out = make_view(out, n, h, w, cout, out_pix_stride);
+  s.w = weight;
+  s.bias = bias;
+  s.ksize = 1;
+  s.stride = 1;
+  s.pad = 0;
+  s.act = act;
+  ConvLaunch l;
+  B200_TRY(conv_prepare(s, &l));
+  return conv_launch(l, static_cast<cudaStream_t>(stream));
+}
+
 int b200_gather_conv_npad(int cout) { return gather_conv_npad(cout); }
 int b200_gather_conv_kpad(int cin, int ksize) { return gather_conv_kpad(cin, ksize); }
 

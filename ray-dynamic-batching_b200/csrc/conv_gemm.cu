@@ -18,6 +18,12 @@ namespace b200 {
 
 static constexpr int BLOCK_M = 128;
 static constexpr int BLOCK_K = 64;
+
+struct ConvParams;
+// k-block kb of a tile -> (tap / input index t, channel offset c0 in that input, weight coordinates (cw, tw)).
+// A K-concatenated 1x1 conv (kb_split > 0) reads input 0 for the first kb_split blocks and input 1 after them, against
+// one weight row [Ca + Cb]; a plain conv walks its taps.
+__device__ __forceinline__ void kb_source(const ConvParams& p, int kb, int& t, int& c0, int& cw, int& tw);
 static constexpr int A_STAGE_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
 static constexpr int CONV_THREADS = 192;
 
@@ -57,7 +63,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   const int t_n = m_tile / p.tiles_h;
   const int w0 = t_w * p.tw, h0 = t_h * p.th, nb0 = t_n * p.tn;
   const int n0 = n_tile * BLOCK_N;
-  const int num_kb = p.num_taps * p.kb_per_tap;
+  const int num_kb = p.num_kb;
 
   // ---- one-time setup ----
   if (warp == 0 && lane == 0) {
@@ -93,11 +99,11 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
         mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
         const uint32_t full = smem_u32(&bar_full[s]);
         mbar_expect_tx(full, Cfg::STAGE_BYTES);
-        const int t = kb / p.kb_per_tap;
-        const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+        int t, c0, cw, tw_;
+        kb_source(p, kb, t, c0, cw, tw_);
         const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
         tma_load_4d(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
-        tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0);
+        tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, cw, tw_, n0);
       }
     }
     __syncwarp();
@@ -222,6 +228,20 @@ struct PConvCfg {
   static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
 };
 
+__device__ __forceinline__ void kb_source(const ConvParams& p, int kb, int& t, int& c0, int& cw, int& tw) {
+  if (p.kb_split > 0) {
+    t = kb >= p.kb_split ? 1 : 0;
+    c0 = (kb - (t ? p.kb_split : 0)) * BLOCK_K;
+    cw = kb * BLOCK_K;
+    tw = 0;
+  } else {
+    t = kb / p.kb_per_tap;
+    c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+    cw = c0;
+    tw = t;
+  }
+}
+
 __device__ __forceinline__ void tile_coords(const ConvParams& p, int tile, int& n_tile, int& w0, int& h0, int& nb0) {
   n_tile = tile % p.n_tiles;
   int m = tile / p.n_tiles;
@@ -264,7 +284,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   const int lane = threadIdx.x & 31;
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t staging = ring + STAGES * Cfg::STAGE_BYTES;
-  const int num_kb = p.num_taps * p.kb_per_tap;
+  const int num_kb = p.num_kb;
   const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
@@ -310,13 +330,13 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const uint32_t ph = (g / STAGES) & 1;
           mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
-          const int t = kb / p.kb_per_tap;
-          const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+          int t, c0, cw, tw_;
+          kb_source(p, kb, t, c0, cw, tw_);
           const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
           if (elect_one()) {
             mbar_expect_tx(full, Cfg::STAGE_BYTES);
             tma_load_4d(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
-            tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0);
+            tma_load_3d(&maps.b, full, a_dst + A_STAGE_BYTES, cw, tw_, n0);
           }
         }
       }
@@ -837,7 +857,7 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
   const int num_pairs = gridDim.x >> 1;
   const uint32_t ring = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t staging = ring + STAGES * Cfg::STAGE_BYTES;
-  const int num_kb = p.num_taps * p.kb_per_tap;
+  const int num_kb = p.num_kb;
   const int my_tiles = (total_pair_tiles - pair + num_pairs - 1) / num_pairs;
 
   // pair tile -> this CTA's 128-pixel m-tile and the shared n-tile
@@ -893,13 +913,13 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
           const uint32_t ph = (g / STAGES) & 1;
           mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
-          const int t = kb / p.kb_per_tap;
-          const int c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
+          int t, c0, cw, tw_;
+          kb_source(p, kb, t, c0, cw, tw_);
           const uint32_t a_dst = ring + s * Cfg::STAGE_BYTES;
           if (elect_one()) {
             if (rank == 0) mbar_expect_tx(full, 2 * Cfg::STAGE_BYTES);   // both CTAs' bytes land on the leader's barrier
             tma_load_4d_2cta(&maps.a[p.tap_map[t]], full, a_dst, c0, w0 + p.tap_dx[t], h0 + p.tap_dy[t], nb0);
-            tma_load_3d_2cta(&maps.b, full, a_dst + A_STAGE_BYTES, c0, t, n0 + static_cast<int>(rank) * (BLOCK_N / 2));
+            tma_load_3d_2cta(&maps.b, full, a_dst + A_STAGE_BYTES, cw, tw_, n0 + static_cast<int>(rank) * (BLOCK_N / 2));
           }
         }
       }
@@ -1107,6 +1127,17 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   const int Wo = (in.W + 2 * s.pad - s.ksize) / s.stride + 1;
   if (Ho != out.H || Wo != out.W || in.N != out.N) return fail(B200_ERR_INVALID, "conv: output geometry mismatch");
   const bool has_res = s.res.base != nullptr;
+  const bool dual = s.in2.base != nullptr;
+  if (dual) {
+    const View& b2 = s.in2;
+    if (s.ksize != 1 || s.stride != 1 || s.pad != 0) return fail(B200_ERR_INVALID, "conv: a second input needs a 1x1 / stride 1 conv");
+    if (s.stride2 != 1 && s.stride2 != 2) return fail(B200_ERR_INVALID, "conv: second-input stride must be 1 or 2");
+    if (in.C % BLOCK_K || b2.C % 8 || b2.pix_stride % 8)
+      return fail(B200_ERR_INVALID, "conv: first input of a K-concatenated conv needs a multiple of 64 channels");
+    if (b2.N != out.N || (b2.H - 1) / s.stride2 + 1 != out.H || (b2.W - 1) / s.stride2 + 1 != out.W)
+      return fail(B200_ERR_INVALID, "conv: second input geometry mismatch");
+    if (has_res) return fail(B200_ERR_INVALID, "conv: a K-concatenated conv takes no residual (the second input replaces it)");
+  }
   if (has_res && (s.res.H != out.H || s.res.W != out.W || s.res.C != out.C || s.res.N != out.N))
     return fail(B200_ERR_INVALID, "conv: residual geometry mismatch");
 
@@ -1116,6 +1147,12 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   const int taps = s.ksize * s.ksize;
   p.num_taps = taps;
   p.kb_per_tap = (in.C + BLOCK_K - 1) / BLOCK_K;
+  p.num_kb = taps * p.kb_per_tap;
+  p.kb_split = 0;
+  if (dual) {
+    p.kb_split = in.C / BLOCK_K;
+    p.num_kb = p.kb_split + (s.in2.C + BLOCK_K - 1) / BLOCK_K;
+  }
   p.cout = out.C;
   p.act = s.act;
   p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
@@ -1123,7 +1160,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.reverse = s.reverse_tiles ? 1 : 0;
   // Tile choice.  Layers with enough arithmetic per byte (K >= 256, Cout >= 128) are bound by shared-memory operand
   // bandwidth in single-CTA mode -> CTA pairs (M = 256), N = 256 when Cout allows.  Thin layers stay single-CTA.
-  const int k_total = in.C * taps;
+  const int k_total = in.C * taps + (dual ? s.in2.C : 0);
   static int res_mode = -1;   // residual layers: 0 single CTA, 1 CTA pair N=128 (deep residual prefetch), 2 CTA pair N=256
   if (res_mode < 0) {
     const char* e = getenv("B200_2CTA_RES_MODE");
@@ -1155,7 +1192,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   // halo kernel: 3x3/s1/p1, Cin <= 64, 16x8-pixel tiles with little padding waste; Cout <= 64, or wider while the layer
   // is too thin in K for the generic kernel (Cin < 64: each of its k-blocks would be mostly padding)
   const long long halo_cover = (long long)((in.W + 7) / 8 * 8) * ((in.H + 15) / 16 * 16);
-  const bool halo = use_halo && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 && s.act != ACT_SIGMOID &&
+  const bool halo = use_halo && !dual && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 && s.act != ACT_SIGMOID &&
                     (out.C <= 64 || (in.C < 64 && out.C <= 256)) && halo_cover * 100 <= (long long)in.W * in.H * 135;
   if (halo) {
     two_cta = false;
@@ -1171,13 +1208,18 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.n_tiles = (out.C + block_n - 1) / block_n;
 
   const uint64_t ips = uint64_t(in.pix_stride) * 2, ops = uint64_t(out.pix_stride) * 2;
-  const bool flat = (s.ksize == 1 && s.stride == 1 && s.pad == 0);
+  const bool flat = (s.ksize == 1 && s.stride == 1 && s.pad == 0) && !(dual && s.stride2 != 1);
   int oW = out.W, oH = out.H, oN = out.N;  // logical output pixel grid used for tiling
   if (flat) {
     oW = out.N * out.H * out.W; oH = 1; oN = 1;
     p.tw = 128; p.th = 1; p.tn = 1;
     B200_TRY(encode_act_view(&L->maps.a[0], in.base, in.C, oW, 1, 1, ips, ips * oW, ips * oW, 128, 1, 1));
     p.tap_map[0] = 0; p.tap_dx[0] = 0; p.tap_dy[0] = 0;
+    if (dual) {
+      const uint64_t ips2 = uint64_t(s.in2.pix_stride) * 2;
+      B200_TRY(encode_act_view(&L->maps.a[1], s.in2.base, s.in2.C, oW, 1, 1, ips2, ips2 * oW, ips2 * oW, 128, 1, 1));
+      p.tap_map[1] = 1; p.tap_dx[1] = 0; p.tap_dy[1] = 0;
+    }
   } else if (halo) {
     p.tw = 8; p.th = 16; p.tn = 1;
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
@@ -1200,6 +1242,14 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
           B200_TRY(encode_act_view(&L->maps.a[py * 2 + px], base, in.C, Wp, Hp, in.N, 2 * ips, 2 * rowb, imgb, p.tw,
                                    p.th, p.tn));
         }
+    }
+    if (dual) {
+      // second input sampled at (stride2 * y, stride2 * x): a view with multiplied strides, tiled like the output
+      const View& b2 = s.in2;
+      const uint64_t ips2 = uint64_t(b2.pix_stride) * 2, rowb2 = ips2 * b2.W, imgb2 = rowb2 * b2.H;
+      B200_TRY(encode_act_view(&L->maps.a[1], b2.base, b2.C, out.W, out.H, out.N, s.stride2 * ips2, s.stride2 * rowb2, imgb2,
+                               p.tw, p.th, p.tn));
+      p.tap_map[1] = 1; p.tap_dx[1] = 0; p.tap_dy[1] = 0;
     }
     for (int r = 0; r < s.ksize; ++r)
       for (int q = 0; q < s.ksize; ++q) {
@@ -1231,8 +1281,9 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   }
   // weights: [Cin, taps, Cout]
   {
-    const uint64_t dims[3] = {uint64_t(in.C), uint64_t(taps), uint64_t(out.C)};
-    const uint64_t str[2] = {uint64_t(in.C) * 2, uint64_t(in.C) * 2 * taps};
+    const uint64_t kc = uint64_t(in.C) + (dual ? uint64_t(s.in2.C) : 0);   // K-concatenated: one weight row [Ca + Cb]
+    const uint64_t dims[3] = {kc, uint64_t(taps), uint64_t(out.C)};
+    const uint64_t str[2] = {kc * 2, kc * 2 * taps};
     const uint32_t box[3] = {halo ? uint32_t(p.pb / 2) : 64u, 1u, uint32_t(two_cta ? block_n / 2 : block_n)};  // a CTA pair loads half each
     B200_TRY(encode_tmap(&L->maps.b, s.w, 3, dims, str, box,
                          !halo || p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B)));
@@ -1240,7 +1291,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   const long long m_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
   if (m_tiles * p.n_tiles > 0x7fffffffLL) return fail(B200_ERR_INVALID, "conv: grid too large");
   L->grid = unsigned(m_tiles * p.n_tiles);
-  L->flops = 2.0 * double(out.N) * out.H * out.W * out.C * double(in.C) * taps;
+  L->flops = 2.0 * double(out.N) * out.H * out.W * out.C * double(k_total);
   return B200_OK;
 }
 

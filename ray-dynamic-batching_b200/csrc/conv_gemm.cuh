@@ -7,6 +7,8 @@ namespace b200 {
 struct ConvSpec {
   View in, out;
   View res;                  // optional residual (base == nullptr -> none); same geometry as `out`
+  View in2;                  // optional second input of a K-concatenated 1x1 conv (base == nullptr -> none): the output is
+  int stride2 = 1;           //   act(W[:, :Ca] . in + W[:, Ca:] . in2[::stride2, ::stride2] + bias), w = [Cout][Ca + Cb]
   const void* w = nullptr;   // bf16 [Cout][k*k][Cin], BatchNorm already folded in
   const float* bias = nullptr;  // fp32 [Cout]
   int ksize = 1, stride = 1, pad = 0;
@@ -27,6 +29,8 @@ struct ConvParams {
   int tw, th, tn;                 // pixels per tile along W, H, N  (tw*th*tn == 128)
   int n_tiles;                    // tiles along Cout
   int num_taps, kb_per_tap;
+  int num_kb;                     // k-blocks per tile (num_taps * kb_per_tap, or both inputs' blocks of a K-concatenated conv)
+  int kb_split;                   // K-concatenated conv: k-blocks [0, kb_split) come from input 0, the rest from input 1; 0 = off
   int cout, act, has_res;  // has_res: 0 none, 1 add before the activation, 2 add after it
   int pb;                  // halo kernel: bytes per pixel of the staged halo (32 / 64 / 128 = swizzle span), K per tap = pb / 2
   int block_n;             // halo kernel: accumulator width (32 or 64)

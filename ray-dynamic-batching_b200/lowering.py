@@ -134,6 +134,7 @@ class PlanBuilder:
         self.toeplitz_stem = True
         self.fuse_stem_pool = os.environ.get('B200_FUSE_STEM_POOL', '1') != '0'   # conv1 + bn1 + relu + maxpool in one kernel
         self.gather_small_cin = True
+        self.fuse_downsample = os.environ.get('B200_FUSE_DOWNSAMPLE', '1') != '0'   # ResNet conv3 + downsample as one GEMM
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
@@ -193,6 +194,31 @@ class PlanBuilder:
             assert (res.h, res.w, res.c, res.cphys) == (ho, wo, cout, cout_p) and np.array_equal(res.cmap, out.cmap)
         self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act,
                            1 if res_after_act else 0], w_off, b_off, name=name)
+        return out
+
+    def conv_dual(self, x: T, weight, bias, x2: T, weight2, bias2, stride2, act, name=""):
+        """act(conv1x1(x) + conv1x1_stride2(x2)) as one K-concatenated GEMM (csrc/conv_gemm.cu, ConvSpec::in2): the last
+        conv of a ResNet bottleneck and its downsample branch, whose output is then neither written nor re-read.
+        weight [Cout, Ca, 1, 1], weight2 [Cout, Cb, 1, 1] (BN folded); biases are added."""
+        cout, ca = weight.shape[:2]
+        cb = weight2.shape[1]
+        assert weight.shape[2:] == (1, 1) and weight2.shape[2:] == (1, 1) and weight2.shape[0] == cout
+        assert ca == x.c and cb == x2.c and x.cphys % 64 == 0
+        assert ((x2.h - 1) // stride2 + 1, (x2.w - 1) // stride2 + 1) == (x.h, x.w)
+        out = self.new_act(x.h, x.w, cout)
+        cap, cbp, cout_p = x.cphys, x2.cphys, out.cphys
+        wp = torch.zeros(cout_p, cap + cbp)
+        wa = torch.zeros(cout, cap)
+        wa[:, torch.as_tensor(x.cmap)] = weight.reshape(cout, ca)
+        wb = torch.zeros(cout, cbp)
+        wb[:, torch.as_tensor(x2.cmap)] = weight2.reshape(cout, cb)
+        wp[torch.as_tensor(out.cmap)] = torch.cat([wa, wb], dim=1)
+        bp = torch.zeros(cout_p)
+        bp[torch.as_tensor(out.cmap)] = bias + bias2
+        w_off = self.add_weights(self.bf16_bits(wp))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        self._op(OP_CONV, [x.buf, x.coff, cap, out.buf, out.coff, cout_p, -1, 0, 1, 1, 0, act, 0,
+                           x2.buf + 1, x2.coff, cbp, stride2], w_off, b_off, name=name)
         return out
 
     def _gather_conv(self, x, weight, bias, stride, pad, act, res, out, name, res_after_act):
@@ -499,10 +525,15 @@ def lower_resnet(model, in_hw=(224, 224)) -> PlanBuilder:
             o = pb.conv(x, w, b, 1, 0, ACT_RELU, name=nm + "conv1")
             w, b = fold_bn(blk.conv2, blk.bn2)
             o = pb.conv(o, w, b, blk.conv2.stride[0], 1, ACT_RELU, name=nm + "conv2")
-            if blk.downsample is not None:
-                w, b = fold_bn(blk.downsample[0], blk.downsample[1])
-                identity = pb.conv(x, w, b, blk.downsample[0].stride[0], 0, ACT_NONE, name=nm + "downsample")
             w, b = fold_bn(blk.conv3, blk.bn3)
+            if blk.downsample is not None and pb.fuse_downsample and o.cphys % 64 == 0:
+                # conv3 and the downsample branch are both 1x1 convs that are summed: one GEMM over [conv2 out | block in]
+                wd, bd = fold_bn(blk.downsample[0], blk.downsample[1])
+                x = pb.conv_dual(o, w, b, x, wd, bd, blk.downsample[0].stride[0], ACT_RELU, name=nm + "conv3+downsample")
+                continue
+            if blk.downsample is not None:
+                wd, bd = fold_bn(blk.downsample[0], blk.downsample[1])
+                identity = pb.conv(x, wd, bd, blk.downsample[0].stride[0], 0, ACT_NONE, name=nm + "downsample")
             x = pb.conv(o, w, b, 1, 0, ACT_RELU, res=identity, name=nm + "conv3")
     v = pb.avgpool(x, name="avgpool")
     y = pb.fc(v, model.fc.weight.detach().float(), model.fc.bias.detach().float(), name="fc")

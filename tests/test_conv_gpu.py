@@ -87,6 +87,47 @@ def test_conv_matches_fp32_reference(b200lib, cuda, case):
     assert bad == 0, "max err %.4g (tol %.4g), %d bad of %d" % (err.max().item(), tol.max().item(), bad, err.numel())
 
 
+@pytest.mark.parametrize("case", [(2, 56, 56, 64, 64, 1, 256, "relu"),      # layer1.0: conv3 + downsample, both stride 1, flat
+                                  (3, 28, 28, 128, 256, 2, 512, "relu"),    # layer2.0: downsample reads every second pixel
+                                  (2, 7, 7, 512, 1024, 2, 2048, "relu"),    # layer4.0: CTA pairs, 24 k-blocks
+                                  (1, 14, 14, 64, 40, 2, 72, "none"),       # ragged second input (40 ch), odd sizes below
+                                  (2, 7, 9, 128, 24, 2, 136, "silu")])
+def test_conv1x1_dual_input(b200lib, cuda, case):
+    """out = act(W[:, :ca] . a + W[:, ca:] . b[::s, ::s] + bias) as one K-concatenated GEMM vs two fp32 convs."""
+    n, h, w, ca, cb, s2, cout, act = case
+    g = torch.Generator(device="cpu").manual_seed(abs(hash(case)) % (2 ** 31))
+    h2, w2 = (h * s2 - (s2 - 1), w * s2 - (s2 - 1)) if case[1] % 2 else (h * s2, w * s2)
+    a = torch.randn(n, h, w, ca, generator=g).to(cuda).to(torch.bfloat16)
+    b2 = torch.randn(n, h2, w2, cb, generator=g).to(cuda).to(torch.bfloat16)
+    wt = (torch.randn(cout, ca + cb, generator=g) / (ca + cb) ** 0.5).to(cuda).to(torch.bfloat16)
+    bias = torch.randn(cout, generator=g).to(cuda)
+    out = torch.full((n, h, w, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_conv1x1_dual_nhwc(ptr(a), n, h, w, ca, 0, ptr(b2), h2, w2, cb, 0, s2, ptr(wt), ptr(bias), ptr(out),
+                                         cout, 0, ACT[act], stream_ptr()), "b200_conv1x1_dual_nhwc")
+    torch.cuda.synchronize()
+    wf = wt.float()
+    y = F.conv2d(a.float().permute(0, 3, 1, 2), wf[:, :ca, None, None], bias) + \
+        F.conv2d(b2.float().permute(0, 3, 1, 2), wf[:, ca:, None, None], None, stride=s2)
+    y = {"none": lambda v: v, "relu": F.relu, "silu": F.silu}[act](y).permute(0, 2, 3, 1)
+    assert not torch.isnan(out.float()).any(), "unwritten output elements"
+    err = (out.float() - y).abs()
+    tol = y.abs() * 2.0 ** -8 + 2e-3
+    assert (err > tol).sum().item() == 0, "max err %.4g" % err.max().item()
+
+
+def test_conv1x1_dual_rejects_bad_shapes(b200lib, cuda):
+    a = torch.zeros(1, 8, 8, 32, device=cuda, dtype=torch.bfloat16)      # first input not a multiple of 64 channels
+    b2 = torch.zeros(1, 8, 8, 64, device=cuda, dtype=torch.bfloat16)
+    wt = torch.zeros(64, 96, device=cuda, dtype=torch.bfloat16)
+    bias = torch.zeros(64, device=cuda)
+    out = torch.empty(1, 8, 8, 64, device=cuda, dtype=torch.bfloat16)
+    assert b200lib.b200_conv1x1_dual_nhwc(ptr(a), 1, 8, 8, 32, 0, ptr(b2), 8, 8, 64, 0, 1, ptr(wt), ptr(bias), ptr(out), 64, 0,
+                                          0, stream_ptr()) != 0
+    a = torch.zeros(1, 8, 8, 64, device=cuda, dtype=torch.bfloat16)
+    assert b200lib.b200_conv1x1_dual_nhwc(ptr(a), 1, 8, 8, 64, 0, ptr(b2), 9, 9, 64, 0, 1, ptr(wt), ptr(bias), ptr(out), 64, 0,
+                                          0, stream_ptr()) != 0          # geometry mismatch
+
+
 def test_conv_channel_slices(b200lib, cuda):
     """Reads a channel slice of a wider buffer and writes into a slice of another (chunk / concat without copies)."""
     g = torch.Generator(device="cpu").manual_seed(7)
