@@ -293,7 +293,7 @@ def main():
     model_bound_s = max(RESNET50_FLOPS_PER_IMG / (peaks["tensor_sustained"] * 1e12),
                         (RESNET50_FUSED_BYTES_PER_IMG + RESNET50_WEIGHT_BYTES / B) / (peaks["hbm"] * 1e9))
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01b_conv_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r01d_conv_traffic.json")
     if B == 256 and os.path.exists(tpath):      # dram bytes per launch from the committed ncu capture of this command
         traffic = json.load(open(tpath))["traffic_bytes_per_launch"]
     roofline = {
