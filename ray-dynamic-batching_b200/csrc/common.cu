@@ -2,6 +2,7 @@
 
 #include <cudaTypedefs.h>
 #include <mutex>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -65,6 +66,24 @@ int encode_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* di
     return fail(B200_ERR_CUDA, m);
   }
   return B200_OK;
+}
+
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+int pdl_min_waves() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_PDL_MIN_WAVES");
+    v = e ? atoi(e) : 3;
+  }
+  return v;
 }
 
 int device_sm_count() {

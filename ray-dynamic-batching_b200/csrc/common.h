@@ -52,4 +52,31 @@ int encode_tmap(CUtensorMap* out, const void* base, int rank, const uint64_t* di
 
 int device_sm_count();
 
+// Launch with programmatic stream serialization (B200_PDL=0 turns it off): the kernel MUST call pdl_wait() (ptx.cuh) before
+// reading anything an earlier kernel of the stream wrote.
+// Measured: the programmatic edge pays off between large persistent kernels (ResNet-50 @256: -2 %) and costs ~2.5 us per
+// edge in graphs of small kernels (YOLOv8n @32: +10 %), so callers pass `big` = "this launch has several waves of tiles".
+bool pdl_enabled();
+int pdl_min_waves();   // B200_PDL_MIN_WAVES (default 3): tiles per SM from which a persistent kernel is launched with the programmatic edge
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl_if(bool big, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = (big && pdl_enabled()) ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  return launch_pdl_if(false, kern, grid, block, smem, stream, static_cast<Args&&>(args)...);
+}
+
 }  // namespace b200

@@ -89,6 +89,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
@@ -312,6 +314,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
@@ -603,6 +607,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp == 0) {
     // =========================== TMA producer: weights once, one halo box per tile ===========================
@@ -900,6 +906,8 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
   cluster_sync_all();      // peer barriers are initialised and TMEM is allocated in both CTAs
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp == 0) {
     // =========================== TMA producer (both CTAs) ===========================
@@ -1325,9 +1333,8 @@ static int launch_persistent_t(const ConvLaunch& l, cudaStream_t stream) {
   }
   const int total = static_cast<int>(l.grid);
   const int ctas = total < device_sm_count() ? total : device_sm_count();
-  conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>
-      <<<ctas, PCONV_THREADS, PConvCfg<BLOCK_N, RES>::SMEM_BYTES, stream>>>(l.maps, l.p, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl_if(total >= pdl_min_waves() * device_sm_count(), conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>, dim3(ctas), dim3(PCONV_THREADS),
+                          PConvCfg<BLOCK_N, RES>::SMEM_BYTES, stream, l.maps, l.p, total));
   return B200_OK;
 }
 
@@ -1368,13 +1375,15 @@ static int launch_2cta_t(const ConvLaunch& l, cudaStream_t stream) {
   cfg.blockDim = dim3(P2CONV_THREADS);
   cfg.dynamicSmemBytes = P2ConvCfg<BLOCK_N, RES>::SMEM_BYTES;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = (pdl_enabled() && pair_tiles >= pdl_min_waves() * max_pairs) ? 1 : 0;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   B200_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, l.maps, l.p, pair_tiles, m_tiles));
   return B200_OK;
 }
@@ -1410,8 +1419,8 @@ static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
   const int total = static_cast<int>(l.grid);
   int ctas = total < device_sm_count() ? total : device_sm_count();
   ctas -= ctas % l.p.n_tiles;    // a CTA keeps ONE channel tile's weights resident: tile stride must preserve tile % n_tiles
-  conv3x3_halo_kernel<PB, RES, ACT><<<ctas, HALO_THREADS, l.halo_smem, stream>>>(l.maps, l.p, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl_if(total >= pdl_min_waves() * device_sm_count(), conv3x3_halo_kernel<PB, RES, ACT>, dim3(ctas), dim3(HALO_THREADS), size_t(l.halo_smem), stream,
+                          l.maps, l.p, total));
   return B200_OK;
 }
 

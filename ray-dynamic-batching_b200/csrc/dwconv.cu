@@ -42,6 +42,8 @@ __global__ void __launch_bounds__(DW_STRIP_THREADS, 3)
 dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho,
                        int Wo, int out_ps, int C4, int strips_h, int strips_w, const float* __restrict__ w,
                        const float* __restrict__ bias, float* __restrict__ se_partial, long long total, int slots) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   constexpr int R = STRIDE == 1 ? 2 : 1;                        // output rows per thread
   constexpr int ROWS = STRIDE == 1 ? 4 : 3;                     // input rows per thread
   constexpr int NCOL = STRIDE == 1 ? DW_TW + 2 : 2 * DW_TW + 1;   // input columns per thread, first one = halo
@@ -167,6 +169,8 @@ __global__ void __launch_bounds__(256)
 dwconv3x3_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho, int Wo,
                  int out_ps, int C8, int stride, const float* __restrict__ w, const float* __restrict__ bias, int act,
                  long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = static_cast<int>(idx % C8);
@@ -257,9 +261,9 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
     const uint16_t* ip = static_cast<const uint16_t*>(in.base);
     uint16_t* op = static_cast<uint16_t*>(out.base);
 #define B200_DW_LAUNCH2(S, A, Q)                                                                                       \
-  dwconv3x3_strip_kernel<S, A, Q><<<grid, DW_STRIP_THREADS, 0, stream>>>(ip, in.H, in.W, in.pix_stride, op, out.H,      \
-                                                                         out.W, out.pix_stride, out.C / 4, strips_h,    \
-                                                                         strips_w, w, bias, se_partial, total, slots)
+  B200_CUDA_OK(launch_pdl(dwconv3x3_strip_kernel<S, A, Q>, dim3(grid), dim3(DW_STRIP_THREADS), size_t(0), stream, ip, in.H,  \
+                          in.W, in.pix_stride, op, out.H, out.W, out.pix_stride, out.C / 4, strips_h, strips_w, w, bias,      \
+                          se_partial, total, slots))
 #define B200_DW_LAUNCH(S, A) do { if (sq) B200_DW_LAUNCH2(S, A, true); else B200_DW_LAUNCH2(S, A, false); } while (0)
     if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU)
       return fail(B200_ERR_INVALID, "dwconv: activation must be none, relu or silu");
@@ -279,10 +283,7 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
   }
   if (se_partial) return fail(B200_ERR_INVALID, "dwconv: fused squeeze needs an output width that is a multiple of 7");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
-  dwconv3x3_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.H, out.W,
-      out.pix_stride, out.C / 8, stride, w, bias, act, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(dwconv3x3_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.H, out.W, out.pix_stride, out.C / 8, stride, w, bias, act, total));
   return B200_OK;
 }
 

@@ -83,6 +83,8 @@ gather_conv_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp < 4) {
     // =========================== gather producers ===========================
@@ -237,8 +239,7 @@ static int gather_launch_t(const CUtensorMap& wmap, const GatherParams& p, cudaS
     configured[dev & 63] = true;
   }
   const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
-  gather_conv_kernel<NPAD><<<ctas, GC_THREADS, smem, stream>>>(wmap, p);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(gather_conv_kernel<NPAD>, dim3(ctas), dim3(GC_THREADS), size_t(smem), stream, wmap, p));
   return B200_OK;
 }
 

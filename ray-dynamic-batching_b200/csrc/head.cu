@@ -17,6 +17,8 @@ static constexpr int FC_WARPS = 8;
 __global__ void __launch_bounds__(FC_WARPS * 32)
 fc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b, float* __restrict__ out,
           int N, int K, int J, float x_scale, int act) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   extern __shared__ __align__(16) float s_x[];  // [FC_NB][K]
   const int n0 = blockIdx.y * FC_NB;
   const int K4 = K >> 2;
@@ -87,8 +89,7 @@ int fc_launch(const float* x, const float* w, const float* b, float* out, int n,
     configured[dev & 63] = true;
   }
   dim3 grid((j + FC_WARPS * FC_JW - 1) / (FC_WARPS * FC_JW), (n + FC_NB - 1) / FC_NB);
-  fc_kernel<<<grid, FC_WARPS * 32, smem, stream>>>(x, w, b, out, n, k, j, x_scale, act);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(fc_kernel, dim3(grid), dim3(FC_WARPS * 32), size_t(smem), stream, x, w, b, out, n, k, j, x_scale, act));
   return B200_OK;
 }
 
@@ -102,6 +103,8 @@ __global__ void __launch_bounds__(SE_THREADS)
 se_gate_kernel(const float* __restrict__ partial, int P, int C, float inv_hw, const float* __restrict__ w1,
                const float* __restrict__ b1, const float* __restrict__ w2t, const float* __restrict__ b2, int S, int JS,
                float* __restrict__ gate) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   extern __shared__ __align__(16) float se_smem[];   // mean[C], hid[S], part[JS][C]
   float* mean = se_smem;
   float* hid = se_smem + C;
@@ -165,8 +168,7 @@ int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw,
   if (js > s) js = s;
   const size_t smem = sizeof(float) * (static_cast<size_t>(c) * (1 + js) + s);
   if (smem > 48 * 1024) return fail(B200_ERR_INVALID, "se_gate: more than ~6k channels unsupported");
-  se_gate_kernel<<<n, SE_THREADS, smem, stream>>>(partial, strips, c, inv_hw, w1, b1, w2t, b2, s, js, gate);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(se_gate_kernel, dim3(n), dim3(SE_THREADS), size_t(smem), stream, partial, strips, c, inv_hw, w1, b1, w2t, b2, s, js, gate));
   return B200_OK;
 }
 
@@ -181,6 +183,8 @@ constexpr int SEH_G = 16, SEH_J = 16, SEH_THREADS = 512, SEH_PAD = 4;
 __global__ void __launch_bounds__(SEH_THREADS)
 se_hidden_kernel(const float* __restrict__ sums, int N, int P, int C, float inv_hw, const float* __restrict__ w1,
                  const float* __restrict__ b1, int S, float* __restrict__ hid) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   extern __shared__ __align__(16) float seh_smem[];   // x[16][C + PAD], w[16][C + PAD], part[8 * 64 * 4]
   const int ld = C + SEH_PAD;
   float* xs = seh_smem;
@@ -265,8 +269,7 @@ int se_hidden_launch(const float* sums, int n, int rows, int c, float inv_hw, co
     configured[dev & 63] = true;
   }
   const dim3 grid((n + SEH_G - 1) / SEH_G, (s + SEH_J - 1) / SEH_J);
-  se_hidden_kernel<<<grid, SEH_THREADS, smem, stream>>>(sums, n, rows, c, inv_hw, w1, b1, s, hid);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(se_hidden_kernel, dim3(grid), dim3(SEH_THREADS), size_t(smem), stream, sums, n, rows, c, inv_hw, w1, b1, s, hid));
   return B200_OK;
 }
 
@@ -274,6 +277,8 @@ constexpr int SES_C = 64, SES_THREADS = 256;
 __global__ void __launch_bounds__(SES_THREADS)
 se_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C,
                 const float* __restrict__ hid, const float* __restrict__ w2t, const float* __restrict__ b2, int S) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   __shared__ __align__(16) float hid_s[256];
   __shared__ __align__(16) float w_s[256 / 4][SES_C];   // up to 64 squeeze units at a time
   __shared__ float part[4][SES_C];
@@ -335,10 +340,7 @@ int se_scale_launch(const View& in, const View& out, const float* hid, const flo
     return fail(B200_ERR_INVALID, "se_scale: shape mismatch");
   if (s <= 0 || s > 256) return fail(B200_ERR_INVALID, "se_scale: squeeze width must be in [1, 256]");
   const dim3 grid((in.C + SES_C - 1) / SES_C, in.N);
-  se_scale_kernel<<<grid, SES_THREADS, 0, stream>>>(static_cast<const uint16_t*>(in.base), in.pix_stride,
-                                                    static_cast<uint16_t*>(out.base), out.pix_stride, in.H * in.W, in.C,
-                                                    hid, w2t, b2, s);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(se_scale_kernel, dim3(grid), dim3(SES_THREADS), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.H * in.W, in.C, hid, w2t, b2, s));
   return B200_OK;
 }
 
@@ -346,6 +348,8 @@ int se_scale_launch(const View& in, const View& out, const float* hid, const flo
 __global__ void __launch_bounds__(256)
 channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C8,
                      const float* __restrict__ gate, long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = static_cast<int>(idx % C8);
@@ -366,10 +370,7 @@ int channel_scale_launch(const View& in, const View& out, const float* gate, cud
   if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W)
     return fail(B200_ERR_INVALID, "channel_scale: shape mismatch");
   const long long total = static_cast<long long>(in.N) * in.H * in.W * (in.C / 8);
-  channel_scale_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride,
-      in.H * in.W, in.C / 8, gate, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(channel_scale_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.H * in.W, in.C / 8, gate, total));
   return B200_OK;
 }
 

@@ -11,6 +11,8 @@ namespace b200 {
 __global__ void __launch_bounds__(256)
 copy_channels_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int C8,
                      long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = static_cast<int>(idx % C8);
@@ -22,16 +24,15 @@ int copy_channels_launch(const View& in, const View& out, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W)
     return fail(B200_ERR_INVALID, "copy_channels: shape mismatch");
   const long long total = static_cast<long long>(in.N) * in.H * in.W * (in.C / 8);
-  copy_channels_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.C / 8,
-      total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(copy_channels_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.C / 8, total));
   return B200_OK;
 }
 
 __global__ void __launch_bounds__(256)
 upsample2x_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int out_ps,
                   int C8, long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = static_cast<int>(idx % C8);
@@ -49,10 +50,7 @@ int upsample2x_launch(const View& in, const View& out, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.N != out.N || 2 * in.H != out.H || 2 * in.W != out.W)
     return fail(B200_ERR_INVALID, "upsample2x: shape mismatch");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
-  upsample2x_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride,
-      in.C / 8, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(upsample2x_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.C / 8, total));
   return B200_OK;
 }
 
@@ -62,6 +60,8 @@ int upsample2x_launch(const View& in, const View& out, cudaStream_t stream) {
 __global__ void __launch_bounds__(256)
 shuffle_concat_kernel(const uint16_t* __restrict__ a, int a_ps, const uint16_t* __restrict__ b, int b_ps,
                       uint16_t* __restrict__ out, int out_ps, int c, int cp, long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int chunks = (2 * cp) >> 3;
@@ -93,10 +93,7 @@ int shuffle_concat_launch(const View& a, const View& b, const View& out, int c, 
       a.W != out.W || b.N != a.N || b.H != a.H || b.W != a.W || out.pix_stride % 8)
     return fail(B200_ERR_INVALID, "shuffle_concat: shape mismatch");
   const long long total = static_cast<long long>(a.N) * a.H * a.W * (2 * cp / 8);
-  shuffle_concat_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, stream>>>(
-      static_cast<const uint16_t*>(a.base), a.pix_stride, static_cast<const uint16_t*>(b.base), b.pix_stride,
-      static_cast<uint16_t*>(out.base), out.pix_stride, c, cp, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(shuffle_concat_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(a.base), a.pix_stride, static_cast<const uint16_t*>(b.base), b.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, c, cp, total));
   return B200_OK;
 }
 

@@ -17,6 +17,8 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
 __global__ void __launch_bounds__(256)
 maxpool_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho, int Wo,
                int out_ps, int C8, int k, int s, int p, long long total) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int c8 = static_cast<int>(idx % C8);
@@ -49,10 +51,7 @@ int maxpool_launch(const View& in, const View& out, int ksize, int stride, int p
     return fail(B200_ERR_INVALID, "maxpool: output geometry mismatch");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
   const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
-  maxpool_kernel<<<blocks, 256, 0, stream>>>(static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride,
-                                             static_cast<uint16_t*>(out.base), out.H, out.W, out.pix_stride, out.C / 8,
-                                             ksize, stride, pad, total);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(maxpool_kernel, dim3(blocks), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.H, out.W, out.pix_stride, out.C / 8, ksize, stride, pad, total));
   return B200_OK;
 }
 
@@ -60,6 +59,8 @@ int maxpool_launch(const View& in, const View& out, int ksize, int stride, int p
 // `gy` slices that are combined through shared memory.  fp32 accumulation, sum * (1/HW) like aten's mean.
 __global__ void __launch_bounds__(256)
 global_avgpool_kernel(const uint16_t* __restrict__ in, int HW, int in_ps, int C8, float* __restrict__ out) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   extern __shared__ float s_part[];  // [slices][C8*8]
   const int n = blockIdx.x;
   const int slices = blockDim.x / C8 > 0 ? blockDim.x / C8 : 1;
@@ -92,8 +93,7 @@ int global_avgpool_launch(const View& in, float* out, cudaStream_t stream) {
     const int slices = 256 / C8 > 0 ? 256 / C8 : 1;
     const int threads = slices * C8;
     const size_t smem = size_t(slices) * C8 * 8 * sizeof(float);
-    global_avgpool_kernel<<<in.N, threads, smem, stream>>>(static_cast<const uint16_t*>(in.base), in.H * in.W,
-                                                           in.pix_stride, C8, out);
+    B200_CUDA_OK(launch_pdl(global_avgpool_kernel, dim3(in.N), dim3(threads), size_t(smem), stream, static_cast<const uint16_t*>(in.base), in.H * in.W, in.pix_stride, C8, out));
   } else {
     return fail(B200_ERR_INVALID, "avgpool: more than 2048 channels unsupported");
   }

@@ -52,6 +52,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Every kernel of the engine is launched with programmatic stream serialization: it may start while its predecessor
+// is still draining, runs its prologue (barrier init, TMEM allocation, descriptor prefetch, constant loads) and must
+// call pdl_wait() before it touches memory the predecessor produces.  pdl_launch_dependents() lets the successor in.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

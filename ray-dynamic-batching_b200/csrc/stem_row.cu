@@ -107,6 +107,8 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   auto tile_coords = [&](int it, int& n_oh, int& oh, int& ow0) {
     const int t = tile0 + it;
@@ -293,6 +295,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   // stem rows of unit u: y in [y_lo, y_hi]
   auto unit_rows = [&](int u, int& n, int& ph0, int& ph1, int& y_lo, int& y_hi) {
@@ -496,8 +500,7 @@ static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p
     configured[dev & 63] = true;
   }
   const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
-  stem_pool_kernel<KS, NOUT, ACT><<<ctas, SP_THREADS, smem, stream>>>(in_map, p);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl_if(p.total_units >= pdl_min_waves() * device_sm_count(), stem_pool_kernel<KS, NOUT, ACT>, dim3(ctas), dim3(SP_THREADS), smem, stream, in_map, p));
   return B200_OK;
 }
 
@@ -513,8 +516,7 @@ static int stem_row_launch_t(const CUtensorMap& in_map, const CUtensorMap& out_m
     configured[dev & 63] = true;
   }
   const int ctas = p.total_tiles < device_sm_count() ? p.total_tiles : device_sm_count();
-  stem_row_kernel<KS, NOUT, ACT><<<ctas, SR2_THREADS, smem, stream>>>(in_map, out_map, p);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl_if(p.total_tiles >= pdl_min_waves() * device_sm_count(), stem_row_kernel<KS, NOUT, ACT>, dim3(ctas), dim3(SR2_THREADS), smem, stream, in_map, out_map, p));
   return B200_OK;
 }
 

@@ -81,6 +81,8 @@ stem_tc_kernel(const __grid_constant__ CUtensorMap wmap, const uint16_t* __restr
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();      // everything above overlapped the previous kernel's tail; activations are read from here on
 
   if (warp < 4) {
     // =========================== im2col producers ===========================

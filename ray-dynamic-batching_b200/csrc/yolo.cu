@@ -20,6 +20,8 @@ __global__ void __launch_bounds__(YD_THREADS)
 yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* __restrict__ hc, int hc_ps, int H, int W,
                    int N, const float* __restrict__ wb, const float* __restrict__ bb, const float* __restrict__ wc,
                    const float* __restrict__ bc, float* __restrict__ out, int a_off, int a_total, float stride) {
+  pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
+                // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   extern __shared__ __align__(16) float s_w[];  // wb [64][CB] | wc [NC][NC] | bb [64] | bc [NC]
   float* s_wb = s_w;
   float* s_wc = s_wb + 4 * REG_MAX * CB;
@@ -119,10 +121,7 @@ int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const fl
     configured[dev & 63] = true;
   }
   const long long total = static_cast<long long>(hb.N) * hb.H * hb.W;
-  yolo_decode_kernel<64, 80><<<static_cast<unsigned>((total + YD_THREADS - 1) / YD_THREADS), YD_THREADS, smem, stream>>>(
-      static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H,
-      hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride);
-  B200_CUDA_OK(cudaGetLastError());
+  B200_CUDA_OK(launch_pdl(yolo_decode_kernel<64, 80>, dim3(static_cast<unsigned>((total + YD_THREADS - 1) / YD_THREADS)), dim3(YD_THREADS), size_t(smem), stream, static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H, hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride));
   return B200_OK;
 }
 
