@@ -121,10 +121,12 @@ B200_API int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int
 
 /* The same depthwise convolution with the squeeze of the SqueezeExcitation block that follows it in MBConv fused in
  * (tv efficientnet.py:153-155 -> tv ops/misc.py:249-250, AdaptiveAvgPool2d(1)): besides `out`, writes fp32
- * strip_sums[n][rows][c], channel sums of the stored outputs of each strip of the image, rows =
- * b200_dwconv3x3_strips(ho, wo, stride) (1 with B200_DW_SQ=1 when an image's strips fit one thread block, which then
- * adds them itself; 0: this output geometry has no strip kernel and the call is rejected -- widths that are a multiple
- * of 7 have one). b200_se_gate / b200_se_hidden add the rows in index order, so the result is deterministic. */
+ * strip_sums[n][rows][c], channel sums of the stored outputs, rows = b200_dwconv3x3_squeeze_rows(c, ho, wo, stride):
+ * 1 when the layer runs on the TMA-tile kernel (stride 1, one row band per image: the block adds its strips itself), else
+ * one row per strip of the strip kernel (b200_dwconv3x3_strips); 0: this output geometry has neither and the call is
+ * rejected -- widths that are a multiple of 7 have one. b200_se_gate / b200_se_hidden add the rows in index order, so
+ * the result is deterministic. */
+B200_API int b200_dwconv3x3_squeeze_rows(int c, int ho, int wo, int stride);
 B200_API int b200_dwconv3x3_strips(int ho, int wo, int stride);
 B200_API int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride,
                                          const float* weight, const float* bias, void* out, int out_pix_stride,

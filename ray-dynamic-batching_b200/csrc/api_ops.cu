@@ -131,6 +131,7 @@ int b200_dwconv3x3_nhwc(const void* in, int n, int h, int w, int c, int in_pix_s
 }
 
 int b200_dwconv3x3_strips(int ho, int wo, int stride) { return dwconv3x3_strips(ho, wo, stride); }
+int b200_dwconv3x3_squeeze_rows(int c, int ho, int wo, int stride) { return dwconv3x3_strips_c(c, ho, wo, stride); }
 
 int b200_dwconv3x3_squeeze_nhwc(const void* in, int n, int h, int w, int c, int in_pix_stride, const float* weight,
                                 const float* bias, void* out, int out_pix_stride, int stride, int act,

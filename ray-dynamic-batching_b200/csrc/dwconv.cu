@@ -17,6 +17,11 @@
 
 namespace b200 {
 
+int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const float* bias, int act, float* sums,
+                       cudaStream_t stream);       // dwconv_tile.cu
+int dwconv3x3_tile_squeeze_rows(int C, int H, int W, int stride);
+int dwconv3x3_strips(int Ho, int Wo, int stride);
+
 constexpr int DW_STRIP_THREADS = 128;
 constexpr int DW_TW = 7;   // strip width: every spatial size of the served classifiers (224 / 2^k) is a multiple of 7
 
@@ -230,6 +235,11 @@ static bool dw_block_reduce() {      // B200_DW_SQ=1: reduce an image's strips i
   return v == 1;
 }
 
+int dwconv3x3_strips_c(int C, int Ho, int Wo, int stride) {
+  if (dwconv3x3_tile_squeeze_rows(C, Ho, Wo, stride)) return 1;      // the tile kernel reduces the strips itself
+  return dwconv3x3_strips(Ho, Wo, stride);
+}
+
 int dwconv3x3_strips(int Ho, int Wo, int stride) {
   const int s = dw_strip_count(Ho, Wo, stride);
   return (dw_block_reduce() && s <= 32) ? (s > 0 ? 1 : 0) : s;
@@ -246,6 +256,10 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
   if (use_strips < 0) {
     const char* e = getenv("B200_DW_STRIPS");
     use_strips = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (stride == 1) {
+    const int rc = dwconv3x3_tile_try(in, out, w, bias, act, se_partial, stream);
+    if (rc <= 0) return rc;        // launched (or failed); 1 = not a layer for the tile kernel
   }
   const int strips = dw_strip_count(out.H, out.W, stride);
   if (strips > 0 && (use_strips || se_partial)) {

@@ -1,0 +1,258 @@
+// Depthwise 3x3 / stride 1 / pad 1 from TMA-staged tiles (+ folded BatchNorm bias, activation, optional fused squeeze).
+//
+// The strip kernel of dwconv.cu reads every input element 2.6 times (each thread loads its own 4 x 9 halo window) and is
+// bound by what one SM can pull from L2.  Here a persistent block takes work items (image, row band, channel group);
+// ONE TMA box per item brings the (rows + 2) x (W + 2) x CG input tile into shared memory -- coordinates outside the image
+// are zero-filled, which is the padding -- so global reads are 1.0x (+ one halo row per band), and the 256 compute
+// threads read their windows from shared memory.  A 3-4 deep ring of tiles keeps the loads ahead of the math.
+//   warps 0-7 : compute.  thread = (channel quad, strip slot); a strip is 2 output rows x 7 columns, windows slide in
+//               registers exactly as in the strip kernel (same FMA order: results are bit-identical)
+//   warp 8    : TMA producer (whole warp in the loop, one elected lane issues)
+// With one band per image the strips of an (image, channel group) all live in one block: their channel sums are added in
+// strip order in shared memory and written as ONE row sums[n][c] (the SE squeeze, deterministic).
+//
+// Replaces the stride-1 depthwise convs of tv shufflenetv2.py:86-96 and efficientnet.py:140-151 (+ the AdaptiveAvgPool2d(1)
+// of ops/misc.py:249-250).
+#include "kernels.cuh"
+#include "ptx.cuh"
+
+namespace b200 {
+
+static constexpr int DT_COMPUTE = 256;
+static constexpr int DT_THREADS = DT_COMPUTE + 32;
+static constexpr int DT_TW = 7;
+static constexpr int DT_MAX_STAGES = 4;
+static constexpr int DT_SMEM_MAX = 220 * 1024;   // dynamic shared memory the kernel may ask for (4 KB static on top)
+
+struct DwTileParams {
+  const float* w;        // [9][C]
+  const float* bias;     // [C]
+  uint16_t* out;
+  float* sums;           // [N][C] or null
+  int out_ps;
+  int C, H, W, N;
+  int cg;                // channels per work item (64, 128 or 256) = TMA box inner dimension
+  int groups;            // ceil(C / cg)
+  int band_h, bands;     // output rows per item, items per image column of groups
+  int stages;
+  int tile_bytes;        // (band_h + 2) * (W + 2) * cg * 2
+  int total_items;       // N * bands * groups
+};
+
+template <int ACT>
+__global__ void __launch_bounds__(DT_THREADS, 1)
+dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ DwTileParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[DT_MAX_STAGES], bar_empty[DT_MAX_STAGES];
+  __shared__ __align__(16) float red[DT_COMPUTE * 4];
+  const int warp = threadIdx.x >> 5;
+  const uint32_t ring = (smem_u32(smem_raw) + 127u) & ~127u;
+  const int my_items = (p.total_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&in_map);
+    for (int s = 0; s < DT_MAX_STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), DT_COMPUTE / 32);     // one arrival per compute warp
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+  pdl_wait();
+
+  auto item_coords = [&](int it, int& n, int& band, int& g) {
+    const int item = blockIdx.x + it * gridDim.x;
+    g = item % p.groups;
+    const int r = item / p.groups;
+    band = r % p.bands;
+    n = r / p.bands;
+  };
+
+  if (warp == DT_COMPUTE / 32) {
+    // =========================== TMA producer ===========================
+    for (int it = 0; it < my_items; ++it) {
+      int n, band, g;
+      item_coords(it, n, band, g);
+      const int s = it % p.stages;
+      mbar_wait(smem_u32(&bar_empty[s]), ((it / p.stages) & 1) ^ 1);
+      if (elect_one()) {
+        const uint32_t full = smem_u32(&bar_full[s]);
+        mbar_expect_tx(full, p.tile_bytes);
+        // box [cg, W + 2, band_h + 2, 1] at (g * cg, -1, band * band_h - 1, n): outside the image -> zeros
+        tma_load_4d(&in_map, full, ring + s * p.tile_bytes, g * p.cg, -1, band * p.band_h - 1, n);
+      }
+    }
+    __syncwarp();
+    return;
+  }
+
+  // =========================== compute ===========================
+  const int quads = p.cg >> 2;                  // channel quads per item
+  const int nslots = DT_COMPUTE / quads;        // strips worked on concurrently
+  const int quad = threadIdx.x % quads;
+  const int slot = threadIdx.x / quads;
+  const int strips_w = p.W / DT_TW;
+  const int row_pitch = (p.W + 2) * p.cg;       // elements per staged input row
+  for (int it = 0; it < my_items; ++it) {
+    int n, band, g;
+    item_coords(it, n, band, g);
+    const int s = it % p.stages;
+    const int c0 = g * p.cg + quad * 4;
+    const bool c_ok = c0 < p.C;                 // the last group of a ragged channel count
+    float wt[9][4], b[4];
+    {
+      const int cc = c_ok ? c0 : 0;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const float4 v = *reinterpret_cast<const float4*>(p.w + k * p.C + cc);
+        wt[k][0] = v.x; wt[k][1] = v.y; wt[k][2] = v.z; wt[k][3] = v.w;
+      }
+      const float4 v = *reinterpret_cast<const float4*>(p.bias + cc);
+      b[0] = v.x; b[1] = v.y; b[2] = v.z; b[3] = v.w;
+    }
+    const int rows = min(p.band_h, p.H - band * p.band_h);      // output rows of this item
+    const int strips = ((rows + 1) >> 1) * strips_w;
+    mbar_wait(smem_u32(&bar_full[s]), (it / p.stages) & 1);
+    const uint32_t tile = ring + s * p.tile_bytes;
+    float sum[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int st = slot; st < strips; st += nslots) {
+      const int sy = st / strips_w, sx = st - sy * strips_w;
+      const int oy0 = sy * 2, ox0 = sx * DT_TW;                 // within the band; staged row r = output row r - 1 + 1
+      // staged tile: row i <-> input row (band0 - 1 + i), column j <-> input column (j - 1)
+      const uint32_t base = tile + (static_cast<uint32_t>(oy0 * row_pitch + ox0 * p.cg + quad * 4) << 1);
+      float win[4][3][4];
+      auto lds4 = [&](int i, int j, float (&v)[4]) {
+        uint32_t lo, hi;
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(base + (static_cast<uint32_t>(i * row_pitch + j * p.cg) << 1)));
+        v[0] = bf16_lo(lo); v[1] = bf16_hi(lo); v[2] = bf16_lo(hi); v[3] = bf16_hi(hi);
+      };
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        lds4(i, 0, win[i][1]);
+        lds4(i, 1, win[i][2]);
+      }
+#pragma unroll
+      for (int j = 0; j < DT_TW; ++j) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+#pragma unroll
+          for (int c = 0; c < 4; ++c) { win[i][0][c] = win[i][1][c]; win[i][1][c] = win[i][2][c]; }
+          lds4(i, j + 2, win[i][2]);
+        }
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          if (oy0 + r >= rows || !c_ok) continue;
+          float acc[4] = {b[0], b[1], b[2], b[3]};
+#pragma unroll
+          for (int dr = 0; dr < 3; ++dr)
+#pragma unroll
+            for (int q = 0; q < 3; ++q)
+#pragma unroll
+              for (int c = 0; c < 4; ++c) acc[c] = fmaf(win[r + dr][q][c], wt[dr * 3 + q][c], acc[c]);
+          uint2 o;
+          o.x = pack_bf16x2(apply_act(acc[0], ACT), apply_act(acc[1], ACT));
+          o.y = pack_bf16x2(apply_act(acc[2], ACT), apply_act(acc[3], ACT));
+          const int oy = band * p.band_h + oy0 + r;
+          *reinterpret_cast<uint2*>(p.out + ((static_cast<size_t>(n) * p.H + oy) * p.W + ox0 + j) * p.out_ps + c0) = o;
+          sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y);
+        }
+      }
+    }
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) mbar_arrive(smem_u32(&bar_empty[s]));      // this warp is done reading the tile
+    if (p.sums) {
+      // one band per image (checked by the host): every strip of (n, channel quad) is in this block
+      named_bar_sync(1, DT_COMPUTE);                                         // previous item's reduction has been read
+      *reinterpret_cast<float4*>(&red[threadIdx.x * 4]) = make_float4(sum[0], sum[1], sum[2], sum[3]);
+      named_bar_sync(1, DT_COMPUTE);
+      if (slot == 0 && c_ok) {
+        float4 t = *reinterpret_cast<float4*>(&red[quad * 4]);
+        for (int k = 1; k < nslots; ++k) {                                   // slot order = strip order: deterministic
+          const float4 v = *reinterpret_cast<float4*>(&red[(k * quads + quad) * 4]);
+          t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
+        }
+        *reinterpret_cast<float4*>(p.sums + static_cast<size_t>(n) * p.C + c0) = t;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------- host
+static bool dw_tile_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_DW_TILE");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+// Geometry the tile kernel takes: stride 1, width a multiple of 7 and at most 56, at least two tiles in the ring.
+static bool dw_tile_plan(int C, int H, int W, DwTileParams* p) {
+  if (W % DT_TW || W > 56 || H < 1 || C % 8) return false;
+  p->band_h = H <= 14 ? H : 14;
+  p->bands = (H + p->band_h - 1) / p->band_h;
+  const int strips = ((p->band_h + 1) / 2) * (W / DT_TW);
+  int cg = strips >= 12 ? 64 : (strips >= 6 ? 128 : 256);
+  const int c64 = (C + 63) / 64 * 64;
+  if (cg > c64) cg = c64 >= 256 ? 256 : (c64 >= 128 ? 128 : 64);
+  p->cg = cg;
+  p->groups = (C + cg - 1) / cg;
+  p->tile_bytes = (p->band_h + 2) * (W + 2) * cg * 2;
+  const int row_bytes = (W + 2) * cg * 2;      // slack after the ring: odd row counts read one row past a tile
+  p->stages = (DT_SMEM_MAX - row_bytes - 256) / p->tile_bytes;
+  if (p->stages > DT_MAX_STAGES) p->stages = DT_MAX_STAGES;
+  return p->stages >= 2;
+}
+
+// 1 when the tile kernel would take this layer and writes ONE row of channel sums per image, else 0
+int dwconv3x3_tile_squeeze_rows(int C, int H, int W, int stride) {
+  DwTileParams p;
+  if (!dw_tile_enabled() || stride != 1 || !dw_tile_plan(C, H, W, &p)) return 0;
+  return p.bands == 1 ? 1 : 0;
+}
+
+template <int ACT>
+static int dw_tile_launch_t(const CUtensorMap& map, const DwTileParams& p, size_t smem, cudaStream_t stream) {
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(dwconv3x3_tile_kernel<ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, DT_SMEM_MAX));
+    configured[dev & 63] = true;
+  }
+  const int ctas = p.total_items < device_sm_count() ? p.total_items : device_sm_count();
+  B200_CUDA_OK(launch_pdl(dwconv3x3_tile_kernel<ACT>, dim3(ctas), dim3(DT_THREADS), smem, stream, map, p));
+  return B200_OK;
+}
+
+// returns B200_OK after launching, or 1 if this layer is not for the tile kernel (the caller falls back to the strip kernel)
+int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const float* bias, int act, float* sums,
+                       cudaStream_t stream) {
+  DwTileParams p;
+  if (!dw_tile_enabled() || !dw_tile_plan(out.C, out.H, out.W, &p)) return 1;
+  if (sums && p.bands != 1) return 1;
+  if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU) return 1;
+  if (in.pix_stride % 8 || (reinterpret_cast<uintptr_t>(in.base) & 15)) return 1;
+  p.w = w; p.bias = bias;
+  p.out = static_cast<uint16_t*>(out.base);
+  p.sums = sums;
+  p.out_ps = out.pix_stride;
+  p.C = out.C; p.H = out.H; p.W = out.W; p.N = out.N;
+  p.total_items = out.N * p.bands * p.groups;
+  CUtensorMap map;
+  {
+    const uint64_t ips = uint64_t(in.pix_stride) * 2;
+    const uint64_t dims[4] = {uint64_t(in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t str[3] = {ips, ips * in.W, ips * in.W * in.H};
+    const uint32_t box[4] = {uint32_t(p.cg), uint32_t(in.W + 2), uint32_t(p.band_h + 2), 1u};
+    B200_TRY(encode_tmap(&map, in.base, 4, dims, str, box, SWZ_NONE));
+  }
+  const size_t smem = size_t(p.stages) * p.tile_bytes + size_t(in.W + 2) * p.cg * 2 + 256;   // + one row: odd row counts read past the tile
+  if (act == ACT_NONE) return dw_tile_launch_t<ACT_NONE>(map, p, smem, stream);
+  if (act == ACT_RELU) return dw_tile_launch_t<ACT_RELU>(map, p, smem, stream);
+  return dw_tile_launch_t<ACT_SILU>(map, p, smem, stream);
+}
+
+}  // namespace b200

@@ -60,7 +60,7 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     if (o.type == OP_DWCONV && o.p[12] > 0) {   // fused squeeze: the side buffer must hold every strip's channel sums
       const BufRec& sb = bufs[o.p[12]];
       const BufRec& ob = bufs[o.p[3]];
-      const int strips = dwconv3x3_strips(ob.h, ob.w, o.p[9]);
+      const int strips = dwconv3x3_strips_c(o.p[5], ob.h, ob.w, o.p[9]);
       if (strips <= 0 || sb.dtype != 1 || int64_t(sb.h) * sb.w * sb.c < int64_t(strips) * o.p[5])
         return fail(B200_ERR_BLOB, "engine: depthwise squeeze buffer too small for this geometry");
     }

@@ -49,7 +49,8 @@ int gather_conv_launch(const View& in, const View& out, const View& res, const v
 
 // ---- depthwise 3x3 (dwconv.cu): fp32 weights [9][C], bias [C]; optional fused squeeze: per-strip fp32 channel sums of
 // the stored outputs, [N][dwconv3x3_strips()][C] (0 strips = this geometry has no strip kernel) ----
-int dwconv3x3_strips(int Ho, int Wo, int stride);
+int dwconv3x3_strips(int Ho, int Wo, int stride);              // strip kernel only
+int dwconv3x3_strips_c(int C, int Ho, int Wo, int stride);     // rows the fused squeeze writes for this layer (tile kernel: 1)
 int dwconv3x3_launch(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
                      float* se_partial /* or null */, cudaStream_t stream);
 

@@ -27,13 +27,20 @@ yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* _
   float* s_wc = s_wb + 4 * REG_MAX * CB;
   float* s_bb = s_wc + NC * NC;
   float* s_bc = s_bb + 4 * REG_MAX;
-  for (int i = threadIdx.x; i < 4 * REG_MAX * CB; i += YD_THREADS) s_wb[i] = wb[i];
-  for (int i = threadIdx.x; i < NC * NC; i += YD_THREADS) s_wc[i] = wc[i];
+  // weights -> shared memory once per block (cp.async: every 16-byte copy in flight at once); the block then walks
+  // anchor tiles with a grid stride, so the 42 KB are fetched ~600 times per launch instead of once per 128 anchors
+  for (int i = threadIdx.x; i < (4 * REG_MAX * CB) / 4; i += YD_THREADS)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(s_wb + i * 4)), "l"(wb + i * 4) : "memory");
+  for (int i = threadIdx.x; i < (NC * NC) / 4; i += YD_THREADS)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(s_wc + i * 4)), "l"(wc + i * 4) : "memory");
   for (int i = threadIdx.x; i < 4 * REG_MAX; i += YD_THREADS) s_bb[i] = bb[i];
   for (int i = threadIdx.x; i < NC; i += YD_THREADS) s_bc[i] = bc[i];
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
-  const long long idx = static_cast<long long>(blockIdx.x) * YD_THREADS + threadIdx.x;
-  if (idx >= static_cast<long long>(N) * H * W) return;
+  const long long total_anchors = static_cast<long long>(N) * H * W;
+  for (long long idx = static_cast<long long>(blockIdx.x) * YD_THREADS + threadIdx.x; idx < total_anchors;
+       idx += static_cast<long long>(gridDim.x) * YD_THREADS) {
   const int a = static_cast<int>(idx % (H * W));
   const int n = static_cast<int>(idx / (H * W));
   const int y = a / W, x = a - y * W;
@@ -105,6 +112,7 @@ yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* _
       o[static_cast<size_t>(4 + j) * a_total] = 1.f / (1.f + expf(-acc));
     }
   }
+  }
 }
 
 int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const float* bb, const float* wc, const float* bc,
@@ -121,7 +129,9 @@ int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const fl
     configured[dev & 63] = true;
   }
   const long long total = static_cast<long long>(hb.N) * hb.H * hb.W;
-  B200_CUDA_OK(launch_pdl(yolo_decode_kernel<64, 80>, dim3(static_cast<unsigned>((total + YD_THREADS - 1) / YD_THREADS)), dim3(YD_THREADS), size_t(smem), stream, static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H, hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride));
+  long long blocks = (total + YD_THREADS - 1) / YD_THREADS;
+  if (blocks > 4LL * device_sm_count()) blocks = 4LL * device_sm_count();     // 4 blocks of 42 KB of weights per SM, grid-stride over anchors
+  B200_CUDA_OK(launch_pdl(yolo_decode_kernel<64, 80>, dim3(static_cast<unsigned>(blocks)), dim3(YD_THREADS), size_t(smem), stream, static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H, hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride));
   return B200_OK;
 }
 

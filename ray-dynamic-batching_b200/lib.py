@@ -46,6 +46,7 @@ SIGNATURES = {
     "b200_dwconv3x3_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                     c_int, c_int, c_void_p]),
     "b200_dwconv3x3_strips": (c_int, [c_int, c_int, c_int]),
+    "b200_dwconv3x3_squeeze_rows": (c_int, [c_int, c_int, c_int, c_int]),
     "b200_dwconv3x3_squeeze_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                             c_int, c_int, c_int, c_void_p, c_void_p]),
     "b200_se_gate": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int,

@@ -300,11 +300,11 @@ class PlanBuilder:
         return out
 
     @staticmethod
-    def dw_strips(ho, wo, stride):
-        """Rows of channel sums per image the fused squeeze writes; 0 = no strip kernel. Asked of the library itself
-        (csrc/dwconv.cu dwconv3x3_strips) so the plan and the kernel cannot disagree."""
+    def dw_strips(c, ho, wo, stride):
+        """Rows of channel sums per image the fused squeeze writes; 0 = no such kernel. Asked of the library itself
+        (csrc/dwconv.cu dwconv3x3_strips_c) so the plan and the kernel cannot disagree."""
         from . import lib as _lib
-        return int(_lib.load().b200_dwconv3x3_strips(int(ho), int(wo), int(stride)))
+        return int(_lib.load().b200_dwconv3x3_squeeze_rows(int(c), int(ho), int(wo), int(stride)))
 
     def dwconv(self, x: T, weight, bias, stride, act, out: Optional[T] = None, name="", squeeze=False):
         """squeeze=True: also returns the fp32 strip-sum buffer [strips][cphys] feeding se_gate (fused SE squeeze)."""
@@ -323,7 +323,7 @@ class PlanBuilder:
         w_off = self.add_weights(wp.numpy().astype(np.float32))
         b_off = self.add_weights(bp.numpy().astype(np.float32))
         if squeeze:
-            strips = self.dw_strips(ho, wo, stride)
+            strips = self.dw_strips(cp, ho, wo, stride)
             assert strips > 0
             sums = self.new_buf(1, strips, cp, dtype=1)
             self._op(OP_DWCONV, [x.buf, x.coff, cp, out.buf, out.coff, cp, -1, 0, 3, stride, 1, act, sums], w_off, b_off,
@@ -616,7 +616,7 @@ def lower_efficientnet_v2(model, in_hw=(224, 224), fuse_se=None) -> PlanBuilder:
                 t = pb.conv(x, w, b, 1, 0, ACT_SILU, name=nm + "expand")
                 w, b = fold_bn(dw[0], dw[1])
                 st = dw[0].stride[0]
-                if fuse_se and pb.dw_strips((t.h - 1) // st + 1, (t.w - 1) // st + 1, st) > 0:
+                if fuse_se and pb.dw_strips(t.cphys, (t.h - 1) // st + 1, (t.w - 1) // st + 1, st) > 0:
                     t, sums = pb.dwconv(t, w, b, st, ACT_SILU, name=nm + "dw", squeeze=True)
                     fcs = (se.fc1.weight.detach().float().flatten(1), se.fc1.bias.detach().float(),
                            se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float())

@@ -163,7 +163,8 @@ def test_stem_conv_tensor_core(b200lib, cuda, k, p, cout, cfg, act):
 
 
 @pytest.mark.parametrize("n,h,w,c,stride,act", [(2, 28, 28, 64, 1, 0), (3, 56, 56, 24, 2, 0), (1, 15, 17, 960, 1, 2),
-                                                (2, 14, 14, 232, 2, 2)])
+                                                (2, 14, 14, 232, 2, 2), (5, 14, 14, 232, 1, 1), (3, 7, 7, 464, 1, 0),
+                                                (2, 28, 28, 120, 1, 2), (1, 9, 14, 40, 1, 1), (4, 42, 21, 72, 1, 0)])
 def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
     x = rnd((n, h, w, c), 1, cuda)
     wt = rnd((c, 1, 3, 3), 2, cuda, torch.float32) / 3
@@ -174,7 +175,7 @@ def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
     check(b200lib.b200_dwconv3x3_nhwc(ptr(x), n, h, w, c, 0, ptr(w9), ptr(b), ptr(out), 0, stride, act, stream_ptr()))
     torch.cuda.synchronize()
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt, b, stride=stride, padding=1, groups=c)
-    ref = (F.silu(ref) if act == 2 else ref).permute(0, 2, 3, 1)
+    ref = (F.silu(ref) if act == 2 else F.relu(ref) if act == 1 else ref).permute(0, 2, 3, 1)
     ok, e = close_bf16(out, ref)
     assert ok, e
 
@@ -189,9 +190,9 @@ def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, 
     wt = rnd((c, 1, 3, 3), 12, cuda, torch.float32) / 3
     b = rnd((c,), 13, cuda, torch.float32)
     ho, wo = (h - 1) // stride + 1, (w - 1) // stride + 1
-    strips = b200lib.b200_dwconv3x3_strips(ho, wo, stride)
+    strips = b200lib.b200_dwconv3x3_squeeze_rows(c, ho, wo, stride)
     raw = ((ho + 1) // 2 if stride == 1 else ho) * (wo // 7)
-    assert strips in (raw, 1)      # 1: B200_DW_SQ=1 reduces up to 32 strips inside the kernel
+    assert strips in (raw, 1)      # 1: the tile kernel (or B200_DW_SQ=1) adds an image's strips itself
     out = torch.full((n, ho, wo, c), float("nan"), device=cuda, dtype=torch.bfloat16)
     sums = torch.full((n, strips, c), float("nan"), device=cuda)
     w9 = wt.reshape(c, 9).t().contiguous()
