@@ -108,6 +108,8 @@ def plan_traffic(blob, batch):
             if p[6] >= 0:
                 b += batch * oh * ow * p[5] * 2
             fl = 2.0 * batch * oh * ow * p[5] * p[2] * k * k
+            if t == lowering.OP_CONV and p[17] > 0:      # folded SE gate [N][Cin] fp32
+                b += batch * p[2] * 4
             if t == lowering.OP_CONV and p[13] > 0:      # K-concatenated second input, sampled with stride p[16]
                 b += batch * oh * ow * p[15] * 2 + p[5] * p[15] * 2
                 fl += 2.0 * batch * oh * ow * p[5] * p[15]

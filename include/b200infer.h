@@ -63,6 +63,14 @@ B200_API int b200_conv1x1_dual_nhwc(const void* in, int n, int h, int w, int cin
                                     int w2, int cin2, int in2_pix_stride, int stride2, const void* weight,
                                     const float* bias, void* out, int cout, int out_pix_stride, int act, void* stream);
 
+/* 1x1 convolution whose input is first multiplied by a per-(image, channel) factor: out = act(W . (in * in_scale[n][c]) +
+ * bias (+ residual)). Replaces `scale * input` of SqueezeExcitation.forward (tv ops/misc.py:256-258) together with the
+ * MBConv project conv that consumes it (tv efficientnet.py:157-163): the scaled activation is never written. The product
+ * is rounded to bf16 in shared memory, exactly where b200_channel_scale_nhwc would have stored it. in_scale fp32 [n][cin]. */
+B200_API int b200_conv1x1_scaled_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const float* in_scale,
+                                      const void* weight, const float* bias, const void* residual, int res_pix_stride,
+                                      void* out, int cout, int out_pix_stride, int act, void* stream);
+
 /* Same contract as b200_conv2d_nhwc for layers with few input channels (cin <= 56, cout <= 256): GEMM-K packs the filter
  * taps (k = tap * cin + c), the im2col tile is gathered into shared memory by cp.async producers. Serves the
  * FusedMBConv 3x3 convolutions of EfficientNetV2 (tv efficientnet.py:172-231) and YOLOv8n's early layers.

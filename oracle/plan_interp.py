@@ -58,7 +58,10 @@ class PlanInterpreter:
             t, p = op["type"], op["p"]
             if t == OP_CONV:
                 cin, cout, k, s, pad, act = p[2], p[5], p[8], p[9], p[10], p[11]
-                x = B[p[0]][..., p[1]:p[1] + cin].permute(0, 3, 1, 2)
+                x = B[p[0]][..., p[1]:p[1] + cin]
+                if p[17] > 0:      # SE gate folded into the conv input: x * gate, rounded to bf16 like the scale op's output
+                    x = _bf16(x * B[p[17] - 1].view(n, 1, 1, -1)[..., :cin])
+                x = x.permute(0, 3, 1, 2)
                 b = self._f32(op["b_off"], cout)
                 if p[13] > 0:      # K-concatenated 1x1 conv: W[:, :cin] . x + W[:, cin:] . x2[::s2, ::s2]
                     cin2, s2 = p[15], p[16]

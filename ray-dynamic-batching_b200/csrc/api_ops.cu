@@ -53,6 +53,26 @@ int b200_conv1x1_dual_nhwc(const void* in, int n, int h, int w, int cin, int in_
   return conv_launch(l, static_cast<cudaStream_t>(stream));
 }
 
+int b200_conv1x1_scaled_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const float* in_scale,
+                             const void* weight, const float* bias, const void* residual, int res_pix_stride, void* out,
+                             int cout, int out_pix_stride, int act, void* stream) {
+  if (n <= 0 || h <= 0 || w <= 0 || !in_scale) return fail(B200_ERR_INVALID, "b200_conv1x1_scaled_nhwc: empty input");
+  ConvSpec s;
+  s.in = make_view(const_cast<void*>(in), n, h, w, cin, in_pix_stride);
+  s.a_scale = in_scale;
+  s.out = make_view(out, n, h, w, cout, out_pix_stride);
+  if (residual) s.res = make_view(const_cast<void*>(residual), n, h, w, cout, res_pix_stride);
+  s.w = weight;
+  s.bias = bias;
+  s.ksize = 1;
+  s.stride = 1;
+  s.pad = 0;
+  s.act = act;
+  ConvLaunch l;
+  B200_TRY(conv_prepare(s, &l));
+  return conv_launch(l, static_cast<cudaStream_t>(stream));
+}
+
 int b200_gather_conv_npad(int cout) { return gather_conv_npad(cout); }
 int b200_gather_conv_kpad(int cin, int ksize) { return gather_conv_kpad(cin, ksize); }
 

@@ -214,14 +214,18 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 //                     epilogue (~0.6 us with SiLU), overlap two of them
 // ================================================================================================================
 static constexpr int PCONV_THREADS = 384;
+static constexpr int PCONV_THREADS_MAX = 512;   // + warps 12-15: A-operand scaler, launched only for layers with ConvSpec::a_scale
 static constexpr int HALO_THREADS = 384;   // warps 0-2: TMA / MMA / DMA, 4-7 and 8-11: two epilogue warpgroups
 
 // Without a residual the staging ring only has to cover the store of the previous tile (2 buffers); the shared memory that
 // frees goes into a deeper A/B ring, which is what the HBM-bound layers need (bytes in flight per SM ~ latency x bandwidth).
-template <int BLOCK_N, int RES>
+// DEEP: long-K layers with few tiles per SM (EfficientNetV2 project convs: K = 960 / 1536, 2-3 tiles per SM) are paced by
+// the ring depth (tile period = (TMA latency + MMA time) / stages), not by the store path: two staging buffers, five stages.
+template <int BLOCK_N, int RES, int DEEP = 0>
 struct PConvCfg {
-  static constexpr int STAGES = RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4);      // A/B ring
-  static constexpr int OUT_BUFS = RES ? (BLOCK_N == 64 ? 6 : 4) : 3;                           // output / residual staging ring
+  static constexpr int STAGES = DEEP ? (BLOCK_N == 64 ? 8 : 5)
+                                     : (RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4));   // A/B ring
+  static constexpr int OUT_BUFS = DEEP ? 2 : (RES ? (BLOCK_N == 64 ? 6 : 4) : 3);              // output / residual staging ring
   static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -263,11 +267,11 @@ __device__ __forceinline__ float act_t(float x) {
 }
 
 // RES: 0 no residual, 1 act(acc + bias + res), 2 act(acc + bias) + res.  ACT: b200::Act.
-template <int BLOCK_N, int RES, int ACT>
-__global__ void __launch_bounds__(PCONV_THREADS, 1)
+template <int BLOCK_N, int RES, int ACT, int DEEP = 0>
+__global__ void __launch_bounds__(PCONV_THREADS_MAX, 1)
 conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p,
                             const int total_tiles) {
-  using Cfg = PConvCfg<BLOCK_N, RES>;
+  using Cfg = PConvCfg<BLOCK_N, RES, DEEP>;
   constexpr int STAGES = Cfg::STAGES;
   constexpr int NB = Cfg::OUT_BUFS;
   constexpr int LA = Cfg::LOOKAHEAD;
@@ -275,6 +279,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[STAGES];
   __shared__ __align__(8) uint64_t bar_empty[STAGES];
+  __shared__ __align__(8) uint64_t bar_scaled[STAGES];   // A tile multiplied by the per-image channel factors (p.a_scale)
   __shared__ __align__(8) uint64_t bar_tmem_full[2];
   __shared__ __align__(8) uint64_t bar_tmem_empty[2];
   __shared__ __align__(8) uint64_t bar_stage_ready[NB];  // staging buffer free (and residual landed, if any)
@@ -297,6 +302,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(smem_u32(&bar_full[s]), 1);
       mbar_init(smem_u32(&bar_empty[s]), 1);
+      mbar_init(smem_u32(&bar_scaled[s]), 128);
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bar_tmem_full[b]), 1);
@@ -359,7 +365,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         for (int kb = 0; kb < num_kb; ++kb, ++g) {
           const int s = g % STAGES;
           const uint32_t ph = (g / STAGES) & 1;
-          mbar_wait(smem_u32(&bar_full[s]), ph);
+          mbar_wait(smem_u32(p.a_scale ? &bar_scaled[s] : &bar_full[s]), ph);
           tc_fence_after();
           const uint32_t a_src = ring + s * Cfg::STAGE_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_src);
@@ -433,6 +439,71 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       if (elect_one()) tma_store_wait_all();
     }
     __syncwarp();
+  } else if (warp >= 12) {
+    // =========================== A-operand scaler (launched only when p.a_scale is set) ===========================
+    // Measured on B200 (EfficientNetV2-S project convs, K = 960 / 1536): this fusion LOSES -- 73 us against 22 us (conv) +
+    // 18 us (separate scale pass).  The read-modify-write of the tile competes with the tensor core's operand reads for the
+    // same shared-memory bandwidth and adds a hop to every ring slot, so it stays an opt-in (B200_FOLD_SE_SCALE=1).
+    // SE excitation folded into the project conv: row r of the A tile (one pixel, 64 channels of this k-block, 128-byte
+    // swizzled) is multiplied by a_scale[image of the pixel][channels] between the TMA load and the MMA, rounding to bf16
+    // exactly where the separate scale kernel stored its result.
+    const int r = threadIdx.x - 384;                       // 0..127: tile row
+    const int sw = r & 7;
+    // row of a_scale of this thread's pixel in tile `it` (null past the tensor): one division per TILE, not per k-block
+    auto gate_row = [&](int it) -> const float* {
+      if (it >= my_tiles) return nullptr;
+      const int tile0_ = blockIdx.x + it * gridDim.x;
+      const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+      int n_tile, w0, h0, nb0;
+      tile_coords(p, tile, n_tile, w0, h0, nb0);
+      const unsigned m = static_cast<unsigned>(w0 + r);    // flat pixel index (1x1 / stride 1 layers are tiled flat)
+      if (static_cast<long long>(m) >= p.a_pixels) return nullptr;
+      return p.a_scale + static_cast<size_t>(m / static_cast<unsigned>(p.a_scale_hw)) * p.a_scale_c;
+    };
+    auto gate_load = [&](const float* grow, int kb, float4 (&gv)[16]) {
+#pragma unroll
+      for (int c = 0; c < 16; ++c)
+        gv[c] = (grow && kb * BLOCK_K + c * 4 < p.a_scale_c) ? *reinterpret_cast<const float4*>(grow + kb * BLOCK_K + c * 4)
+                                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    float4 cur[16], nxt[16];
+    const float* grow = gate_row(0);
+    gate_load(grow, 0, cur);
+    uint32_t g = 0;
+    for (int it = 0; it < my_tiles; ++it) {
+      const float* grow_next = nullptr;
+      for (int kb = 0; kb < num_kb; ++kb, ++g) {
+        const int s = g % STAGES;
+        if (kb + 1 == num_kb) {
+          grow_next = gate_row(it + 1);
+          gate_load(grow_next, 0, nxt);
+        } else {
+          gate_load(grow, kb + 1, nxt);
+        }
+        mbar_wait(smem_u32(&bar_full[s]), (g / STAGES) & 1);
+        const uint32_t row = ring + s * Cfg::STAGE_BYTES + r * 128;
+        uint32_t v[8][4];
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[c][0]), "=r"(v[c][1]), "=r"(v[c][2]), "=r"(v[c][3])
+                       : "r"(row + ((c ^ sw) << 4)));
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          const float4 g0 = cur[2 * c], g1 = cur[2 * c + 1];
+          const uint32_t o0 = pack_bf16x2(bf16_lo(v[c][0]) * g0.x, bf16_hi(v[c][0]) * g0.y);
+          const uint32_t o1 = pack_bf16x2(bf16_lo(v[c][1]) * g0.z, bf16_hi(v[c][1]) * g0.w);
+          const uint32_t o2 = pack_bf16x2(bf16_lo(v[c][2]) * g1.x, bf16_hi(v[c][2]) * g1.y);
+          const uint32_t o3 = pack_bf16x2(bf16_lo(v[c][3]) * g1.z, bf16_hi(v[c][3]) * g1.w);
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row + ((c ^ sw) << 4)), "r"(o0), "r"(o1), "r"(o2), "r"(o3)
+                       : "memory");
+        }
+        fence_proxy_async_smem();                          // generic-proxy writes -> visible to the tensor core's reads
+        mbar_arrive(smem_u32(&bar_scaled[s]));
+#pragma unroll
+        for (int c = 0; c < 16; ++c) cur[c] = nxt[c];
+      }
+      grow = grow_next;
+    }
   } else if (warp >= 4) {
     // =========================== epilogue ===========================
     const int wg = (warp - 4) >> 2;                  // epilogue warpgroup 0 / 1 <-> accumulator 0 / 1
@@ -1136,6 +1207,8 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   if (Ho != out.H || Wo != out.W || in.N != out.N) return fail(B200_ERR_INVALID, "conv: output geometry mismatch");
   const bool has_res = s.res.base != nullptr;
   const bool dual = s.in2.base != nullptr;
+  if (s.a_scale && (s.ksize != 1 || s.stride != 1 || s.pad != 0 || dual))
+    return fail(B200_ERR_INVALID, "conv: input scaling needs a plain 1x1 / stride 1 conv");
   if (dual) {
     const View& b2 = s.in2;
     if (s.ksize != 1 || s.stride != 1 || s.pad != 0) return fail(B200_ERR_INVALID, "conv: a second input needs a 1x1 / stride 1 conv");
@@ -1166,6 +1239,10 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
   p.bias = s.bias;
   p.reverse = s.reverse_tiles ? 1 : 0;
+  p.a_scale = s.a_scale;
+  p.a_scale_hw = in.H * in.W;
+  p.a_scale_c = in.C;
+  p.a_pixels = static_cast<long long>(in.N) * in.H * in.W;
   // Tile choice.  Layers with enough arithmetic per byte (K >= 256, Cout >= 128) are bound by shared-memory operand
   // bandwidth in single-CTA mode -> CTA pairs (M = 256), N = 256 when Cout allows.  Thin layers stay single-CTA.
   const int k_total = in.C * taps + (dual ? s.in2.C : 0);
@@ -1187,6 +1264,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   bool two_cta = use_2cta() && ((out.C >= 256 && k_total >= 256) ||
                                 (out.C >= 128 && pair128_min_k > 0 && k_total >= pair128_min_k));
   int block_n = two_cta ? (out.C >= 256 ? 256 : 128) : (out.C <= 64 ? 64 : 128);
+  if (s.a_scale) two_cta = false, block_n = out.C <= 64 ? 64 : 128;      // the scaler role lives in the single-CTA kernel
   if (two_cta && has_res) {
     // residual layers: CTA pairs pay off only with enough K per tile to hide the residual prefetch (layer4 conv3: K = 512)
     if (res_mode == 0 || (res_mode == 2 && k_total < res_min_k)) { two_cta = false; block_n = 128; }
@@ -1321,27 +1399,40 @@ static bool use_persistent() {
   return v == 1;
 }
 
-template <int BLOCK_N, int RES, int ACT>
+template <int BLOCK_N, int RES, int ACT, int DEEP = 0>
 static int launch_persistent_t(const ConvLaunch& l, cudaStream_t stream) {
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
+  using Cfg = PConvCfg<BLOCK_N, RES, DEEP>;
   if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>,
-                                      cudaFuncAttributeMaxDynamicSharedMemorySize, PConvCfg<BLOCK_N, RES>::SMEM_BYTES));
+    B200_CUDA_OK(cudaFuncSetAttribute(conv_gemm_persistent_kernel<BLOCK_N, RES, ACT, DEEP>,
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     configured[dev & 63] = true;
   }
   const int total = static_cast<int>(l.grid);
   const int ctas = total < device_sm_count() ? total : device_sm_count();
-  B200_CUDA_OK(launch_pdl_if(total >= pdl_min_waves() * device_sm_count(), conv_gemm_persistent_kernel<BLOCK_N, RES, ACT>, dim3(ctas), dim3(PCONV_THREADS),
-                          PConvCfg<BLOCK_N, RES>::SMEM_BYTES, stream, l.maps, l.p, total));
+  B200_CUDA_OK(launch_pdl_if(total >= pdl_min_waves() * device_sm_count(), conv_gemm_persistent_kernel<BLOCK_N, RES, ACT, DEEP>,
+                             dim3(ctas), dim3(l.p.a_scale ? PCONV_THREADS_MAX : PCONV_THREADS), Cfg::SMEM_BYTES, stream, l.maps,
+                             l.p, total));
   return B200_OK;
+}
+
+static bool deep_ring(const ConvLaunch& l) {     // B200_CONV_DEEP=0 turns the deep-ring variant off
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_DEEP");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1 && l.p.num_kb >= 8 && static_cast<long long>(l.grid) <= 8LL * device_sm_count();
 }
 
 template <int BLOCK_N, int RES>
 static int launch_persistent_act(const ConvLaunch& l, cudaStream_t stream) {
   switch (l.p.act) {
-    case ACT_NONE: return launch_persistent_t<BLOCK_N, RES, ACT_NONE>(l, stream);
+    case ACT_NONE:
+      if (BLOCK_N == 128 && RES != 2 && deep_ring(l)) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, (BLOCK_N == 128 && RES != 2) ? 1 : 0>(l, stream);
+      return launch_persistent_t<BLOCK_N, RES, ACT_NONE>(l, stream);
     case ACT_RELU: return launch_persistent_t<BLOCK_N, RES, ACT_RELU>(l, stream);
     case ACT_SILU: return launch_persistent_t<BLOCK_N, RES, ACT_SILU>(l, stream);
     case ACT_SIGMOID: return launch_persistent_t<BLOCK_N, RES, ACT_SIGMOID>(l, stream);

@@ -7,6 +7,8 @@ namespace b200 {
 struct ConvSpec {
   View in, out;
   View res;                  // optional residual (base == nullptr -> none); same geometry as `out`
+  const float* a_scale = nullptr;   // optional per-(image, input channel) fp32 factor [N][Cin] applied to the input (SE
+                                    //   excitation folded into the project conv); 1x1 / stride 1 only
   View in2;                  // optional second input of a K-concatenated 1x1 conv (base == nullptr -> none): the output is
   int stride2 = 1;           //   act(W[:, :Ca] . in + W[:, Ca:] . in2[::stride2, ::stride2] + bias), w = [Cout][Ca + Cb]
   const void* w = nullptr;   // bf16 [Cout][k*k][Cin], BatchNorm already folded in
@@ -38,6 +40,9 @@ struct ConvParams {
   int reverse;             // walk the tiles last-to-first (alternated layer by layer so a layer starts on what is still in L2)
   signed char tap_map[9], tap_dx[9], tap_dy[9];
   const float* bias;
+  const float* a_scale;    // null, or [N][a_scale_c] fp32: the A tile is multiplied by it in shared memory before the MMA
+  int a_scale_hw, a_scale_c;   // pixels per image, channels per image row of a_scale
+  long long a_pixels;      // N * H * W (rows past it are TMA zero fill)
 };
 
 struct ConvLaunch {

@@ -100,16 +100,17 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
     const int s = it % p.stages;
     const int c0 = g * p.cg + quad * 4;
     const bool c_ok = c0 < p.C;                 // the last group of a ragged channel count
-    float wt[9][4], b[4];
+    // channels are kept as two float2 pairs so that every tap is two FFMA2 (the kernel is issue-bound, not memory-bound)
+    float2 wt[9][2], b[2];
     {
       const int cc = c_ok ? c0 : 0;
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
         const float4 v = *reinterpret_cast<const float4*>(p.w + k * p.C + cc);
-        wt[k][0] = v.x; wt[k][1] = v.y; wt[k][2] = v.z; wt[k][3] = v.w;
+        wt[k][0] = make_float2(v.x, v.y); wt[k][1] = make_float2(v.z, v.w);
       }
       const float4 v = *reinterpret_cast<const float4*>(p.bias + cc);
-      b[0] = v.x; b[1] = v.y; b[2] = v.z; b[3] = v.w;
+      b[0] = make_float2(v.x, v.y); b[1] = make_float2(v.z, v.w);
     }
     const int rows = min(p.band_h, p.H - band * p.band_h);      // output rows of this item
     const int strips = ((rows + 1) >> 1) * strips_w;
@@ -118,14 +119,15 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
     float sum[4] = {0.f, 0.f, 0.f, 0.f};
     for (int st = slot; st < strips; st += nslots) {
       const int sy = st / strips_w, sx = st - sy * strips_w;
-      const int oy0 = sy * 2, ox0 = sx * DT_TW;                 // within the band; staged row r = output row r - 1 + 1
+      const int oy0 = sy * 2, ox0 = sx * DT_TW;                 // within the band
       // staged tile: row i <-> input row (band0 - 1 + i), column j <-> input column (j - 1)
       const uint32_t base = tile + (static_cast<uint32_t>(oy0 * row_pitch + ox0 * p.cg + quad * 4) << 1);
-      float win[4][3][4];
-      auto lds4 = [&](int i, int j, float (&v)[4]) {
+      float2 win[4][3][2];
+      auto lds4 = [&](int i, int j, float2 (&v)[2]) {
         uint32_t lo, hi;
         asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(base + (static_cast<uint32_t>(i * row_pitch + j * p.cg) << 1)));
-        v[0] = bf16_lo(lo); v[1] = bf16_hi(lo); v[2] = bf16_lo(hi); v[3] = bf16_hi(hi);
+        v[0] = make_float2(bf16_lo(lo), bf16_hi(lo));
+        v[1] = make_float2(bf16_lo(hi), bf16_hi(hi));
       };
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -136,26 +138,27 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
       for (int j = 0; j < DT_TW; ++j) {
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-#pragma unroll
-          for (int c = 0; c < 4; ++c) { win[i][0][c] = win[i][1][c]; win[i][1][c] = win[i][2][c]; }
+          win[i][0][0] = win[i][1][0]; win[i][0][1] = win[i][1][1];
+          win[i][1][0] = win[i][2][0]; win[i][1][1] = win[i][2][1];
           lds4(i, j + 2, win[i][2]);
         }
 #pragma unroll
         for (int r = 0; r < 2; ++r) {
           if (oy0 + r >= rows || !c_ok) continue;
-          float acc[4] = {b[0], b[1], b[2], b[3]};
+          float2 acc0 = b[0], acc1 = b[1];
 #pragma unroll
           for (int dr = 0; dr < 3; ++dr)
 #pragma unroll
-            for (int q = 0; q < 3; ++q)
-#pragma unroll
-              for (int c = 0; c < 4; ++c) acc[c] = fmaf(win[r + dr][q][c], wt[dr * 3 + q][c], acc[c]);
+            for (int q = 0; q < 3; ++q) {      // same (row, column) order on top of the bias as the strip kernel: bit-identical
+              acc0 = ffma2(win[r + dr][q][0], wt[dr * 3 + q][0], acc0);
+              acc1 = ffma2(win[r + dr][q][1], wt[dr * 3 + q][1], acc1);
+            }
           uint2 o;
-          o.x = pack_bf16x2(apply_act(acc[0], ACT), apply_act(acc[1], ACT));
-          o.y = pack_bf16x2(apply_act(acc[2], ACT), apply_act(acc[3], ACT));
+          o.x = pack_bf16x2(apply_act(acc0.x, ACT), apply_act(acc0.y, ACT));
+          o.y = pack_bf16x2(apply_act(acc1.x, ACT), apply_act(acc1.y, ACT));
           const int oy = band * p.band_h + oy0 + r;
           *reinterpret_cast<uint2*>(p.out + ((static_cast<size_t>(n) * p.H + oy) * p.W + ox0 + j) * p.out_ps + c0) = o;
-          sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y);
+          if (p.sums) { sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y); }
         }
       }
     }

@@ -83,6 +83,11 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
           int64_t(sb.h) * sb.w * sb.c < int64_t(o.p[1]) * o.p[2] || int64_t(gb.h) * gb.w * gb.c < o.p[2])
         return fail(B200_ERR_BLOB, "engine: squeeze-excitation gate buffers do not match its shape");
     }
+    if (o.type == OP_CONV && o.p[17] != 0) {
+      if (o.p[17] < 0 || o.p[17] > int(hdr.n_bufs) || bufs[o.p[17] - 1].dtype != 1 ||
+          int64_t(bufs[o.p[17] - 1].h) * bufs[o.p[17] - 1].w * bufs[o.p[17] - 1].c < o.p[2])
+        return fail(B200_ERR_BLOB, "engine: conv input-scale buffer does not match its input channels");
+    }
     if (o.type == OP_CONV && (o.p[13] < 0 || o.p[13] > int(hdr.n_bufs)))
       return fail(B200_ERR_BLOB, "engine: conv references an unknown second input");
     const int64_t offs[4] = {o.w_off, o.b_off, o.w2_off, o.b2_off};
@@ -142,6 +147,7 @@ int Engine::plan_for(int batch, BatchPlan** out) {
       s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
       s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];
       s.res_after_act = p[12] != 0;
+      if (p[17] > 0) s.a_scale = reinterpret_cast<const float*>(buf_dev[p[17] - 1]);   // SE gate [N][Cin] fp32, buffer id + 1
       if (p[13] > 0) {      // K-concatenated second input: buffer id + 1, channel offset, channels, stride
         s.in2 = view(p[13] - 1, p[14], p[15], batch);
         s.stride2 = p[16];

@@ -167,7 +167,7 @@ class PlanBuilder:
 
     # ---- ops ----
     def conv(self, x: T, weight, bias, stride, pad, act, res: Optional[T] = None, out: Optional[T] = None, name="",
-             res_after_act=False):
+             res_after_act=False, in_scale: Optional[T] = None):
         """weight: fp32 [Cout, Cin, k, k] (already BN-folded); x.c == Cin logical channels; physical channels padded to 8."""
         cout, cin, k, _ = weight.shape
         assert cin == x.c, (cin, x.c)
@@ -178,7 +178,7 @@ class PlanBuilder:
         cin_p, cout_p = x.cphys, out.cphys
         halo = (self.halo_small_cin and k == 3 and stride == 1 and pad == 1 and cin_p <= 64 and cout_p <= 256 and
                 ((x.w + 7) // 8 * 8) * ((x.h + 15) // 16 * 16) * 100 <= x.w * x.h * 135)   # conv_prepare's halo rule
-        if not halo and self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
+        if in_scale is None and not halo and self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
                                                        (k == 1 and cin_p % 64 != 0 and cin_p <= self.gather_1x1_max_cin)):
             return self._gather_conv(x, weight, bias, stride, pad, act, res, out, name, res_after_act)
         wp = torch.zeros(cout_p, k * k, cin_p)
@@ -192,8 +192,12 @@ class PlanBuilder:
         rb, rc = (res.buf, res.coff) if res is not None else (-1, 0)
         if res is not None:
             assert (res.h, res.w, res.c, res.cphys) == (ho, wo, cout, cout_p) and np.array_equal(res.cmap, out.cmap)
-        self._op(OP_CONV, [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act,
-                           1 if res_after_act else 0], w_off, b_off, name=name)
+        pr = [x.buf, x.coff, cin_p, out.buf, out.coff, cout_p, rb, rc, k, stride, pad, act, 1 if res_after_act else 0]
+        if in_scale is not None:      # SE gate [cin_p] fp32 folded into this conv's input (csrc/conv_gemm.cu, ConvSpec::a_scale)
+            assert (k, stride, pad) == (1, 1, 0) and self.bufs[in_scale.buf][3] == 1 and in_scale.cphys == cin_p
+            assert x.coff == 0 and self.bufs[x.buf][2] == cin_p
+            pr += [0, 0, 0, 0, in_scale.buf + 1]
+        self._op(OP_CONV, pr, w_off, b_off, name=name)
         return out
 
     def conv_dual(self, x: T, weight, bias, x2: T, weight2, bias2, stride2, act, name=""):
@@ -590,6 +594,9 @@ def lower_efficientnet_v2(model, in_hw=(224, 224), fuse_se=None) -> PlanBuilder:
         fuse_se = os.environ.get("B200_FUSE_SE", "1") != "0"
     # hidden + (fc2 + scale) instead of gate + scale: measured equal within noise on B200 (3.87 vs 3.81 ms @128), off
     split_se = os.environ.get("B200_SPLIT_SE", "0") == "1"
+    # x * gate inside the project conv instead of a scale pass: bit-exact but slower on B200 (the in-smem rescale competes
+    # with the tensor core for shared-memory bandwidth: 73 vs 22 + 18 us per block), so off by default
+    fold_scale = os.environ.get("B200_FOLD_SE_SCALE", "0") == "1"
     feats = model.features
     w, b = fold_bn(feats[0][0], feats[0][1])
     x = pb.stem(pb.input(), w, b, 2, 1, ACT_SILU, name="features.0")
@@ -632,9 +639,13 @@ def lower_efficientnet_v2(model, in_hw=(224, 224), fuse_se=None) -> PlanBuilder:
                               name=nm + "se.fc1")
                     s = pb.fc(s, se.fc2.weight.detach().float().flatten(1), se.fc2.bias.detach().float(), ACT_SIGMOID,
                               name=nm + "se.fc2")
+                w, b = fold_bn(proj[0], proj[1])
+                if s is not None and fold_scale:
+                    # SE excitation folded into the project conv: its A tile is scaled in shared memory, no scale pass
+                    x = pb.conv(t, w, b, 1, 0, ACT_NONE, res=res, name=nm + "se.scale+project", in_scale=s)
+                    continue
                 if s is not None:
                     t = pb.scale(t, s, name=nm + "se.scale")
-                w, b = fold_bn(proj[0], proj[1])
                 x = pb.conv(t, w, b, 1, 0, ACT_NONE, res=res, name=nm + "project")
             else:
                 raise NotImplementedError(type(blk))

@@ -115,6 +115,31 @@ def test_conv1x1_dual_input(b200lib, cuda, case):
     assert (err > tol).sum().item() == 0, "max err %.4g" % err.max().item()
 
 
+@pytest.mark.parametrize("case", [(128, 14, 14, 960, 160, True), (5, 7, 7, 1536, 256, True), (3, 14, 14, 512, 128, False),
+                                  (2, 9, 5, 200, 72, False)])
+def test_conv1x1_with_folded_se_scale(b200lib, cuda, case):
+    """out = W . bf16(x * gate[n][c]) + bias (+ residual): identical to channel_scale followed by the plain conv."""
+    n, h, w, cin, cout, use_res = case
+    g = torch.Generator(device="cpu").manual_seed(abs(hash(case)) % (2 ** 31))
+    x = torch.randn(n, h, w, cin, generator=g).to(cuda).to(torch.bfloat16)
+    gate = torch.sigmoid(torch.randn(n, cin, generator=g)).to(cuda)
+    wt = (torch.randn(cout, 1, 1, cin, generator=g) / cin ** 0.5).to(cuda).to(torch.bfloat16)
+    bias = torch.randn(cout, generator=g).to(cuda)
+    res = torch.randn(n, h, w, cout, generator=g).to(cuda).to(torch.bfloat16) if use_res else None
+    out = torch.full((n, h, w, cout), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_conv1x1_scaled_nhwc(ptr(x), n, h, w, cin, 0, ptr(gate), ptr(wt), ptr(bias), ptr(res), 0, ptr(out), cout,
+                                           0, ACT["none"], stream_ptr()), "b200_conv1x1_scaled_nhwc")
+    scaled = torch.empty_like(x)
+    check(b200lib.b200_channel_scale_nhwc(ptr(x), n, h, w, cin, 0, ptr(gate), ptr(scaled), 0, stream_ptr()))
+    two_pass = run_conv(b200lib, scaled, wt, bias, res, 1, 0, "none")
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "unwritten output elements"
+    assert torch.equal(out.view(torch.int16), two_pass.view(torch.int16)), (out.float() - two_pass.float()).abs().max().item()
+    ref = ref_conv(scaled, wt, bias, res, 1, 0, "none")
+    err = (out.float() - ref).abs()
+    assert (err > ref.abs() * 2.0 ** -8 + 2e-3).sum().item() == 0
+
+
 def test_conv1x1_dual_rejects_bad_shapes(b200lib, cuda):
     a = torch.zeros(1, 8, 8, 32, device=cuda, dtype=torch.bfloat16)      # first input not a multiple of 64 channels
     b2 = torch.zeros(1, 8, 8, 64, device=cuda, dtype=torch.bfloat16)
