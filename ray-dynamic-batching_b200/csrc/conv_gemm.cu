@@ -223,9 +223,14 @@ static constexpr int HALO_THREADS = 384;   // warps 0-2: TMA / MMA / DMA, 4-7 an
 // the ring depth (tile period = (TMA latency + MMA time) / stages), not by the store path: two staging buffers, five stages.
 template <int BLOCK_N, int RES, int DEEP = 0>
 struct PConvCfg {
-  static constexpr int STAGES = DEEP ? (BLOCK_N == 64 ? 8 : 5)
-                                     : (RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4));   // A/B ring
-  static constexpr int OUT_BUFS = DEEP ? 2 : (RES ? (BLOCK_N == 64 ? 6 : 4) : 3);              // output / residual staging ring
+  // DEEP == 2: thin-K layers (one or two k-blocks per tile: 1x1 convs with Cin <= 128 and no residual) are paced by the
+  // store path -- measured on a 24 -> 64 1x1 conv: the DMA thread sat in cp.async.bulk.wait_group.read 80 % of the time and
+  // the epilogue waited for a staging buffer -- so the shared memory goes into staging buffers instead of ring stages.
+  static constexpr int STAGES = DEEP == 2 ? (BLOCK_N == 64 ? 4 : 3)
+                              : DEEP == 1 ? (BLOCK_N == 64 ? 8 : 5)
+                                          : (RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4));   // A/B ring
+  static constexpr int OUT_BUFS = DEEP == 2 ? (BLOCK_N == 64 ? 8 : 4)
+                                : DEEP == 1 ? 2 : (RES ? (BLOCK_N == 64 ? 6 : 4) : 3);         // output / residual staging ring
   static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
@@ -1427,14 +1432,28 @@ static bool deep_ring(const ConvLaunch& l) {     // B200_CONV_DEEP=0 turns the d
   return v == 1 && l.p.num_kb >= 8 && static_cast<long long>(l.grid) <= 8LL * device_sm_count();
 }
 
+static bool deep_staging(const ConvLaunch& l) {     // B200_CONV_THIN=0 turns the deep-staging variant off
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_THIN");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1 && l.p.num_kb <= 2 && static_cast<long long>(l.grid) >= 8LL * device_sm_count();
+}
+
 template <int BLOCK_N, int RES>
 static int launch_persistent_act(const ConvLaunch& l, cudaStream_t stream) {
   switch (l.p.act) {
     case ACT_NONE:
       if (BLOCK_N == 128 && RES != 2 && deep_ring(l)) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, (BLOCK_N == 128 && RES != 2) ? 1 : 0>(l, stream);
+      if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, RES == 0 ? 2 : 0>(l, stream);
       return launch_persistent_t<BLOCK_N, RES, ACT_NONE>(l, stream);
-    case ACT_RELU: return launch_persistent_t<BLOCK_N, RES, ACT_RELU>(l, stream);
-    case ACT_SILU: return launch_persistent_t<BLOCK_N, RES, ACT_SILU>(l, stream);
+    case ACT_RELU:
+      if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_RELU, RES == 0 ? 2 : 0>(l, stream);
+      return launch_persistent_t<BLOCK_N, RES, ACT_RELU>(l, stream);
+    case ACT_SILU:
+      if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_SILU, RES == 0 ? 2 : 0>(l, stream);
+      return launch_persistent_t<BLOCK_N, RES, ACT_SILU>(l, stream);
     case ACT_SIGMOID: return launch_persistent_t<BLOCK_N, RES, ACT_SIGMOID>(l, stream);
   }
   return fail(B200_ERR_INVALID, "conv: unknown activation");
