@@ -100,7 +100,9 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
     const int s = it % p.stages;
     const int c0 = g * p.cg + quad * 4;
     const bool c_ok = c0 < p.C;                 // the last group of a ragged channel count
-    // channels are kept as two float2 pairs so that every tap is two FFMA2 (the kernel is issue-bound, not memory-bound)
+    // channels are kept as two float2 pairs so that every tap is two FFMA2.  Measured: halving the FMA issue slots this way
+    // changed nothing (28.4 -> 29.4 us on 14 x 14 x 960 @128), and neither did 1.0x input reads (strip kernel: 31 us) or
+    // sixteen compute warps (32 us): what paces this layer at ~2x its HBM bound is still not identified.
     float2 wt[9][2], b[2];
     {
       const int cc = c_ok ? c0 : 0;
