@@ -115,6 +115,193 @@ yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* _
   }
 }
 
+// ----------------------------------------------------------------------------------------------------------------
+// The same decode with the two final 1x1 convolutions on the tensor cores (warp-level mma.sync m16n8k16, bf16 x bf16 ->
+// fp32).  The SIMT version above spends 10.5 k FMAs per anchor with one broadcast shared-memory load per 4 FMAs and runs
+// at ~30 % of the FP32 pipe (185 us for the 80 x 80 level at batch 32).  Precision is kept by splitting every fp32
+// weight into two bf16 terms, w = hi + lo (|w - hi - lo| <= 2^-17 |w|): the hidden activations are bf16 already, so
+// x . hi + x . lo accumulated in fp32 differs from the fp32 product only in the last bits, and the DFL logits still
+// never see a bf16 rounding.  A warp owns 32 anchors (two m16 tiles); fragments follow the PTX m16n8k16 layout:
+//   A (row = anchor): a0 (g, 2t..), a1 (g+8, 2t..), a2 (g, 2t+8..), a3 (g+8, 2t+8..)   g = lane / 4, t = lane % 4
+//   B (col = output): b0 (k = 2t.., n = g), b1 (k = 2t+8.., n = g)       C: c0,c1 (g, 2t, 2t+1), c2,c3 (g+8, ...)
+// A side's 16 DFL bins of one anchor therefore sit in the four lanes of a quad: softmax by two xor-shuffles.
+// ----------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+static constexpr int YM_THREADS = 128;
+
+template <int CB, int NC>
+__global__ void __launch_bounds__(YM_THREADS)
+yolo_decode_mma_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* __restrict__ hc, int hc_ps, int H, int W,
+                       int N, const float* __restrict__ wb, const float* __restrict__ bb, const float* __restrict__ wc,
+                       const float* __restrict__ bc, float* __restrict__ out, int a_off, int a_total, float stride) {
+  constexpr int NB = 4 * REG_MAX;            // box-branch outputs (64)
+  constexpr int KPB = CB + 8, KPC = NC + 8;  // padded row lengths: a quad's 32-bit loads of 8 rows hit 32 distinct banks
+  static_assert(CB % 16 == 0 && NC % 16 == 0 && NC % 8 == 0, "K must be a multiple of the MMA K");
+  pdl_wait();
+  extern __shared__ __align__(16) uint16_t s_y[];   // wb_hi [NB][KPB] | wb_lo | wc_hi [NC][KPC] | wc_lo | bb [NB] f32 | bc [NC] f32
+  uint16_t* wbh = s_y;
+  uint16_t* wbl = wbh + NB * KPB;
+  uint16_t* wch = wbl + NB * KPB;
+  uint16_t* wcl = wch + NC * KPC;
+  float* s_bb = reinterpret_cast<float*>(wcl + NC * KPC);
+  float* s_bc = s_bb + NB;
+  auto split = [](float w, uint16_t& hi, uint16_t& lo) {
+    const __nv_bfloat16 h = __float2bfloat16_rn(w);
+    const __nv_bfloat16 l = __float2bfloat16_rn(w - __bfloat162float(h));
+    hi = *reinterpret_cast<const uint16_t*>(&h);
+    lo = *reinterpret_cast<const uint16_t*>(&l);
+  };
+  for (int i = threadIdx.x; i < NB * CB; i += YM_THREADS) split(wb[i], wbh[(i / CB) * KPB + i % CB], wbl[(i / CB) * KPB + i % CB]);
+  for (int i = threadIdx.x; i < NC * NC; i += YM_THREADS) split(wc[i], wch[(i / NC) * KPC + i % NC], wcl[(i / NC) * KPC + i % NC]);
+  for (int i = threadIdx.x; i < NB; i += YM_THREADS) s_bb[i] = bb[i];
+  for (int i = threadIdx.x; i < NC; i += YM_THREADS) s_bc[i] = bc[i];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const long long total_anchors = static_cast<long long>(N) * H * W;
+  const int HW = H * W;
+  for (long long base = (static_cast<long long>(blockIdx.x) * (YM_THREADS / 32) + warp) * 32; base < total_anchors;
+       base += static_cast<long long>(gridDim.x) * (YM_THREADS / 32) * 32) {
+    // the four anchor rows this lane touches: tile mt, half h -> anchor base + mt * 16 + h * 8 + g (clamped for loads)
+    long long arow[2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) arow[mt][h] = base + mt * 16 + h * 8 + g;
+    auto clampa = [&](long long a) { return a < total_anchors ? a : total_anchors - 1; };
+
+    // ---------------- box branch: 64 hidden -> 4 sides x 16 bins, DFL, dist2bbox ----------------
+    {
+      uint32_t afr[2][CB / 16][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        const uint16_t* r0 = hb + clampa(arow[mt][0]) * hb_ps;
+        const uint16_t* r1 = hb + clampa(arow[mt][1]) * hb_ps;
+#pragma unroll
+        for (int ks = 0; ks < CB / 16; ++ks) {
+          afr[mt][ks][0] = *reinterpret_cast<const uint32_t*>(r0 + ks * 16 + 2 * t);
+          afr[mt][ks][1] = *reinterpret_cast<const uint32_t*>(r1 + ks * 16 + 2 * t);
+          afr[mt][ks][2] = *reinterpret_cast<const uint32_t*>(r0 + ks * 16 + 2 * t + 8);
+          afr[mt][ks][3] = *reinterpret_cast<const uint32_t*>(r1 + ks * 16 + 2 * t + 8);
+        }
+      }
+      float dist[2][2][4];      // [tile][half][side]
+#pragma unroll 1
+      for (int s = 0; s < 4; ++s) {
+        float acc[2][2][4];     // [tile][n-tile of the side][c0..c3]
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          const float b0 = s_bb[s * REG_MAX + nt * 8 + 2 * t], b1 = s_bb[s * REG_MAX + nt * 8 + 2 * t + 1];
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) { acc[mt][nt][0] = b0; acc[mt][nt][1] = b1; acc[mt][nt][2] = b0; acc[mt][nt][3] = b1; }
+        }
+#pragma unroll
+        for (int ks = 0; ks < CB / 16; ++ks)
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            const int off = (s * REG_MAX + nt * 8 + g) * KPB + ks * 16 + 2 * t;
+            const uint32_t h0 = *reinterpret_cast<const uint32_t*>(wbh + off), h1 = *reinterpret_cast<const uint32_t*>(wbh + off + 8);
+            const uint32_t l0 = *reinterpret_cast<const uint32_t*>(wbl + off), l1 = *reinterpret_cast<const uint32_t*>(wbl + off + 8);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+              mma_bf16_16816(acc[mt][nt], afr[mt][ks], h0, h1);
+              mma_bf16_16816(acc[mt][nt], afr[mt][ks], l0, l1);
+            }
+          }
+        // softmax expectation over the side's 16 bins: this lane holds bins 2t, 2t+1 (n-tile 0) and 8+2t, 9+2t (n-tile 1)
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float v0 = acc[mt][0][2 * h], v1 = acc[mt][0][2 * h + 1], v2 = acc[mt][1][2 * h], v3 = acc[mt][1][2 * h + 1];
+            float m = fmaxf(fmaxf(v0, v1), fmaxf(v2, v3));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+            m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+            const float e0 = expf(v0 - m), e1 = expf(v1 - m), e2 = expf(v2 - m), e3 = expf(v3 - m);
+            float den = e0 + e1 + e2 + e3;
+            float num = e0 * (2 * t) + e1 * (2 * t + 1) + e2 * (8 + 2 * t) + e3 * (9 + 2 * t);
+            den += __shfl_xor_sync(0xffffffffu, den, 1); num += __shfl_xor_sync(0xffffffffu, num, 1);
+            den += __shfl_xor_sync(0xffffffffu, den, 2); num += __shfl_xor_sync(0xffffffffu, num, 2);
+            dist[mt][h][s] = num / den;
+          }
+      }
+      // the four lanes of a quad hold the same four distances: lane t writes output component t (cx, cy, w, h)
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long idx = arow[mt][h];
+          if (idx >= total_anchors) continue;
+          const int a = static_cast<int>(idx % HW), n = static_cast<int>(idx / HW);
+          const int y = a / W, x = a - y * W;
+          const float ax = static_cast<float>(x) + 0.5f, ay = static_cast<float>(y) + 0.5f;
+          const float x1 = ax - dist[mt][h][0], y1 = ay - dist[mt][h][1], x2 = ax + dist[mt][h][2], y2 = ay + dist[mt][h][3];
+          const float comp = t == 0 ? (x1 + x2) * 0.5f * stride : t == 1 ? (y1 + y2) * 0.5f * stride
+                           : t == 2 ? (x2 - x1) * stride : (y2 - y1) * stride;
+          out[(static_cast<size_t>(n) * (4 + NC) + t) * a_total + a_off + a] = comp;
+        }
+    }
+    // ---------------- class branch: 80 hidden -> 80 classes, sigmoid ----------------
+    {
+      uint32_t afr[2][NC / 16][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        const uint16_t* r0 = hc + clampa(arow[mt][0]) * hc_ps;
+        const uint16_t* r1 = hc + clampa(arow[mt][1]) * hc_ps;
+#pragma unroll
+        for (int ks = 0; ks < NC / 16; ++ks) {
+          afr[mt][ks][0] = *reinterpret_cast<const uint32_t*>(r0 + ks * 16 + 2 * t);
+          afr[mt][ks][1] = *reinterpret_cast<const uint32_t*>(r1 + ks * 16 + 2 * t);
+          afr[mt][ks][2] = *reinterpret_cast<const uint32_t*>(r0 + ks * 16 + 2 * t + 8);
+          afr[mt][ks][3] = *reinterpret_cast<const uint32_t*>(r1 + ks * 16 + 2 * t + 8);
+        }
+      }
+      size_t obase[2][2];
+      bool live[2][2];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const long long idx = clampa(arow[mt][h]);
+          live[mt][h] = arow[mt][h] < total_anchors;
+          obase[mt][h] = static_cast<size_t>(idx / HW) * (4 + NC) * a_total + a_off + static_cast<size_t>(idx % HW);
+        }
+#pragma unroll 1
+      for (int nt = 0; nt < NC / 8; ++nt) {
+        const float b0 = s_bc[nt * 8 + 2 * t], b1 = s_bc[nt * 8 + 2 * t + 1];
+        float acc[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) { acc[mt][0] = b0; acc[mt][1] = b1; acc[mt][2] = b0; acc[mt][3] = b1; }
+#pragma unroll
+        for (int ks = 0; ks < NC / 16; ++ks) {
+          const int off = (nt * 8 + g) * KPC + ks * 16 + 2 * t;
+          const uint32_t h0 = *reinterpret_cast<const uint32_t*>(wch + off), h1 = *reinterpret_cast<const uint32_t*>(wch + off + 8);
+          const uint32_t l0 = *reinterpret_cast<const uint32_t*>(wcl + off), l1 = *reinterpret_cast<const uint32_t*>(wcl + off + 8);
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt) {
+            mma_bf16_16816(acc[mt], afr[mt][ks], h0, h1);
+            mma_bf16_16816(acc[mt], afr[mt][ks], l0, l1);
+          }
+        }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            if (!live[mt][h]) continue;
+            float* o = out + obase[mt][h] + static_cast<size_t>(4 + nt * 8 + 2 * t) * a_total;
+            o[0] = 1.f / (1.f + expf(-acc[mt][2 * h]));
+            o[a_total] = 1.f / (1.f + expf(-acc[mt][2 * h + 1]));
+          }
+      }
+    }
+  }
+}
+
 int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const float* bb, const float* wc, const float* bc,
                        float* out, int a_off, int a_total, float stride, cudaStream_t stream) {
   if (hb.C != 64 || hc.C != 80) return fail(B200_ERR_INVALID, "yolo_decode: expects 64 box-hidden and 80 class-hidden channels");
@@ -129,6 +316,25 @@ int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const fl
     configured[dev & 63] = true;
   }
   const long long total = static_cast<long long>(hb.N) * hb.H * hb.W;
+  static int use_mma = -1;
+  if (use_mma < 0) {
+    const char* e = getenv("B200_YOLO_MMA");
+    use_mma = (e && e[0] == '1') ? 1 : 0;      // opt-in until it has been run against the oracle on a GPU
+  }
+  if (use_mma && hb.pix_stride % 2 == 0 && hc.pix_stride % 2 == 0) {
+    const size_t sm = (size_t(2) * 64 * (64 + 8) + size_t(2) * 80 * (80 + 8)) * 2 + (64 + 80) * sizeof(float);
+    static bool conf_mma[64] = {};
+    if (!conf_mma[dev & 63]) {
+      B200_CUDA_OK(cudaFuncSetAttribute(yolo_decode_mma_kernel<64, 80>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      conf_mma[dev & 63] = true;
+    }
+    long long blk = (total + YM_THREADS - 1) / YM_THREADS;
+    if (blk > 4LL * device_sm_count()) blk = 4LL * device_sm_count();
+    B200_CUDA_OK(launch_pdl(yolo_decode_mma_kernel<64, 80>, dim3(static_cast<unsigned>(blk)), dim3(YM_THREADS), sm, stream,
+                            static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base),
+                            hc.pix_stride, hb.H, hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride));
+    return B200_OK;
+  }
   long long blocks = (total + YD_THREADS - 1) / YD_THREADS;
   if (blocks > 4LL * device_sm_count()) blocks = 4LL * device_sm_count();     // 4 blocks of 42 KB of weights per SM, grid-stride over anchors
   B200_CUDA_OK(launch_pdl(yolo_decode_kernel<64, 80>, dim3(static_cast<unsigned>(blocks)), dim3(YD_THREADS), size_t(smem), stream, static_cast<const uint16_t*>(hb.base), hb.pix_stride, static_cast<const uint16_t*>(hc.base), hc.pix_stride, hb.H, hb.W, hb.N, wb, bb, wc, bc, out, a_off, a_total, stride));
