@@ -319,7 +319,7 @@ int yolo_decode_launch(const View& hb, const View& hc, const float* wb, const fl
   static int use_mma = -1;
   if (use_mma < 0) {
     const char* e = getenv("B200_YOLO_MMA");
-    use_mma = (e && e[0] == '1') ? 1 : 0;      // opt-in until it has been run against the oracle on a GPU
+    use_mma = (e && e[0] == '0') ? 0 : 1;      // B200_YOLO_MMA=0: the SIMT version above
   }
   if (use_mma && hb.pix_stride % 2 == 0 && hc.pix_stride % 2 == 0) {
     const size_t sm = (size_t(2) * 64 * (64 + 8) + size_t(2) * 80 * (80 + 8)) * 2 + (64 + 80) * sizeof(float);
