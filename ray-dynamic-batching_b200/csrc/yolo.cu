@@ -126,12 +126,6 @@ yolo_decode_kernel(const uint16_t* __restrict__ hb, int hb_ps, const uint16_t* _
 //   B (col = output): b0 (k = 2t.., n = g), b1 (k = 2t+8.., n = g)       C: c0,c1 (g, 2t, 2t+1), c2,c3 (g+8, ...)
 // A side's 16 DFL bins of one anchor therefore sit in the four lanes of a quad: softmax by two xor-shuffles.
 // ----------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-
 static constexpr int YM_THREADS = 128;
 
 template <int CB, int NC>
