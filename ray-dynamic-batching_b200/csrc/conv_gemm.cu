@@ -654,7 +654,9 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   const int lane = threadIdx.x & 31;
   const uint32_t wres = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t halo = wres + 9 * tap_bytes;
-  const uint32_t staging = halo + HS * halo_stride;
+  const int planes = p.halo_s2 ? 4 : 1;                    // stride 2: parity planes (py, px) of the input, plane = py * 2 + px
+  const int stage_bytes = planes * halo_stride;
+  const uint32_t staging = halo + HS * stage_bytes;
   const int my_tiles = (total_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
   if (warp == 0 && lane == 0) {
@@ -707,8 +709,9 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         mbar_wait(smem_u32(&bar_halo_empty[hb]), ((it / HS) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_halo_full[hb]);
         if (elect_one()) {
-          mbar_expect_tx(full, halo_bytes);
-          tma_load_4d(&maps.a[0], full, halo + hb * halo_stride, 0, w0 - 1, h0 - 1, nb0);   // box [PB/2, 10, 18, 1]
+          mbar_expect_tx(full, planes * halo_bytes);
+          for (int pl = 0; pl < planes; ++pl)     // box [PB/2, 10, 18, 1] of the input (stride 1) or of each parity plane
+            tma_load_4d(&maps.a[pl], full, halo + hb * stage_bytes + pl * halo_stride, 0, w0 - 1, h0 - 1, nb0);
         }
       }
     }
@@ -735,11 +738,19 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         mbar_wait(smem_u32(&bar_halo_full[hb]), (it / HS) & 1);
         tc_fence_after();
         const uint32_t acc = tmem_base + b * BLOCK_N;
-        const uint32_t a_lo = a_lo0 + hb * (halo_stride >> 4);   // no carry out of the 14-bit address field: smem < 256 KB
+        const uint32_t a_lo = a_lo0 + hb * (stage_bytes >> 4);   // no carry out of the 14-bit address field: smem < 256 KB
+        const bool s2 = p.halo_s2 != 0;
         if (elect_one()) {
 #pragma unroll
           for (int t = 0; t < 9; ++t) {
-            const uint32_t a_t = a_lo + ((((t / 3) * HALO_PITCH_PX + (t % 3)) * PB) >> 4);
+            // stride 1: view shifted by (dy, dx) pixels.  stride 2: tap (dy, dx) reads in(2y + dy - 1, 2x + dx - 1) = parity
+            // plane (dy != 1, dx != 1) at (y - (dy == 0), x - (dx == 0)): with the box origin at (y0 - 1, x0 - 1) that is a
+            // shift of (dy != 0, dx != 0) pixels inside the plane's 18 x 10 box.  Both offsets are compile-time constants.
+            const int dy = t / 3, dx = t % 3;
+            const uint32_t off1 = static_cast<uint32_t>((dy * HALO_PITCH_PX + dx) * PB) >> 4;
+            const uint32_t off2 = static_cast<uint32_t>(((dy != 1 ? 2 : 0) + (dx != 1 ? 1 : 0)) * halo_stride +
+                                                        ((dy != 0 ? 1 : 0) * HALO_PITCH_PX + (dx != 0 ? 1 : 0)) * PB) >> 4;
+            const uint32_t a_t = a_lo + (s2 ? off2 : off1);
             const uint32_t b_t = b_lo0 + t * wtap;
 #pragma unroll
             for (int k = 0; k < KSTEPS; ++k)
@@ -1282,16 +1293,25 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   }
   // halo kernel: 3x3/s1/p1, Cin <= 64, 16x8-pixel tiles with little padding waste; Cout <= 64, or wider while the layer
   // is too thin in K for the generic kernel (Cin < 64: each of its k-blocks would be mostly padding)
-  const long long halo_cover = (long long)((in.W + 7) / 8 * 8) * ((in.H + 15) / 16 * 16);
-  const bool halo = use_halo && !dual && s.ksize == 3 && s.stride == 1 && s.pad == 1 && in.C <= 64 && s.act != ACT_SIGMOID &&
-                    (out.C <= 64 || (in.C < 64 && out.C <= 256)) && halo_cover * 100 <= (long long)in.W * in.H * 135;
+  const long long halo_cover = (long long)((out.W + 7) / 8 * 8) * ((out.H + 15) / 16 * 16);   // tiles are laid over the OUTPUT
+  static int use_halo_s2 = -1;
+  if (use_halo_s2 < 0) {
+    const char* e = getenv("B200_CONV_HALO_S2");
+    use_halo_s2 = (e && e[0] == '0') ? 0 : 1;
+  }
+  // stride 2 (Cin <= 32 only: a stage holds four parity planes): YOLOv8n layers 1 and 3, EfficientNetV2 features.2.0
+  const bool halo_s2 = use_halo_s2 && s.stride == 2 && in.C <= 32 && in.W >= 2 && in.H >= 2;
+  const bool halo = use_halo && !dual && s.ksize == 3 && (s.stride == 1 || halo_s2) && s.pad == 1 && in.C <= 64 &&
+                    s.act != ACT_SIGMOID && (out.C <= 64 || (in.C < 64 && out.C <= 256)) &&
+                    halo_cover * 100 <= (long long)out.W * out.H * 135;
   if (halo) {
     two_cta = false;
     block_n = out.C <= 32 ? 32 : 64;
     p.pb = in.C <= 16 ? 32 : (in.C <= 32 ? 64 : 128);
     p.block_n = block_n;
-    p.halo_stages = p.pb == 128 ? 3 : 4;
-    L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages);
+    p.halo_s2 = s.stride == 2 ? 1 : 0;
+    p.halo_stages = p.halo_s2 ? (p.pb == 64 ? 2 : 4) : (p.pb == 128 ? 3 : 4);
+    L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages * (p.halo_s2 ? 4 : 1));
   }
   L->halo = halo;
   L->block_n = block_n;
@@ -1317,8 +1337,18 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const uint64_t dims[4] = {uint64_t(in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
     const uint64_t str[3] = {ips, rowb, imgb};
     const uint32_t box[4] = {uint32_t(p.pb / 2), uint32_t(HALO_PITCH_PX), uint32_t(HALO_ROWS), 1u};
-    B200_TRY(encode_tmap(&L->maps.a[0], in.base, 4, dims, str, box,
-                         p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B)));
+    const Swizzle swz = p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B);
+    if (!p.halo_s2) {
+      B200_TRY(encode_tmap(&L->maps.a[0], in.base, 4, dims, str, box, swz));
+    } else {
+      for (int py = 0; py < 2; ++py)
+        for (int px = 0; px < 2; ++px) {      // parity plane (py, px)(i, j) = in(2i + py, 2j + px): a view with doubled strides
+          const uint64_t pd[4] = {uint64_t(in.C), uint64_t((in.W - px + 1) / 2), uint64_t((in.H - py + 1) / 2), uint64_t(in.N)};
+          const uint64_t ps[3] = {2 * ips, 2 * rowb, imgb};
+          const char* base = static_cast<const char*>(in.base) + (uint64_t(py) * in.W + px) * ips;
+          B200_TRY(encode_tmap(&L->maps.a[py * 2 + px], base, 4, pd, ps, box, swz));
+        }
+    }
   } else {
     pick_tile(oW, oH, oN, &p.tw, &p.th, &p.tn);
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
@@ -1523,7 +1553,7 @@ static int launch_halo_t(const ConvLaunch& l, cudaStream_t stream) {
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
     B200_CUDA_OK(cudaFuncSetAttribute(conv3x3_halo_kernel<PB, RES, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      HaloCfg::smem_bytes(PB, 64, PB == 128 ? 3 : 4)));
+                                      216 * 1024));      // >= every (swizzle span, stride, stages) configuration
     configured[dev & 63] = true;
   }
   const int total = static_cast<int>(l.grid);

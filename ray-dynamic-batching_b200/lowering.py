@@ -136,6 +136,7 @@ class PlanBuilder:
         self.gather_small_cin = True
         self.fuse_downsample = os.environ.get('B200_FUSE_DOWNSAMPLE', '1') != '0'   # ResNet conv3 + downsample as one GEMM
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
+        self.halo_stride2 = os.environ.get('B200_CONV_HALO_S2', '1') != '0'      # 3x3/s2 with Cin <= 32 too (parity planes)
         self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
 
     # ---- buffers / weights ----
@@ -176,8 +177,9 @@ class PlanBuilder:
             out = self.new_act(ho, wo, cout)
         assert (out.h, out.w, out.c) == (ho, wo, cout)
         cin_p, cout_p = x.cphys, out.cphys
-        halo = (self.halo_small_cin and k == 3 and stride == 1 and pad == 1 and cin_p <= 64 and cout_p <= 256 and
-                ((x.w + 7) // 8 * 8) * ((x.h + 15) // 16 * 16) * 100 <= x.w * x.h * 135)   # conv_prepare's halo rule
+        halo = (self.halo_small_cin and k == 3 and pad == 1 and cout_p <= 256 and
+                ((stride == 1 and cin_p <= 64) or (stride == 2 and self.halo_stride2 and cin_p <= 32 and x.w >= 2 and x.h >= 2))
+                and ((wo + 7) // 8 * 8) * ((ho + 15) // 16 * 16) * 100 <= wo * ho * 135)   # conv_prepare's halo rule
         if in_scale is None and not halo and self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
                                                        (k == 1 and cin_p % 64 != 0 and cin_p <= self.gather_1x1_max_cin)):
             return self._gather_conv(x, weight, bias, stride, pad, act, res, out, name, res_after_act)

@@ -66,6 +66,11 @@ CASES = [
     (2, 30, 30, 8, 40, 3, 1, 1, "relu", False),      # halo kernel, Cin = 8, W not a multiple of 8, Cout 40 -> N = 64
     (5, 48, 40, 48, 136, 3, 1, 1, "none", True),     # halo kernel, odd batch, three channel tiles, last one ragged (136 = 2*64 + 8)
     (1, 17, 9, 16, 200, 3, 1, 1, "relu", False),     # too much tile padding for the halo kernel: generic kernel, thin K
+    (2, 320, 320, 16, 32, 3, 2, 1, "silu", False),   # halo kernel, stride 2 through parity planes (YOLOv8n layer 1), 32-byte pixels
+    (3, 160, 160, 32, 64, 3, 2, 1, "silu", False),   # halo kernel, stride 2, 64-byte pixels (YOLOv8n layer 3)
+    (2, 112, 112, 24, 96, 3, 2, 1, "silu", False),   # halo kernel, stride 2, two channel tiles (EfficientNetV2 features.2.0)
+    (1, 31, 45, 8, 24, 3, 2, 1, "relu", False),      # halo kernel, stride 2, odd input sizes (ragged parity planes)
+    (2, 64, 48, 32, 40, 3, 2, 1, "none", True),      # halo kernel, stride 2 with a residual
 ]
 
 
