@@ -740,6 +740,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
         const uint32_t acc = tmem_base + b * BLOCK_N;
         const uint32_t a_lo = a_lo0 + hb * (stage_bytes >> 4);   // no carry out of the 14-bit address field: smem < 256 KB
         const bool s2 = p.halo_s2 != 0;
+        const int ksteps = p.halo_ksteps;
         if (elect_one()) {
 #pragma unroll
           for (int t = 0; t < 9; ++t) {
@@ -754,7 +755,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
             const uint32_t b_t = b_lo0 + t * wtap;
 #pragma unroll
             for (int k = 0; k < KSTEPS; ++k)
-              umma_bf16(acc, make_u64(a_t + 2 * k, a_hi), make_u64(b_t + 2 * k, b_hi), idesc, (t | k) != 0 ? 1u : 0u);
+              if (k < ksteps)     // channels from 16 * ksteps on are zero padding of the PB-byte pixel slot
+                umma_bf16(acc, make_u64(a_t + 2 * k, a_hi), make_u64(b_t + 2 * k, b_hi), idesc, (t | k) != 0 ? 1u : 0u);
           }
           umma_commit(smem_u32(&bar_halo_empty[hb]));
           umma_commit(smem_u32(&bar_tmem_full[b]));
@@ -1310,6 +1312,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     p.pb = in.C <= 16 ? 32 : (in.C <= 32 ? 64 : 128);
     p.block_n = block_n;
     p.halo_s2 = s.stride == 2 ? 1 : 0;
+    p.halo_ksteps = (in.C + 15) / 16;
     p.halo_stages = p.halo_s2 ? (p.pb == 64 ? 2 : 4) : (p.pb == 128 ? 3 : 4);
     L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages * (p.halo_s2 ? 4 : 1));
   }

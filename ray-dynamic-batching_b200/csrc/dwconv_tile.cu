@@ -22,7 +22,7 @@ static constexpr int DT_COMPUTE = 256;
 static constexpr int DT_THREADS = DT_COMPUTE + 32;
 static constexpr int DT_TW = 7;
 static constexpr int DT_MAX_STAGES = 4;
-static constexpr int DT_SMEM_MAX = 220 * 1024;   // dynamic shared memory the kernel may ask for (4 KB static on top)
+static constexpr int DT_SMEM_MAX = 216 * 1024;   // dynamic shared memory the kernel may ask for (8 KB static on top)
 
 struct DwTileParams {
   const float* w;        // [9][C]
@@ -39,15 +39,20 @@ struct DwTileParams {
   int total_items;       // N * bands * groups
 };
 
-template <int ACT>
+template <int ACT, int CG, bool SQ>
 __global__ void __launch_bounds__(DT_THREADS, 1)
 dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ DwTileParams p) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[DT_MAX_STAGES], bar_empty[DT_MAX_STAGES];
-  __shared__ __align__(16) float red[DT_COMPUTE * 4];
+  __shared__ __align__(16) float red[2][DT_COMPUTE * 4];
   const int warp = threadIdx.x >> 5;
   const uint32_t ring = (smem_u32(smem_raw) + 127u) & ~127u;
-  const int my_items = (p.total_items - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  // A block takes a CONTIGUOUS run of items, ordered (channel group, image, band): the group -- and with it the 9 + 1
+  // weight vectors every thread keeps in registers -- changes once or twice per block instead of with every item.
+  const int per = (p.total_items + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int item0 = blockIdx.x * per;
+  const int my_items = max(0, min(per, p.total_items - item0));
+  const int per_group = p.N * p.bands;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&in_map);
@@ -61,50 +66,47 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
   pdl_launch_dependents();
   pdl_wait();
 
-  auto item_coords = [&](int it, int& n, int& band, int& g) {
-    const int item = blockIdx.x + it * gridDim.x;
-    g = item % p.groups;
-    const int r = item / p.groups;
-    band = r % p.bands;
-    n = r / p.bands;
-  };
-
   if (warp == DT_COMPUTE / 32) {
     // =========================== TMA producer ===========================
+    int g = item0 / per_group, r = item0 - g * per_group;
     for (int it = 0; it < my_items; ++it) {
-      int n, band, g;
-      item_coords(it, n, band, g);
+      const int n = r / p.bands, band = r - n * p.bands;
       const int s = it % p.stages;
       mbar_wait(smem_u32(&bar_empty[s]), ((it / p.stages) & 1) ^ 1);
       if (elect_one()) {
         const uint32_t full = smem_u32(&bar_full[s]);
         mbar_expect_tx(full, p.tile_bytes);
-        // box [cg, W + 2, band_h + 2, 1] at (g * cg, -1, band * band_h - 1, n): outside the image -> zeros
-        tma_load_4d(&in_map, full, ring + s * p.tile_bytes, g * p.cg, -1, band * p.band_h - 1, n);
+        // box [CG, W + 2, band_h + 2, 1] at (g * CG, -1, band * band_h - 1, n): outside the image -> zeros
+        tma_load_4d(&in_map, full, ring + s * p.tile_bytes, g * CG, -1, band * p.band_h - 1, n);
       }
+      if (++r == per_group) { r = 0; ++g; }
     }
     __syncwarp();
     return;
   }
 
   // =========================== compute ===========================
-  const int quads = p.cg >> 2;                  // channel quads per item
-  const int nslots = DT_COMPUTE / quads;        // strips worked on concurrently
-  const int quad = threadIdx.x % quads;
-  const int slot = threadIdx.x / quads;
+  // The inner loop is instruction-issue bound (ncu: 111 instructions per 4-channel output before this layout, 18 of
+  // them the FFMA2s), so everything that is not math is hoisted: CG is a template parameter (shared-memory offsets of
+  // the window loads are immediates off four row registers), stores walk two row pointers, validity is two
+  // per-strip predicates instead of a branch per output, SiLU and the squeeze sums run on packed f32x2 lanes.
+  constexpr int QUADS = CG >> 2;                // channel quads per item
+  constexpr int NSLOTS = DT_COMPUTE / QUADS;    // strips worked on concurrently
+  const int quad = threadIdx.x % QUADS;
+  const int slot = threadIdx.x / QUADS;
   const int strips_w = p.W / DT_TW;
-  const int row_pitch = (p.W + 2) * p.cg;       // elements per staged input row
+  const uint32_t row_pitch = static_cast<uint32_t>(p.W + 2) * CG * 2;      // bytes per staged input row
+  const size_t out_row = static_cast<size_t>(p.W) * p.out_ps;              // elements per output row
+  float2 wt[9][2], b[2];
+  int g = item0 / per_group, r = item0 - g * per_group;
+  int g_loaded = -1;
   for (int it = 0; it < my_items; ++it) {
-    int n, band, g;
-    item_coords(it, n, band, g);
+    const int n = r / p.bands, band = r - n * p.bands;
     const int s = it % p.stages;
-    const int c0 = g * p.cg + quad * 4;
+    const int c0 = g * CG + quad * 4;
     const bool c_ok = c0 < p.C;                 // the last group of a ragged channel count
-    // channels are kept as two float2 pairs so that every tap is two FFMA2.  Measured: halving the FMA issue slots this way
-    // changed nothing (28.4 -> 29.4 us on 14 x 14 x 960 @128), and neither did 1.0x input reads (strip kernel: 31 us) or
-    // sixteen compute warps (32 us): what paces this layer at ~2x its HBM bound is still not identified.
-    float2 wt[9][2], b[2];
-    {
+    if (g != g_loaded) {
+      g_loaded = g;
       const int cc = c_ok ? c0 : 0;
 #pragma unroll
       for (int k = 0; k < 9; ++k) {
@@ -117,24 +119,33 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
     const int rows = min(p.band_h, p.H - band * p.band_h);      // output rows of this item
     const int strips = ((rows + 1) >> 1) * strips_w;
     mbar_wait(smem_u32(&bar_full[s]), (it / p.stages) & 1);
-    const uint32_t tile = ring + s * p.tile_bytes;
-    float sum[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int st = slot; st < strips; st += nslots) {
+    const uint32_t tile = ring + s * p.tile_bytes + quad * 8;
+    uint16_t* const out_item = p.out + (static_cast<size_t>(n) * p.H + band * p.band_h) * out_row + c0;
+    float2 sum0 = make_float2(0.f, 0.f), sum1 = make_float2(0.f, 0.f);
+    for (int st = slot; st < strips; st += NSLOTS) {
       const int sy = st / strips_w, sx = st - sy * strips_w;
       const int oy0 = sy * 2, ox0 = sx * DT_TW;                 // within the band
+      const bool ok[2] = {c_ok, c_ok && oy0 + 1 < rows};        // an odd row count leaves the strip's second row outside
       // staged tile: row i <-> input row (band0 - 1 + i), column j <-> input column (j - 1)
-      const uint32_t base = tile + (static_cast<uint32_t>(oy0 * row_pitch + ox0 * p.cg + quad * 4) << 1);
+      uint32_t rowa[4];
+      rowa[0] = tile + oy0 * row_pitch + ox0 * (CG * 2);
+#pragma unroll
+      for (int i = 1; i < 4; ++i) rowa[i] = rowa[i - 1] + row_pitch;
+      uint16_t* outp[2];
+      outp[0] = out_item + oy0 * out_row + static_cast<size_t>(ox0) * p.out_ps;
+      outp[1] = outp[0] + out_row;
       float2 win[4][3][2];
-      auto lds4 = [&](int i, int j, float2 (&v)[2]) {
-        uint32_t lo, hi;
-        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(base + (static_cast<uint32_t>(i * row_pitch + j * p.cg) << 1)));
-        v[0] = make_float2(bf16_lo(lo), bf16_hi(lo));
-        v[1] = make_float2(bf16_lo(hi), bf16_hi(hi));
-      };
+#define DT_LDS(i, j, v)                                                                                              \
+  {                                                                                                                  \
+    uint32_t lo_, hi_;                                                                                               \
+    asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo_), "=r"(hi_) : "r"(rowa[i] + (j) * (CG * 2)));        \
+    v[0] = make_float2(bf16_lo(lo_), bf16_hi(lo_));                                                                  \
+    v[1] = make_float2(bf16_lo(hi_), bf16_hi(hi_));                                                                  \
+  }
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        lds4(i, 0, win[i][1]);
-        lds4(i, 1, win[i][2]);
+        DT_LDS(i, 0, win[i][1]);
+        DT_LDS(i, 1, win[i][2]);
       }
 #pragma unroll
       for (int j = 0; j < DT_TW; ++j) {
@@ -142,44 +153,55 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
         for (int i = 0; i < 4; ++i) {
           win[i][0][0] = win[i][1][0]; win[i][0][1] = win[i][1][1];
           win[i][1][0] = win[i][2][0]; win[i][1][1] = win[i][2][1];
-          lds4(i, j + 2, win[i][2]);
+          DT_LDS(i, j + 2, win[i][2]);
         }
 #pragma unroll
-        for (int r = 0; r < 2; ++r) {
-          if (oy0 + r >= rows || !c_ok) continue;
+        for (int rr = 0; rr < 2; ++rr) {
           float2 acc0 = b[0], acc1 = b[1];
 #pragma unroll
           for (int dr = 0; dr < 3; ++dr)
 #pragma unroll
             for (int q = 0; q < 3; ++q) {      // same (row, column) order on top of the bias as the strip kernel: bit-identical
-              acc0 = ffma2(win[r + dr][q][0], wt[dr * 3 + q][0], acc0);
-              acc1 = ffma2(win[r + dr][q][1], wt[dr * 3 + q][1], acc1);
+              acc0 = ffma2(win[rr + dr][q][0], wt[dr * 3 + q][0], acc0);
+              acc1 = ffma2(win[rr + dr][q][1], wt[dr * 3 + q][1], acc1);
             }
+          acc0 = apply_act2<ACT>(acc0);
+          acc1 = apply_act2<ACT>(acc1);
           uint2 o;
-          o.x = pack_bf16x2(apply_act(acc0.x, ACT), apply_act(acc0.y, ACT));
-          o.y = pack_bf16x2(apply_act(acc1.x, ACT), apply_act(acc1.y, ACT));
-          const int oy = band * p.band_h + oy0 + r;
-          *reinterpret_cast<uint2*>(p.out + ((static_cast<size_t>(n) * p.H + oy) * p.W + ox0 + j) * p.out_ps + c0) = o;
-          if (p.sums) { sum[0] += bf16_lo(o.x); sum[1] += bf16_hi(o.x); sum[2] += bf16_lo(o.y); sum[3] += bf16_hi(o.y); }
+          o.x = pack_bf16x2(acc0.x, acc0.y);
+          o.y = pack_bf16x2(acc1.x, acc1.y);
+          if (ok[rr]) {
+            *reinterpret_cast<uint2*>(outp[rr]) = o;
+            if (SQ) {     // sums of the ROUNDED outputs, as the squeeze of the stored tensor would see them
+              sum0 = fadd2(sum0, make_float2(bf16_lo(o.x), bf16_hi(o.x)));
+              sum1 = fadd2(sum1, make_float2(bf16_lo(o.y), bf16_hi(o.y)));
+            }
+          }
+          outp[rr] += p.out_ps;
         }
       }
+#undef DT_LDS
     }
     __syncwarp();
     if ((threadIdx.x & 31) == 0) mbar_arrive(smem_u32(&bar_empty[s]));      // this warp is done reading the tile
-    if (p.sums) {
-      // one band per image (checked by the host): every strip of (n, channel quad) is in this block
-      named_bar_sync(1, DT_COMPUTE);                                         // previous item's reduction has been read
-      *reinterpret_cast<float4*>(&red[threadIdx.x * 4]) = make_float4(sum[0], sum[1], sum[2], sum[3]);
+    if (SQ) {
+      // one band per image (checked by the host): every strip of (n, channel quad) is in this block.  red[] is double
+      // buffered by item parity: whoever writes red[it & 1] has passed the barrier of item it - 1, which the reducing
+      // threads reach only after they have read red[it & 1] for item it - 2.
+      float* const rd = red[it & 1];
+      *reinterpret_cast<float4*>(&rd[threadIdx.x * 4]) = make_float4(sum0.x, sum0.y, sum1.x, sum1.y);
       named_bar_sync(1, DT_COMPUTE);
       if (slot == 0 && c_ok) {
-        float4 t = *reinterpret_cast<float4*>(&red[quad * 4]);
-        for (int k = 1; k < nslots; ++k) {                                   // slot order = strip order: deterministic
-          const float4 v = *reinterpret_cast<float4*>(&red[(k * quads + quad) * 4]);
+        float4 t = *reinterpret_cast<float4*>(&rd[quad * 4]);
+#pragma unroll
+        for (int k = 1; k < NSLOTS; ++k) {                                   // slot order = strip order: deterministic
+          const float4 v = *reinterpret_cast<float4*>(&rd[(k * QUADS + quad) * 4]);
           t.x += v.x; t.y += v.y; t.z += v.z; t.w += v.w;
         }
         *reinterpret_cast<float4*>(p.sums + static_cast<size_t>(n) * p.C + c0) = t;
       }
     }
+    if (++r == per_group) { r = 0; ++g; }
   }
 }
 
@@ -218,18 +240,28 @@ int dwconv3x3_tile_squeeze_rows(int C, int H, int W, int stride) {
   return p.bands == 1 ? 1 : 0;
 }
 
-template <int ACT>
+template <int ACT, int CG, bool SQ>
 static int dw_tile_launch_t(const CUtensorMap& map, const DwTileParams& p, size_t smem, cudaStream_t stream) {
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(dwconv3x3_tile_kernel<ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, DT_SMEM_MAX));
+    B200_CUDA_OK(cudaFuncSetAttribute(dwconv3x3_tile_kernel<ACT, CG, SQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, DT_SMEM_MAX));
     configured[dev & 63] = true;
   }
   const int ctas = p.total_items < device_sm_count() ? p.total_items : device_sm_count();
-  B200_CUDA_OK(launch_pdl(dwconv3x3_tile_kernel<ACT>, dim3(ctas), dim3(DT_THREADS), smem, stream, map, p));
+  B200_CUDA_OK(launch_pdl(dwconv3x3_tile_kernel<ACT, CG, SQ>, dim3(ctas), dim3(DT_THREADS), smem, stream, map, p));
   return B200_OK;
+}
+
+template <int ACT>
+static int dw_tile_launch_a(const CUtensorMap& map, const DwTileParams& p, size_t smem, cudaStream_t stream) {
+  const bool sq = p.sums != nullptr;
+  switch (p.cg) {
+    case 64: return sq ? dw_tile_launch_t<ACT, 64, true>(map, p, smem, stream) : dw_tile_launch_t<ACT, 64, false>(map, p, smem, stream);
+    case 128: return sq ? dw_tile_launch_t<ACT, 128, true>(map, p, smem, stream) : dw_tile_launch_t<ACT, 128, false>(map, p, smem, stream);
+    default: return sq ? dw_tile_launch_t<ACT, 256, true>(map, p, smem, stream) : dw_tile_launch_t<ACT, 256, false>(map, p, smem, stream);
+  }
 }
 
 // returns B200_OK after launching, or 1 if this layer is not for the tile kernel (the caller falls back to the strip kernel)
@@ -255,9 +287,9 @@ int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const fl
     B200_TRY(encode_tmap(&map, in.base, 4, dims, str, box, SWZ_NONE));
   }
   const size_t smem = size_t(p.stages) * p.tile_bytes + size_t(in.W + 2) * p.cg * 2 + 256;   // + one row: odd row counts read past the tile
-  if (act == ACT_NONE) return dw_tile_launch_t<ACT_NONE>(map, p, smem, stream);
-  if (act == ACT_RELU) return dw_tile_launch_t<ACT_RELU>(map, p, smem, stream);
-  return dw_tile_launch_t<ACT_SILU>(map, p, smem, stream);
+  if (act == ACT_NONE) return dw_tile_launch_a<ACT_NONE>(map, p, smem, stream);
+  if (act == ACT_RELU) return dw_tile_launch_a<ACT_RELU>(map, p, smem, stream);
+  return dw_tile_launch_a<ACT_SILU>(map, p, smem, stream);
 }
 
 }  // namespace b200

@@ -269,6 +269,21 @@ enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_SILU = 2, ACT_SIGMOID = 3 };
 // SiLU / sigmoid for the conv epilogues.  Branch-free so the compiler can interleave columns; the default form
 // costs ONE special-function op per element (MUFU.TANH, relative error 2^-11, i.e. 8x below a bf16 half-ulp of the
 // stored result) instead of ex2 + rcp: the epilogue of a K=64 1x1 layer is special-function-unit bound otherwise.
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  float2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<uint64_t&>(d))
+      : "l"(reinterpret_cast<uint64_t&>(a)), "l"(reinterpret_cast<uint64_t&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  float2 d;
+  asm("add.rn.f32x2 %0, %1, %2;"
+      : "=l"(reinterpret_cast<uint64_t&>(d))
+      : "l"(reinterpret_cast<uint64_t&>(a)), "l"(reinterpret_cast<uint64_t&>(b)));
+  return d;
+}
+
 #ifndef B200_SILU_TANH
 #define B200_SILU_TANH 1
 #endif
@@ -291,6 +306,21 @@ __device__ __forceinline__ float sigmoid_f(float x) {
 #else
   return __fdividef(1.f, 1.f + __expf(-x));
 #endif
+}
+
+// two lanes at once; each lane's result is bit-identical to apply_act (same roundings: mul, tanh.approx, fma)
+template <int ACT>
+__device__ __forceinline__ float2 apply_act2(float2 x) {
+  if (ACT == ACT_RELU) return make_float2(fmaxf(x.x, 0.f), fmaxf(x.y, 0.f));
+#if B200_SILU_TANH
+  if (ACT == ACT_SILU) {
+    const float2 h = fmul2(x, make_float2(0.5f, 0.5f));
+    return ffma2(h, make_float2(tanh_approx(h.x), tanh_approx(h.y)), h);
+  }
+#else
+  if (ACT == ACT_SILU) return make_float2(silu_f(x.x), silu_f(x.y));
+#endif
+  return x;
 }
 
 __device__ __forceinline__ float apply_act(float x, int act) {
