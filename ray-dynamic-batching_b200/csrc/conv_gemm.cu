@@ -215,7 +215,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ 
 // ================================================================================================================
 static constexpr int PCONV_THREADS = 384;
 static constexpr int PCONV_THREADS_MAX = 512;   // + warps 12-15: A-operand scaler, launched only for layers with ConvSpec::a_scale
-static constexpr int HALO_THREADS = 384;   // warps 0-2: TMA / MMA / DMA, 4-7 and 8-11: two epilogue warpgroups
+static constexpr int HALO_WGS = 4;          // epilogue warpgroups = accumulators in TMEM = tiles in their epilogue at once
+static constexpr int HALO_THREADS = 128 + HALO_WGS * 128;   // warps 0-2: TMA / MMA / DMA, then one warpgroup per accumulator
 
 // Without a residual the staging ring only has to cover the store of the previous tile (2 buffers); the shared memory that
 // frees goes into a deeper A/B ring, which is what the HBM-bound layers need (bytes in flight per SM ~ latency x bandwidth).
@@ -603,14 +604,13 @@ static constexpr int HALO_ROWS = 18, HALO_PITCH_PX = 10;   // exactly the 18 x 1
 static constexpr int HALO_MAX_STAGES = 4;
 
 struct HaloCfg {
-  static constexpr int OUT_BUFS = 4;
-  static constexpr int LOOKAHEAD = 2;
+  static constexpr int MAX_OUT_BUFS = 8;    // staging buffers (4, 6 or 8: what fits); residual prefetch runs half of them ahead
   static constexpr int OUT_BYTES = BLOCK_M * 64 * 2;
   static constexpr int halo_bytes(int pb) { return HALO_ROWS * HALO_PITCH_PX * pb; }               // what TMA delivers
   static constexpr int halo_stride(int pb) { return (halo_bytes(pb) + 1023) / 1024 * 1024; }       // stage pitch
   static constexpr int w_bytes(int pb, int n) { return 9 * n * pb; }
-  static constexpr int smem_bytes(int pb, int n, int stages) {
-    return w_bytes(pb, n) + stages * halo_stride(pb) + OUT_BUFS * OUT_BYTES + 1024;
+  static constexpr int smem_bytes(int pb, int n, int stages, int out_bufs) {
+    return w_bytes(pb, n) + stages * halo_stride(pb) + out_bufs * OUT_BYTES + 1024;
   }
 };
 
@@ -633,8 +633,8 @@ __global__ void __launch_bounds__(HALO_THREADS, 1)
 conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant__ ConvParams p, const int total_tiles) {
   using Cfg = HaloCfg;
   constexpr int BLOCK_N = 64;          // accumulator stride in TMEM and bias buffer size; the tile's width is p.block_n
-  constexpr int NB = Cfg::OUT_BUFS;
-  constexpr int LA = Cfg::LOOKAHEAD;
+  constexpr int NACC = HALO_WGS;
+  const int NB = p.halo_out_bufs, LA = NB >> 1;
   const int N = p.block_n, HS = p.halo_stages;
   constexpr int halo_bytes = Cfg::halo_bytes(PB), halo_stride = Cfg::halo_stride(PB);
   const int tap_bytes = N * PB;
@@ -643,12 +643,12 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   __shared__ __align__(8) uint64_t bar_halo_full[HALO_MAX_STAGES];
   __shared__ __align__(8) uint64_t bar_halo_empty[HALO_MAX_STAGES];
   __shared__ __align__(8) uint64_t bar_w_full;
-  __shared__ __align__(8) uint64_t bar_tmem_full[2];
-  __shared__ __align__(8) uint64_t bar_tmem_empty[2];
-  __shared__ __align__(8) uint64_t bar_stage_ready[NB];
-  __shared__ __align__(8) uint64_t bar_out_ready[NB];
+  __shared__ __align__(8) uint64_t bar_tmem_full[NACC];
+  __shared__ __align__(8) uint64_t bar_tmem_empty[NACC];
+  __shared__ __align__(8) uint64_t bar_stage_ready[Cfg::MAX_OUT_BUFS];
+  __shared__ __align__(8) uint64_t bar_out_ready[Cfg::MAX_OUT_BUFS];
   __shared__ uint32_t tmem_base_s;
-  __shared__ __align__(16) float bias_s[2][BLOCK_N];
+  __shared__ __align__(16) float bias_s[NACC][BLOCK_N];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -668,7 +668,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       mbar_init(smem_u32(&bar_halo_full[b]), 1);
       mbar_init(smem_u32(&bar_halo_empty[b]), 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < NACC; ++b) {
       mbar_init(smem_u32(&bar_tmem_full[b]), 1);
       mbar_init(smem_u32(&bar_tmem_empty[b]), 128);
     }
@@ -679,7 +679,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
     }
     fence_barrier_init();
   } else if (warp == 1) {
-    tmem_alloc<2 * BLOCK_N>(smem_u32(&tmem_base_s));
+    tmem_alloc<NACC * BLOCK_N>(smem_u32(&tmem_base_s));
   }
   tc_fence_before();
   __syncthreads();
@@ -733,8 +733,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       const uint32_t wtap = static_cast<uint32_t>(tap_bytes) >> 4;
       mbar_wait(smem_u32(&bar_w_full), 0);
       for (int it = 0; it < my_tiles; ++it) {
-        const int b = it & 1, hb = it % HS;
-        mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it >> 1) & 1) ^ 1);
+        const int b = it % NACC, hb = it % HS;
+        mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it / NACC) & 1) ^ 1);
         mbar_wait(smem_u32(&bar_halo_full[hb]), (it / HS) & 1);
         tc_fence_after();
         const uint32_t acc = tmem_base + b * BLOCK_N;
@@ -789,11 +789,6 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       };
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
-        if (LA == 0) {
-          // no prefetch distance: staging[it % NB] was last read by the store of tile it - NB; stores issued so far: <= it - 1
-          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - 1) : "memory");
-          acquire_staging(it);
-        }
         // store of tile it, once its epilogue is done
         {
           const int tile0_ = blockIdx.x + it * gridDim.x;
@@ -811,11 +806,15 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
             tma_store_commit();
           }
         }
-        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
-        // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
+        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - NB / 2);
+        // stores issued so far are tiles <= it, so allowing the NB / 2 most recent groups to be pending is enough.
         const int j = it + LA;
-        if (LA > 0 && j < my_tiles) {
-          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+        if (j < my_tiles) {
+          if (elect_one()) {
+            if (LA == 2) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+            else if (LA == 3) asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory");
+          }
           acquire_staging(j);
         }
       }
@@ -824,8 +823,10 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
     __syncwarp();
   } else if (warp >= 4) {
     // =========================== epilogue ===========================
-    // Two warpgroups, one per accumulator: group g drains every second tile.  With N <= 64 the per-tile epilogue
-    // (TMEM load -> bias/residual/activation -> staging, ~2700 cycles of mostly latency) is longer than the tile's MMAs.
+    // HALO_WGS warpgroups, one per accumulator: group g drains tiles g, g + HALO_WGS, ...  A group is one warp per
+    // scheduler walking a dependent chain (TMEM load -> bias/residual/activation -> pack -> staging): ~1500-2700 cycles
+    // of mostly latency per tile, longer than a thin layer's MMAs.  Such layers are paced by how many of these chains run
+    // side by side, hence four groups and four accumulators.
     const int wg = (warp - 4) >> 2;
     const int epi_tid = (threadIdx.x - 128) & 127;  // 0..127 within the group
     const int quarter = warp & 3;
@@ -842,10 +843,10 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       }
       named_bar_sync(1 + wg, 128);
     }
-    for (int it = wg; it < my_tiles; it += 2) {
+    for (int it = wg; it < my_tiles; it += NACC) {
       const int b = wg;
       const int ob = it % NB;
-      mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
+      mbar_wait(smem_u32(&bar_tmem_full[b]), (it / NACC) & 1);
       tc_fence_after();
       mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
       const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
@@ -894,7 +895,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<2 * BLOCK_N>(tmem_base);
+    tmem_dealloc<NACC * BLOCK_N>(tmem_base);
   }
 }
 
@@ -1314,7 +1315,11 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     p.halo_s2 = s.stride == 2 ? 1 : 0;
     p.halo_ksteps = (in.C + 15) / 16;
     p.halo_stages = p.halo_s2 ? (p.pb == 64 ? 2 : 4) : (p.pb == 128 ? 3 : 4);
-    L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages * (p.halo_s2 ? 4 : 1));
+    p.halo_out_bufs = 8;       // as many staging buffers as fit next to the weights and the halo ring (216 KB in all)
+    while (p.halo_out_bufs > 4 &&
+           HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages * (p.halo_s2 ? 4 : 1), p.halo_out_bufs) > 216 * 1024)
+      p.halo_out_bufs -= 2;
+    L->halo_smem = HaloCfg::smem_bytes(p.pb, block_n, p.halo_stages * (p.halo_s2 ? 4 : 1), p.halo_out_bufs);
   }
   L->halo = halo;
   L->block_n = block_n;

@@ -37,6 +37,7 @@ struct ConvParams {
   int pb;                  // halo kernel: bytes per pixel of the staged halo (32 / 64 / 128 = swizzle span), K per tap = pb / 2
   int block_n;             // halo kernel: accumulator width (32 or 64)
   int halo_stages;         // halo kernel: halo boxes in flight (2 or 4)
+  int halo_out_bufs;       // halo kernel: output staging buffers (4, 6 or 8)
   int halo_ksteps;         // halo kernel: K16 steps per tap = ceil(Cin / 16) (<= PB / 32: a 48-channel layer skips the all-zero fourth)
   int halo_s2;             // halo kernel: stride 2 -- a stage holds the four parity planes of the input (18 x 10 each)
   int reverse;             // walk the tiles last-to-first (alternated layer by layer so a layer starts on what is still in L2)
