@@ -159,10 +159,153 @@ se_gate_kernel(const float* __restrict__ partial, int P, int C, float inv_hw, co
   }
 }
 
+// The same gate spread over clusters of 8 CTAs.  The one-block-per-image kernel above drags both weight matrices
+// (2 * S * C * 4 bytes, 786 KB at C = 1536) through every SM behind chains of dependent L2 round trips: 8-19 us a layer,
+// 30 layers.  Here CTA r of a cluster owns the channel slice [r * KS, (r + 1) * KS) of BOTH matrices, staged in shared
+// memory once, and the cluster walks over groups of 8 images:
+//   1. stage its slice of the group's sums (cp.async)
+//   2. partial fc1 over its slice: part[g][j]                                   (a split-K of fc1 over the cluster)
+//   3. cluster barrier; CTA r adds the 8 partials of image r in rank order through distributed shared memory
+//      (deterministic), applies bias + SiLU and writes the hidden units into every CTA's hid[][]; cluster barrier
+//   4. fc2 + sigmoid for its channel slice of the 8 images
+// Each CTA moves 2 * S * KS * 4 bytes of weights (98 KB at C = 1536) once, and up to 18 clusters share the images.
+constexpr int SEC_R = 8, SEC_G = 8, SEC_THREADS = 512, SEC_SMAX = 64, SEC_PAD = 4;
+__global__ void __cluster_dims__(SEC_R, 1, 1) __launch_bounds__(SEC_THREADS)
+se_gate_cluster_kernel(const float* __restrict__ partial, int N, int P, int C, float inv_hw, const float* __restrict__ w1,
+                       const float* __restrict__ b1, const float* __restrict__ w2t, const float* __restrict__ b2, int S,
+                       int KS, float* __restrict__ gate) {
+  pdl_wait();
+  extern __shared__ __align__(16) float sec_smem[];   // xs[8][KS + 4], w1s[S][KS + 4], w2s[S][KS], part[8][64], hid[8][64]
+  const int ld = KS + SEC_PAD;
+  float* xs = sec_smem;
+  float* w1s = xs + SEC_G * ld;
+  float* w2s = w1s + S * ld;
+  float* part = w2s + S * KS;
+  float* hid = part + SEC_G * SEC_SMAX;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster = blockIdx.x / SEC_R, clusters = gridDim.x / SEC_R;
+  const int k0 = rank * KS;
+  const int kw = max(0, min(KS, C - k0));             // channels of this slice (multiple of 4; 0 for a surplus CTA)
+  const int Q = KS >> 2, qw = kw >> 2;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  auto copy16 = [](float* dst, const float* src, bool ok) {   // !ok: no bytes are read, the 16 bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(ok ? 16 : 0) : "memory");
+  };
+  for (int r = warp; r < 2 * S; r += SEC_THREADS / 32) {       // the two weight slices: once per CTA
+    const bool first = r < S;
+    const float* src = (first ? w1 + static_cast<size_t>(r) * C : w2t + static_cast<size_t>(r - S) * C) + k0;
+    float* dst = first ? w1s + r * ld : w2s + (r - S) * KS;
+    for (int q = lane; q < Q; q += 32) copy16(dst + q * 4, q < qw ? src + q * 4 : w1, q < qw);
+  }
+  const int groups = (N + SEC_G - 1) / SEC_G;
+  for (int grp = cluster; grp < groups; grp += clusters) {
+    const int g0 = grp * SEC_G;
+    // ---- 1. this group's sums (row 0 of every image; further rows are added below)
+    if (warp < SEC_G) {
+      const bool img = g0 + warp < N;
+      const float* src = partial + static_cast<size_t>(img ? g0 + warp : 0) * P * C + k0;
+      for (int q = lane; q < Q; q += 32) copy16(xs + warp * ld + q * 4, q < qw ? src + q * 4 : partial, img && q < qw);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (P > 1) {                                       // the depthwise kernel left one row of sums per strip: add them in order
+      if (warp < SEC_G && g0 + warp < N) {
+        for (int q = lane; q < qw; q += 32) {
+          float4 v = *reinterpret_cast<float4*>(xs + warp * ld + q * 4);
+          for (int p = 1; p < P; ++p) {
+            const float4 u = *reinterpret_cast<const float4*>(partial + (static_cast<size_t>(g0 + warp) * P + p) * C + k0 + q * 4);
+            v.x += u.x; v.y += u.y; v.z += u.z; v.w += u.w;
+          }
+          *reinterpret_cast<float4*>(xs + warp * ld + q * 4) = v;
+        }
+      }
+      __syncthreads();
+    }
+    // ---- 2. partial fc1: thread = (image g, unit j); a warp shares g (its x loads are broadcasts), rows of w1s are
+    //         KS + 4 floats apart, so the 8 lanes of a 16-byte phase hit 8 different bank quads
+    {
+      const int g = threadIdx.x >> 6, jj = threadIdx.x & 63;
+      float acc = 0.f;
+      if (jj < S) {
+        const float* xr = xs + g * ld;
+        const float* wr = w1s + jj * ld;
+#pragma unroll 4
+        for (int q = 0; q < qw; ++q) {
+          const float4 a = *reinterpret_cast<const float4*>(xr + q * 4);
+          const float4 u = *reinterpret_cast<const float4*>(wr + q * 4);
+          acc = fmaf(a.x, u.x, acc); acc = fmaf(a.y, u.y, acc); acc = fmaf(a.z, u.z, acc); acc = fmaf(a.w, u.w, acc);
+        }
+      }
+      part[g * SEC_SMAX + jj] = acc;
+    }
+    cluster_sync_all();
+    // ---- 3. CTA r: the 8 partials of image r (rank order), bias + SiLU, broadcast to every CTA's hid[][]
+    if (threadIdx.x < SEC_SMAX && threadIdx.x < S) {
+      const int jj = threadIdx.x;
+      const uint32_t pa = smem_u32(part + rank * SEC_SMAX + jj);
+      float v = 0.f;
+#pragma unroll
+      for (uint32_t r = 0; r < SEC_R; ++r) v += ld_cluster_f32(cluster_map(pa, r));
+      const float z = v * inv_hw + b1[jj];
+      const float h = z / (1.f + expf(-z));
+      const uint32_t ha = smem_u32(hid + rank * SEC_SMAX + jj);
+#pragma unroll
+      for (uint32_t r = 0; r < SEC_R; ++r) st_cluster_f32(cluster_map(ha, r), h);
+    }
+    cluster_sync_all();
+    // ---- 4. fc2 + sigmoid: thread = (channel quad, image), hidden units broadcast from shared memory
+    for (int item = threadIdx.x; item < qw * SEC_G; item += SEC_THREADS) {
+      const int g = item / qw, q = item - g * qw;
+      if (g0 + g >= N) continue;
+      float4 a = *reinterpret_cast<const float4*>(b2 + k0 + q * 4);
+      const float* hr = hid + g * SEC_SMAX;
+#pragma unroll 8
+      for (int jj = 0; jj < S; ++jj) {
+        const float4 wv = *reinterpret_cast<const float4*>(w2s + jj * KS + q * 4);
+        const float h0 = hr[jj];
+        a.x = fmaf(h0, wv.x, a.x); a.y = fmaf(h0, wv.y, a.y); a.z = fmaf(h0, wv.z, a.z); a.w = fmaf(h0, wv.w, a.w);
+      }
+      float4 o;
+      o.x = 1.f / (1.f + expf(-a.x)); o.y = 1.f / (1.f + expf(-a.y)); o.z = 1.f / (1.f + expf(-a.z)); o.w = 1.f / (1.f + expf(-a.w));
+      *reinterpret_cast<float4*>(gate + static_cast<size_t>(g0 + g) * C + k0 + q * 4) = o;
+    }
+    // the next group's part[] / hid[] writes are ordered behind this group's reads by the two cluster barriers: a CTA
+    // writes part[] only after its own step 4, and hid[] only after every CTA has passed the first barrier of the next group
+    __syncthreads();                                   // xs is restaged next
+  }
+}
+
+static bool se_cluster_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_SE_CLUSTER");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 int se_gate_launch(const float* partial, int n, int strips, int c, float inv_hw, const float* w1, const float* b1,
                    const float* w2t, const float* b2, int s, float* gate, cudaStream_t stream) {
   if (n <= 0 || strips <= 0 || c <= 0 || s <= 0) return fail(B200_ERR_INVALID, "se_gate: empty shape");
   if (c % 4) return fail(B200_ERR_INVALID, "se_gate: channels must be a multiple of 4");
+  if (se_cluster_enabled() && s <= SEC_SMAX) {
+    const int ks = (c + 4 * SEC_R - 1) / (4 * SEC_R) * 4;
+    const size_t smem = sizeof(float) * (static_cast<size_t>(SEC_G + s) * (ks + SEC_PAD) + static_cast<size_t>(s) * ks + 2 * SEC_G * SEC_SMAX);
+    if (smem <= 200 * 1024) {
+      static bool configured[64] = {};
+      int dev = 0;
+      B200_CUDA_OK(cudaGetDevice(&dev));
+      if (!configured[dev & 63]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(se_gate_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured[dev & 63] = true;
+      }
+      const int groups = (n + SEC_G - 1) / SEC_G, max_clusters = device_sm_count() / SEC_R;
+      const int clusters = groups < max_clusters ? groups : max_clusters;
+      B200_CUDA_OK(launch_pdl(se_gate_cluster_kernel, dim3(clusters * SEC_R), dim3(SEC_THREADS), size_t(smem), stream, partial, n, strips, c, inv_hw, w1, b1, w2t, b2, s, ks, gate));
+      return B200_OK;
+    }
+  }
   int js = SE_THREADS / (c / 4);
   js = js < 1 ? 1 : (js > 8 ? 8 : js);
   if (js > s) js = s;
