@@ -143,11 +143,11 @@ class PlanBuilder:
         self.tensor_core_stem = True
         self.toeplitz_stem = True
         self.fuse_stem_pool = os.environ.get('B200_FUSE_STEM_POOL', '1') != '0'   # conv1 + bn1 + relu + maxpool in one kernel
-        self.gather_small_cin = True
+        self.gather_small_cin = os.environ.get('B200_GATHER_SMALL_CIN', '1') != '0'   # 3x3 convs with Cin <= 56 the halo kernel does not take: packed-K gather kernel
         self.fuse_downsample = os.environ.get('B200_FUSE_DOWNSAMPLE', '1') != '0'   # ResNet conv3 + downsample as one GEMM
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
         self.halo_stride2 = os.environ.get('B200_CONV_HALO_S2', '1') != '0'      # 3x3/s2 with Cin <= 32 too (parity planes)
-        self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '56'))
+        self.gather_1x1_max_cin = int(__import__('os').environ.get('B200_GATHER_1X1_MAX_CIN', '0'))
 
     # ---- buffers / weights ----
     def new_buf(self, h, w, c, dtype=0):
