@@ -79,4 +79,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   return launch_pdl_if(false, kern, grid, block, smem, stream, static_cast<Args&&>(args)...);
 }
 
+// multiplier for fast_div (ptx.cuh): floor(2^32 / d) + 1; unused for d < 2
+inline unsigned fast_div_mul(int d) { return d < 2 ? 0u : static_cast<unsigned>((1ull << 32) / static_cast<unsigned>(d)) + 1u; }
+
 }  // namespace b200

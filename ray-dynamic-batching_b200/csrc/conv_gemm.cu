@@ -247,7 +247,7 @@ __device__ __forceinline__ void kb_source(const ConvParams& p, int kb, int& t, i
     cw = kb * BLOCK_K;
     tw = 0;
   } else {
-    t = kb / p.kb_per_tap;
+    t = fast_div(kb, p.kb_per_tap, p.mul_kb_per_tap);
     c0 = (kb - t * p.kb_per_tap) * BLOCK_K;
     cw = c0;
     tw = t;
@@ -255,12 +255,12 @@ __device__ __forceinline__ void kb_source(const ConvParams& p, int kb, int& t, i
 }
 
 __device__ __forceinline__ void tile_coords(const ConvParams& p, int tile, int& n_tile, int& w0, int& h0, int& nb0) {
-  n_tile = tile % p.n_tiles;
-  int m = tile / p.n_tiles;
-  const int t_w = m % p.tiles_w;
-  m /= p.tiles_w;
-  const int t_h = m % p.tiles_h;
-  const int t_n = m / p.tiles_h;
+  const int m = fast_div(tile, p.n_tiles, p.mul_n_tiles);
+  n_tile = tile - m * p.n_tiles;
+  const int mw = fast_div(m, p.tiles_w, p.mul_tiles_w);
+  const int t_w = m - mw * p.tiles_w;
+  const int t_n = fast_div(mw, p.tiles_h, p.mul_tiles_h);
+  const int t_h = mw - t_n * p.tiles_h;
   w0 = t_w * p.tw; h0 = t_h * p.th; nb0 = t_n * p.tn;
 }
 
@@ -524,7 +524,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       const int b = it & 1;
       const int bb = wg;
       const int ob = it % NB;
-      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      const int n0 = (tile - static_cast<int>(fast_div(tile, p.n_tiles, p.mul_n_tiles)) * p.n_tiles) * BLOCK_N;
       named_bar_sync(1 + wg, 128);               // every thread of the group is done reading the previous tile's bias
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
         const int c = n0 + i;
@@ -700,19 +700,23 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
           for (int t = 0; t < 9; ++t) tma_load_3d(&maps.b, smem_u32(&bar_w_full), wres + t * tap_bytes, 0, t, n0);
         }
       }
+      // ring positions are running counters (stage, phase): HS and NB are run-time values, and a division per tile in a
+      // warp that runs alone costs more than the TMA it is about to issue
+      int hb = 0;
+      uint32_t hph = 0;
       for (int it = 0; it < my_tiles; ++it) {
         const int tile0_ = blockIdx.x + it * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
         int n_tile, w0, h0, nb0;
         tile_coords(p, tile, n_tile, w0, h0, nb0);
-        const int hb = it % HS;
-        mbar_wait(smem_u32(&bar_halo_empty[hb]), ((it / HS) & 1) ^ 1);
+        mbar_wait(smem_u32(&bar_halo_empty[hb]), hph ^ 1);
         const uint32_t full = smem_u32(&bar_halo_full[hb]);
         if (elect_one()) {
           mbar_expect_tx(full, planes * halo_bytes);
           for (int pl = 0; pl < planes; ++pl)     // box [PB/2, 10, 18, 1] of the input (stride 1) or of each parity plane
             tma_load_4d(&maps.a[pl], full, halo + hb * stage_bytes + pl * halo_stride, 0, w0 - 1, h0 - 1, nb0);
         }
+        if (++hb == HS) { hb = 0; hph ^= 1; }
       }
     }
     __syncwarp();
@@ -732,10 +736,12 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       const uint32_t a_lo0 = static_cast<uint32_t>(adesc0), b_lo0 = static_cast<uint32_t>(bdesc0);
       const uint32_t wtap = static_cast<uint32_t>(tap_bytes) >> 4;
       mbar_wait(smem_u32(&bar_w_full), 0);
+      int hb = 0;
+      uint32_t hph = 0;
       for (int it = 0; it < my_tiles; ++it) {
-        const int b = it % NACC, hb = it % HS;
+        const int b = it % NACC;
         mbar_wait(smem_u32(&bar_tmem_empty[b]), ((it / NACC) & 1) ^ 1);
-        mbar_wait(smem_u32(&bar_halo_full[hb]), (it / HS) & 1);
+        mbar_wait(smem_u32(&bar_halo_full[hb]), hph);
         tc_fence_after();
         const uint32_t acc = tmem_base + b * BLOCK_N;
         const uint32_t a_lo = a_lo0 + hb * (stage_bytes >> 4);   // no carry out of the 14-bit address field: smem < 256 KB
@@ -762,6 +768,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
           umma_commit(smem_u32(&bar_tmem_full[b]));
         }
         __syncwarp();
+        if (++hb == HS) { hb = 0; hph ^= 1; }
       }
     }
   } else if (warp == 2) {
@@ -769,10 +776,10 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
     {
       // whole warp in the loops, single-thread work under elect_one() (always the same lane, so the bulk-group
       // bookkeeping of the TMA stores stays with one thread)
-      auto acquire_staging = [&](int j) {  // make staging[j % NB] available to the epilogue of tile j
+      auto acquire_staging = [&](int j, int jb) {  // make staging[jb = j % NB] available to the epilogue of tile j
         const int tile0_ = blockIdx.x + j * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
-        const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
+        const uint32_t rdy = smem_u32(&bar_stage_ready[jb]);
         if (RES) {
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
@@ -780,14 +787,16 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
             mbar_expect_tx(rdy, Cfg::OUT_BYTES);
 #pragma unroll
             for (int q = 0; q < BLOCK_N / 64; ++q)
-              tma_load_4d(&maps.r, rdy, staging + (j % NB) * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * N + q * 64,
+              tma_load_4d(&maps.r, rdy, staging + jb * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n_tile * N + q * 64,
                           w0, h0, nb0);
           }
         } else {
           if (elect_one()) mbar_arrive(rdy);
         }
       };
-      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
+      for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j, j);
+      int ob = 0;
+      uint32_t oph = 0;
       for (int it = 0; it < my_tiles; ++it) {
         // store of tile it, once its epilogue is done
         {
@@ -796,8 +805,7 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
           const int n0 = n_tile * N;
-          const int ob = it % NB;
-          mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
+          mbar_wait(smem_u32(&bar_out_ready[ob]), oph);
           if (elect_one()) {
 #pragma unroll
             for (int q = 0; q < BLOCK_N / 64; ++q)
@@ -815,8 +823,9 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
             else if (LA == 3) asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
             else asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory");
           }
-          acquire_staging(j);
+          acquire_staging(j, ob + LA >= NB ? ob + LA - NB : ob + LA);
         }
+        if (++ob == NB) { ob = 0; oph ^= 1; }
       }
       if (elect_one()) tma_store_wait_all();
     }
@@ -843,12 +852,13 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       }
       named_bar_sync(1 + wg, 128);
     }
+    int ob = wg;                  // = it % NB (NB >= NACC), advanced by NACC per tile of this group
+    uint32_t oph = 0;             // = (it / NB) & 1
     for (int it = wg; it < my_tiles; it += NACC) {
       const int b = wg;
-      const int ob = it % NB;
       mbar_wait(smem_u32(&bar_tmem_full[b]), (it / NACC) & 1);
       tc_fence_after();
-      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
+      mbar_wait(smem_u32(&bar_stage_ready[ob]), oph);
       const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
       const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
@@ -889,6 +899,8 @@ conv3x3_halo_kernel(const __grid_constant__ ConvMaps maps, const __grid_constant
       mbar_arrive(smem_u32(&bar_tmem_empty[b]));   // accumulator may be overwritten by tile it+2
       fence_proxy_async_smem();                    // staging writes -> visible to the TMA store
       mbar_arrive(smem_u32(&bar_out_ready[ob]));
+      ob += NACC;
+      if (ob >= NB) { ob -= NB; oph ^= 1; }
     }
   }
 
@@ -960,13 +972,14 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
   auto my_coords = [&](int it, int& n0, int& w0, int& h0, int& nb0) {
     const int pt0 = pair + it * num_pairs;
     const int pt = (p.reverse & 1) ? total_pair_tiles - 1 - pt0 : pt0;
-    const int n_tile = pt % p.n_tiles;
-    int m = (pt / p.n_tiles) * 2 + static_cast<int>(rank);
+    const int pm = fast_div(pt, p.n_tiles, p.mul_n_tiles);
+    const int n_tile = pt - pm * p.n_tiles;
+    int m = pm * 2 + static_cast<int>(rank);
     if (m >= m_tiles) m = m_tiles;            // phantom tile of an odd tail: coordinates past the tensor (TMA clips)
-    const int t_w = m % p.tiles_w;
-    m /= p.tiles_w;
-    const int t_h = m % p.tiles_h;
-    const int t_n = m / p.tiles_h;
+    const int mw = fast_div(m, p.tiles_w, p.mul_tiles_w);
+    const int t_w = m - mw * p.tiles_w;
+    const int t_n = fast_div(mw, p.tiles_h, p.mul_tiles_h);
+    const int t_h = mw - t_n * p.tiles_h;
     w0 = t_w * p.tw; h0 = t_h * p.th; nb0 = t_n * p.tn;
     n0 = n_tile * BLOCK_N;
   };
@@ -1118,7 +1131,8 @@ conv_gemm_2cta_kernel(const __grid_constant__ ConvMaps maps, const __grid_consta
     for (int it = 0; it < my_tiles && h < SUBS; ++it) {
       const int b = it & 1;
       const int pt0_ = pair + it * num_pairs;
-      const int n0 = (((p.reverse & 1) ? total_pair_tiles - 1 - pt0_ : pt0_) % p.n_tiles) * BLOCK_N;
+      const int ptn_ = (p.reverse & 1) ? total_pair_tiles - 1 - pt0_ : pt0_;
+      const int n0 = (ptn_ - static_cast<int>(fast_div(ptn_, p.n_tiles, p.mul_n_tiles)) * p.n_tiles) * BLOCK_N;
       for (int i = epi_tid; i < SUB_N; i += 128) {
         const int c = n0 + h * SUB_N + i;
         bias_s[b % NBIAS][h * SUB_N + i] = (c < p.cout) ? p.bias[c] : 0.f;
@@ -1397,6 +1411,10 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   p.tiles_w = (oW + p.tw - 1) / p.tw;
   p.tiles_h = (oH + p.th - 1) / p.th;
   p.tiles_n = (oN + p.tn - 1) / p.tn;
+  p.mul_n_tiles = fast_div_mul(p.n_tiles);
+  p.mul_tiles_w = fast_div_mul(p.tiles_w);
+  p.mul_tiles_h = fast_div_mul(p.tiles_h);
+  p.mul_kb_per_tap = fast_div_mul(p.kb_per_tap);
 
   // output (+ residual) maps share the tile geometry
   {

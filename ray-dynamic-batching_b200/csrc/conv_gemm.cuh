@@ -30,6 +30,7 @@ struct ConvParams {
   int tiles_w, tiles_h, tiles_n;  // M-tile grid (pixels)
   int tw, th, tn;                 // pixels per tile along W, H, N  (tw*th*tn == 128)
   int n_tiles;                    // tiles along Cout
+  unsigned mul_n_tiles, mul_tiles_w, mul_tiles_h, mul_kb_per_tap;   // fast_div multipliers of the four divisors above
   int num_taps, kb_per_tap;
   int num_kb;                     // k-blocks per tile (num_taps * kb_per_tap, or both inputs' blocks of a K-concatenated conv)
   int kb_split;                   // K-concatenated conv: k-blocks [0, kb_split) come from input 0, the rest from input 1; 0 = off

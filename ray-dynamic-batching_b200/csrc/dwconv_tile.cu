@@ -37,6 +37,7 @@ struct DwTileParams {
   int stages;
   int tile_bytes;        // (band_h + 2) * (W + 2) * cg * 2
   int total_items;       // N * bands * groups
+  unsigned mul_strips_w; // fast_div multiplier of W / 7
 };
 
 template <int ACT, int CG, bool SQ>
@@ -69,17 +70,20 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
   if (warp == DT_COMPUTE / 32) {
     // =========================== TMA producer ===========================
     int g = item0 / per_group, r = item0 - g * per_group;
+    int n = r / p.bands, band = r - n * p.bands;       // running (group, image, band) and ring (stage, phase) counters:
+    int s = 0;                                         // no division per item in a warp that runs alone
+    uint32_t ph = 0;
     for (int it = 0; it < my_items; ++it) {
-      const int n = r / p.bands, band = r - n * p.bands;
-      const int s = it % p.stages;
-      mbar_wait(smem_u32(&bar_empty[s]), ((it / p.stages) & 1) ^ 1);
+      mbar_wait(smem_u32(&bar_empty[s]), ph ^ 1);
       if (elect_one()) {
         const uint32_t full = smem_u32(&bar_full[s]);
         mbar_expect_tx(full, p.tile_bytes);
         // box [CG, W + 2, band_h + 2, 1] at (g * CG, -1, band * band_h - 1, n): outside the image -> zeros
         tma_load_4d(&in_map, full, ring + s * p.tile_bytes, g * CG, -1, band * p.band_h - 1, n);
       }
-      if (++r == per_group) { r = 0; ++g; }
+      if (++s == p.stages) { s = 0; ph ^= 1; }
+      if (++band == p.bands) { band = 0; ++n; }
+      if (++r == per_group) { r = 0; n = 0; ++g; }
     }
     __syncwarp();
     return;
@@ -99,10 +103,12 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
   const size_t out_row = static_cast<size_t>(p.W) * p.out_ps;              // elements per output row
   float2 wt[9][2], b[2];
   int g = item0 / per_group, r = item0 - g * per_group;
+  int n = r / p.bands, band = r - n * p.bands;
+  int s = 0;
+  uint32_t ph = 0;
   int g_loaded = -1;
+  const uint32_t mul_strips_w = p.mul_strips_w;
   for (int it = 0; it < my_items; ++it) {
-    const int n = r / p.bands, band = r - n * p.bands;
-    const int s = it % p.stages;
     const int c0 = g * CG + quad * 4;
     const bool c_ok = c0 < p.C;                 // the last group of a ragged channel count
     if (g != g_loaded) {
@@ -118,12 +124,12 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
     }
     const int rows = min(p.band_h, p.H - band * p.band_h);      // output rows of this item
     const int strips = ((rows + 1) >> 1) * strips_w;
-    mbar_wait(smem_u32(&bar_full[s]), (it / p.stages) & 1);
+    mbar_wait(smem_u32(&bar_full[s]), ph);
     const uint32_t tile = ring + s * p.tile_bytes + quad * 8;
     uint16_t* const out_item = p.out + (static_cast<size_t>(n) * p.H + band * p.band_h) * out_row + c0;
     float2 sum0 = make_float2(0.f, 0.f), sum1 = make_float2(0.f, 0.f);
     for (int st = slot; st < strips; st += NSLOTS) {
-      const int sy = st / strips_w, sx = st - sy * strips_w;
+      const int sy = fast_div(st, strips_w, mul_strips_w), sx = st - sy * strips_w;
       const int oy0 = sy * 2, ox0 = sx * DT_TW;                 // within the band
       const bool ok[2] = {c_ok, c_ok && oy0 + 1 < rows};        // an odd row count leaves the strip's second row outside
       // staged tile: row i <-> input row (band0 - 1 + i), column j <-> input column (j - 1)
@@ -201,7 +207,9 @@ dwconv3x3_tile_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_c
         *reinterpret_cast<float4*>(p.sums + static_cast<size_t>(n) * p.C + c0) = t;
       }
     }
-    if (++r == per_group) { r = 0; ++g; }
+    if (++s == p.stages) { s = 0; ph ^= 1; }
+    if (++band == p.bands) { band = 0; ++n; }
+    if (++r == per_group) { r = 0; n = 0; ++g; }
   }
 }
 
@@ -278,6 +286,7 @@ int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const fl
   p.out_ps = out.pix_stride;
   p.C = out.C; p.H = out.H; p.W = out.W; p.N = out.N;
   p.total_items = out.N * p.bands * p.groups;
+  p.mul_strips_w = fast_div_mul(out.W / DT_TW);
   CUtensorMap map;
   {
     const uint64_t ips = uint64_t(in.pix_stride) * 2;

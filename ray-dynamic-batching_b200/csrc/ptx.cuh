@@ -171,6 +171,16 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
   return r;
 }
+// n / d for n < 2^31 without the ~25-instruction division sequence (I2F, MUFU.RCP, F2I, fix-ups: 150-250 cycles when one
+// warp walks it alone, which is what the single-warp TMA producers of the persistent kernels do once or more per tile).
+// mul = floor(2^32 / d) + 1 (fast_div_mul on the host, d >= 2); the estimate is exact or one too large.
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, uint32_t d, uint32_t mul) {
+  if (d == 1) return n;
+  uint32_t q = __umulhi(n, mul);
+  if (q * d > n) --q;
+  return q;
+}
+
 // distributed shared memory: address of the same shared-memory location in CTA `rank` of this cluster
 __device__ __forceinline__ uint32_t cluster_map(uint32_t smem_addr, uint32_t rank) {
   uint32_t r;

@@ -19,8 +19,8 @@
 namespace b200 {
 
 static constexpr int SR_THREADS = 256;
-static constexpr int SR2_THREADS = 384;   // stem_row_kernel: two epilogue warpgroups (warps 4-7 and 8-11)
-static constexpr int SR_STAGES = 4;
+static constexpr int SR_WGS = 4;          // stem_row_kernel: epilogue warpgroups = accumulators in TMEM
+static constexpr int SR2_THREADS = 128 + SR_WGS * 128;
 // An input row is staged as 18 groups of 16 pixels (128 B each): TMA moves whole 128-byte lines (a box with a 16-byte inner
 // dimension costs 8x more TMA work).  The box starts 16 pixels left of the tile's first *output* pixel pair, i.e. 12 pixels
 // (96 B) before the first window, so descriptors start at +96.
@@ -34,6 +34,10 @@ static constexpr int SR_OUT_BYTES = 128 * 128;       // one staged output tile (
 template <int KS, int NOUT_>
 struct StemCfg {
   static constexpr int KR = KS;                       // kernel rows = input rows per output row
+  // input boxes in flight.  A 3x3 stem's box is 6.9 KB: four of them per SM are 4 MB over the GPU, and with ~1.5 us of loaded
+  // latency that caps the input stream at ~2.7 TB/s (ncu: the epilogue groups wait for accumulators, the tensor pipe is 6 %
+  // busy) -> ten.  A 7x7 stem's box is 16 KB and the kernel is paced by its 14 MMAs per row -> four.
+  static constexpr int STAGES = KS == 3 ? 10 : 4;
   static constexpr int PAD = KS / 2;
   static constexpr int KC = (KS + 2) / 2 & ~1;        // 7 -> 4 chunks (8 pixels), 3 -> 2 chunks (4 pixels)
   static constexpr int MMAS = KC / 2;                 // K = 16 (two chunks) per MMA
@@ -59,6 +63,7 @@ struct StemRowParams {
   const float* bias;     // [64]
   int Ho, Wo, segs;      // segs = ceil(Wo / 128)
   int total_tiles;       // N * Ho * segs
+  unsigned mul_segs, mul_Ho;   // fast_div multipliers
 };
 
 template <int KS, int NOUT, int ACT>
@@ -68,14 +73,14 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   using G = StemCfg<KS, NOUT>;
   constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[SR_WGS], bar_t_empty[SR_WGS];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[64];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring = base;
-  const uint32_t wsm = ring + SR_STAGES * SR_STAGE_BYTES + 256;   // +256: rows m >= 112 of the last kernel row read past it
+  const uint32_t wsm = ring + G::STAGES * SR_STAGE_BYTES + 256;   // +256: rows m >= 112 of the last kernel row read past it
   const uint32_t stage_out = (wsm + SR_W_BYTES + 1023u) & ~1023u;
   const int per_cta = (p.total_tiles + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
   const int tile0 = static_cast<int>(blockIdx.x) * per_cta;
@@ -90,17 +95,17 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&in_map);
     tma_prefetch_desc(&out_map);
-    for (int s = 0; s < SR_STAGES; ++s) {
+    for (int s = 0; s < G::STAGES; ++s) {
       mbar_init(smem_u32(&bar_full[s]), 1);
       mbar_init(smem_u32(&bar_empty[s]), 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < SR_WGS; ++b) {
       mbar_init(smem_u32(&bar_t_full[b]), 1);
       mbar_init(smem_u32(&bar_t_empty[b]), 128);
     }
     fence_barrier_init();
   } else if (warp == 1) {
-    tmem_alloc<G::TMEM_COLS>(smem_u32(&tmem_base_s));
+    tmem_alloc<SR_WGS * NOUT>(smem_u32(&tmem_base_s));
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -112,9 +117,9 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
 
   auto tile_coords = [&](int it, int& n_oh, int& oh, int& ow0) {
     const int t = tile0 + it;
-    const int seg = t % p.segs;
-    n_oh = t / p.segs;               // = n * Ho + oh
-    oh = n_oh % p.Ho;
+    n_oh = fast_div(t, p.segs, p.mul_segs);               // = n * Ho + oh
+    const int seg = t - n_oh * p.segs;
+    oh = n_oh - static_cast<int>(fast_div(n_oh, p.Ho, p.mul_Ho)) * p.Ho;
     ow0 = seg * 128;
   };
 
@@ -123,13 +128,13 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     for (int it = 0; it < my_tiles; ++it) {
       int n_oh, oh, ow0;
       tile_coords(it, n_oh, oh, ow0);
-      const int s = it % SR_STAGES;
-      mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
+      const int s = it % G::STAGES;
+      mbar_wait(smem_u32(&bar_empty[s]), ((it / G::STAGES) & 1) ^ 1);
       const uint32_t full = smem_u32(&bar_full[s]);
       if (elect_one()) {
         mbar_expect_tx(full, G::KR * SR_ROW_BYTES);
         // box [64 (16 pixels), 18 groups, 7 rows, 1 image] at (0, ow0/8 - 1, 2*oh - 3, n); outside the image -> zeros
-        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - G::PAD, n_oh / p.Ho);
+        tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, ow0 / 8 - 1, 2 * oh - G::PAD, fast_div(n_oh, p.Ho, p.mul_Ho));
       }
     }
     __syncwarp();
@@ -137,9 +142,9 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
       for (int it = 0; it < my_tiles; ++it) {
-        const int b = it & 1, s = it % SR_STAGES;
-        mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
-        mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
+        const int b = it % SR_WGS, s = it % G::STAGES;
+        mbar_wait(smem_u32(&bar_t_empty[b]), ((it / SR_WGS) & 1) ^ 1);
+        mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
         tc_fence_after();
         const uint32_t a0 = ring + s * SR_STAGE_BYTES;
         if (elect_one()) {
@@ -160,20 +165,20 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
     }
     __syncwarp();
   } else if (warp >= 4) {
-    // two epilogue warpgroups: group g drains accumulator g of every second tile, so the per-tile latency chain
-    // (TMEM load -> convert -> smem -> store) of one tile overlaps the next tile's
-    const int wg = (warp - 4) >> 2;              // 0 or 1
+    // SR_WGS epilogue warpgroups: group g drains accumulator g of every SR_WGS-th tile, so the per-tile latency chains
+    // (TMEM load -> convert -> smem -> store, one warp per scheduler) of SR_WGS tiles overlap
+    const int wg = (warp - 4) >> 2;              // 0 .. SR_WGS - 1
     const int epi_tid = (threadIdx.x - 128) & 127;
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const int sw = row & 7;
-    for (int it = wg; it < my_tiles; it += 2) {
+    for (int it = wg; it < my_tiles; it += SR_WGS) {
       const int b = wg;
       int n_oh, oh, ow0;
       tile_coords(it, n_oh, oh, ow0);
       if (epi_tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // this group's previous store has read staging[b]
       named_bar_sync(1 + 2 * wg, 128);
-      mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
+      mbar_wait(smem_u32(&bar_t_full[b]), (it / SR_WGS) & 1);
       tc_fence_after();
       const uint32_t dst_row = stage_out + b * SR_OUT_BYTES + row * 128;
       const uint32_t acc = tmem_base + b * NOUT + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -213,7 +218,7 @@ stem_row_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constan
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<G::TMEM_COLS>(tmem_base);
+    tmem_dealloc<SR_WGS * NOUT>(tmem_base);
   }
 }
 
@@ -252,7 +257,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   using G = StemCfg<KS, NOUT>;
   constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[SR_STAGES], bar_empty[SR_STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[2], bar_t_empty[2];
   __shared__ __align__(8) uint64_t bar_row_ready[SP_RING], bar_row_free[SP_RING];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[64];
@@ -260,7 +265,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring = base;
-  const uint32_t wsm = ring + SR_STAGES * SR_STAGE_BYTES + 256;
+  const uint32_t wsm = ring + G::STAGES * SR_STAGE_BYTES + 256;
   const uint32_t rows = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // SP_RING stem rows [128 px][128 B], chunk-swizzled
   const int per_cta = (p.total_units + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
   const int unit0 = static_cast<int>(blockIdx.x) * per_cta;
@@ -274,7 +279,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   if (threadIdx.x < NOUT) bias_s[threadIdx.x] = p.bias[threadIdx.x];
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&in_map);
-    for (int s = 0; s < SR_STAGES; ++s) {
+    for (int s = 0; s < G::STAGES; ++s) {
       mbar_init(smem_u32(&bar_full[s]), 1);
       mbar_init(smem_u32(&bar_empty[s]), 1);
     }
@@ -314,8 +319,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         int n, ph0, ph1, y_lo, y_hi;
         unit_rows(u, n, ph0, ph1, y_lo, y_hi);
         for (int y = y_lo; y <= y_hi; ++y, ++it) {
-          const int s = it % SR_STAGES;
-          mbar_wait(smem_u32(&bar_empty[s]), ((it / SR_STAGES) & 1) ^ 1);
+          const int s = it % G::STAGES;
+          mbar_wait(smem_u32(&bar_empty[s]), ((it / G::STAGES) & 1) ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
           if (elect_one()) {
             mbar_expect_tx(full, G::KR * SR_ROW_BYTES);
@@ -333,9 +338,9 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         int n, ph0, ph1, y_lo, y_hi;
         unit_rows(u, n, ph0, ph1, y_lo, y_hi);
         for (int y = y_lo; y <= y_hi; ++y, ++it) {
-          const int b = it & 1, s = it % SR_STAGES;
+          const int b = it & 1, s = it % G::STAGES;
           mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
-          mbar_wait(smem_u32(&bar_full[s]), (it / SR_STAGES) & 1);
+          mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
           tc_fence_after();
           const uint32_t a0 = ring + s * SR_STAGE_BYTES;
           if (elect_one()) {
@@ -491,7 +496,7 @@ static int stem_in_map(CUtensorMap* m, const View& in, int krows) {
 template <int KS, int NOUT, int ACT>
 static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p, cudaStream_t stream) {
   using G = StemCfg<KS, NOUT>;
-  const size_t smem = size_t(SR_STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
+  const size_t smem = size_t(G::STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -507,7 +512,7 @@ static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p
 template <int KS, int NOUT, int ACT>
 static int stem_row_launch_t(const CUtensorMap& in_map, const CUtensorMap& out_map, const StemRowParams& p, cudaStream_t stream) {
   using G = StemCfg<KS, NOUT>;
-  const size_t smem = size_t(SR_STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + 2 * SR_OUT_BYTES + 1024;
+  const size_t smem = size_t(G::STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + SR_WGS * SR_OUT_BYTES + 1024;
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -579,6 +584,8 @@ int stem_row_launch_k(const View& in, const View& out, const void* w, const floa
   p.Ho = out.H; p.Wo = out.W;
   p.segs = (out.W + 127) / 128;
   p.total_tiles = out.N * out.H * p.segs;
+  p.mul_segs = fast_div_mul(p.segs);
+  p.mul_Ho = fast_div_mul(p.Ho);
   const int nout = stem_nout(out.C);
   B200_STEM_DISPATCH(stem_row_launch_t, in_map, out_map, p, stream);
 }
