@@ -80,6 +80,9 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 }
 
 // multiplier for fast_div (ptx.cuh): floor(2^32 / d) + 1; unused for d < 2
+struct FastDiv { unsigned d, mul; };   // divisor and its multiplier, passed to kernels by value
 inline unsigned fast_div_mul(int d) { return d < 2 ? 0u : static_cast<unsigned>((1ull << 32) / static_cast<unsigned>(d)) + 1u; }
+
+inline FastDiv make_fast_div(long long d) { return FastDiv{static_cast<unsigned>(d), fast_div_mul(static_cast<int>(d))}; }
 
 }  // namespace b200

@@ -45,14 +45,15 @@ __device__ __forceinline__ void dw_unpack(const uint2 r, float (&v)[4]) {
 template <int STRIDE, int ACT, bool SQ>
 __global__ void __launch_bounds__(DW_STRIP_THREADS, 3)
 dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho,
-                       int Wo, int out_ps, int C4, int strips_h, int strips_w, const float* __restrict__ w,
-                       const float* __restrict__ bias, float* __restrict__ se_partial, long long total, int slots) {
+                       int Wo, int out_ps, FastDiv C4d, FastDiv strips_hd, FastDiv strips_wd, const float* __restrict__ w,
+                       const float* __restrict__ bias, float* __restrict__ se_partial, unsigned total, int slots) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
   constexpr int R = STRIDE == 1 ? 2 : 1;                        // output rows per thread
   constexpr int ROWS = STRIDE == 1 ? 4 : 3;                     // input rows per thread
   constexpr int NCOL = STRIDE == 1 ? DW_TW + 2 : 2 * DW_TW + 1;   // input columns per thread, first one = halo
   __shared__ float4 red[SQ ? DW_STRIP_THREADS : 1];
+  const int C4 = static_cast<int>(C4d.d), strips_h = static_cast<int>(strips_hd.d), strips_w = static_cast<int>(strips_wd.d);
   int c4, sx, sy, n;
   bool active;
   if (SQ) {
@@ -66,14 +67,14 @@ dwconv3x3_strip_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps,
     active = slot < strips_h * strips_w && c4 < C4;
     if (!active) { c4 = 0; sx = 0; sy = 0; }                    // idle lanes still reach the barrier below
   } else {
-    const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit, multiply-high division (see fast_div)
     if (idx >= total) return;
-    c4 = static_cast<int>(idx % C4);
-    long long t = idx / C4;
-    sx = static_cast<int>(t % strips_w);
-    t /= strips_w;
-    sy = static_cast<int>(t % strips_h);
-    n = static_cast<int>(t / strips_h);
+    const unsigned t = fast_div(idx, C4d);
+    c4 = static_cast<int>(idx - t * C4d.d);
+    const unsigned t2 = fast_div(t, strips_wd);
+    sx = static_cast<int>(t - t2 * strips_wd.d);
+    n = static_cast<int>(fast_div(t2, strips_hd));
+    sy = static_cast<int>(t2 - n * strips_hd.d);
     active = true;
   }
   const int C = C4 * 4;
@@ -270,14 +271,16 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
     while (slots < strips) slots <<= 1;
     const int qn = DW_STRIP_THREADS / slots;
     const long long total = static_cast<long long>(out.N) * strips * (out.C / 4);
+    if (total >= (1ll << 31)) return fail(B200_ERR_INVALID, "dwconv: tensor too large");
     const unsigned grid = sq ? static_cast<unsigned>(out.N) * static_cast<unsigned>((out.C / 4 + qn - 1) / qn)
                              : static_cast<unsigned>((total + DW_STRIP_THREADS - 1) / DW_STRIP_THREADS);
     const uint16_t* ip = static_cast<const uint16_t*>(in.base);
     uint16_t* op = static_cast<uint16_t*>(out.base);
 #define B200_DW_LAUNCH2(S, A, Q)                                                                                       \
   B200_CUDA_OK(launch_pdl(dwconv3x3_strip_kernel<S, A, Q>, dim3(grid), dim3(DW_STRIP_THREADS), size_t(0), stream, ip, in.H,  \
-                          in.W, in.pix_stride, op, out.H, out.W, out.pix_stride, out.C / 4, strips_h, strips_w, w, bias,      \
-                          se_partial, total, slots))
+                          in.W, in.pix_stride, op, out.H, out.W, out.pix_stride, make_fast_div(out.C / 4),                   \
+                          make_fast_div(strips_h), make_fast_div(strips_w), w, bias, se_partial, static_cast<unsigned>(total), \
+                          slots))
 #define B200_DW_LAUNCH(S, A) do { if (sq) B200_DW_LAUNCH2(S, A, true); else B200_DW_LAUNCH2(S, A, false); } while (0)
     if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU)
       return fail(B200_ERR_INVALID, "dwconv: activation must be none, relu or silu");

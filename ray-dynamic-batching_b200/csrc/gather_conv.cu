@@ -35,6 +35,7 @@ struct GatherParams {
   int act, res_mode;
   long long total_pix;
   int total_tiles;
+  FastDiv Wod, Hod;     // multiply-high division by Wo and Ho (128 gather threads decompose a pixel index per tile)
 };
 
 template <int NPAD>
@@ -96,10 +97,10 @@ gather_conv_kernel(const __grid_constant__ CUtensorMap wmap, const __grid_consta
       const long long pix = static_cast<long long>(tile0 + it) * 128 + m;
       const bool valid = pix < p.total_pix;
       const long long pp = valid ? pix : 0;
-      const int ow = static_cast<int>(pp % p.Wo);
-      const long long t1 = pp / p.Wo;
-      const int oh = static_cast<int>(t1 % p.Ho);
-      const int n = static_cast<int>(t1 / p.Ho);
+      const unsigned t1 = fast_div(static_cast<unsigned>(pp), p.Wod);        // total_pix < 2^31 (checked by the host)
+      const int ow = static_cast<int>(static_cast<unsigned>(pp) - t1 * p.Wod.d);
+      const int n = static_cast<int>(fast_div(t1, p.Hod));
+      const int oh = static_cast<int>(t1 - n * p.Hod.d);
       const int y0 = oh * p.stride - p.pad, x0 = ow * p.stride - p.pad;
       const uint16_t* img = p.in + static_cast<size_t>(n) * p.H * p.W * p.in_ps;
       for (int kb = 0; kb < p.kb; ++kb, ++g) {
@@ -276,7 +277,10 @@ int gather_conv_launch(const View& in, const View& out, const View& res, const v
   p.act = act;
   p.res_mode = res.base ? (res_after_act ? 2 : 1) : 0;
   p.total_pix = static_cast<long long>(out.N) * out.H * out.W;
+  if (p.total_pix >= (1ll << 31) - 128) return fail(B200_ERR_INVALID, "gather_conv: tensor too large");
   p.total_tiles = static_cast<int>((p.total_pix + 127) / 128);
+  p.Wod = make_fast_div(out.W);
+  p.Hod = make_fast_div(out.H);
   if (npad == 32) return gather_launch_t<32>(wmap, p, stream);
   if (npad == 64) return gather_launch_t<64>(wmap, p, stream);
   if (npad == 128) return gather_launch_t<128>(wmap, p, stream);

@@ -489,16 +489,17 @@ int se_scale_launch(const View& in, const View& out, const float* hid, const flo
 
 // y[n,h,w,c] = x[n,h,w,c] * gate[n][c]
 __global__ void __launch_bounds__(256)
-channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int HW, int C8,
-                     const float* __restrict__ gate, long long total) {
+channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, FastDiv HW,
+                     FastDiv C8d, const float* __restrict__ gate, unsigned total) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-  if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % C8);
-  const long long pix = idx / C8;
-  const int n = static_cast<int>(pix / HW);
-  const uint4 v = *reinterpret_cast<const uint4*>(in + pix * in_ps + c8 * 8);
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;     // 32-bit index math with multiply-high division: the
+  if (idx >= total) return;                                       // 64-bit % and / cost more than the 16 bytes a thread moves
+  const int C8 = static_cast<int>(C8d.d);
+  const unsigned pix = fast_div(idx, C8d);
+  const int c8 = static_cast<int>(idx - pix * C8d.d);
+  const int n = static_cast<int>(fast_div(pix, HW));
+  const uint4 v = *reinterpret_cast<const uint4*>(in + static_cast<size_t>(pix) * in_ps + c8 * 8);
   const float4 g0 = *reinterpret_cast<const float4*>(gate + static_cast<size_t>(n) * C8 * 8 + c8 * 8);
   const float4 g1 = *reinterpret_cast<const float4*>(gate + static_cast<size_t>(n) * C8 * 8 + c8 * 8 + 4);
   uint4 o;
@@ -506,14 +507,15 @@ channel_scale_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __res
   o.y = pack_bf16x2(bf16_lo(v.y) * g0.z, bf16_hi(v.y) * g0.w);
   o.z = pack_bf16x2(bf16_lo(v.z) * g1.x, bf16_hi(v.z) * g1.y);
   o.w = pack_bf16x2(bf16_lo(v.w) * g1.z, bf16_hi(v.w) * g1.w);
-  *reinterpret_cast<uint4*>(out + pix * out_ps + c8 * 8) = o;
+  *reinterpret_cast<uint4*>(out + static_cast<size_t>(pix) * out_ps + c8 * 8) = o;
 }
 
 int channel_scale_launch(const View& in, const View& out, const float* gate, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W)
     return fail(B200_ERR_INVALID, "channel_scale: shape mismatch");
   const long long total = static_cast<long long>(in.N) * in.H * in.W * (in.C / 8);
-  B200_CUDA_OK(launch_pdl(channel_scale_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.H * in.W, in.C / 8, gate, total));
+  if (total >= (1ll << 31)) return fail(B200_ERR_INVALID, "channel_scale: tensor too large");
+  B200_CUDA_OK(launch_pdl(channel_scale_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, make_fast_div(in.H * in.W), make_fast_div(in.C / 8), gate, static_cast<unsigned>(total)));
   return B200_OK;
 }
 

@@ -9,38 +9,40 @@
 namespace b200 {
 
 __global__ void __launch_bounds__(256)
-copy_channels_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, int C8,
-                     long long total) {
+copy_channels_kernel(const uint16_t* __restrict__ in, int in_ps, uint16_t* __restrict__ out, int out_ps, FastDiv C8,
+                     unsigned total) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % C8);
-  const long long pix = idx / C8;
-  *reinterpret_cast<uint4*>(out + pix * out_ps + c8 * 8) = *reinterpret_cast<const uint4*>(in + pix * in_ps + c8 * 8);
+  const unsigned pix = fast_div(idx, C8);
+  const int c8 = static_cast<int>(idx - pix * C8.d);
+  *reinterpret_cast<uint4*>(out + static_cast<size_t>(pix) * out_ps + c8 * 8) =
+      *reinterpret_cast<const uint4*>(in + static_cast<size_t>(pix) * in_ps + c8 * 8);
 }
 
 int copy_channels_launch(const View& in, const View& out, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.N != out.N || in.H != out.H || in.W != out.W)
     return fail(B200_ERR_INVALID, "copy_channels: shape mismatch");
   const long long total = static_cast<long long>(in.N) * in.H * in.W * (in.C / 8);
-  B200_CUDA_OK(launch_pdl(copy_channels_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.C / 8, total));
+  if (total >= (1ll << 31)) return fail(B200_ERR_INVALID, "copy_channels: tensor too large");
+  B200_CUDA_OK(launch_pdl(copy_channels_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, make_fast_div(in.C / 8), static_cast<unsigned>(total)));
   return B200_OK;
 }
 
 __global__ void __launch_bounds__(256)
 upsample2x_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int out_ps,
-                  int C8, long long total) {
+                  FastDiv C8, FastDiv W2, FastDiv H2, unsigned total) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % C8);
-  long long pix = idx / C8;
-  const int ow = static_cast<int>(pix % (2 * W));
-  pix /= 2 * W;
-  const int oh = static_cast<int>(pix % (2 * H));
-  const int n = static_cast<int>(pix / (2 * H));
+  const unsigned pix = fast_div(idx, C8);
+  const int c8 = static_cast<int>(idx - pix * C8.d);
+  const unsigned row = fast_div(pix, W2);
+  const int ow = static_cast<int>(pix - row * W2.d);
+  const int n = static_cast<int>(fast_div(row, H2));
+  const int oh = static_cast<int>(row - n * H2.d);
   const uint4 v =
       *reinterpret_cast<const uint4*>(in + ((static_cast<size_t>(n) * H + (oh >> 1)) * W + (ow >> 1)) * in_ps + c8 * 8);
   *reinterpret_cast<uint4*>(out + ((static_cast<size_t>(n) * 2 * H + oh) * 2 * W + ow) * out_ps + c8 * 8) = v;
@@ -50,7 +52,8 @@ int upsample2x_launch(const View& in, const View& out, cudaStream_t stream) {
   if (in.C != out.C || in.C % 8 || in.N != out.N || 2 * in.H != out.H || 2 * in.W != out.W)
     return fail(B200_ERR_INVALID, "upsample2x: shape mismatch");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
-  B200_CUDA_OK(launch_pdl(upsample2x_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, in.C / 8, total));
+  if (total >= (1ll << 31)) return fail(B200_ERR_INVALID, "upsample2x: tensor too large");
+  B200_CUDA_OK(launch_pdl(upsample2x_kernel, dim3(static_cast<unsigned>((total + 255) / 256)), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.pix_stride, make_fast_div(in.C / 8), make_fast_div(2 * in.W), make_fast_div(2 * in.H), static_cast<unsigned>(total)));
   return B200_OK;
 }
 

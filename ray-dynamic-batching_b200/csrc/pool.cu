@@ -15,18 +15,19 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
 }
 
 __global__ void __launch_bounds__(256)
-maxpool_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, int Ho, int Wo,
-               int out_ps, int C8, int k, int s, int p, long long total) {
+maxpool_kernel(const uint16_t* __restrict__ in, int H, int W, int in_ps, uint16_t* __restrict__ out, FastDiv Hod,
+               FastDiv Wod, int out_ps, FastDiv C8, int k, int s, int p, unsigned total) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
-  const long long idx = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
-  const int c8 = static_cast<int>(idx % C8);
-  long long pix = idx / C8;
-  const int ow = static_cast<int>(pix % Wo);
-  pix /= Wo;
-  const int oh = static_cast<int>(pix % Ho);
-  const int n = static_cast<int>(pix / Ho);
+  const int Ho = static_cast<int>(Hod.d), Wo = static_cast<int>(Wod.d);
+  const unsigned pix = fast_div(idx, C8);
+  const int c8 = static_cast<int>(idx - pix * C8.d);
+  const unsigned row = fast_div(pix, Wod);
+  const int ow = static_cast<int>(pix - row * Wod.d);
+  const int n = static_cast<int>(fast_div(row, Hod));
+  const int oh = static_cast<int>(row - n * Hod.d);
   const uint32_t NEG = 0xFF80FF80u;  // bf16 -inf pair
   uint4 m = make_uint4(NEG, NEG, NEG, NEG);
   const int y0 = oh * s - p, x0 = ow * s - p;
@@ -50,8 +51,9 @@ int maxpool_launch(const View& in, const View& out, int ksize, int stride, int p
   if ((in.H + 2 * pad - ksize) / stride + 1 != out.H || (in.W + 2 * pad - ksize) / stride + 1 != out.W || in.N != out.N)
     return fail(B200_ERR_INVALID, "maxpool: output geometry mismatch");
   const long long total = static_cast<long long>(out.N) * out.H * out.W * (out.C / 8);
+  if (total >= (1ll << 31)) return fail(B200_ERR_INVALID, "maxpool: tensor too large");
   const unsigned blocks = static_cast<unsigned>((total + 255) / 256);
-  B200_CUDA_OK(launch_pdl(maxpool_kernel, dim3(blocks), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), out.H, out.W, out.pix_stride, out.C / 8, ksize, stride, pad, total));
+  B200_CUDA_OK(launch_pdl(maxpool_kernel, dim3(blocks), dim3(256), size_t(0), stream, static_cast<const uint16_t*>(in.base), in.H, in.W, in.pix_stride, static_cast<uint16_t*>(out.base), make_fast_div(out.H), make_fast_div(out.W), out.pix_stride, make_fast_div(out.C / 8), ksize, stride, pad, static_cast<unsigned>(total)));
   return B200_OK;
 }
 

@@ -6,6 +6,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "common.h"
+
 namespace b200 {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -180,6 +182,8 @@ __device__ __forceinline__ uint32_t fast_div(uint32_t n, uint32_t d, uint32_t mu
   if (q * d > n) --q;
   return q;
 }
+
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, FastDiv f) { return fast_div(n, f.d, f.mul); }
 
 // distributed shared memory: address of the same shared-memory location in CTA `rank` of this cluster
 __device__ __forceinline__ uint32_t cluster_map(uint32_t smem_addr, uint32_t rank) {
