@@ -164,7 +164,10 @@ def test_stem_conv_tensor_core(b200lib, cuda, k, p, cout, cfg, act):
 
 @pytest.mark.parametrize("n,h,w,c,stride,act", [(2, 28, 28, 64, 1, 0), (3, 56, 56, 24, 2, 0), (1, 15, 17, 960, 1, 2),
                                                 (2, 14, 14, 232, 2, 2), (5, 14, 14, 232, 1, 1), (3, 7, 7, 464, 1, 0),
-                                                (2, 28, 28, 120, 1, 2), (1, 9, 14, 40, 1, 1), (4, 42, 21, 72, 1, 0)])
+                                                (2, 28, 28, 120, 1, 2), (1, 9, 14, 40, 1, 1), (4, 42, 21, 72, 1, 0),
+                                                # tile kernel: many items per block with the channel group changing inside a run,
+                                                # ragged last group, two bands per image
+                                                (160, 14, 14, 200, 1, 2), (300, 7, 7, 40, 1, 0), (41, 28, 28, 72, 1, 1)])
 def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
     x = rnd((n, h, w, c), 1, cuda)
     wt = rnd((c, 1, 3, 3), 2, cuda, torch.float32) / 3
@@ -235,6 +238,36 @@ def test_dwconv3x3_fused_squeeze_and_se_gate(b200lib, cuda, n, h, w, c, stride, 
     assert torch.allclose(hid, F.silu(mean @ w1.t() + b1), rtol=1e-4, atol=1e-5)
     ok, e = close_bf16(scaled, out.float() * want.view(n, 1, 1, c))
     assert ok, e
+
+
+@pytest.mark.parametrize("n,c,sq,rows", [(19, 1536, 64, 1), (150, 960, 40, 1), (8, 512, 32, 3), (1, 256, 16, 1),
+                                         (33, 40, 10, 2), (9, 1056, 44, 1), (3, 24, 8, 7), (5, 200, 13, 1)])
+def test_se_gate_many_images_ragged_slices(b200lib, cuda, n, c, sq, rows):
+    """The gate alone, at shapes the fused test does not reach: more image groups than clusters (150 images), channel
+    counts that leave the last CTAs of a cluster a short or empty slice (40, 200, 1056), odd squeeze widths, several rows
+    of sums per image.  Against torch in fp32 (tv ops/misc.py:249-254)."""
+    g = torch.Generator().manual_seed(100 + n)
+    sums = torch.randn(n, rows, c, generator=g).to(cuda)
+    hw = 49
+    w1 = (torch.randn(sq, c, generator=g) / c ** 0.5).to(cuda)
+    b1 = torch.randn(sq, generator=g).to(cuda)
+    w2 = (torch.randn(c, sq, generator=g) / sq ** 0.5).to(cuda)
+    b2 = torch.randn(c, generator=g).to(cuda)
+    w2t = w2.t().contiguous()
+    gate = torch.full((n, c), float("nan"), device=cuda)
+    check(b200lib.b200_se_gate(ptr(sums), n, rows, c, 1.0 / hw, ptr(w1), ptr(b1), ptr(w2t), ptr(b2), sq, ptr(gate),
+                               stream_ptr()))
+    torch.cuda.synchronize()
+    mean = sums.sum(dim=1) / hw
+    want = torch.sigmoid(F.silu(mean @ w1.t() + b1) @ w2.t() + b2)
+    assert torch.isfinite(gate).all()
+    assert torch.allclose(gate, want, rtol=1e-4, atol=2e-5), (gate - want).abs().max().item()
+    # deterministic: a second launch gives the same bits
+    gate2 = torch.empty_like(gate)
+    check(b200lib.b200_se_gate(ptr(sums), n, rows, c, 1.0 / hw, ptr(w1), ptr(b1), ptr(w2t), ptr(b2), sq, ptr(gate2),
+                               stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(gate, gate2)
 
 
 def test_dwconv3x3_squeeze_rejects_widths_without_strips(b200lib, cuda):
