@@ -17,8 +17,8 @@
 
 namespace b200 {
 
-int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const float* bias, int act, float* sums,
-                       cudaStream_t stream);       // dwconv_tile.cu
+int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
+                       float* sums, cudaStream_t stream);       // dwconv_tile.cu
 int dwconv3x3_tile_squeeze_rows(int C, int H, int W, int stride);
 int dwconv3x3_strips(int Ho, int Wo, int stride);
 
@@ -258,8 +258,8 @@ int dwconv3x3_launch(const View& in, const View& out, const float* w, const floa
     const char* e = getenv("B200_DW_STRIPS");
     use_strips = (e && e[0] == '0') ? 0 : 1;
   }
-  if (stride == 1) {
-    const int rc = dwconv3x3_tile_try(in, out, w, bias, act, se_partial, stream);
+  {
+    const int rc = dwconv3x3_tile_try(in, out, w, bias, stride, act, se_partial, stream);
     if (rc <= 0) return rc;        // launched (or failed); 1 = not a layer for the tile kernel
   }
   const int strips = dw_strip_count(out.H, out.W, stride);

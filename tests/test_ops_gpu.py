@@ -167,7 +167,10 @@ def test_stem_conv_tensor_core(b200lib, cuda, k, p, cout, cfg, act):
                                                 (2, 28, 28, 120, 1, 2), (1, 9, 14, 40, 1, 1), (4, 42, 21, 72, 1, 0),
                                                 # tile kernel: many items per block with the channel group changing inside a run,
                                                 # ragged last group, two bands per image
-                                                (160, 14, 14, 200, 1, 2), (300, 7, 7, 40, 1, 0), (41, 28, 28, 72, 1, 1)])
+                                                (160, 14, 14, 200, 1, 2), (300, 7, 7, 40, 1, 0), (41, 28, 28, 72, 1, 1),
+                                                # stride-2 tiles: odd input sizes, 32-channel groups, several bands, ragged groups
+                                                (3, 27, 28, 24, 2, 1), (70, 112, 112, 24, 2, 0), (9, 55, 56, 120, 2, 2),
+                                                (40, 14, 14, 232, 2, 0), (2, 13, 13, 8, 2, 2)])
 def test_dwconv3x3(b200lib, cuda, n, h, w, c, stride, act):
     x = rnd((n, h, w, c), 1, cuda)
     wt = rnd((c, 1, 3, 3), 2, cuda, torch.float32) / 3
