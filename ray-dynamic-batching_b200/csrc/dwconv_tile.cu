@@ -284,7 +284,8 @@ static bool dw_tile_enabled() {
 // Geometry the tile kernel takes: OUTPUT width a multiple of 7 and at most 56, at least two tiles in the ring.
 // Stride 1: bands of 14 rows, channel group by how many strips a band has.  Stride 2 (a tile is four times the output):
 // the (channel group, band height) pair with the best product of slot use, halo overhead and channel padding.
-static bool dw_tile_plan(int C, int H, int W, int stride, DwTileParams* p) {
+// one_band: the caller wants the fused squeeze, which needs a whole image per item.
+static bool dw_tile_plan(int C, int H, int W, int stride, bool one_band, DwTileParams* p) {
   if (W % DT_TW || W > 56 || H < 1 || C % 8) return false;
   p->stride = stride;
   if (stride == 1) {
@@ -309,7 +310,7 @@ static bool dw_tile_plan(int C, int H, int W, int stride, DwTileParams* p) {
     if (cg == 32 && C > 32) continue;
     if (cg > 64 && cg > (C + 63) / 64 * 64) continue;
     const int groups = (C + cg - 1) / cg, nslots = DT_COMPUTE / (cg / 4);
-    for (int bh = H; bh >= 1; --bh) {
+    for (int bh = H; bh >= (one_band ? H : 1); --bh) {
       const int tile_bytes = (2 * bh + 1) * (2 * W + 1) * cg * 2;
       int stages = (DT_SMEM_MAX - 256) / ((tile_bytes + 127) & ~127);
       if (stages < 2) continue;
@@ -331,7 +332,7 @@ static bool dw_tile_plan(int C, int H, int W, int stride, DwTileParams* p) {
 // 1 when the tile kernel would take this layer and writes ONE row of channel sums per image, else 0
 int dwconv3x3_tile_squeeze_rows(int C, int H, int W, int stride) {
   DwTileParams p;
-  if (!dw_tile_enabled() || (stride == 2 && !dw_tile_s2_enabled()) || !dw_tile_plan(C, H, W, stride, &p)) return 0;
+  if (!dw_tile_enabled() || (stride == 2 && !dw_tile_s2_enabled()) || !dw_tile_plan(C, H, W, stride, true, &p)) return 0;
   return p.bands == 1 ? 1 : 0;
 }
 
@@ -371,7 +372,7 @@ static int dw_tile_launch_s(int act, const CUtensorMap& map, const DwTileParams&
 int dwconv3x3_tile_try(const View& in, const View& out, const float* w, const float* bias, int stride, int act,
                        float* sums, cudaStream_t stream) {
   DwTileParams p;
-  if (!dw_tile_enabled() || (stride == 2 && !dw_tile_s2_enabled()) || !dw_tile_plan(out.C, out.H, out.W, stride, &p)) return 1;
+  if (!dw_tile_enabled() || (stride == 2 && !dw_tile_s2_enabled()) || !dw_tile_plan(out.C, out.H, out.W, stride, sums != nullptr, &p)) return 1;
   if (sums && p.bands != 1) return 1;
   if (act != ACT_NONE && act != ACT_RELU && act != ACT_SILU) return 1;
   if (in.pix_stride % 8 || (reinterpret_cast<uintptr_t>(in.base) & 15)) return 1;
