@@ -41,7 +41,20 @@ def phys_channels(c):
     The extra channels are never written (buffers start zeroed) and meet zero weights. B200_PAD_24=0 turns it off."""
     if c == 24 and os.environ.get("B200_PAD_24", "1") != "0":
         return 32
-    return pad8(c)
+    return line_channels(c)
+
+
+def line_channels(c):
+    """pad8(c), or the next multiple of 64 channels (128-byte lines) when that costs at most 12 % more bytes: a TMA box row
+    of 64 channels that starts at pixel * 240 bytes (120 channels) straddles two 128-byte lines on most pixels, and the
+    thin 1x1 convs of ShuffleNetV2 (58 / 116 / 232-channel halves) were waiting on exactly those loads (ncu: the MMA warp
+    and the producer both stalled on the A/B ring at 17 GB/s per SM). B200_PAD_LINE=0 turns it off."""
+    p8 = pad8(c)
+    p64 = (c + 63) // 64 * 64
+    pct = int(os.environ.get("B200_PAD_LINE_PCT", "12"))
+    if c > 32 and p64 != p8 and p64 * 100 <= p8 * (100 + pct) and os.environ.get("B200_PAD_LINE", "1") != "0":
+        return p64
+    return p8
 
 
 def stem_cout_tile(cout):
@@ -437,11 +450,11 @@ class PlanBuilder:
 
     def shuffle(self, a: T, b: T, name=""):
         """ShuffleNetV2 cat + channel_shuffle(groups=2): logical out[2i] = a[i], out[2i+1] = b[i]. The result is stored
-        as two halves [0, cp) and [cp, 2cp) (cp = pad8(c)) holding logical [0, c) and [c, 2c): chunk(2) of the next unit
+        as two halves [0, cp) and [cp, 2cp) (cp = line_channels(c)) holding logical [0, c) and [c, 2c): chunk(2) of the next unit
         is then two 16-byte aligned slices."""
         assert a.c == b.c and (a.h, a.w) == (b.h, b.w)
         assert np.array_equal(a.cmap, np.arange(a.c)) and np.array_equal(b.cmap, np.arange(b.c))
-        c, cp = a.c, pad8(a.c)
+        c, cp = a.c, line_channels(a.c)
         ob = self.new_buf(a.h, a.w, 2 * cp)
         cmap = np.concatenate([np.arange(c), cp + np.arange(c)])
         self._op(OP_SHUFFLE, [a.buf, a.coff, a.cphys, ob, 0, 2 * cp, -1, 0, 0, 0, 0, 0, b.buf, b.coff, c, cp], name=name)
