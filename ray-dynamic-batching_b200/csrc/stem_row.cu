@@ -38,6 +38,10 @@ struct StemCfg {
   // latency that caps the input stream at ~2.7 TB/s (ncu: the epilogue groups wait for accumulators, the tensor pipe is 6 %
   // busy) -> ten.  A 7x7 stem's box is 16 KB and the kernel is paced by its 14 MMAs per row -> four.
   static constexpr int STAGES = KS == 3 ? 10 : 4;
+  // fused max-pool: stem rows kept in shared memory.  Pooled row ph needs rows 2ph-1 .. 2ph+1 and frees two of them only
+  // when it is done; with four slots the drain groups could run one row ahead of the pooling group and waited for a
+  // free slot half of the time (ncu, 3x3 stem).  Eight (six next to the 7x7 stem's larger input ring) decouple them.
+  static constexpr int POOL_RING = KS == 3 ? 8 : 6;
   static constexpr int PAD = KS / 2;
   static constexpr int KC = (KS + 2) / 2 & ~1;        // 7 -> 4 chunks (8 pixels), 3 -> 2 chunks (4 pixels)
   static constexpr int MMAS = KC / 2;                 // K = 16 (two chunks) per MMA
@@ -240,6 +244,7 @@ struct StemPoolParams {
   int Ho, Wo;           // stem output size
   int bands;            // bands per image = ceil((Ho/2) / SP_BAND)
   int total_units;      // N * bands
+  unsigned mul_ch;      // fast_div multiplier of cout / 8
 };
 
 __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
@@ -249,7 +254,6 @@ __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
 }
 
 static constexpr int SP_THREADS = 512;   // warps 0: TMA, 1: MMA, 4-7 / 8-11: drain of accumulator 0 / 1, 12-15: pooling
-static constexpr int SP_RING = 4;        // stem rows kept in shared memory
 
 template <int KS, int NOUT, int ACT>
 __global__ void __launch_bounds__(SP_THREADS, 1)
@@ -258,7 +262,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[2], bar_t_empty[2];
-  __shared__ __align__(8) uint64_t bar_row_ready[SP_RING], bar_row_free[SP_RING];
+  __shared__ __align__(8) uint64_t bar_row_ready[G::POOL_RING], bar_row_free[G::POOL_RING];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[64];
 
@@ -266,7 +270,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring = base;
   const uint32_t wsm = ring + G::STAGES * SR_STAGE_BYTES + 256;
-  const uint32_t rows = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // SP_RING stem rows [128 px][128 B], chunk-swizzled
+  const uint32_t rows = (wsm + SR_W_BYTES + 1023u) & ~1023u;     // G::POOL_RING stem rows [128 px][128 B], chunk-swizzled
   const int per_cta = (p.total_units + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
   const int unit0 = static_cast<int>(blockIdx.x) * per_cta;
   const int my_units = max(0, min(per_cta, p.total_units - unit0));
@@ -287,7 +291,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       mbar_init(smem_u32(&bar_t_full[b]), 1);
       mbar_init(smem_u32(&bar_t_empty[b]), 128);
     }
-    for (int r = 0; r < SP_RING; ++r) {
+    for (int r = 0; r < G::POOL_RING; ++r) {
       mbar_init(smem_u32(&bar_row_ready[r]), 128);
       mbar_init(smem_u32(&bar_row_free[r]), 128);
     }
@@ -368,14 +372,14 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;     // stem pixel (ow) owned by this thread
     const int sw = row & 7;
-    int it = 0;                               // stem rows processed by this CTA (ring slot = it % SP_RING)
+    int it = 0;                               // stem rows processed by this CTA (ring slot = it % G::POOL_RING)
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
-        const int b = it & 1, slot = it % SP_RING;
+        const int b = it & 1, slot = it % G::POOL_RING;
         if (b != dwg) continue;
-        mbar_wait(smem_u32(&bar_row_free[slot]), ((it / SP_RING) & 1) ^ 1);   // pooling is done with the row that lived here
+        mbar_wait(smem_u32(&bar_row_free[slot]), ((it / G::POOL_RING) & 1) ^ 1);   // pooling is done with the row that lived here
         mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
         tc_fence_after();
         const uint32_t dst_row = rows + slot * SR_OUT_BYTES + row * 128;
@@ -415,15 +419,15 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
-        const int slot = it % SP_RING;
-        mbar_wait(smem_u32(&bar_row_ready[slot]), (it / SP_RING) & 1);
+        const int slot = it % G::POOL_RING;
+        mbar_wait(smem_u32(&bar_row_ready[slot]), (it / G::POOL_RING) & 1);
         const bool pool = (y & 1) && (y >> 1) >= ph0;     // y = 2*ph + 1 completes pooled row ph (rows y-2, y-1, y)
         if (pool) {
           const int ph = y >> 1;
           uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
           const int CH = p.cout >> 3;               // 16-byte chunks per pooled pixel
           for (int item = ptid; item < Wp * CH; item += 128) {
-            const int pw = item / CH, chunk = item - pw * CH;
+            const int pw = fast_div(item, CH, p.mul_ch), chunk = item - pw * CH;
             // Branch-free window: a tap outside the image is replaced by its in-window neighbour (max is idempotent), so
             // the nine 16-byte loads are independent and issue back to back; with a branch per tap this loop was
             // latency-bound and the pooling warps were the kernel's bottleneck.  Only the left column (pw = 0) and the top
@@ -432,7 +436,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
 #pragma unroll
             for (int dy = 0; dy < 3; ++dy) {
               const int back = (y - 2 + dy < y_lo) ? 1 : 2 - dy;      // rows y-2, y-1, y live in slots it-2, it-1, it
-              const uint32_t rbase = rows + ((it - back) % SP_RING) * SR_OUT_BYTES;
+              const uint32_t rbase = rows + ((it - back) % G::POOL_RING) * SR_OUT_BYTES;
 #pragma unroll
               for (int dx = 0; dx < 3; ++dx) {
                 const int xx = max(2 * pw - 1 + dx, 0);
@@ -450,8 +454,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
             *reinterpret_cast<uint4*>(orow + static_cast<size_t>(pw) * p.out_ps + chunk * 8) = m;
           }
           // rows y-2 (top, second and last use) and y-1 (middle, only use) are no longer needed
-          if (y - 2 >= y_lo) mbar_arrive(smem_u32(&bar_row_free[(it - 2) % SP_RING]));
-          mbar_arrive(smem_u32(&bar_row_free[(it - 1) % SP_RING]));
+          if (y - 2 >= y_lo) mbar_arrive(smem_u32(&bar_row_free[(it - 2) % G::POOL_RING]));
+          mbar_arrive(smem_u32(&bar_row_free[(it - 1) % G::POOL_RING]));
         }
         if (y == y_hi) mbar_arrive(smem_u32(&bar_row_free[slot]));   // last row of the band: nobody below will need it
       }
@@ -496,7 +500,7 @@ static int stem_in_map(CUtensorMap* m, const View& in, int krows) {
 template <int KS, int NOUT, int ACT>
 static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p, cudaStream_t stream) {
   using G = StemCfg<KS, NOUT>;
-  const size_t smem = size_t(G::STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + SP_RING * SR_OUT_BYTES + 1024;
+  const size_t smem = size_t(G::STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 1024 + G::POOL_RING * SR_OUT_BYTES + 1024;
   static bool configured[64] = {};
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
@@ -554,6 +558,7 @@ int stem_pool_launch_k(const View& in, const View& out, const void* w, const flo
   p.Ho = Ho; p.Wo = Wo;
   p.bands = (Ho / 2 + SP_BAND - 1) / SP_BAND;
   p.total_units = in.N * p.bands;
+  p.mul_ch = fast_div_mul(p.cout >> 3);
   const int nout = stem_nout(out.C);
   B200_STEM_DISPATCH(stem_pool_launch_t, in_map, p, stream);
 }
