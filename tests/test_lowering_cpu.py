@@ -1,0 +1,79 @@
+"""Host-side layout rules of the lowering (no GPU): physical channel counts, ShuffleNetV2's padded halves, and the
+multiply-high division the kernels use for index math (csrc/ptx.cuh `fast_div`, csrc/common.h `fast_div_mul`), restated
+in Python integers and checked for exactness over the whole range the kernels rely on."""
+import random
+
+import numpy as np
+import pytest
+
+import rdb_b200  # noqa: F401
+from rdb_b200 import lowering, synth
+
+
+def test_physical_channel_rules():
+    # multiples of 8 by default
+    for c in (3, 8, 16, 40, 48, 64, 96, 160, 256, 960, 1536):
+        assert lowering.phys_channels(c) == lowering.pad8(c)
+    # 48-byte pixels -> 64-byte pixels; the 80-channel class branch of YOLOv8n -> 128
+    assert lowering.phys_channels(24) == 32
+    assert lowering.phys_channels(80) == 128
+    # 128-byte lines when that costs at most 12 %: ShuffleNetV2's 58 / 116 / 232-channel halves
+    assert lowering.line_channels(58) == 64
+    assert lowering.line_channels(116) == 128
+    assert lowering.line_channels(232) == 256
+    assert lowering.line_channels(464) == 512
+    # too expensive: stays a multiple of 8
+    assert lowering.line_channels(48) == 48
+    assert lowering.line_channels(160) == 160
+    assert lowering.line_channels(80) == 80
+    for c in range(1, 2049):
+        p = lowering.line_channels(c)
+        assert p >= c and p % 8 == 0 and p * 100 <= lowering.pad8(c) * 112
+
+
+def test_shufflenet_halves_are_line_aligned():
+    """Every shuffle writes two halves of `line_channels(c)` channels; the chunk(2) views of the next unit start on a
+    128-byte line, and every logical channel maps inside its half."""
+    pb = lowering.lower("shufflenet_v2_x1_0", synth.make_model("shufflenet_v2_x1_0", n_proto=8))
+    _, _, ops, _ = lowering.parse_blob(pb.to_blob())
+    shuffles = [op for op in ops if op["type"] == lowering.OP_SHUFFLE]
+    assert len(shuffles) == 16
+    for op in shuffles:
+        p = op["p"]
+        c, cp, out_c = p[14], p[15], p[5]
+        assert cp == lowering.line_channels(c) and out_c == 2 * cp
+        assert (cp * 2) % 128 == 0          # second half starts on a 128-byte line
+
+
+def _fast_div(n, d):
+    """csrc/ptx.cuh fast_div with csrc/common.h fast_div_mul, in Python integers (32-bit wrap-around included)."""
+    if d == 1:
+        return n
+    mul = ((1 << 32) // d + 1) & 0xFFFFFFFF
+    q = (n * mul) >> 32
+    if ((q * d) & 0xFFFFFFFF) > n:
+        q -= 1
+    return q
+
+
+def test_fast_div_is_exact_below_2_31():
+    rng = random.Random(7)
+    edge = [0, 1, 2, 3, (1 << 31) - 1, (1 << 31) - 2, (1 << 30), (1 << 30) + 1]
+    for d in list(range(1, 1026)) + [1536, 2048, 3136, 4096, 12544, 50176, 65535, 65536, 65537, (1 << 31) - 1]:
+        ns = edge + [rng.randrange(1 << 31) for _ in range(200)]
+        ns += [k * d + e for k in (1, 2, 1000, ((1 << 31) - 1) // d) for e in (-1, 0, 1)]
+        for n in ns:
+            if 0 <= n < (1 << 31):
+                assert _fast_div(n, d) == n // d, (n, d)
+
+
+@pytest.mark.parametrize("d", [1, 2, 3, 7, 28, 49, 148, 784])
+def test_fast_div_exhaustive_small_range(d):
+    n = np.arange(0, 1 << 20, dtype=np.uint64)
+    mul = np.uint64(((1 << 32) // d + 1) & 0xFFFFFFFF)
+    q = (n * mul) >> np.uint64(32)
+    q = q - ((q * np.uint64(d)) > n).astype(np.uint64)
+    want = n // np.uint64(d)
+    if d == 1:
+        q = n
+    assert np.array_equal(q, want)
