@@ -22,21 +22,23 @@ fc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float*
   extern __shared__ __align__(16) float s_x[];  // [FC_NB][K]
   const int n0 = blockIdx.y * FC_NB;
   const int K4 = K >> 2;
-  for (int i = threadIdx.x; i < FC_NB * K4; i += blockDim.x) {
-    const int r = i / K4, c = i - r * K4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (n0 + r < N) v = reinterpret_cast<const float4*>(x + static_cast<size_t>(n0 + r) * K)[c];
-    reinterpret_cast<float4*>(s_x)[i] = v;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int r = warp; r < FC_NB; r += FC_WARPS) {          // one warp per staged row: no index division
+    const bool ok = n0 + r < N;
+    const float4* src = reinterpret_cast<const float4*>(x + static_cast<size_t>(ok ? n0 + r : 0) * K);
+    for (int c = lane; c < K4; c += 32)
+      reinterpret_cast<float4*>(s_x)[r * K4 + c] = ok ? src[c] : make_float4(0.f, 0.f, 0.f, 0.f);
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int j0 = (blockIdx.x * FC_WARPS + warp) * FC_JW;
   if (j0 >= J) return;
-  float acc[FC_JW][FC_NB];
+  // packed f32x2 accumulators (even / odd k of every float4): the kernel is issue-bound (ncu: 30 M warp instructions,
+  // 16 M of them FFMA), FFMA2 halves the math instructions; the two lanes are added before the warp reduction
+  float2 acc2[FC_JW][FC_NB];
 #pragma unroll
   for (int a = 0; a < FC_JW; ++a)
 #pragma unroll
-    for (int r = 0; r < FC_NB; ++r) acc[a][r] = 0.f;
+    for (int r = 0; r < FC_NB; ++r) acc2[a][r] = make_float2(0.f, 0.f);
   const float4* wr[FC_JW];
 #pragma unroll
   for (int a = 0; a < FC_JW; ++a) wr[a] = reinterpret_cast<const float4*>(w + static_cast<size_t>(min(j0 + a, J - 1)) * K);
@@ -49,13 +51,16 @@ fc_kernel(const float* __restrict__ x, const float* __restrict__ w, const float*
       const float4 xv = reinterpret_cast<const float4*>(s_x)[r * K4 + c];
 #pragma unroll
       for (int a = 0; a < FC_JW; ++a) {
-        acc[a][r] = fmaf(xv.x, wv[a].x, acc[a][r]);
-        acc[a][r] = fmaf(xv.y, wv[a].y, acc[a][r]);
-        acc[a][r] = fmaf(xv.z, wv[a].z, acc[a][r]);
-        acc[a][r] = fmaf(xv.w, wv[a].w, acc[a][r]);
+        acc2[a][r] = ffma2(make_float2(xv.x, xv.y), make_float2(wv[a].x, wv[a].y), acc2[a][r]);
+        acc2[a][r] = ffma2(make_float2(xv.z, xv.w), make_float2(wv[a].z, wv[a].w), acc2[a][r]);
       }
     }
   }
+  float acc[FC_JW][FC_NB];
+#pragma unroll
+  for (int a = 0; a < FC_JW; ++a)
+#pragma unroll
+    for (int r = 0; r < FC_NB; ++r) acc[a][r] = acc2[a][r].x + acc2[a][r].y;
 #pragma unroll
   for (int a = 0; a < FC_JW; ++a)
 #pragma unroll
