@@ -57,9 +57,9 @@ int maxpool_launch(const View& in, const View& out, int ksize, int stride, int p
   return B200_OK;
 }
 
-// Global average pool: block = (image, 256 threads); thread owns a 16-byte channel chunk and strides over pixels in
+// Global average pool: block = (image, up to 1024 threads); thread owns a 16-byte channel chunk and strides over pixels in
 // `gy` slices that are combined through shared memory.  fp32 accumulation, sum * (1/HW) like aten's mean.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 global_avgpool_kernel(const uint16_t* __restrict__ in, int HW, int in_ps, int C8, float* __restrict__ out) {
   pdl_wait();   // launched with programmatic stream serialization: inputs are valid from here on (no early trigger:
                 // a multi-wave kernel must not share its SMs with the waiting blocks of its successor)
@@ -70,6 +70,7 @@ global_avgpool_kernel(const uint16_t* __restrict__ in, int HW, int in_ps, int C8
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (sl < slices) {
     const uint16_t* base = in + static_cast<size_t>(n) * HW * in_ps + c8 * 8;
+#pragma unroll 4
     for (int p = sl; p < HW; p += slices) {
       const uint4 v = *reinterpret_cast<const uint4*>(base + static_cast<size_t>(p) * in_ps);
       acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
@@ -92,7 +93,9 @@ int global_avgpool_launch(const View& in, float* out, cudaStream_t stream) {
   const int C8 = in.C / 8;
   // when C8 > 256 a block walks several channel chunks: launch ceil(C8/256) column blocks via grid.y
   if (C8 <= 256) {
-    const int slices = 256 / C8 > 0 ? 256 / C8 : 1;
+    // as many pixel slices as fit 1024 threads: a 7 x 7 x 2048 image is 49 loads per thread with 256 threads and the
+    // 256 blocks of a batch were 1.7 waves of 8 warps; with 4 slices all blocks are resident at once
+    const int slices = 1024 / C8 > 0 ? 1024 / C8 : 1;
     const int threads = slices * C8;
     const size_t smem = size_t(slices) * C8 * 8 * sizeof(float);
     B200_CUDA_OK(launch_pdl(global_avgpool_kernel, dim3(in.N), dim3(threads), size_t(smem), stream, static_cast<const uint16_t*>(in.base), in.H * in.W, in.pix_stride, C8, out));
