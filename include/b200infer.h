@@ -225,7 +225,10 @@ B200_API int b200_collate(b200_engine* e, const void* packed, const uint64_t* of
  * touches -- live in a fixed array inside the library image: B200_NOALLOC_MAX_IMAGES * 16 B + 1.5 KB = 17.5 KB held by every
  * GPU that loads the library, until exit.  n > B200_NOALLOC_MAX_IMAGES is refused with B200_ERR_INVALID.  Never calls
  * cudaMalloc/cudaFree or any allocating routine.  The first call on each device also resolves the array's device
- * address: make that first call before starting any stream capture.  All calls share the one array, which keeps the last
+ * address, and with lazy module loading the CUDA runtime loads the kernel code onto the device then: make one warm-up
+ * call per device during actor start-up (before any stream capture); from the second call on, device memory in use does
+ * not change across a call.  A stream that is being captured is refused with B200_ERR_INVALID (the table uploads read
+ * host stack memory).  packed_dev that is not 16-byte aligned is served by the byte-wise kernel.  All calls share the one array, which keeps the last
  * call's tables: two calls whose GPU work overlaps (different streams, or threads) race on it -- keep them on one
  * stream, or order them with events.  mean3/std3: per-channel normalisation ((u8/255 - mean) / std); other arguments as
  * b200_collate. */

@@ -190,7 +190,9 @@ int collate_u8_launch(const uint8_t* src_base, const CollateItem* items_dev, con
                       cudaStream_t stream) {
   if (n < 0 || padded_batch < n || padded_batch <= 0) return fail(B200_ERR_INVALID, "collate: bad batch counts");
   if (out_h <= 0 || out_w <= 0) return fail(B200_ERR_INVALID, "collate: bad output size");
-  bool flat = (out_h * out_w) % 2 == 0;
+  // the flat kernel reads 16-byte vectors: the base pointer and every offset must be 16-byte aligned, otherwise the
+  // general kernel (byte loads) takes the batch
+  bool flat = (out_h * out_w) % 2 == 0 && (reinterpret_cast<uintptr_t>(src_base) % 16) == 0;
   for (int i = 0; i < n && flat; ++i)
     flat = items_host[i].h == out_h && items_host[i].w == out_w && (items_host[i].offset % 16) == 0;
   if (flat) {
@@ -198,8 +200,14 @@ int collate_u8_launch(const uint8_t* src_base, const CollateItem* items_dev, con
     collate_u8_flat_kernel<<<grid, CT_THREADS, 0, stream>>>(src_base, items_dev, n, out_h * out_w, lut_dev,
                                                             static_cast<uint16_t*>(out));
   } else {
-    if (mode != COLLATE_PAD && mode != COLLATE_RESIZE && mode != COLLATE_LETTERBOX)
-      return fail(B200_ERR_INVALID, "collate: image size differs from the model input and no resize mode given");
+    if (mode != COLLATE_IDENTITY && mode != COLLATE_PAD && mode != COLLATE_RESIZE && mode != COLLATE_LETTERBOX)
+      return fail(B200_ERR_INVALID, "collate: unknown preprocess mode");
+    if (mode == COLLATE_IDENTITY) {   // same-size images that missed the vector path only for alignment: plain copy
+      for (int i = 0; i < n; ++i)
+        if (items_host[i].h != out_h || items_host[i].w != out_w)
+          return fail(B200_ERR_INVALID, "collate: image size differs from the model input and no resize mode given");
+      mode = COLLATE_PAD;
+    }
     dim3 grid((out_h * out_w + 255) / 256, padded_batch);
     collate_u8_general_kernel<<<grid, 256, 0, stream>>>(src_base, items_dev, n, out_h, out_w, mode, fill, lut_dev,
                                                         static_cast<uint16_t*>(out));

@@ -8,6 +8,11 @@
 // everything the kernel needs beyond the caller's input and output -- the per-image descriptor table and the 3x256
 // normalisation table -- in one fixed array that lives inside the loaded library image.
 //
+// "Allocates nothing" holds from the second call on a device onwards: the first call resolves the array's address, and
+// with lazy module loading the CUDA runtime itself loads the library image and this kernel's code onto the device at
+// that moment (driver-internal device memory).  An actor therefore makes one warm-up call per device while it is
+// still initialising, before it reports its memory as settled.
+//
 // Cost: every GPU that loads libb200infer.so holds B200_NOALLOC_MAX_IMAGES * 16 B + 1.5 KB (= 17.5 KB) until the process
 // exits, whether or not this entry point is ever called.
 #include "kernels.cuh"
@@ -56,6 +61,12 @@ extern "C" int b200_collate_u8_noalloc(const void* packed_dev, const uint64_t* o
   if (!out_nhwc4_bf16_dev || !mean3 || !std3 || (n > 0 && (!packed_dev || !offsets || !hw)))
     return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: null argument");
   if (fill < 0 || fill > 255) return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: fill must be a byte value");
+  // The two table uploads below read host stack memory that is gone when this function returns; recorded into a graph
+  // they would be replayed from dead memory, so a stream that is being captured is refused.
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  B200_CUDA_OK(cudaStreamIsCapturing(stream, &cap));
+  if (cap != cudaStreamCaptureStatusNone)
+    return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: the stream is being captured; call it outside stream capture");
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   NoAllocScratch* scratch = nullptr;
