@@ -84,18 +84,21 @@ def load_reference_classes(clock, models_config):
 
 
 def main():
-    rng = random.Random(293)
+    rng_small, rng_large = random.Random(293), random.Random(2930)
     cases = []
-    for ci in range(60):
+    # cases 0..59: batch sizes of configs[0] (1-32); cases 60..83: the sizes configs[1]-[3] are quoted on (64-512).
+    # The two groups draw from separate generators so that adding the second group left the first one unchanged.
+    for ci in range(84):
+        rng = rng_small if ci < 60 else rng_large
         slo = rng.choice([40, 1500, 2000, 4000])
-        bs = rng.choice([1, 2, 4, 8, 16, 32])
+        bs = rng.choice([1, 2, 4, 8, 16, 32]) if ci < 60 else rng.choice([64, 128, 256, 512])
         lat_ms = rng.choice([1.0, 5.0, 14.4, 53.1, 107.57])
         n_items = rng.choice([0, 1, bs, bs + 1, 2 * bs, 2 * bs + 3, 5 * bs])
-        max_size = rng.choice([4, 100, 2000])
+        max_size = rng.choice([4, 100, 2000]) if ci < 60 else rng.choice([100, 2000, 4000])
         clock = ScriptedTime()
         models_config = {"resnet": {"SLO": slo, "base_rate": 0}}
         BatchRequest, RequestQueue = load_reference_classes(clock, models_config)
-        profile = {"resnet": {b: {"avg_latency_ms": lat_ms} for b in (1, 2, 4, 8, 16, 32)}}
+        profile = {"resnet": {b: {"avg_latency_ms": lat_ms} for b in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512)}}
         q = RequestQueue("resnet", max_size=max_size, batch_profile=profile)
         arrivals, accepted = [], []
         for i in range(n_items):
@@ -137,6 +140,7 @@ def main():
         record["metrics"] = {k: v for k, v in q.metrics.items()}
         record["stats"] = q.get_stats() if not record["spin"] else None
         cases.append(record)
+    rng = rng_small
     # percentile bookkeeping: one long run of completions through the reference get_stats (scheduler.py:343-372)
     clock = ScriptedTime()
     BatchRequest, RequestQueue = load_reference_classes(clock, {"resnet": {"SLO": 50, "base_rate": 0}})
@@ -149,7 +153,7 @@ def main():
         lat_inputs.append((n_ids, arr, done))
         q.record_batch_completion(BatchRequest("resnet", [], n_ids, ["x"] * n_ids, arr), done)
     stats_case = dict(slo=50, completions=lat_inputs, stats=q.get_stats(), n_latencies=len(q.metrics["latencies"]))
-    json.dump(dict(generated_from=REF, cases=cases, stats_case=stats_case), open(OUT, "w"), indent=1)
+    json.dump(dict(generated_from=REF, cases=cases, stats_case=stats_case), open(OUT, "w"), separators=(",", ":"))
     print("wrote", OUT, len(cases), "cases;", sum(c["spin"] for c in cases), "spin")
 
 

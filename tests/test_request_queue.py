@@ -24,7 +24,7 @@ class Clock:
 
 def build(case, compat=True):
     clock = Clock()
-    profile = {"resnet": {b: {"avg_latency_ms": case["avg_latency_ms"]} for b in (1, 2, 4, 8, 16, 32)}}
+    profile = {"resnet": {b: {"avg_latency_ms": case["avg_latency_ms"]} for b in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512)}}
     q = B200RequestQueue("resnet", max_size=case["max_size"], batch_profile=profile, compat=compat, clock=clock,
                          slo_ms=case["slo"])
     accepted = []
