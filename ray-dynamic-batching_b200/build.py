@@ -25,7 +25,7 @@ def sources():
     return sorted(f for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _stamp():
+def source_stamp():
     h = hashlib.sha256()
     for root in (CSRC, os.path.join(HERE, "..", "include")):
         for f in sorted(os.listdir(root)):
@@ -39,7 +39,7 @@ def _stamp():
 def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     stamp_file = os.path.join(OBJ, "stamp")
-    stamp = _stamp()
+    stamp = source_stamp()
     if not force and os.path.exists(LIB) and os.path.exists(stamp_file) and open(stamp_file).read() == stamp:
         return LIB
     if not os.path.exists(NVCC):

@@ -19,7 +19,7 @@ COLLATE_IDENTITY, COLLATE_PAD, COLLATE_RESIZE, COLLATE_LETTERBOX = 0, 1, 2, 3
 
 
 class B200Model:
-    def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True):
+    def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True, in_hw=None):
         if not torch.cuda.is_available():
             raise _lib.B200Error("B200Model needs a CUDA device (sm_100); there is no CPU fallback")
         self.lib = _lib.load()
@@ -28,7 +28,7 @@ class B200Model:
         if blob is None:
             if module is None:
                 raise ValueError("need a module to lower or a prebuilt blob")
-            pb = _lowering.lower(kind, module)
+            pb = _lowering.lower(kind, module, **({} if in_hw is None else {'in_hw': tuple(in_hw)}))
             blob = pb.to_blob()
             self.out_logical = pb.out_logical
             self.op_names = list(pb.names)

@@ -33,6 +33,26 @@ def synthetic_images(n, h=224, w=224, seed=1000, dtype=torch.uint8):
     return out
 
 
+def heldout_images(n, h=224, w=224, seed=900000, jitter=0.08, n_proto=None):
+    """Held-out requests for top-1 agreement: image i is a NEW sample of planted class i % n_proto -- the class's coarse
+    colour layout (the 7x7 control grid of synthetic image 1000 + class) with every grid value jittered (sigma `jitter`)
+    and fresh pixel noise, both from generator seed + i.  None of them is one of the images the classifier was planted
+    on; the fp32 reference still recovers the class, with margins (top-1 minus top-2 logit) spread from a few
+    hundredths up to ~0.5, so agreement on this set is decided by the engine's logit error, not by construction."""
+    n_proto = n_proto or N_PROTO
+    out = torch.empty(n, h, w, 3, dtype=torch.uint8)
+    for i in range(n):
+        g0 = torch.Generator().manual_seed(1000 + i % n_proto)
+        grid = torch.rand(1, 3, 7, 7, generator=g0)
+        g = torch.Generator().manual_seed(seed + i)
+        grid = (grid + jitter * torch.randn(1, 3, 7, 7, generator=g)).clamp_(0, 1)
+        base = torch.nn.functional.interpolate(grid, size=(h, w), mode="bilinear", align_corners=False)[0]
+        noise = (torch.rand(3, h, w, generator=g) - 0.5) * 0.25
+        img = ((base + noise).clamp_(0, 1) * 255).round_()
+        out[i] = img.permute(1, 2, 0).to(torch.uint8)
+    return out
+
+
 def reference_requests(n, h=224, w=224, seed=2000):
     """Reference-native requests: torch.randn(3,224,224) fp32 CHW (293-project/src/test_scheduler.py:89)."""
     return [torch.randn(3, h, w, generator=torch.Generator().manual_seed(seed + i)) for i in range(n)]
@@ -95,10 +115,50 @@ def _plant_classifier(model, fc: nn.Linear, in_hw, seed, n_proto, planted, mean,
         fc.bias.copy_((-gain * (w @ mu)).float())
 
 
+def _plant_classifier_lda(model, fc: nn.Linear, in_hw, seed, n_proto, planted, mean, std, samples=4, jitter=0.08, lam=1.0):
+    """Linear-discriminant head: `samples` jittered samples of each of the n_proto classes (heldout_images with seeds
+    600000 + 1000 s: disjoint from the evaluation seeds) give class means mu_c and the within-class scatter S_w of the
+    pooled fp32 features; W[:n_proto] = planted' * (S_w + lam * mean diag)^-1 (mu_c - mu), b = -W mu, remaining rows random
+    directions of the same norm.  Unlike the nearest-prototype head this one does not key on one noise realisation: the
+    fp32 reference classifies NEW samples of a class correctly, which is what a top-1 agreement figure needs."""
+    feats = []
+    hook = fc.register_forward_pre_hook(lambda mod, inp: feats.append(inp[0].detach().clone()))
+    with torch.no_grad():
+        for s_i in range(samples):
+            imgs = heldout_images(n_proto, in_hw[0], in_hw[1], seed=600000 + 1000 * s_i, jitter=jitter, n_proto=n_proto)
+            for i in range(0, n_proto, 32):
+                model(normalize_u8(imgs[i:i + 32], mean, std))
+    hook.remove()
+    f = torch.cat(feats).double().view(samples, n_proto, -1)
+    mu_c = f.mean(0)
+    mu = mu_c.mean(0)
+    dw = (f - mu_c).reshape(samples * n_proto, -1)
+    sw = dw.t() @ dw / (samples * n_proto)
+    d = mu_c - mu
+    a = sw + lam * sw.diag().mean() * torch.eye(sw.shape[0], dtype=torch.float64)
+    wp = torch.linalg.solve(a, d.t()).t()
+    g = torch.Generator().manual_seed(seed)
+    w = torch.randn(fc.out_features, fc.in_features, generator=g, dtype=torch.float64)
+    w = w / w.norm(dim=1, keepdim=True) * wp.norm(dim=1).mean()
+    w[:n_proto] = wp
+    gain = planted / float((wp * d).sum(1).mean())
+    with torch.no_grad():
+        fc.weight.copy_((gain * w).float())
+        fc.bias.copy_((-gain * (w @ mu)).float())
+
+
+def _plant(head, *a, **k):
+    if head == "prototype":
+        return _plant_classifier(*a, **k)
+    if head == "lda":
+        return _plant_classifier_lda(*a, **k)
+    raise ValueError("head must be 'prototype' or 'lda'")
+
+
 N_PROTO = 128  # classes 0..N_PROTO-1 are planted on synthetic images 1000..1000+N_PROTO-1
 
 
-def make_resnet50(seed=0, damp=0.25, planted=1.5, n_proto=N_PROTO):
+def make_resnet50(seed=0, damp=0.25, planted=1.5, n_proto=N_PROTO, head="prototype"):
     import torchvision
     torch.manual_seed(seed)
     m = torchvision.models.resnet50(weights=None)
@@ -106,11 +166,11 @@ def make_resnet50(seed=0, damp=0.25, planted=1.5, n_proto=N_PROTO):
         for blk in [b for l in (m.layer1, m.layer2, m.layer3, m.layer4) for b in l]:
             blk.bn3.weight.fill_(damp)
     _calibrate_bn(m, (3, 224, 224), seed + 1)
-    _plant_classifier(m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
+    _plant(head, m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
     return m.eval()
 
 
-def make_shufflenet(seed=0, planted=0.8, n_proto=N_PROTO, bn_bias=1.0):
+def make_shufflenet(seed=0, planted=0.8, n_proto=N_PROTO, bn_bias=1.0, head="prototype"):
     """No residual adds to damp here; a positive BatchNorm beta keeps most ReLU inputs positive, i.e. the random network
     out of the chaotic regime where a 2^-9 rounding perturbation grows ~1.4x per unit (measured with the CPU interpreter)."""
     import torchvision
@@ -121,11 +181,11 @@ def make_shufflenet(seed=0, planted=0.8, n_proto=N_PROTO, bn_bias=1.0):
             if isinstance(mod, nn.BatchNorm2d):
                 mod.bias.fill_(bn_bias)
     _calibrate_bn(m, (3, 224, 224), seed + 1)
-    _plant_classifier(m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
+    _plant(head, m, m.fc, (224, 224), seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
     return m.eval()
 
 
-def make_efficientnet_v2_s(seed=0, damp=0.25, planted=1.0, n_proto=N_PROTO, in_hw=(224, 224)):
+def make_efficientnet_v2_s(seed=0, damp=0.25, planted=1.0, n_proto=N_PROTO, in_hw=(224, 224), head="prototype"):
     import torchvision
     torch.manual_seed(seed)
     m = torchvision.models.efficientnet_v2_s(weights=None)
@@ -135,7 +195,7 @@ def make_efficientnet_v2_s(seed=0, damp=0.25, planted=1.0, n_proto=N_PROTO, in_h
                 if getattr(blk, "use_res_connect", False):
                     blk.block[-1][1].weight.fill_(damp)     # BatchNorm of the block's last conv (residual branch)
     _calibrate_bn(m, (3, in_hw[0], in_hw[1]), seed + 1, batches=2, batch_size=8)
-    _plant_classifier(m, m.classifier[1], in_hw, seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
+    _plant(head, m, m.classifier[1], in_hw, seed + 2, n_proto, planted, IMAGENET_MEAN, IMAGENET_STD)
     return m.eval()
 
 
