@@ -194,6 +194,25 @@ typedef struct b200_engine b200_engine;
  * memory for `max_batch` up front. Not thread-safe: one engine per actor process, like the reference's models dict. */
 B200_API int b200_engine_create(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
                                 b200_engine** out);
+/* Same, with options.  B200_ENGINE_KEEP_BUFFERS: every activation buffer keeps memory of its own, so b200_engine_buffer /
+ * b200_engine_read_buffer see each layer's output after a forward (the per-layer parity tests).  Default (flags = 0):
+ * activation buffers whose lifetimes in the plan do not overlap share addresses -- the engine then holds about what
+ * torch holds for the same forward (`peak_memory_mb` of the reference's profiles, profiling/ModelProfiler.py:85-112,
+ * which 293-project/src/nexus.py:222-226 sums to decide what fits on a GPU); only the model input, the fp32 vectors
+ * and the output stay readable after a forward. */
+#define B200_ENGINE_KEEP_BUFFERS 1u
+B200_API int b200_engine_create_ex(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
+                                   unsigned flags, b200_engine** out);
+/* Prepares `n` batch sizes ahead of traffic: TMA descriptors, one eager pass and the CUDA-graph capture each (the
+ * reference's actor loads its models before serving, scheduler.py:409-417; its first batches pay cuDNN autotuning
+ * instead).  A worker that pads batches to a fixed set of bucket sizes calls this once at load; afterwards b200_infer of
+ * those sizes only replays graphs.  Synchronises `stream`. */
+B200_API int b200_engine_warmup(b200_engine* e, const int* batches, int n, void* stream);
+/* Device memory the engine holds right now (weights, activation arena, tables, staging) and the activation part of it. */
+B200_API int b200_engine_memory(b200_engine* e, size_t* device_bytes, size_t* activation_bytes);
+/* What b200_engine_create_ex(blob, max_batch, flags) would hold, without touching a device: the figure a batch-size
+ * profile reports as peak memory (ModelProfiler.py:355-357 `peak_memory_mb`). */
+B200_API int b200_plan_memory(const void* blob, size_t nbytes, int max_batch, unsigned flags, size_t* device_bytes);
 B200_API void b200_engine_destroy(b200_engine* e);
 B200_API int b200_engine_info(b200_engine* e, int* in_h, int* in_w, int* out_dim, int* max_batch, int* n_ops);
 B200_API int b200_engine_set_graphs(b200_engine* e, int enabled); /* CUDA-graph replay per batch size (default on) */
@@ -254,6 +273,46 @@ B200_API int b200_decode_yolo(b200_engine* e, const float* head, int batch, floa
  * out (host or device, fp32 [batch][out_dim]) receives the result with an async copy on `stream`; NULL skips the copy.
  * Replaces `outputs = model(inputs)` and `outputs.cpu()` (scheduler.py:449-450, 468). No host synchronisation inside. */
 B200_API int b200_infer(b200_engine* e, const void* in_nhwc_bf16, int batch, float* out, void* stream);
+
+/* ---- request ring (what B200Scheduler.submit_request / SlabRequestQueue.get_batch bind) ------------------------------
+ * The per-model FIFO of the reference (293-project/src/scheduler.py:190-372: RequestQueue over ray.util.queue.Queue, a
+ * queue actor reached by RPC, python/ray/util/queue.py:20-305) as a lock-free multi-producer / multi-consumer ring in
+ * caller-provided memory (a shared-memory segment mapped by the submitting process and by every model-actor process).
+ * A request is its raw bytes (uint8 HWC image) in a fixed-size slot plus a 128-byte descriptor; a consumer owns the
+ * slots it popped until it releases them, so queued or in-flight requests are never overwritten.  Host code only. */
+#define B200_RING_ID_BYTES 100
+/* Bytes of memory a ring of `nslots` slots of `slot_bytes` needs (header + descriptors + payload area). */
+B200_API size_t b200_ring_bytes(uint32_t nslots, uint32_t slot_bytes);
+/* RequestQueue.__init__ (scheduler.py:193-222): max_queued is its max_size (2000 at scheduler.py:632); nslots >=
+ * max_queued leaves room for requests that were popped but whose batch is still being copied to a GPU.
+ * `mem` 128-byte aligned, zero or garbage; call once, before any other process uses the ring. */
+B200_API int b200_ring_init(void* mem, size_t bytes, uint32_t nslots, uint32_t slot_bytes, uint32_t max_queued);
+B200_API int b200_ring_layout(void* mem, uint32_t* nslots, uint32_t* slot_bytes, uint32_t* max_queued, uint64_t* payload_off,
+                              uint64_t* total_bytes);
+/* RequestQueue.add_request (scheduler.py:238-254): 1 = queued, 0 = queue full (dropped and counted), < 0 = misuse.
+ * `arrival` is the caller's time.time() (scheduler.py:246). */
+B200_API int b200_ring_push(void* mem, const char* request_id, const void* payload, uint32_t nbytes, int h, int w, int c,
+                            double arrival);
+/* The same for n equal-size requests `stride` bytes apart (an ingress thread that received a burst); ids: n entries of
+ * B200_RING_ID_BYTES, or NULL for "<id_prefix><first_index + i>".  Returns how many were queued. */
+B200_API int b200_ring_push_many(void* mem, int n, const char* ids, const char* id_prefix, long long first_index,
+                                 const void* payloads, size_t stride, uint32_t nbytes, int h, int w, int c, double arrival);
+/* One round of RequestQueue.get_batch (scheduler.py:275-289): claims up to max_items requests in FIFO order, drops the
+ * ones for which  arrival + slo_s < now + expected_latency_s  (scheduler.py:281; counted in *discarded) and returns
+ * the others: slot numbers (payload of slot s at payload_off + s * slot_bytes), sequence numbers (for release), arrival
+ * times, [h, w] pairs, byte counts, ids (B200_RING_ID_BYTES each).  Any output except slots / seqs may be NULL. */
+B200_API int b200_ring_pop(void* mem, int max_items, double now, double expected_latency_s, double slo_s, uint32_t* slots,
+                           uint64_t* seqs, double* arrivals, int32_t* hw, uint32_t* nbytes, char* ids, int* discarded);
+/* Gives popped slots back to the producers (after the batch's host-to-device copy has completed). */
+B200_API int b200_ring_release(void* mem, const uint64_t* seqs, int n);
+B200_API long long b200_ring_qsize(void* mem);
+/* RequestQueue.record_batch_completion (scheduler.py:324-341): returns the number of SLO violations recorded. */
+B200_API int b200_ring_record(void* mem, double latency_ms, int n_requests, double slo_ms);
+/* RequestQueue.get_stats (scheduler.py:343-372) over the same window of latencies the reference's list would hold:
+ * out[0..10] = total_requests, dropped_requests, slo_violations, queue_size, last_latency, avg_latency, p95_latency,
+ * p99_latency, discarded_stale, completed_requests, completed_batches.  Visible to every process that maps the ring
+ * (the reference's actors update a pickled copy of the metrics that the driver never sees). */
+B200_API int b200_ring_stats(void* mem, double* out, int n_out);
 
 #ifdef __cplusplus
 }

@@ -11,7 +11,8 @@ Engine::~Engine() {
   cudaSetDevice(device);
   for (auto& kv : plans)
     if (kv.second->graph) cudaGraphExecDestroy(kv.second->graph);
-  for (char* p : buf_dev) cudaFree(p);
+  cudaFree(arena_dev);
+  cudaFree(vec_dev);
   cudaFree(weights_dev);
   cudaFree(lut_dev);
   cudaFree(stage_dev);
@@ -23,7 +24,7 @@ Engine::~Engine() {
   if (capture_stream) cudaStreamDestroy(capture_stream);
 }
 
-int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_batch_in, int device_in) {
+int Engine::parse(const char* kind_in, const void* blob, size_t nbytes, int max_batch_in) {
   if (!blob || nbytes < sizeof(BlobHeader)) return fail(B200_ERR_BLOB, "engine: blob too small");
   memcpy(&hdr, blob, sizeof(hdr));
   if (memcmp(hdr.magic, "B200PLAN", 8) != 0 || hdr.version != 1) return fail(B200_ERR_BLOB, "engine: bad magic/version");
@@ -36,13 +37,6 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     return fail(B200_ERR_BLOB, "engine: truncated blob");
   if (max_batch_in <= 0) return fail(B200_ERR_INVALID, "engine: max_batch must be positive");
   max_batch = max_batch_in;
-  device = device_in;
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(B200_ERR_NO_DEVICE, "engine: no CUDA device");
-  B200_CUDA_OK(cudaSetDevice(device));
-  cudaDeviceProp prop;
-  B200_CUDA_OK(cudaGetDeviceProperties(&prop, device));
-  if (prop.major != 10) return fail(B200_ERR_NO_DEVICE, std::string("engine: needs an sm_100 device, found ") + prop.name);
 
   const char* base = static_cast<const char*>(blob);
   bufs.resize(hdr.n_bufs);
@@ -55,7 +49,8 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     const int ids[3] = {o.p[0], o.p[3], o.p[6]};
     for (int k = 0; k < 3; ++k)
       if (ids[k] >= int(hdr.n_bufs) || (k < 2 && ids[k] < 0)) return fail(B200_ERR_BLOB, "engine: op references unknown buffer");
-    if ((o.type == OP_DWCONV || o.type == OP_SCALE || o.type == OP_SE_SCALE) && (o.p[12] < 0 || o.p[12] >= int(hdr.n_bufs)))
+    if ((o.type == OP_DWCONV || o.type == OP_SCALE || o.type == OP_SE_SCALE || o.type == OP_SHUFFLE ||
+         o.type == OP_YOLO_DECODE) && (o.p[12] < 0 || o.p[12] >= int(hdr.n_bufs)))
       return fail(B200_ERR_BLOB, "engine: op references unknown side buffer");
     if (o.type == OP_DWCONV && o.p[12] > 0) {   // fused squeeze: the side buffer must hold every strip's channel sums
       const BufRec& sb = bufs[o.p[12]];
@@ -94,15 +89,123 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
     for (int64_t off : offs)
       if (off >= int64_t(hdr.weights_bytes)) return fail(B200_ERR_BLOB, "engine: weight offset out of range");
   }
+  return B200_OK;
+}
 
+// Buffers an op reads or writes (mirrors run_ops): ids[] gets up to 6 entries, returns how many.
+static int op_buffers(const OpRec& o, int ids[6]) {
+  int n = 0;
+  const int32_t* p = o.p;
+  ids[n++] = p[0];
+  ids[n++] = p[3];
+  switch (o.type) {
+    case OP_CONV:
+      if (p[6] >= 0) ids[n++] = p[6];
+      if (p[13] > 0) ids[n++] = p[13] - 1;
+      if (p[17] > 0) ids[n++] = p[17] - 1;
+      break;
+    case OP_GATHER_CONV:
+      if (p[6] >= 0) ids[n++] = p[6];
+      break;
+    case OP_DWCONV:
+      if (p[12] > 0) ids[n++] = p[12];
+      break;
+    case OP_SCALE: case OP_SE_SCALE: case OP_SHUFFLE: case OP_YOLO_DECODE:
+      ids[n++] = p[12];
+      break;
+    default:
+      break;
+  }
+  return n;
+}
+
+// Activation memory by liveness.  A bf16 buffer is live from the first op that touches it to the last one; two buffers
+// whose live ranges do not intersect may share addresses (the ops run in plan order on one stream, and a kernel launched
+// with the programmatic edge still waits for its predecessor to finish before it touches global memory).  Placement:
+// largest buffer first, each at the lowest offset that is free of every already-placed buffer alive at the same time.
+// Not shared, on purpose: the model input (a caller may read it back, or collate the next batch, at any time) and the
+// fp32 vector buffers (tiny; and stale fp32 bits read as bf16 padding channels could be NaN patterns, which zero weights
+// do not cancel -- stale bf16 activations are always finite).
+void Engine::plan_arena(bool reuse, std::vector<size_t>* offsets, size_t* arena, size_t* vec) const {
+  const int nb = static_cast<int>(bufs.size());
+  std::vector<int> first(nb, 1 << 30), last(nb, -1);
+  for (int i = 0; i < static_cast<int>(ops.size()); ++i) {
+    int ids[6];
+    const int n = op_buffers(ops[i], ids);
+    for (int k = 0; k < n; ++k) {
+      first[ids[k]] = std::min(first[ids[k]], i);
+      last[ids[k]] = std::max(last[ids[k]], i);
+    }
+  }
+  auto bytes_of = [&](int b) { return (buf_bytes_per_image(b) * size_t(max_batch) + 256 + 255) / 256 * 256; };
+  offsets->assign(nb, 0);
+  size_t vtop = 0, atop = 0;
+  std::vector<int> order;
+  for (int b = 0; b < nb; ++b) {
+    if (bufs[b].dtype == 1) {
+      (*offsets)[b] = vtop;
+      vtop += bytes_of(b);
+    } else {
+      order.push_back(b);
+    }
+  }
+  std::sort(order.begin(), order.end(), [&](int x, int y) {
+    const size_t bx = bytes_of(x), by = bytes_of(y);
+    return bx != by ? bx > by : x < y;
+  });
+  std::vector<int> placed;
+  for (int b : order) {
+    const bool pinned = !reuse || b == hdr.in_buf || last[b] < 0;
+    size_t off = 0;
+    if (pinned) {
+      first[b] = -1;            // alive for the whole plan
+      last[b] = 1 << 30;
+    }
+    // candidate offsets: 0 and the end of every conflicting buffer; take the lowest that fits
+    std::vector<std::pair<size_t, size_t>> busy;   // [begin, end) of placed buffers alive together with b
+    for (int q : placed)
+      if (!(last[q] < first[b] || last[b] < first[q])) busy.emplace_back((*offsets)[q], (*offsets)[q] + bytes_of(q));
+    std::sort(busy.begin(), busy.end());
+    for (const auto& iv : busy) {
+      if (off + bytes_of(b) <= iv.first) break;
+      off = std::max(off, iv.second);
+    }
+    (*offsets)[b] = off;
+    atop = std::max(atop, off + bytes_of(b));
+    placed.push_back(b);
+  }
+  *arena = std::max<size_t>(atop, 256);
+  *vec = std::max<size_t>(vtop, 256);
+}
+
+size_t Engine::fixed_bytes() const {
+  return std::max<uint64_t>(hdr.weights_bytes, 256) + sizeof(uint16_t) * 3 * 256 + sizeof(CollateItem) * size_t(max_batch);
+}
+
+int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_batch_in, int device_in, unsigned flags) {
+  B200_TRY(parse(kind_in, blob, nbytes, max_batch_in));
+  device = device_in;
+  keep_buffers = (flags & B200_ENGINE_KEEP_BUFFERS) != 0;
+  if (const char* e = getenv("B200_ARENA_REUSE"))
+    if (e[0] == '0') keep_buffers = true;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(B200_ERR_NO_DEVICE, "engine: no CUDA device");
+  B200_CUDA_OK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  B200_CUDA_OK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10) return fail(B200_ERR_NO_DEVICE, std::string("engine: needs an sm_100 device, found ") + prop.name);
+
+  const char* base = static_cast<const char*>(blob);
   B200_CUDA_OK(cudaMalloc(&weights_dev, std::max<uint64_t>(hdr.weights_bytes, 256)));
   B200_CUDA_OK(cudaMemcpy(weights_dev, base + hdr.weights_offset, hdr.weights_bytes, cudaMemcpyHostToDevice));
+  std::vector<size_t> offsets;
+  plan_arena(!keep_buffers, &offsets, &arena_bytes, &vec_bytes);
+  B200_CUDA_OK(cudaMalloc(&arena_dev, arena_bytes));
+  B200_CUDA_OK(cudaMemset(arena_dev, 0, arena_bytes));
+  B200_CUDA_OK(cudaMalloc(&vec_dev, vec_bytes));
+  B200_CUDA_OK(cudaMemset(vec_dev, 0, vec_bytes));
   buf_dev.assign(hdr.n_bufs, nullptr);
-  for (uint32_t b = 0; b < hdr.n_bufs; ++b) {
-    const size_t bytes = buf_bytes_per_image(b) * size_t(max_batch) + 256;
-    B200_CUDA_OK(cudaMalloc(&buf_dev[b], bytes));
-    B200_CUDA_OK(cudaMemset(buf_dev[b], 0, bytes));
-  }
+  for (uint32_t b = 0; b < hdr.n_bufs; ++b) buf_dev[b] = (bufs[b].dtype == 1 ? vec_dev : arena_dev) + offsets[b];
   uint16_t lut[3 * 256];
   build_norm_lut(hdr.mean, hdr.stdv, lut);
   B200_CUDA_OK(cudaMalloc(&lut_dev, sizeof(lut)));
@@ -111,6 +214,7 @@ int Engine::init(const char* kind_in, const void* blob, size_t nbytes, int max_b
   B200_CUDA_OK(cudaMallocHost(&items_host, sizeof(CollateItem) * max_batch * ITEM_SLOTS));
   for (auto& ev : item_events) B200_CUDA_OK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   B200_CUDA_OK(cudaStreamCreateWithFlags(&capture_stream, cudaStreamNonBlocking));
+  device_bytes = fixed_bytes() + arena_bytes + vec_bytes;
   return B200_OK;
 }
 
@@ -277,6 +381,23 @@ int Engine::run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last) {
   return B200_OK;
 }
 
+static int capture_plan(Engine& e, BatchPlan& plan) {
+  const int n = static_cast<int>(plan.ops.size());
+  cudaGraph_t g = nullptr;
+  B200_CUDA_OK(cudaStreamBeginCapture(e.capture_stream, cudaStreamCaptureModeThreadLocal));
+  int rc = e.run_ops(plan, e.capture_stream, 0, n - 1);
+  cudaError_t err = cudaStreamEndCapture(e.capture_stream, &g);
+  if (rc != 0) {
+    if (g) cudaGraphDestroy(g);
+    return rc;
+  }
+  if (err != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(err));
+  err = cudaGraphInstantiate(&plan.graph, g, 0);
+  cudaGraphDestroy(g);
+  if (err != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(err));
+  return B200_OK;
+}
+
 int Engine::run(int batch, cudaStream_t stream) {
   if (batch <= 0 || batch > max_batch)
     return fail(B200_ERR_INVALID, "engine: batch " + std::to_string(batch) + " outside [1, " + std::to_string(max_batch) + "]");
@@ -290,22 +411,26 @@ int Engine::run(int batch, cudaStream_t stream) {
     launches += n;
     return B200_OK;
   }
-  if (!plan->graph) {
-    cudaGraph_t g = nullptr;
-    B200_CUDA_OK(cudaStreamBeginCapture(capture_stream, cudaStreamCaptureModeThreadLocal));
-    int rc = run_ops(*plan, capture_stream, 0, n - 1);
-    cudaError_t e = cudaStreamEndCapture(capture_stream, &g);
-    if (rc != 0) {
-      if (g) cudaGraphDestroy(g);
-      return rc;
-    }
-    if (e != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph capture: ") + cudaGetErrorString(e));
-    e = cudaGraphInstantiate(&plan->graph, g, 0);
-    cudaGraphDestroy(g);
-    if (e != cudaSuccess) return fail(B200_ERR_CUDA, std::string("graph instantiate: ") + cudaGetErrorString(e));
-  }
+  if (!plan->graph) B200_TRY(capture_plan(*this, *plan));
   B200_CUDA_OK(cudaGraphLaunch(plan->graph, stream));
   launches += n;
+  return B200_OK;
+}
+
+// Everything the first two calls of a batch size would do (descriptors, eager pass, graph capture), done up front on
+// whatever the buffers hold, so that the first served batch of that size already replays a graph.
+int Engine::warm(int batch, cudaStream_t stream) {
+  if (batch <= 0 || batch > max_batch) return fail(B200_ERR_INVALID, "engine: warm-up batch outside [1, max_batch]");
+  BatchPlan* plan = nullptr;
+  B200_TRY(plan_for(batch, &plan));
+  const int n = static_cast<int>(plan->ops.size());
+  if (!plan->warmed) {
+    B200_TRY(run_ops(*plan, stream, 0, n - 1));
+    B200_CUDA_OK(cudaStreamSynchronize(stream));
+    plan->warmed = true;
+    launches += n;
+  }
+  if (use_graphs && !plan->graph) B200_TRY(capture_plan(*this, *plan));
   return B200_OK;
 }
 
@@ -320,11 +445,16 @@ extern "C" {
 
 int b200_engine_create(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
                        b200_engine** out) {
+  return b200_engine_create_ex(model_kind, blob, nbytes, max_batch, device, 0u, out);
+}
+
+int b200_engine_create_ex(const char* model_kind, const void* blob, size_t nbytes, int max_batch, int device,
+                          unsigned flags, b200_engine** out) {
   if (!out) return fail(B200_ERR_INVALID, "b200_engine_create: out is null");
   *out = nullptr;
   b200_engine* h = new (std::nothrow) b200_engine;
   if (!h) return fail(B200_ERR_INVALID, "b200_engine_create: out of host memory");
-  int rc = h->e.init(model_kind, blob, nbytes, max_batch, device);
+  int rc = h->e.init(model_kind, blob, nbytes, max_batch, device, flags);
   if (rc != 0) {
     std::string msg = last_error_cstr();
     delete h;
@@ -335,6 +465,32 @@ int b200_engine_create(const char* model_kind, const void* blob, size_t nbytes, 
 }
 
 void b200_engine_destroy(b200_engine* h) { delete h; }
+
+int b200_engine_warmup(b200_engine* h, const int* batches, int n, void* stream_) {
+  if (!h || (n > 0 && !batches)) return fail(B200_ERR_INVALID, "b200_engine_warmup: null argument");
+  B200_CUDA_OK(cudaSetDevice(h->e.device));
+  for (int i = 0; i < n; ++i) B200_TRY(h->e.warm(batches[i], static_cast<cudaStream_t>(stream_)));
+  B200_CUDA_OK(cudaStreamSynchronize(static_cast<cudaStream_t>(stream_)));
+  return B200_OK;
+}
+
+int b200_engine_memory(b200_engine* h, size_t* device_bytes, size_t* activation_bytes) {
+  if (!h) return fail(B200_ERR_INVALID, "null engine");
+  if (device_bytes) *device_bytes = h->e.device_bytes;
+  if (activation_bytes) *activation_bytes = h->e.arena_bytes + h->e.vec_bytes;
+  return B200_OK;
+}
+
+int b200_plan_memory(const void* blob, size_t nbytes, int max_batch, unsigned flags, size_t* device_bytes) {
+  if (!device_bytes) return fail(B200_ERR_INVALID, "b200_plan_memory: null output");
+  Engine e;
+  B200_TRY(e.parse(nullptr, blob, nbytes, max_batch));
+  std::vector<size_t> offsets;
+  size_t arena = 0, vec = 0;
+  e.plan_arena((flags & B200_ENGINE_KEEP_BUFFERS) == 0, &offsets, &arena, &vec);
+  *device_bytes = e.fixed_bytes() + arena + vec;
+  return B200_OK;
+}
 
 int b200_engine_info(b200_engine* h, int* in_h, int* in_w, int* out_dim, int* max_batch, int* n_ops) {
   if (!h) return fail(B200_ERR_INVALID, "null engine");
@@ -457,10 +613,12 @@ int b200_collate(b200_engine* h, const void* packed, const uint64_t* offsets, co
   if (!src_on_device && n > 0) {
     if (packed_bytes > e.stage_bytes) {
       if (e.stage_dev) B200_CUDA_OK(cudaFree(e.stage_dev));
+      e.device_bytes -= e.stage_bytes;
       e.stage_dev = nullptr;
       e.stage_bytes = 0;
       const size_t want = packed_bytes + packed_bytes / 4 + 4096;
       B200_CUDA_OK(cudaMalloc(&e.stage_dev, want));
+      e.device_bytes += want;
       e.stage_bytes = want;
     }
     B200_CUDA_OK(cudaMemcpyAsync(e.stage_dev, packed, packed_bytes, cudaMemcpyHostToDevice, stream));
@@ -487,7 +645,10 @@ int b200_collate_f32(b200_engine* h, const float* stacked_chw, int n, int padded
   const size_t per = size_t(3) * e.hdr.in_h * e.hdr.in_w;
   const float* src = stacked_chw;
   if (!src_on_device && n > 0) {
-    if (!e.stage_f32_dev) B200_CUDA_OK(cudaMalloc(&e.stage_f32_dev, per * sizeof(float) * e.max_batch));
+    if (!e.stage_f32_dev) {
+      B200_CUDA_OK(cudaMalloc(&e.stage_f32_dev, per * sizeof(float) * e.max_batch));
+      e.device_bytes += per * sizeof(float) * e.max_batch;
+    }
     B200_CUDA_OK(cudaMemcpyAsync(e.stage_f32_dev, stacked_chw, per * sizeof(float) * n, cudaMemcpyHostToDevice, stream));
     src = e.stage_f32_dev;
   }

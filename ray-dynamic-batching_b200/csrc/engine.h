@@ -66,7 +66,12 @@ struct Engine {
   int device = 0;
   bool use_graphs = true;
   char* weights_dev = nullptr;
-  std::vector<char*> buf_dev;
+  std::vector<char*> buf_dev;        // per buffer: its address inside `arena_dev` (bf16) or `vec_dev` (fp32)
+  char* arena_dev = nullptr;         // bf16 activations, buffers with disjoint lifetimes share addresses (plan_arena)
+  char* vec_dev = nullptr;           // fp32 vector buffers (pooled features, SE sums / gates, logits): never shared
+  size_t arena_bytes = 0, vec_bytes = 0;
+  size_t device_bytes = 0;           // everything this engine holds on the device right now
+  bool keep_buffers = false;         // B200_ENGINE_KEEP_BUFFERS: every buffer keeps its own memory (debug reads)
   uint16_t* lut_dev = nullptr;
   // collate staging
   uint8_t* stage_dev = nullptr;
@@ -82,7 +87,12 @@ struct Engine {
   long long launches = 0;  // kernels launched so far (graph nodes counted per replay)
 
   ~Engine();
-  int init(const char* kind, const void* blob, size_t nbytes, int max_batch, int device);
+  int init(const char* kind, const void* blob, size_t nbytes, int max_batch, int device, unsigned flags = 0);
+  int parse(const char* kind, const void* blob, size_t nbytes, int max_batch);   // header + tables, validated; no CUDA
+  // offsets of every buffer inside the two device allocations for `max_batch`; returns their sizes
+  void plan_arena(bool reuse, std::vector<size_t>* offsets, size_t* arena, size_t* vec) const;
+  size_t fixed_bytes() const;        // weights + tables + collate item ring: what init() allocates besides the buffers
+  int warm(int batch, cudaStream_t stream);   // eager pass + graph capture for one batch size
   View view(int buf, int coff, int c, int batch) const;
   int plan_for(int batch, BatchPlan** out);
   int run_ops(BatchPlan& plan, cudaStream_t stream, int first, int last);

@@ -18,8 +18,25 @@ from . import lowering as _lowering
 COLLATE_IDENTITY, COLLATE_PAD, COLLATE_RESIZE, COLLATE_LETTERBOX = 0, 1, 2, 3
 
 
+def default_buckets(max_batch):
+    """1, 2, 4, 8, then steps of 8 to 64, of 32 to 256, of 64 beyond: padding waste stays under ~25 % from 8 up, under
+    ~12 % from 64 up, and a full-size engine (512) prepares 26 graphs."""
+    b = [1, 2, 4, 8]
+    b += list(range(16, 65, 8)) + list(range(96, 257, 32)) + list(range(320, 1025, 64))
+    return [x for x in b if x <= max_batch] + ([max_batch] if max_batch not in b else [])
+
+
+def plan_memory_bytes(blob, max_batch, keep_buffers=False):
+    """Device bytes an engine created from `blob` at `max_batch` holds (no device needed)."""
+    out = ctypes.c_size_t()
+    _lib.check(_lib.load().b200_plan_memory(blob, len(blob), int(max_batch), _lib.ENGINE_KEEP_BUFFERS if keep_buffers else 0,
+                                            ctypes.byref(out)), "b200_plan_memory")
+    return out.value
+
+
 class B200Model:
-    def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True, in_hw=None):
+    def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True, in_hw=None,
+                 keep_buffers=False, buckets=None):
         if not torch.cuda.is_available():
             raise _lib.B200Error("B200Model needs a CUDA device (sm_100); there is no CPU fallback")
         self.lib = _lib.load()
@@ -39,8 +56,9 @@ class B200Model:
         self.max_batch = max_batch
         self._h = ctypes.c_void_p()
         torch.cuda.set_device(self.device)
-        _lib.check(self.lib.b200_engine_create(kind.encode(), blob, len(blob), max_batch, device,
-                                               ctypes.byref(self._h)), "b200_engine_create")
+        flags = _lib.ENGINE_KEEP_BUFFERS if keep_buffers else 0
+        _lib.check(self.lib.b200_engine_create_ex(kind.encode(), blob, len(blob), max_batch, device, flags,
+                                                  ctypes.byref(self._h)), "b200_engine_create")
         ih, iw, od, mb, nops = (ctypes.c_int() for _ in range(5))
         _lib.check(self.lib.b200_engine_info(self._h, ih, iw, od, mb, nops))
         self.in_h, self.in_w, self.out_dim, self.n_ops = ih.value, iw.value, od.value, nops.value
@@ -51,6 +69,11 @@ class B200Model:
         self._pinned = None
         self._slots = None
         self._slot_i = 0
+        # batch-size buckets: a served batch of n requests is padded (zero images) to the next bucket, so the engine only
+        # ever runs the sizes it captured graphs for at load.  None = every size runs as is (one graph per distinct size).
+        self.buckets = None
+        if buckets is not None:
+            self.set_buckets(default_buckets(max_batch) if buckets == "auto" else buckets)
 
     # ---- lifecycle (mirrors .eval()/.to()/.cpu() so the reference's load/unload code keeps working) ----
     def eval(self):
@@ -72,6 +95,33 @@ class B200Model:
             self.close()
         except Exception:
             pass
+
+    # ---- buckets / memory ----
+    def set_buckets(self, buckets, warm=True):
+        b = sorted({int(x) for x in buckets if 0 < int(x) <= self.max_batch} | {self.max_batch})
+        self.buckets = b
+        if warm:
+            self.warmup(b)
+
+    def bucket_for(self, n):
+        """Smallest prepared batch size >= n (n itself when the engine has no buckets)."""
+        if not self.buckets:
+            return n
+        import bisect
+        i = bisect.bisect_left(self.buckets, n)
+        if i == len(self.buckets):
+            raise _lib.B200Error("batch %d exceeds engine max_batch %d" % (n, self.max_batch))
+        return self.buckets[i]
+
+    def warmup(self, batches):
+        arr = (ctypes.c_int * len(batches))(*[int(x) for x in batches])
+        _lib.check(self.lib.b200_engine_warmup(self._h, arr, len(batches), self._stream()), "b200_engine_warmup")
+
+    def memory_bytes(self):
+        """(device bytes the engine holds now, the activation part of it)."""
+        tot, act = ctypes.c_size_t(), ctypes.c_size_t()
+        _lib.check(self.lib.b200_engine_memory(self._h, ctypes.byref(tot), ctypes.byref(act)))
+        return tot.value, act.value
 
     # ---- helpers ----
     def _stream(self):
@@ -153,6 +203,8 @@ class B200Model:
         return out[:n, :self.out_logical]
 
     # ---- pipelined host path: the H2D copy of batch i+1 overlaps the forward of batch i ----
+    N_SLOTS = 3
+
     class _Slot:
         def __init__(self, model):
             self.staging = None
@@ -160,37 +212,63 @@ class B200Model:
             self.copied = torch.cuda.Event()
             self.done = torch.cuda.Event()
             self.n = 0
+            self.busy = False
             self.out_logical = model.out_logical
 
         def result(self):
-            """Blocks until this batch is finished; returns the fp32 outputs [n, out] in pinned host memory."""
+            """Blocks until this batch is finished; returns the fp32 outputs [n, out] -- a VIEW of this slot's pinned
+            buffer, valid until the slot is handed out again (N_SLOTS - 1 submissions later): copy it to keep it."""
             self.done.synchronize()
+            self.busy = False
             return self.out_host[:self.n, :self.out_logical]
 
-    def infer_packed_async(self, packed_host, offsets, hw, n, padded_batch=None, mode=COLLATE_IDENTITY, total_bytes=None):
-        """Asynchronous engine-native call: `packed_host` (pinned uint8) -> H2D on a side stream -> collate -> forward ->
-        D2H into a pinned slot.  Returns a handle whose .result() waits for this batch only.  Two slots: at most two
-        batches are in flight, and the copy of one overlaps the compute of the other."""
+    def _next_slot(self, total):
         if self._slots is None:
-            self._slots = [B200Model._Slot(self), B200Model._Slot(self)]
+            self._slots = [B200Model._Slot(self) for _ in range(self.N_SLOTS)]
             self._copy_stream = torch.cuda.Stream(self.device)
-        slot = self._slots[self._slot_i % 2]
+        slot = self._slots[self._slot_i % self.N_SLOTS]
         self._slot_i += 1
-        slot.done.synchronize()                      # the previous user of this slot has been consumed
-        total = int(total_bytes if total_bytes is not None else packed_host.numel())
+        if slot.busy:
+            raise _lib.B200Error("more than %d batches in flight: collect .result() of earlier batches first"
+                                 % (self.N_SLOTS - 1))
+        slot.done.synchronize()                      # the previous user of this slot has left the GPU
         if slot.staging is None or slot.staging.numel() < total:
             slot.staging = torch.empty(total + total // 4 + 4096, dtype=torch.uint8, device=self.device)
+        return slot
+
+    def _launch_slot(self, slot, offsets, hw, n, padded_batch, mode, total):
         compute = torch.cuda.current_stream(self.device)
-        with torch.cuda.stream(self._copy_stream):
-            slot.staging[:total].copy_(packed_host[:total], non_blocking=True)
-            slot.copied.record(self._copy_stream)
         compute.wait_event(slot.copied)
         pb = padded_batch or n
         self.collate_u8(slot.staging, offsets, hw, n, pb, mode, total)
         _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(slot.out_host), self._stream()), "b200_infer")
         slot.n = n
+        slot.busy = True
         slot.done.record(compute)
         return slot
+
+    def infer_packed_async(self, packed_host, offsets, hw, n, padded_batch=None, mode=COLLATE_IDENTITY, total_bytes=None):
+        """Asynchronous engine-native call: `packed_host` (pinned uint8) -> H2D on a side stream -> collate -> forward ->
+        D2H into a pinned slot.  Returns a handle whose .result() waits for this batch only.  N_SLOTS - 1 batches may be
+        in flight: the copy of one overlaps the compute of the other."""
+        total = int(total_bytes if total_bytes is not None else packed_host.numel())
+        slot = self._next_slot(total)
+        with torch.cuda.stream(self._copy_stream):
+            slot.staging[:total].copy_(packed_host[:total], non_blocking=True)
+            slot.copied.record(self._copy_stream)
+        return self._launch_slot(slot, offsets, hw, n, padded_batch, mode, total)
+
+    def infer_runs_async(self, slab, runs, offsets, hw, n, padded_batch=None, mode=COLLATE_IDENTITY, total_bytes=None):
+        """Same for a batch that sits in a page-locked request slab as a few contiguous runs of slots:
+        runs = [(slab byte offset, byte count, staging byte offset)], one DMA each; `offsets` are the images' positions
+        in the staging buffer."""
+        total = int(total_bytes)
+        slot = self._next_slot(total)
+        with torch.cuda.stream(self._copy_stream):
+            for src, nbytes, dst in runs:
+                slot.staging[dst:dst + nbytes].copy_(slab[src:src + nbytes], non_blocking=True)
+            slot.copied.record(self._copy_stream)
+        return self._launch_slot(slot, offsets, hw, n, padded_batch, mode, total)
 
     def decode_yolo(self, batch, conf=0.25, iou=0.45, max_det=300, head=None):
         """Class-aware NMS on the device over the [batch, 84, A] head output of the last forward (or `head`).

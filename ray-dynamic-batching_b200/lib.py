@@ -67,6 +67,10 @@ SIGNATURES = {
     "b200_shuffle_concat_nhwc": (c_int, [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                          c_void_p]),
     "b200_engine_create": (c_int, [c_char_p, c_void_p, c_size_t, c_int, c_int, ctypes.POINTER(c_void_p)]),
+    "b200_engine_create_ex": (c_int, [c_char_p, c_void_p, c_size_t, c_int, c_int, ctypes.c_uint, ctypes.POINTER(c_void_p)]),
+    "b200_engine_warmup": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "b200_engine_memory": (c_int, [c_void_p, ctypes.POINTER(c_size_t), ctypes.POINTER(c_size_t)]),
+    "b200_plan_memory": (c_int, [c_void_p, c_size_t, c_int, ctypes.c_uint, ctypes.POINTER(c_size_t)]),
     "b200_engine_destroy": (None, [c_void_p]),
     "b200_engine_info": (c_int, [c_void_p, c_int_p, c_int_p, c_int_p, c_int_p, c_int_p]),
     "b200_engine_set_graphs": (c_int, [c_void_p, c_int]),
@@ -81,7 +85,22 @@ SIGNATURES = {
     "b200_collate_f32": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "b200_decode_yolo": (c_int, [c_void_p, c_void_p, c_int, c_float, c_float, c_int, c_void_p, c_void_p, c_void_p]),
     "b200_infer": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "b200_ring_bytes": (c_size_t, [ctypes.c_uint32, ctypes.c_uint32]),
+    "b200_ring_init": (c_int, [c_void_p, c_size_t, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32]),
+    "b200_ring_layout": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b200_ring_push": (c_int, [c_void_p, c_char_p, c_void_p, ctypes.c_uint32, c_int, c_int, c_int, ctypes.c_double]),
+    "b200_ring_push_many": (c_int, [c_void_p, c_int, c_void_p, c_char_p, ctypes.c_longlong, c_void_p, c_size_t,
+                                    ctypes.c_uint32, c_int, c_int, c_int, ctypes.c_double]),
+    "b200_ring_pop": (c_int, [c_void_p, c_int, ctypes.c_double, ctypes.c_double, ctypes.c_double, c_void_p, c_void_p,
+                              c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b200_ring_release": (c_int, [c_void_p, c_void_p, c_int]),
+    "b200_ring_qsize": (ctypes.c_longlong, [c_void_p]),
+    "b200_ring_record": (c_int, [c_void_p, ctypes.c_double, c_int, ctypes.c_double]),
+    "b200_ring_stats": (c_int, [c_void_p, c_void_p, c_int]),
 }
+
+
+ENGINE_KEEP_BUFFERS = 1   # B200_ENGINE_KEEP_BUFFERS in include/b200infer.h
 
 
 class B200Error(RuntimeError):

@@ -60,25 +60,58 @@ class _DequeBacking:
 
 
 class PinnedSlab:
-    """Ring of pinned host memory holding uint8 request payloads in arrival order (16-byte aligned slots)."""
+    """Ring of pinned host memory holding uint8 request payloads in arrival order (16-byte aligned slots).
+
+    A payload stays where it is until it is released -- by get_batch for a request it discards, by
+    record_batch_completion for the requests of a finished batch.  push() never overwrites an unreleased payload: when
+    the ring has no room it returns None and the request is queued without a slab position (its tensor still travels
+    in the tuple, so the worker packs it the slow way)."""
 
     def __init__(self, nbytes):
         import torch
         self.buf = torch.empty(nbytes, dtype=torch.uint8, pin_memory=torch.cuda.is_available())
         self.nbytes = nbytes
-        self.head = 0
+        self.head = 0                 # next write position
+        self.live = deque()           # [offset, need, released] in push order; live[0] is the oldest payload still held
+        self.by_off = {}
+
+    def _place(self, need):
+        """Offset for `need` bytes that overlaps no held payload, or None.  Held payloads form one arc of the ring from the
+        oldest (live[0]) to head; releases out of order only leave holes inside the arc, which are not reused."""
+        if not self.live:
+            self.head = 0
+            return 0 if need <= self.nbytes else None
+        tail = self.live[0][0]
+        if self.head > tail:                                   # arc [tail, head): free space is [head, end) and [0, tail)
+            if self.head + need <= self.nbytes:
+                return self.head
+            return 0 if need <= tail else None
+        return self.head if self.head + need <= tail else None  # arc wraps the end: free space is [head, tail)
 
     def push(self, tensor):
         n = tensor.numel()
         need = (n + 15) // 16 * 16
         if need > self.nbytes:
             raise ValueError("request larger than the pinned slab")
-        if self.head + need > self.nbytes:
-            self.head = 0                      # wrap: the oldest payloads are long consumed (queue is bounded)
-        off = self.head
+        off = self._place(need)
+        if off is None:
+            return None
         self.buf[off:off + n].copy_(tensor.reshape(-1))
-        self.head += need
+        ent = [off, need, False]
+        self.live.append(ent)
+        self.by_off[off] = ent
+        self.head = off + need
         return off
+
+    def release(self, off):
+        ent = self.by_off.pop(off, None)
+        if ent is None:
+            return
+        ent[2] = True
+        while self.live and self.live[0][2]:
+            self.live.popleft()
+        if not self.live:
+            self.head = 0
 
 
 class B200RequestQueue:
@@ -151,6 +184,8 @@ class B200RequestQueue:
                     request_id, input_tensor, arrival_time = item[0], item[1], item[2]
                     if self._stale(arrival_time, batch_size):
                         discard += 1
+                        if len(item) > 3 and item[3] is not None and self.slab is not None:
+                            self.slab.release(item[3])
                         continue
                     request_ids.append(request_id)
                     inputs.append(input_tensor)
@@ -169,6 +204,10 @@ class B200RequestQueue:
         """scheduler.py:324-341."""
         latency = (completion_time - batch.arrival_time) * 1000
         count = 0
+        if getattr(batch, "slab", None) is not None and batch.slab_offsets:
+            for off in batch.slab_offsets:                     # the batch has left the host: its payloads may be overwritten
+                batch.slab.release(off)
+            batch.slab_offsets = None
         self.metrics['last_latency'] = latency
         for _ in batch.request_ids:
             if latency > self.slo_target:

@@ -58,13 +58,17 @@ def test_collate_f32_bit_exact(resnet):
 
 def test_per_layer_against_plan_interpreter(resnet):
     """Every activation buffer of the CUDA engine vs the CPU interpreter of the same plan (same bf16 storage points)."""
-    module, model = resnet
+    module, shared = resnet
+    # an engine of its own that keeps every buffer: the serving engines let buffers with disjoint lifetimes share memory
+    model = B200Model(shared.kind, blob=shared.blob, max_batch=4, keep_buffers=True)
+    model.op_names = shared.op_names
     n = 3
     imgs = synth.synthetic_images(n)
     x = synth.normalize_u8(imgs, synth.IMAGENET_MEAN, synth.IMAGENET_STD)
     it = PlanInterpreter(model.blob, lowering.parse_blob)
     _, B = it.run(to_nhwc4(x), keep_all=True)
     logits = model.infer_u8(list(imgs))
+    assert torch.equal(logits.cpu(), shared.infer_u8(list(imgs)).cpu()), "shared and unshared activation memory must agree"
     torch.cuda.synchronize()
     worst = []
     for op_i, op in enumerate(it.ops):
@@ -84,6 +88,11 @@ def test_per_layer_against_plan_interpreter(resnet):
         assert err <= 0.06 * scale, "op %d (%s): max err %.4g vs scale %.4g" % (op_i, model.op_names[op_i], err, scale)
     worst.sort(reverse=True)
     print("worst layers:", worst[:3])
+    keep_total, _ = model.memory_bytes()
+    model.close()
+    share_total, share_act = shared.memory_bytes()
+    print("engine memory at max_batch %d: %.0f MB with shared activation memory" % (shared.max_batch, share_total / 2 ** 20))
+    assert share_act > 0
 
 
 def test_logits_and_top1_vs_fp32_cpu_reference(resnet):

@@ -49,13 +49,16 @@ def test_head_boxes_and_scores_vs_fp32_reference(yolo):
 
 
 def test_per_layer_against_plan_interpreter(yolo):
-    module, model = yolo
+    module, shared = yolo
+    model = B200Model("yolov8n", blob=shared.blob, max_batch=2, keep_buffers=True)   # every buffer readable afterwards
+    model.op_names = shared.op_names
     n = 2
     imgs = synth.synthetic_images(n, 640, 640)
     x = imgs.permute(0, 3, 1, 2).float().div(255)
     it = PlanInterpreter(model.blob, lowering.parse_blob)
     _, B = it.run(to_nhwc4(x), keep_all=True)
-    model.infer_u8(list(imgs))
+    out = model.infer_u8(list(imgs))
+    assert torch.equal(out.cpu(), shared.infer_u8(list(imgs)).cpu()), "shared and unshared activation memory must agree"
     torch.cuda.synchronize()
     for op_i, op in enumerate(it.ops):
         if op["type"] == lowering.OP_YOLO_DECODE:
