@@ -310,7 +310,8 @@ B200_API long long b200_ring_qsize(void* mem);
 B200_API int b200_ring_record(void* mem, double latency_ms, int n_requests, double slo_ms);
 /* RequestQueue.get_stats (scheduler.py:343-372) over the same window of latencies the reference's list would hold:
  * out[0..10] = total_requests, dropped_requests, slo_violations, queue_size, last_latency, avg_latency, p95_latency,
- * p99_latency, discarded_stale, completed_requests, completed_batches.  Visible to every process that maps the ring
+ * p99_latency, discarded_stale, completed_requests, completed_batches, and with n_out >= 12 out[11] = the largest batch
+ * latency recorded since init (the window above holds only the last 900-1000 requests).  Visible to every process that maps the ring
  * (the reference's actors update a pickled copy of the metrics that the driver never sees). */
 B200_API int b200_ring_stats(void* mem, double* out, int n_out);
 

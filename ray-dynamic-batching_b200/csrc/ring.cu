@@ -48,6 +48,7 @@ struct alignas(128) RingHeader {
   std::atomic<uint64_t> completed_batches;
   std::atomic<uint64_t> lat_count;           // latencies ever appended; entry i lives at lat[i % LAT_CAP]
   std::atomic<uint64_t> last_latency_bits;   // double, bit-cast
+  std::atomic<uint64_t> max_latency_bits;    // largest batch latency ever recorded (non-negative doubles order like their bits)
   double lat[LAT_CAP];
 };
 
@@ -108,6 +109,7 @@ int b200_ring_init(void* mem, size_t bytes, uint32_t nslots, uint32_t slot_bytes
   h->completed_batches.store(0);
   h->lat_count.store(0);
   h->last_latency_bits.store(0);
+  h->max_latency_bits.store(0);
   RingDesc* d = descs_of(h);
   for (uint32_t i = 0; i < nslots; ++i) {
     new (&d[i]) RingDesc;
@@ -265,6 +267,10 @@ int b200_ring_record(void* mem, double latency_ms, int n_requests, double slo_ms
   uint64_t bits;
   memcpy(&bits, &latency_ms, 8);
   h->last_latency_bits.store(bits, std::memory_order_relaxed);
+  if (latency_ms > 0) {
+    uint64_t cur = h->max_latency_bits.load(std::memory_order_relaxed);
+    while (bits > cur && !h->max_latency_bits.compare_exchange_weak(cur, bits, std::memory_order_relaxed)) {}
+  }
   const uint64_t first = h->lat_count.fetch_add(uint64_t(n_requests), std::memory_order_acq_rel);
   for (int i = 0; i < n_requests; ++i) h->lat[(first + i) % LAT_CAP] = latency_ms;
   int viol = 0;
@@ -297,12 +303,17 @@ int b200_ring_stats(void* mem, double* out, int n_out) {
   out[5] = out[6] = out[7] = 0.0;
   if (win > 0) {
     std::vector<double> v(win);
-    double sum = 0.0;
+    // sum(latencies) / len(latencies) as CPython >= 3.12 evaluates it: compensated (Neumaier) summation in list order
+    volatile double total = 0.0, comp = 0.0;
     for (uint64_t i = 0; i < win; ++i) {
-      v[i] = h->lat[(n - win + i) % LAT_CAP];
-      sum += v[i];
+      const double x = h->lat[(n - win + i) % LAT_CAP];
+      v[i] = x;
+      const double t = total + x;
+      if (fabs(total) >= fabs(x)) comp = comp + ((total - t) + x);
+      else comp = comp + ((x - t) + total);
+      total = t;
     }
-    out[5] = sum / double(win);
+    out[5] = (total + comp) / double(win);
     std::sort(v.begin(), v.end());
     out[6] = v[size_t(double(win) * 0.95)];
     out[7] = v[size_t(double(win) * 0.99)];
@@ -310,6 +321,10 @@ int b200_ring_stats(void* mem, double* out, int n_out) {
   out[8] = double(h->discarded_stale.load());
   out[9] = double(h->completed_requests.load());
   out[10] = double(h->completed_batches.load());
+  if (n_out >= 12) {
+    const uint64_t mb = h->max_latency_bits.load();
+    memcpy(&out[11], &mb, 8);
+  }
   return B200_OK;
 }
 

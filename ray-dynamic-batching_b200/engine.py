@@ -35,6 +35,8 @@ def plan_memory_bytes(blob, max_batch, keep_buffers=False):
 
 
 class B200Model:
+    is_b200_engine = True
+
     def __init__(self, kind, module=None, blob=None, max_batch=256, device=0, use_graphs=True, in_hw=None,
                  keep_buffers=False, buckets=None):
         if not torch.cuda.is_available():

@@ -21,33 +21,55 @@ FIELDNAMES = ['batch_size', 'status', 'avg_latency_ms', 'std_latency_ms', 'throu
 
 
 def engine_memory_mb(model, batch_size: int) -> float:
-    """Device memory the engine needs for `batch_size`: weights + every activation buffer of the plan."""
-    hdr, bufs, _, weights = _lowering.parse_blob(model.blob)
-    per_image = sum(h * w * c * (4 if dt else 2) for h, w, c, dt in bufs)
-    return (len(weights) + per_image * batch_size) / (1024.0 * 1024.0)
+    """Device memory an engine created for `batch_size` holds: weights, the activation arena (buffers with disjoint
+    lifetimes share addresses), tables -- b200_plan_memory, the same planner b200_engine_create runs.  This is the column
+    nexus.py sums to decide which sessions fit on a GPU together (nexus.py:222-226), so it has to be what an actor sized
+    for that batch really holds, not a per-image estimate."""
+    from .engine import plan_memory_bytes
+    return plan_memory_bytes(model.blob, batch_size) / (1024.0 * 1024.0)
 
 
-def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_runs: int = 10) -> List[dict]:
-    """One row per batch size (ModelProfiler.profile_batch_size, :114-178)."""
+def _time_batch(model, bs, out, warmup_runs, num_runs):
+    dev = model.device
+    for _ in range(warmup_runs + 2):            # +2: the first two calls of a batch size are eager / graph capture
+        model.infer_resident(bs, out)
+    torch.cuda.synchronize(dev)
+    lat = []
+    for _ in range(num_runs):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        model.infer_resident(bs, out)
+        e1.record()
+        e1.synchronize()
+        lat.append(e0.elapsed_time(e1))
+    return lat
+
+
+def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_runs: int = 10, dense: bool = False) -> List[dict]:
+    """One row per batch size (ModelProfiler.profile_batch_size, :114-178).
+
+    dense=True emits EVERY integer batch size from 1 to max(batch_sizes), like the reference's sweep
+    (profiling/run_profiler.py:188-197, batch_size_step=1): nexus.py indexes the profile by arbitrary integers
+    (`profile[ceil(duty * rate / 1000)]`, nexus.py:213-214; `profile[batch_size]`, scheduler.py:281), so a sparse table
+    raises KeyError there.  Only the sizes in `batch_sizes` are timed -- they are the buckets a worker pads batches to --
+    and a size in between gets the latency of the bucket it would run in; memory is computed per size."""
     dev = model.device
     total_mem_mb = torch.cuda.get_device_properties(dev).total_memory / (1024.0 * 1024.0)
+    timed = {}
+    for bs in sorted(set(batch_sizes)):
+        if bs > model.max_batch:
+            continue
+        out = torch.empty(bs, model.out_dim, device=dev, dtype=torch.float32)
+        timed[bs] = _time_batch(model, bs, out, warmup_runs, num_runs)
     rows = []
-    for bs in batch_sizes:
+    keys = sorted(timed)
+    sizes = range(1, keys[-1] + 1) if dense and keys else sorted(set(batch_sizes))
+    for bs in sizes:
         if bs > model.max_batch:
             rows.append({'batch_size': bs, 'status': 'exceeds_max_batch'})
             continue
-        out = torch.empty(bs, model.out_dim, device=dev, dtype=torch.float32)
-        for _ in range(warmup_runs + 2):            # +2: the first two calls of a batch size are eager / graph capture
-            model.infer_resident(bs, out)
-        torch.cuda.synchronize(dev)
-        lat = []
-        for _ in range(num_runs):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            model.infer_resident(bs, out)
-            e1.record()
-            e1.synchronize()
-            lat.append(e0.elapsed_time(e1))
+        bucket = next(k for k in keys if k >= bs)
+        lat = timed[bucket]
         avg = sum(lat) / len(lat)
         mem = engine_memory_mb(model, bs)
         thr = bs / (avg / 1000.0)

@@ -194,6 +194,10 @@ class B200RequestQueue:
                     count += 1
             if inputs:
                 slab_offsets = offs if all(o is not None for o in offs) else None
+                if slab_offsets is None and self.slab is not None:
+                    for o in offs:                 # mixed batch: it travels by its tensors, the slab copies are not needed
+                        if o is not None:
+                            self.slab.release(o)
                 return BatchRequest(self.model_name, inputs, len(inputs), request_ids, earliest_arrival,
                                     slab_offsets, self.slab if slab_offsets is not None else None), discard
         except Exception as e:  # noqa: BLE001 - reference: log, fall through to (None, 0)

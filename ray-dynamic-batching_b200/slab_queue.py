@@ -32,6 +32,7 @@ from . import lib as _lib
 from .request_queue import BatchRequest, models_config
 
 ID_BYTES = 100   # B200_RING_ID_BYTES
+_CREATED_HERE = set()   # segments this process created (their tracker entry belongs to the creator)
 
 
 class SlabInputs:
@@ -74,11 +75,20 @@ class SlabRequestQueue:
             nslots = int(max_size) + int(in_flight_slots)
             nbytes = int(self._lib.b200_ring_bytes(nslots, int(slot_bytes)))
             self._shm = shared_memory.SharedMemory(create=True, size=nbytes + 4096, name=name)
+            _CREATED_HERE.add(self._shm.name)
         else:
             self._shm = shared_memory.SharedMemory(name=name)
-            try:     # an attaching process must not unlink the segment when it exits (Python < 3.13 registers it anyway)
+            # An attaching process must not unlink the segment when it exits, but Python < 3.13 registers it with the
+            # process's resource tracker anyway.  A multiprocessing child shares its parent's tracker (registering
+            # twice is harmless there, unregistering would drop the creator's entry); an unrelated process has a tracker
+            # of its own, which would unlink the segment behind the creator's back: take the entry out of that one.
+            try:
+                import multiprocessing
                 from multiprocessing import resource_tracker
-                resource_tracker.unregister(self._shm._name, "shared_memory")
+                child = multiprocessing.parent_process() is not None or \
+                    getattr(multiprocessing.current_process(), "_inheriting", False)   # still unpickling its arguments
+                if not child and self._shm.name not in _CREATED_HERE:
+                    resource_tracker.unregister(self._shm._name, "shared_memory")
             except Exception:  # noqa: BLE001
                 pass
         self.name = self._shm.name
@@ -254,8 +264,8 @@ class SlabRequestQueue:
         return rc
 
     def raw_stats(self):
-        out = np.zeros(11, np.float64)
-        _lib.check(self._lib.b200_ring_stats(self._mem, out.ctypes.data, 11), "b200_ring_stats")
+        out = np.zeros(12, np.float64)
+        _lib.check(self._lib.b200_ring_stats(self._mem, out.ctypes.data, 12), "b200_ring_stats")
         return out
 
     def get_stats(self) -> Dict:
@@ -267,7 +277,8 @@ class SlabRequestQueue:
             stats.update(avg_latency=0, p95_latency=0, p99_latency=0)
         else:
             stats.update(avg_latency=float(o[5]), p95_latency=float(o[6]), p99_latency=float(o[7]))
-        stats.update(discarded_stale=int(o[8]), completed_requests=int(o[9]), completed_batches=int(o[10]))
+        stats.update(discarded_stale=int(o[8]), completed_requests=int(o[9]), completed_batches=int(o[10]),
+                     max_latency=float(o[11]))
         return stats
 
 

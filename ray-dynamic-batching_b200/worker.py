@@ -90,7 +90,7 @@ class B200GPUWorker:
         """scheduler.py:409-417: registry entry -> device.  A registry entry may be a ready B200Model, an nn.Module (lowered
         here), or a dict {'kind', 'blob'} (a plan lowered once by the scheduler process and shipped to every actor)."""
         entry = self.model_registry[model_name]
-        if isinstance(entry, B200Model):
+        if isinstance(entry, B200Model) or getattr(entry, "is_b200_engine", False):
             return entry
         cap = self._engine_batch(model_name, sessions)
         if isinstance(entry, dict):
@@ -233,6 +233,13 @@ class B200GPUWorker:
             return True
         return False
 
+    @staticmethod
+    def _backlog(q) -> int:
+        if hasattr(q, "qsize"):
+            return q.qsize()
+        inner = getattr(q, "queue", None)
+        return inner.qsize() if inner is not None else 0
+
     def _drain(self, request_queues, results, keep=0):
         while len(self._inflight) > keep:
             results.append(self.finish_batch(self._inflight.popleft(), request_queues))
@@ -254,8 +261,17 @@ class B200GPUWorker:
                 self._inflight.append(self.process_batch_async(batch, request_queues, discard_count))
                 before = len(results)
                 self._drain(request_queues, results, keep=self.pipeline_depth - 1)
-                spent = results[-1]['processing_time'] if len(results) > before and self.pipeline_depth == 1 \
-                    else (time.time() - t_slice) * 1000
+                if self.pipeline_depth == 1:
+                    spent = results[-1]['processing_time'] if len(results) > before else (time.time() - t_slice) * 1000
+                else:
+                    # Pipelined: while another full batch is already waiting the loop goes straight on (the wait for the
+                    # batch before this one, in _drain above, paces it at the GPU's speed, and the next batch's upload
+                    # overlaps this one's forward).  Otherwise there is idle time ahead: a batch is never held in flight
+                    # across a sleep, so its latency does not grow by the rest of the slice.
+                    if self._backlog(request_queues[s.model_name]) >= s.batch_size:
+                        continue
+                    self._drain(request_queues, results)
+                    spent = (time.time() - t_slice) * 1000
                 remaining = time_slice - spent
                 if remaining > 0:
                     sleep(remaining / 1000)

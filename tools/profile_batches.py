@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Re-profiles a model on the B200 engine in the reference's `_summary.csv` schema (profiling/ModelProfiler.py).
-Usage: python tools/profile_batches.py kind out.csv [max_batch]"""
+Usage: python tools/profile_batches.py kind out.csv [max_batch]
+The CSV has one row per integer batch size 1..max_batch (what nexus.py indexes); the bucket sizes are the timed ones."""
 import os
 import sys
 
@@ -16,10 +17,11 @@ def main():
     max_batch = int(sys.argv[3]) if len(sys.argv) > 3 else 256
     module = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
     model = B200Model(kind, module, max_batch=max_batch)
-    sizes = [b for b in (1, 2, 4, 8, 16, 32, 64, 96, 128, 192, 256, 384, 512) if b <= max_batch]
-    rows = profiler.profile_batches(model, sizes)
+    from rdb_b200.engine import default_buckets
+    sizes = default_buckets(max_batch)          # the sizes a worker pads batches to; every integer row is emitted
+    rows = profiler.profile_batches(model, sizes, dense=True)
     profiler.save_summary_csv(rows, out)
-    for r in rows:
+    for r in [r for r in rows if r['batch_size'] in sizes]:
         print("%4d  %8.3f ms  %9.1f img/s  %8.1f MB" % (r['batch_size'], r['avg_latency_ms'], r['throughput'], r['peak_memory_mb']))
 
 

@@ -1,105 +1,190 @@
 #!/usr/bin/env python
-"""Serving simulation of the reference's actor loop on one GPU: a feeder thread submits uint8 requests to a
-B200RequestQueue at a given rate (constant, or the reference driver's slope pattern rate = elapsed * slope,
-293-project/src/test_scheduler.py:77-79); a B200GPUWorker pulls batches (get_batch -> process_batch) back to back.
-Reports batch latency percentiles exactly as RequestQueue.get_stats does (scheduler.py:343-372) against the model's SLO.
+"""Serving run through the drop-in surface at deployment shape: B200Scheduler (one model-actor PROCESS per GPU) fed by
+client PROCESSES that write uint8 requests into the shared-memory request rings; every latency figure is read from
+RequestQueue.get_stats (293-project/src/scheduler.py:343-372) exactly as the reference's metrics display does.
 
-  python tools/serve_sim.py --model resnet --rate 20000 --seconds 4 --batch 256 [--slope 0]
+  python tools/serve_sim.py --models resnet --gpus 1 --rate 70000 --seconds 5 --batch 256
+  python tools/serve_sim.py --models resnet --gpus 8 --rate 560000 --seconds 5 --clients 16
+  python tools/serve_sim.py --models resnet,efficientnet,yolov8 --gpus 8 --rates 200000,40000,20000 --seconds 6   # configs[4]
+  python tools/serve_sim.py --models resnet --gpus 1 --slope 3000 --seconds 10        # reference load pattern, rate = t * slope
+
+Schedules: by default a static one (every GPU serves every listed model, occupancy split evenly, batch sizes from
+--batch / --batches) installed with set_schedule; --dynamic lets the rate monitor and the squishy bin packing decide.
+Prints one JSON line.
 """
 import argparse
 import json
+import multiprocessing as mp
 import os
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-import torch
 
-import rdb_b200  # noqa: F401
-from rdb_b200 import synth
-from rdb_b200.engine import B200Model
-from rdb_b200.request_queue import B200RequestQueue, models_config
-from rdb_b200.worker import B200GPUWorker, MODEL_KINDS
+DEFAULT_BATCH = {"resnet": 256, "shufflenet": 512, "efficientnet": 128, "yolov8": 32}
+PROFILE_CSV = {"resnet": "resnet50", "shufflenet": "shufflenet", "efficientnet": "efficientnetv2", "yolov8": "yolov8n"}
 
 
-class Session:
-    def __init__(self, model_name, batch_size):
-        self.model_name, self.batch_size = model_name, batch_size
+def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, start_at, report):
+    """One load-generator process: bursts of `burst` requests at `rate` req/s into one model's ring."""
+    import rdb_b200  # noqa: F401
+    from rdb_b200 import synth
+    pool = synth.synthetic_images(4 * burst, hw, hw, seed=8000 + seed).contiguous().numpy()
+    p = pool.shape[0]
+    while time.time() < start_at:
+        time.sleep(0.001)
+    t0 = time.perf_counter()
+    i = sub = drop = 0
+    while True:
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+        target = slope * el * el / 2 if slope > 0 else rate * el
+        while i + burst <= target:
+            j = i % p
+            if j + burst > p:
+                j = 0
+            ok = queue.add_requests(pool[j:j + burst], prefix, i)
+            sub += ok
+            drop += burst - ok
+            i += burst
+        time.sleep(0.0002)
+    report.put((prefix, sub, drop, time.perf_counter() - t0))
+    queue.close()
+
+
+def load_profiles(models, max_bs=512):
+    from rdb_b200 import profiler, serving
+    out = {}
+    for m in models:
+        path = os.path.join(ROOT, "profiles", "b200_batch_profiles", "%s_b200_summary.csv" % PROFILE_CSV[m])
+        d = profiler.load_csv_to_dict(path) if os.path.exists(path) else {}
+        d = {k: v for k, v in d.items() if 'avg_latency_ms' in v}
+        if not d:
+            raise SystemExit("no batch profile for %s (%s)" % (m, path))
+        for v in d.values():
+            v.setdefault('peak_memory_mb', 1000.0)
+        out[m] = serving.dense_profile(d, max(max_bs, max(d)))
+    return out
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="resnet")
-    ap.add_argument("--rate", type=float, default=20000.0)
+    ap.add_argument("--models", default="resnet")
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--rate", type=float, default=60000.0, help="total offered req/s (single model)")
+    ap.add_argument("--rates", default="", help="offered req/s per model, comma separated (mixed runs)")
     ap.add_argument("--slope", type=float, default=0.0)
-    ap.add_argument("--seconds", type=float, default=4.0)
-    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--seconds", type=float, default=5.0)
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--batches", default="")
+    ap.add_argument("--clients", type=int, default=0, help="client processes per model (default: 2 per GPU, at most 16)")
+    ap.add_argument("--burst", type=int, default=16)
+    ap.add_argument("--dynamic", action="store_true")
+    ap.add_argument("--pipeline-depth", type=int, default=2)
+    ap.add_argument("--metrics-file", default=os.path.join(ROOT, "gpurun_out", "metrics.json"))
+    ap.add_argument("--out", default="")
     args = ap.parse_args()
-    kind = MODEL_KINDS[args.model]
-    module = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
-    model = B200Model(kind, module, max_batch=2 * args.batch)
-    h, w = model.in_h, model.in_w
-    pool = list(synth.synthetic_images(32, h, w))
-    # batch profile (avg_latency_ms per batch size) measured on this engine, like profiling/ModelProfiler does offline
-    profile = {}
-    for bs in sorted({1, 8, 32, 64, 128, args.batch, 2 * args.batch}):
-        imgs = [pool[i % 32] for i in range(bs)]
-        for _ in range(3):
-            model.infer_u8(imgs)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        for _ in range(5):
-            model.infer_u8(imgs).cpu()
-        profile[bs] = {"avg_latency_ms": (time.perf_counter() - t0) / 5 * 1e3}
-    slab = 4000 * ((h * w * 3 + 15) // 16 * 16)
-    q = B200RequestQueue(args.model, max_size=2000, batch_profile={args.model: profile}, compat=False,
-                         pinned_slab_bytes=slab)
-    worker = B200GPUWorker("B200_0", 0, [(Session(args.model, args.batch), 1.0)], 1.0, {args.model: model},
-                           max_batch=2 * args.batch)
-    stop = threading.Event()
-    submitted = [0, 0]
 
-    def feeder():
-        t0 = time.perf_counter()
-        i = 0
-        while not stop.is_set():
-            el = time.perf_counter() - t0
-            if el >= args.seconds:
+    import rdb_b200  # noqa: F401
+    from rdb_b200 import packing, synth
+    from rdb_b200.request_queue import models_config
+    from rdb_b200.scheduler import B200Scheduler
+    from rdb_b200.worker import MODEL_KINDS
+
+    models = [m for m in args.models.split(",") if m]
+    rates = [float(x) for x in args.rates.split(",")] if args.rates else [args.rate / len(models)] * len(models)
+    batches = [int(x) for x in args.batches.split(",")] if args.batches else \
+        [args.batch or DEFAULT_BATCH[m] for m in models]
+    profile = load_profiles(models)
+    registry = {}
+    for m in models:
+        kind = MODEL_KINDS[m]
+        registry[m] = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
+    os.makedirs(os.path.dirname(args.metrics_file), exist_ok=True)
+    t_load = time.time()
+    sched = B200Scheduler(profile, monitoring_interval=1.0, rate_change_threshold=0.05, model_registry=registry,
+                          num_gpus=args.gpus, worker_mode="process", max_batch=max(batches), preload=models,
+                          pipeline_depth=args.pipeline_depth, metrics_file=args.metrics_file, metrics_interval=1.0,
+                          max_queue_size=max(2000, 6 * max(batches) * args.gpus),
+                          in_flight_slots=4 * max(batches) * args.gpus + 256)
+    out = {"models": models, "gpus": args.gpus, "seconds": args.seconds, "batches": dict(zip(models, batches))}
+    try:
+        if not sched.wait_ready(900):
+            raise SystemExit("actors did not come up")
+        out["actor_load_s"] = time.time() - t_load
+        if args.dynamic:
+            sched.start_monitoring()
+        else:
+            nodes = []
+            for g in range(args.gpus):
+                sessions = []
+                duty = 0.0
+                for m, b, r in zip(models, batches, rates):
+                    lat = profile[m][b]['avg_latency_ms']
+                    duty += lat
+                    sessions.append((packing.session(m, models_config[m]['SLO'] / 2.2, r / args.gpus, b), lat))
+                nodes.append(packing.node([(s, lat / duty) for s, lat in sessions], duty_cycle=duty))
+            sched.set_schedule(nodes)
+        time.sleep(0.5)
+        ctx = mp.get_context("spawn")
+        report = ctx.Queue()
+        n_clients = args.clients or min(16, 2 * args.gpus)
+        start_at = time.time() + 6.0 + 0.5 * n_clients * len(models)       # spawned clients import torch first
+        procs = []
+        for m, r in zip(models, rates):
+            for c in range(n_clients):
+                procs.append(ctx.Process(target=client_main, daemon=True,
+                                         args=(sched.request_queues[m], sched.model_registry[m]['in_hw'][0], r / n_clients,
+                                               args.seconds, args.slope / n_clients, args.burst, "%s_c%d_" % (m, c),
+                                               100 * len(procs), start_at, report)))
+        for p in procs:
+            p.start()
+        while time.time() < start_at:
+            time.sleep(0.01)
+        t0 = time.time()
+        reports = [report.get(timeout=args.seconds + 120) for _ in procs]
+        t_feed = time.time() - t0
+        deadline = time.time() + 30
+        while time.time() < deadline:
+            if all(q.get_stats()["completed_requests"] + q.get_stats()["discarded_stale"] >= q.get_stats()["total_requests"]
+                   for q in sched.request_queues.values()):
                 break
-            target = args.slope * el * el / 2 if args.slope > 0 else args.rate * el
-            while i < target:
-                ok = q.add_request("r%d" % i, pool[i % 32])
-                submitted[0 if ok else 1] += 1
-                i += 1
-            time.sleep(0.0005)
-
-    th = threading.Thread(target=feeder, daemon=True)
-    t_start = time.perf_counter()
-    th.start()
-    batches = served = 0
-    sizes = []
-    while th.is_alive() or not q.empty():
-        batch, discard = q.get_batch(args.batch)
-        if batch is None:
-            time.sleep(0.0002)
-            continue
-        worker.process_batch(batch, {args.model: q}, discard)
-        batches += 1
-        served += batch.batch_size
-        sizes.append(batch.batch_size)
-    wall = time.perf_counter() - t_start
-    stats = q.get_stats()
-    out = {"model": args.model, "kind": kind, "pattern": "slope %.0f/s^2" % args.slope if args.slope else "constant",
-           "offered_rate": args.rate if not args.slope else None, "seconds": args.seconds, "batch_target": args.batch,
-           "submitted": submitted[0], "dropped_full_queue": submitted[1], "served": served, "batches": batches,
-           "mean_batch": sum(sizes) / max(1, len(sizes)), "throughput_img_s": served / wall,
-           "slo_ms": models_config[args.model]["SLO"], "slo_violations": stats["slo_violations"],
-           "avg_latency_ms": stats["avg_latency"], "p95_latency_ms": stats["p95_latency"],
-           "p99_latency_ms": stats["p99_latency"],
-           "profile_ms": {k: round(v["avg_latency_ms"], 3) for k, v in profile.items()}}
-    print(json.dumps(out))
+            time.sleep(0.005)
+        wall = time.time() - t0
+        for p in procs:
+            p.join(timeout=10)
+        out.update(wall_s=wall, feed_s=t_feed, pattern=("slope %.0f/s^2" % args.slope) if args.slope else "constant",
+                   clients_per_model=n_clients, burst=args.burst, dynamic=args.dynamic,
+                   pipeline_depth=args.pipeline_depth)
+        per = {}
+        total_served = 0
+        for m, r in zip(models, rates):
+            st = sched.request_queues[m].get_stats()
+            sub = sum(x[1] for x in reports if x[0].startswith(m + "_c"))
+            drop = sum(x[2] for x in reports if x[0].startswith(m + "_c"))
+            total_served += st["completed_requests"]
+            per[m] = {"offered_rate": r if not args.slope else None, "submitted": sub, "dropped_full_queue": drop,
+                      "served": st["completed_requests"], "batches": st["completed_batches"],
+                      "mean_batch": st["completed_requests"] / max(1, st["completed_batches"]),
+                      "throughput_img_s": st["completed_requests"] / wall, "slo_ms": sched.request_queues[m].slo_target,
+                      "slo_violations": st["slo_violations"], "discarded_stale": st["discarded_stale"],
+                      "avg_latency_ms": st["avg_latency"], "p95_latency_ms": st["p95_latency"],
+                      "p99_latency_ms": st["p99_latency"], "max_latency_ms": st["max_latency"]}
+        out["per_model"] = per
+        out["throughput_img_s"] = total_served / wall
+        if args.dynamic:
+            out["schedule_updates"] = sched.metrics["schedule_updates"]
+            out["nodes"] = [n.to_dict() for n in sched.nodes]
+    finally:
+        out["workers"] = sched.stop(timeout=30)
+        sched.close()
+    line = json.dumps(out, default=str)
+    print(line)
+    if args.out:
+        with open(args.out, "a") as f:
+            f.write(line + "\n")
 
 
 if __name__ == "__main__":
