@@ -43,7 +43,7 @@ MODELS = {
     "efficientnet_v2_s": dict(batch=128, hw=224, cfg="configs[3]", name="EfficientNetV2-S", flops=5.700e9, bytes=59.43e6,
                               weights=42.5e6, slo_name="efficientnet",
                               at={384: dict(flops=16.73e9, bytes=174.2e6)}),
-    "yolov8n": dict(batch=32, hw=640, cfg="configs[4]", name="YOLOv8n", flops=8.76e9, bytes=123.3e6, weights=6.4e6,
+    "yolov8n": dict(batch=32, hw=640, cfg="configs[4]", name="YOLOv8n", flops=8.743e9, bytes=77.6e6, weights=6.3e6,
                     slo_name="yolov8"),
 }
 LOGIT_TOL = 2e-2        # north star: logits within 2e-2 max-abs
