@@ -232,7 +232,12 @@ B200_API int b200_engine_read_buffer(b200_engine* e, int buf, int batch, void* h
  * padded NHWC(C=4) bf16 batch of `padded_batch` images, normalised with the blob's mean/std; slots >= n are zero.
  * Replaces torch.stack(batch.inputs) (scheduler.py:443) + the client-side ToTensor/Normalize/Resize
  * (profiling/run_profiler.py:63-70). mode: 0 identity (sizes must equal the model input), 1 pad top-left, 2 bilinear
- * resize, 3 letterbox. src_on_device=0: `packed` is host memory (pinned for an async copy) and is staged with one H2D
+ * resize (no antialias), 3 letterbox, 4 = transforms.Resize((H, W)): bilinear WITH antialias stretched to the model
+ * input, 5 = transforms.Resize(S) + CenterCrop(S) for a square S x S model input (short side to S with antialias,
+ * long side int(S * long / short), centre crop) -- both with torch's antialias weights, one rounding at the end: within
+ * 1 in the last uint8 bit of torchvision.transforms.v2.functional.resize(uint8, antialias=True) before normalisation.
+ * A request with hw[i][1] < 0 is a single-channel (grayscale) image of width -hw[i][1], h * w bytes, expanded L -> RGB
+ * like PIL's convert("RGB") (31 of the 2000 images of sample-models/yolov8/workload are grayscale). src_on_device=0: `packed` is host memory (pinned for an async copy) and is staged with one H2D
  * copy; 1: it is already a device pointer. out = NULL writes straight into the engine's input buffer. */
 B200_API int b200_collate(b200_engine* e, const void* packed, const uint64_t* offsets, const int32_t* hw, int n,
                           int padded_batch, int mode, int src_on_device, size_t packed_bytes, void* out_nhwc_bf16,

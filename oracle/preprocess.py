@@ -16,7 +16,7 @@ parity-unpinned against the reference and pinned only between this oracle and th
 """
 import numpy as np
 
-MODE_IDENTITY, MODE_PAD, MODE_RESIZE, MODE_LETTERBOX = 0, 1, 2, 3
+MODE_IDENTITY, MODE_PAD, MODE_RESIZE, MODE_LETTERBOX = 0, 1, 2, 3      # 4, 5: the antialiased resizes, defined below
 
 
 def f32_to_bf16_bits(x):
@@ -81,7 +81,8 @@ def resize_u8(img, rh, rw):
 
 
 def preprocess_u8(img, out_h, out_w, mode, fill):
-    """uint8 HWC of any size -> uint8 [out_h, out_w, 3] canvas according to `mode`."""
+    """uint8 HWC (or single-channel) of any size -> uint8 [out_h, out_w, 3] canvas according to `mode`."""
+    img = to_rgb(img)
     h, w, _ = img.shape
     if mode == MODE_IDENTITY:
         if (h, w) != (out_h, out_w):
@@ -91,6 +92,10 @@ def preprocess_u8(img, out_h, out_w, mode, fill):
     canvas = np.full((out_h, out_w, 3), fill, dtype=np.uint8)
     if mode == MODE_PAD:
         canvas[:rh, :rw] = img[:rh, :rw]
+    elif mode == MODE_RESIZE_AA:
+        return resize_aa_u8(img, out_h, out_w)
+    elif mode == MODE_RESIZE_SHORT_AA:
+        return resize_short_side_center_crop_u8(img, out_h, out_w)
     else:
         canvas[top:top + rh, left:left + rw] = resize_u8(img, rh, rw)
     return canvas
@@ -118,3 +123,68 @@ def collate_f32chw(tensors, padded_batch):
     for i, t in enumerate(tensors):
         out[i, :, :, :3] = f32_to_bf16_bits(np.asarray(t, dtype=np.float32)).transpose(1, 2, 0)
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# The reference's own resize: transforms.Resize(224) / Resize((224, 224)) (profiling/run_profiler.py:63-70,
+# 293-project/src/milind-code/scheduler.py:24-27) = bilinear WITH antialias.  Oracle of record:
+# torchvision.transforms.v2.functional.resize(uint8 CHW tensor, antialias=True) on the CPU; the arithmetic lives in
+# torch (ATen/native/cpu/UpSampleKernel.cpp, _compute_indices_min_size_weights_aa + the separable aa kernel), restated
+# here in float64 with ONE rounding at the end.  torch's uint8 path rounds to uint8 between its horizontal and vertical
+# pass and uses fixed-point weights, so the two may differ by 1 in the last bit; tests/test_oracle_preprocess.py pins this
+# restatement to torchvision within that 1 LSB on the committed golden vectors (tests/golden/resize_aa_golden.npz).
+# ---------------------------------------------------------------------------------------------------------------------
+MODE_RESIZE_AA, MODE_RESIZE_SHORT_AA = 4, 5
+
+
+def aa_weights(in_size, out_size):
+    """Per output index: (first input index, normalised triangle weights), torch's antialias bilinear."""
+    scale = in_size / out_size
+    support = scale if scale >= 1.0 else 1.0
+    invscale = 1.0 / scale if scale >= 1.0 else 1.0
+    out = []
+    for i in range(out_size):
+        center = scale * (i + 0.5)
+        xmin = max(int(center - support + 0.5), 0)
+        xmax = min(int(center + support + 0.5), in_size)
+        j = np.arange(xmin, xmax, dtype=np.float64)
+        w = np.clip(1.0 - np.abs((j - center + 0.5) * invscale), 0.0, None)
+        out.append((xmin, w / w.sum()))
+    return out
+
+
+def resize_aa_u8(img, oh, ow):
+    """Antialiased bilinear resize of a uint8 HWC image to (oh, ow): separable triangle filter, float64, one rounding."""
+    h, w, c = img.shape
+    src = img.astype(np.float64)
+    tmp = np.empty((h, ow, c), dtype=np.float64)
+    for x, (x0, wx) in enumerate(aa_weights(w, ow)):
+        tmp[:, x, :] = np.tensordot(src[:, x0:x0 + len(wx), :], wx, axes=([1], [0]))
+    out = np.empty((oh, ow, c), dtype=np.float64)
+    for y, (y0, wy) in enumerate(aa_weights(h, oh)):
+        out[y] = np.tensordot(wy, tmp[y0:y0 + len(wy)], axes=([0], [0]))
+    return np.clip(np.floor(out + 0.5), 0, 255).astype(np.uint8)
+
+
+def short_side_size(h, w, size):
+    """torchvision _compute_resized_output_size for an int size: short side -> size, long side -> int(size * long / short)."""
+    short, long_ = (w, h) if w <= h else (h, w)
+    new_short, new_long = size, int(size * long_ / short)
+    return (new_long, new_short) if w <= h else (new_short, new_long)      # (new_h, new_w)
+
+
+def resize_short_side_center_crop_u8(img, oh, ow):
+    """Resize(min(oh, ow)) (short side, antialias) followed by CenterCrop((oh, ow)) -- the crop is what lets requests of
+    different aspect ratios share one batch tensor; torchvision's CenterCrop offsets: int(round((H - oh) / 2.0))."""
+    h, w, _ = img.shape
+    nh, nw = short_side_size(h, w, min(oh, ow))
+    r = resize_aa_u8(img, nh, nw)
+    top, left = int(round((nh - oh) / 2.0)), int(round((nw - ow) / 2.0))
+    return r[top:top + oh, left:left + ow]
+
+
+def to_rgb(img):
+    """PIL's L -> RGB for a single-channel request (31 of the 2000 workload images are grayscale): the value is replicated."""
+    if img.ndim == 2:
+        img = img[:, :, None]
+    return np.repeat(img, 3, axis=2) if img.shape[2] == 1 else img

@@ -84,7 +84,9 @@ collate_u8_general_kernel(const uint8_t* __restrict__ src_base, const CollateIte
     *dst = make_uint2(0, 0);
     return;
   }
-  const CollateItem it = items[slot];
+  CollateItem it = items[slot];
+  const int nch = it.w < 0 ? 1 : 3;          // w < 0: a single-channel (grayscale) request of width -w, expanded L -> RGB
+  it.w = abs(it.w);
   const uint8_t* src = src_base + it.offset;
   const int oy = pix / out_w, ox = pix - oy * out_w;
   int r, g, b;
@@ -108,8 +110,8 @@ collate_u8_general_kernel(const uint8_t* __restrict__ src_base, const CollateIte
   if (y < 0 || y >= rh || x < 0 || x >= rw) {
     r = g = b = fill;
   } else if (mode == COLLATE_PAD || (rh == it.h && rw == it.w)) {
-    const uint8_t* p = src + (static_cast<size_t>(y) * it.w + x) * 3;
-    r = p[0]; g = p[1]; b = p[2];
+    const uint8_t* p = src + (static_cast<size_t>(y) * it.w + x) * nch;
+    r = p[0]; g = p[nch == 3 ? 1 : 0]; b = p[nch == 3 ? 2 : 0];
   } else {
     // bilinear, half-pixel centres, fixed point with 10 fractional bits; result rounded to uint8 (like a uint8 resize)
     const long long sx_num = static_cast<long long>(2 * x + 1) * it.w - rw;   // = (2*srcx) * rw   (srcx = (x+.5)*w/rw-.5)
@@ -123,20 +125,97 @@ collate_u8_general_kernel(const uint8_t* __restrict__ src_base, const CollateIte
     if (x0 >= it.w - 1) { x0 = it.w - 1; wx = 0; }
     if (y0 >= it.h - 1) { y0 = it.h - 1; wy = 0; }
     const int x1 = min(x0 + 1, it.w - 1), y1 = min(y0 + 1, it.h - 1);
-    const uint8_t* p00 = src + (static_cast<size_t>(y0) * it.w + x0) * 3;
-    const uint8_t* p01 = src + (static_cast<size_t>(y0) * it.w + x1) * 3;
-    const uint8_t* p10 = src + (static_cast<size_t>(y1) * it.w + x0) * 3;
-    const uint8_t* p11 = src + (static_cast<size_t>(y1) * it.w + x1) * 3;
+    const uint8_t* p00 = src + (static_cast<size_t>(y0) * it.w + x0) * nch;
+    const uint8_t* p01 = src + (static_cast<size_t>(y0) * it.w + x1) * nch;
+    const uint8_t* p10 = src + (static_cast<size_t>(y1) * it.w + x0) * nch;
+    const uint8_t* p11 = src + (static_cast<size_t>(y1) * it.w + x1) * nch;
     int c[3];
 #pragma unroll
-    for (int k = 0; k < 3; ++k) {
+    for (int kk = 0; kk < 3; ++kk) {
+      const int k = nch == 3 ? kk : 0;
       const int top_v = p00[k] * (1024 - wx) + p01[k] * wx;
       const int bot_v = p10[k] * (1024 - wx) + p11[k] * wx;
-      c[k] = static_cast<int>((static_cast<long long>(top_v) * (1024 - wy) + static_cast<long long>(bot_v) * wy +
-                               (1 << 19)) >> 20);
+      c[kk] = static_cast<int>((static_cast<long long>(top_v) * (1024 - wy) + static_cast<long long>(bot_v) * wy +
+                                (1 << 19)) >> 20);
     }
     r = c[0]; g = c[1]; b = c[2];
   }
+  uint2 o;
+  o.x = uint32_t(s_lut[r]) | (uint32_t(s_lut[256 + g]) << 16);
+  o.y = uint32_t(s_lut[512 + b]);
+  *dst = o;
+}
+
+// ----------------------------------------------------------------------------------------------------------------
+// The reference's own resize: transforms.Resize(224) / Resize((224, 224)) (profiling/run_profiler.py:63-70,
+// 293-project/src/milind-code/scheduler.py:24-27) = bilinear WITH antialias.  The arithmetic is torch's
+// (_compute_indices_min_size_weights_aa, ATen/native/cpu/UpSampleKernel.cpp): per axis, scale = in / out, support =
+// max(scale, 1), centre = scale * (i + 0.5), taps [int(centre - support + 0.5), int(centre + support + 0.5)) clipped to the
+// image, triangle weights 1 - |(j - centre + 0.5) / max(scale, 1)| normalised to 1.  One thread per output pixel walks
+// its (taps_y x taps_x) window once -- a single rounding at the end, where torch's uint8 path rounds between its two
+// passes: within 1 in the last bit of torchvision (oracle/preprocess.py resize_aa_u8, pinned to torchvision's output).
+// COLLATE_RESIZE_AA stretches to the canvas; COLLATE_RESIZE_SHORT_AA resizes the short side to the (square) canvas size
+// and centre-crops the long one, torchvision's Resize(s) + CenterCrop(s) with its integer size and offset rules.
+// ----------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+collate_u8_aa_kernel(const uint8_t* __restrict__ src_base, const CollateItem* __restrict__ items, int n, int out_h,
+                     int out_w, int mode, const uint16_t* __restrict__ lut, uint16_t* __restrict__ out) {
+  __shared__ uint16_t s_lut[3 * 256];
+  for (int i = threadIdx.x; i < 3 * 256; i += blockDim.x) s_lut[i] = lut[i];
+  __syncthreads();
+  const int slot = blockIdx.y;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= out_h * out_w) return;
+  uint2* dst = reinterpret_cast<uint2*>(out) + static_cast<size_t>(slot) * out_h * out_w + pix;
+  if (slot >= n) {
+    *dst = make_uint2(0, 0);
+    return;
+  }
+  CollateItem it = items[slot];
+  const int nch = it.w < 0 ? 1 : 3;
+  it.w = abs(it.w);
+  const uint8_t* src = src_base + it.offset;
+  const int oy = pix / out_w, ox = pix - oy * out_w;
+  int nh = out_h, nw = out_w, top = 0, left = 0;
+  if (mode == COLLATE_RESIZE_SHORT_AA) {
+    // torchvision _compute_resized_output_size: short side -> s, long side -> int(s * long / short)
+    const int sz = min(out_h, out_w);
+    if (it.w <= it.h) { nw = sz; nh = static_cast<int>(static_cast<long long>(sz) * it.h / it.w); }
+    else              { nh = sz; nw = static_cast<int>(static_cast<long long>(sz) * it.w / it.h); }
+    // CenterCrop: int(round((N - out) / 2.0)), Python's round (ties to even)
+    const int dy = nh - out_h, dx = nw - out_w;
+    top = (dy & 1) ? ((dy >> 1) + ((dy >> 1) & 1)) : (dy >> 1);
+    left = (dx & 1) ? ((dx >> 1) + ((dx >> 1) & 1)) : (dx >> 1);
+  }
+  const int ry = oy + top, rx = ox + left;              // position in the resized image
+  const float sy = static_cast<float>(it.h) / nh, sx = static_cast<float>(it.w) / nw;
+  const float sup_y = fmaxf(sy, 1.f), sup_x = fmaxf(sx, 1.f);
+  const float inv_y = 1.f / sup_y, inv_x = 1.f / sup_x;
+  const float cy = sy * (ry + 0.5f), cx = sx * (rx + 0.5f);
+  const int y0 = max(static_cast<int>(cy - sup_y + 0.5f), 0), y1 = min(static_cast<int>(cy + sup_y + 0.5f), it.h);
+  const int x0 = max(static_cast<int>(cx - sup_x + 0.5f), 0), x1 = min(static_cast<int>(cx + sup_x + 0.5f), it.w);
+  float acc0 = 0.f, acc1 = 0.f, acc2 = 0.f, wsum_y = 0.f, wsum_x = 0.f;
+  for (int x = x0; x < x1; ++x) wsum_x += fmaxf(1.f - fabsf((x - cx + 0.5f) * inv_x), 0.f);
+  for (int y = y0; y < y1; ++y) {
+    const float wy = fmaxf(1.f - fabsf((y - cy + 0.5f) * inv_y), 0.f);
+    wsum_y += wy;
+    const uint8_t* row = src + (static_cast<size_t>(y) * it.w + x0) * nch;
+    float r0 = 0.f, r1 = 0.f, r2 = 0.f;
+    if (nch == 3) {
+      for (int x = x0; x < x1; ++x, row += 3) {
+        const float wx = fmaxf(1.f - fabsf((x - cx + 0.5f) * inv_x), 0.f);
+        r0 += wx * row[0]; r1 += wx * row[1]; r2 += wx * row[2];
+      }
+    } else {
+      for (int x = x0; x < x1; ++x, ++row) r0 += fmaxf(1.f - fabsf((x - cx + 0.5f) * inv_x), 0.f) * row[0];
+      r1 = r2 = r0;
+    }
+    acc0 += wy * r0; acc1 += wy * r1; acc2 += wy * r2;
+  }
+  const float norm = 1.f / (wsum_x * wsum_y);
+  const int r = min(255, max(0, static_cast<int>(floorf(acc0 * norm + 0.5f))));
+  const int g = min(255, max(0, static_cast<int>(floorf(acc1 * norm + 0.5f))));
+  const int b = min(255, max(0, static_cast<int>(floorf(acc2 * norm + 0.5f))));
   uint2 o;
   o.x = uint32_t(s_lut[r]) | (uint32_t(s_lut[256 + g]) << 16);
   o.y = uint32_t(s_lut[512 + b]);
@@ -200,6 +279,15 @@ int collate_u8_launch(const uint8_t* src_base, const CollateItem* items_dev, con
     collate_u8_flat_kernel<<<grid, CT_THREADS, 0, stream>>>(src_base, items_dev, n, out_h * out_w, lut_dev,
                                                             static_cast<uint16_t*>(out));
   } else {
+    if (mode == COLLATE_RESIZE_AA || mode == COLLATE_RESIZE_SHORT_AA) {
+      if (mode == COLLATE_RESIZE_SHORT_AA && out_h != out_w)
+        return fail(B200_ERR_INVALID, "collate: short-side resize + centre crop needs a square model input");
+      dim3 grid((out_h * out_w + 255) / 256, padded_batch);
+      collate_u8_aa_kernel<<<grid, 256, 0, stream>>>(src_base, items_dev, n, out_h, out_w, mode, lut_dev,
+                                                     static_cast<uint16_t*>(out));
+      B200_CUDA_OK(cudaGetLastError());
+      return B200_OK;
+    }
     if (mode != COLLATE_IDENTITY && mode != COLLATE_PAD && mode != COLLATE_RESIZE && mode != COLLATE_LETTERBOX)
       return fail(B200_ERR_INVALID, "collate: unknown preprocess mode");
     if (mode == COLLATE_IDENTITY) {   // same-size images that missed the vector path only for alignment: plain copy

@@ -78,8 +78,9 @@ extern "C" int b200_collate_u8_noalloc(const void* packed_dev, const uint64_t* o
     items[i].offset = offsets[i];
     items[i].h = hw[2 * i];
     items[i].w = hw[2 * i + 1];
-    if (items[i].h <= 0 || items[i].w <= 0) return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: empty image");
-    if (offsets[i] + uint64_t(items[i].h) * items[i].w * 3 > packed_bytes)
+    if (items[i].h <= 0 || items[i].w == 0) return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: empty image");
+    const uint64_t wpx = items[i].w < 0 ? uint64_t(-int64_t(items[i].w)) : uint64_t(items[i].w);   // w < 0: grayscale
+    if (offsets[i] + uint64_t(items[i].h) * wpx * (items[i].w < 0 ? 1 : 3) > packed_bytes)
       return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: image " + std::to_string(i) + " exceeds the packed buffer");
     if (mode == COLLATE_IDENTITY && (items[i].h != out_h || items[i].w != out_w))
       return fail(B200_ERR_INVALID, "b200_collate_u8_noalloc: image " + std::to_string(i) + " is not out_h x out_w");

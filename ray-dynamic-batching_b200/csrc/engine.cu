@@ -603,8 +603,9 @@ int b200_collate(b200_engine* h, const void* packed, const uint64_t* offsets, co
     items_host[i].offset = offsets[i];
     items_host[i].h = hw[2 * i];
     items_host[i].w = hw[2 * i + 1];
-    if (hw[2 * i] <= 0 || hw[2 * i + 1] <= 0) return fail(B200_ERR_INVALID, "b200_collate: empty image");
-    if (offsets[i] + uint64_t(hw[2 * i]) * hw[2 * i + 1] * 3 > packed_bytes)
+    if (hw[2 * i] <= 0 || hw[2 * i + 1] == 0) return fail(B200_ERR_INVALID, "b200_collate: empty image");
+    const uint64_t wpx = hw[2 * i + 1] < 0 ? uint64_t(-int64_t(hw[2 * i + 1])) : uint64_t(hw[2 * i + 1]);   // w < 0: grayscale
+    if (offsets[i] + uint64_t(hw[2 * i]) * wpx * (hw[2 * i + 1] < 0 ? 1 : 3) > packed_bytes)
       return fail(B200_ERR_INVALID, "b200_collate: image " + std::to_string(i) + " exceeds the packed buffer");
     if (mode == COLLATE_IDENTITY && (hw[2 * i] != e.hdr.in_h || hw[2 * i + 1] != e.hdr.in_w))
       return fail(B200_ERR_INVALID, "b200_collate: image " + std::to_string(i) + " is not the model input size");

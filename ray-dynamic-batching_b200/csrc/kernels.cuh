@@ -10,7 +10,8 @@ struct CollateItem {
   uint64_t offset;  // byte offset of the image inside the staged uint8 buffer (multiple of 16 for the fast path)
   int32_t h, w;     // source height / width (HWC, 3 channels)
 };
-enum : int { COLLATE_IDENTITY = 0, COLLATE_PAD = 1, COLLATE_RESIZE = 2, COLLATE_LETTERBOX = 3 };
+enum : int { COLLATE_IDENTITY = 0, COLLATE_PAD = 1, COLLATE_RESIZE = 2, COLLATE_LETTERBOX = 3, COLLATE_RESIZE_AA = 4,
+              COLLATE_RESIZE_SHORT_AA = 5 };
 void build_norm_lut(const float mean[3], const float stdv[3], uint16_t lut[3 * 256]);
 int collate_u8_launch(const uint8_t* src_base, const CollateItem* items_dev, const CollateItem* items_host, int n,
                       int padded_batch, int out_h, int out_w, int mode, int fill, const uint16_t* lut_dev, void* out,

@@ -15,7 +15,7 @@ import torch
 from . import lib as _lib
 from . import lowering as _lowering
 
-COLLATE_IDENTITY, COLLATE_PAD, COLLATE_RESIZE, COLLATE_LETTERBOX = 0, 1, 2, 3
+COLLATE_IDENTITY, COLLATE_PAD, COLLATE_RESIZE, COLLATE_LETTERBOX, COLLATE_RESIZE_AA, COLLATE_RESIZE_SHORT_AA = 0, 1, 2, 3, 4, 5
 
 
 def default_buckets(max_batch):
@@ -176,7 +176,8 @@ class B200Model:
         total = 0
         for i, im in enumerate(images):
             offsets[i] = total
-            hw[i] = (im.shape[0], im.shape[1])
+            gray = im.dim() == 2 or im.shape[2] == 1            # single-channel request: width passed negative (L -> RGB)
+            hw[i] = (im.shape[0], -im.shape[1] if gray else im.shape[1])
             total += (im.numel() + 15) // 16 * 16
         if self._pinned is None or self._pinned.numel() < total:
             self._pinned = torch.empty(max(total, 1), dtype=torch.uint8, pin_memory=True)

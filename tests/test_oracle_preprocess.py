@@ -80,3 +80,43 @@ def test_identity_rejects_wrong_size_and_bad_counts():
         opre.preprocess_u8(np.zeros((10, 10, 3), np.uint8), 224, 224, opre.MODE_IDENTITY, 0)
     with pytest.raises(ValueError):
         opre.collate_u8([np.zeros((4, 4, 3), np.uint8)] * 3, 2, 4, 4, MEAN, STD)
+
+
+# ---- the reference's antialiased Resize (profiling/run_profiler.py:63-70): oracle restatement pinned to torchvision ----
+def _resize_golden():
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    import make_resize_golden as mk
+    return mk, np.load(os.path.join(os.path.dirname(__file__), "golden", "resize_aa_golden.npz"))
+
+
+def test_antialias_resize_oracle_within_one_lsb_of_torchvision_golden():
+    mk, g = _resize_golden()
+    from oracle import preprocess as op
+    worst, differing, total = 0, 0, 0
+    for i, (h, w) in enumerate(mk.SIZES):
+        img = mk.make_image(i, h, w).permute(1, 2, 0).numpy()
+        cases = [("stretch32_%d" % i, op.resize_aa_u8, 32), ("short32_%d" % i, op.resize_short_side_center_crop_u8, 32)]
+        if i in mk.FULL:
+            cases += [("stretch112_%d" % i, op.resize_aa_u8, 112), ("short112_%d" % i, op.resize_short_side_center_crop_u8, 112)]
+        for key, fn, s in cases:
+            got, want = fn(img, s, s), g[key]
+            assert got.shape == want.shape == (s, s, 3), key          # sizes and crop offsets exact
+            d = np.abs(got.astype(np.int16) - want.astype(np.int16))
+            worst, differing, total = max(worst, int(d.max())), differing + int((d > 0).sum()), total + d.size
+    print("antialias resize: worst |oracle - torchvision| = %d LSB, %d of %d values differ" % (worst, differing, total))
+    assert worst <= 1                                                  # <= 1 uint8 LSB before normalisation
+    gray = mk.make_image(100, 368, 304, gray=True).permute(1, 2, 0).numpy()
+    got = op.resize_short_side_center_crop_u8(op.to_rgb(gray), 32, 32)
+    assert np.abs(got.astype(np.int16) - g["gray_short32"].astype(np.int16)).max() <= 1
+
+
+def test_short_side_size_rule_matches_torchvision():
+    import torch
+    import torchvision.transforms.v2.functional as TF
+    from oracle import preprocess as op
+    for h, w in [(375, 500), (500, 375), (333, 500), (48, 80), (2592, 3328), (203, 940), (940, 203), (224, 224), (225, 224)]:
+        want = tuple(TF.resize(torch.zeros(3, h, w, dtype=torch.uint8), [224], antialias=True).shape[1:])
+        assert op.short_side_size(h, w, 224) == want
+    img = np.arange(6 * 8 * 3, dtype=np.uint8).reshape(6, 8, 3)
+    assert np.array_equal(op.resize_aa_u8(img, 6, 8), img)             # same size: the antialias weights collapse to identity
