@@ -305,7 +305,8 @@ B200_API int b200_ring_push_many(void* mem, int n, const char* ids, const char* 
 /* One round of RequestQueue.get_batch (scheduler.py:275-289): claims up to max_items requests in FIFO order, drops the
  * ones for which  arrival + slo_s < now + expected_latency_s  (scheduler.py:281; counted in *discarded) and returns
  * the others: slot numbers (payload of slot s at payload_off + s * slot_bytes), sequence numbers (for release), arrival
- * times, [h, w] pairs, byte counts, ids (B200_RING_ID_BYTES each).  Any output except slots / seqs may be NULL. */
+ * times, [h, w] pairs (w negated for a single-channel request, the convention b200_collate takes), byte counts, ids
+ * (B200_RING_ID_BYTES each).  Any output except slots / seqs may be NULL. */
 B200_API int b200_ring_pop(void* mem, int max_items, double now, double expected_latency_s, double slo_s, uint32_t* slots,
                            uint64_t* seqs, double* arrivals, int32_t* hw, uint32_t* nbytes, char* ids, int* discarded);
 /* Gives popped slots back to the producers (after the batch's host-to-device copy has completed). */

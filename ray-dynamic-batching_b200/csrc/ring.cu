@@ -240,7 +240,7 @@ int b200_ring_pop(void* mem, int max_items, double now, double expected_latency_
     slots[out] = static_cast<uint32_t>(seq % h->nslots);
     seqs[out] = seq;
     if (arrivals) arrivals[out] = d.arrival;
-    if (hw) { hw[2 * out] = d.h; hw[2 * out + 1] = d.w; }
+    if (hw) { hw[2 * out] = d.h; hw[2 * out + 1] = d.c == 1 ? -static_cast<int32_t>(d.w) : d.w; }   // grayscale: negative width (b200_collate)
     if (nbytes) nbytes[out] = d.nbytes;
     if (ids) memcpy(ids + size_t(out) * B200_RING_ID_BYTES, d.id, B200_RING_ID_BYTES);
     ++out;

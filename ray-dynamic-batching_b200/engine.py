@@ -71,6 +71,9 @@ class B200Model:
         self._pinned = None
         self._slots = None
         self._slot_i = 0
+        # detection models: {"conf", "iou", "max_det"} makes the asynchronous path run the class-aware NMS on the device
+        # and hand back detections [n, max_det, 6]; None hands back the raw [84][A] head.  Set before the first async call.
+        self.nms = None
         # batch-size buckets: a served batch of n requests is padded (zero images) to the next bucket, so the engine only
         # ever runs the sizes it captured graphs for at load.  None = every size runs as is (one graph per distinct size).
         self.buckets = None
@@ -211,7 +214,15 @@ class B200Model:
     class _Slot:
         def __init__(self, model):
             self.staging = None
-            self.out_host = torch.empty(model.max_batch, model.out_dim, dtype=torch.float32, pin_memory=True)
+            self.nms = model.nms
+            if self.nms:          # detections leave the GPU, not the [84][A] head (2.8 MB per 640 x 640 image)
+                md = int(self.nms["max_det"])
+                self.boxes_dev = torch.zeros(model.max_batch, md, 6, device=model.device, dtype=torch.float32)
+                self.counts_dev = torch.zeros(model.max_batch, device=model.device, dtype=torch.int32)
+                self.out_host = torch.empty(model.max_batch, md, 6, dtype=torch.float32, pin_memory=True)
+                self.counts_host = torch.empty(model.max_batch, dtype=torch.int32, pin_memory=True)
+            else:
+                self.out_host = torch.empty(model.max_batch, model.out_dim, dtype=torch.float32, pin_memory=True)
             self.copied = torch.cuda.Event()
             self.done = torch.cuda.Event()
             self.n = 0
@@ -220,9 +231,12 @@ class B200Model:
 
         def result(self):
             """Blocks until this batch is finished; returns the fp32 outputs [n, out] -- a VIEW of this slot's pinned
-            buffer, valid until the slot is handed out again (N_SLOTS - 1 submissions later): copy it to keep it."""
+            buffer, valid until the slot is handed out again (N_SLOTS - 1 submissions later): copy it to keep it.
+            With NMS on (model.nms): [n, max_det, 6] = x1, y1, x2, y2, score, class; rows past an image's count are zero."""
             self.done.synchronize()
             self.busy = False
+            if self.nms:
+                return self.out_host[:self.n]
             return self.out_host[:self.n, :self.out_logical]
 
     def _next_slot(self, total):
@@ -244,7 +258,16 @@ class B200Model:
         compute.wait_event(slot.copied)
         pb = padded_batch or n
         self.collate_u8(slot.staging, offsets, hw, n, pb, mode, total)
-        _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(slot.out_host), self._stream()), "b200_infer")
+        if slot.nms:
+            _lib.check(self.lib.b200_infer(self._h, None, pb, None, self._stream()), "b200_infer")
+            slot.boxes_dev[:pb].zero_()
+            _lib.check(self.lib.b200_decode_yolo(self._h, None, pb, float(slot.nms["conf"]), float(slot.nms["iou"]),
+                                                 int(slot.nms["max_det"]), _lib.ptr(slot.boxes_dev),
+                                                 _lib.ptr(slot.counts_dev), self._stream()), "b200_decode_yolo")
+            slot.out_host[:pb].copy_(slot.boxes_dev[:pb], non_blocking=True)
+            slot.counts_host[:pb].copy_(slot.counts_dev[:pb], non_blocking=True)
+        else:
+            _lib.check(self.lib.b200_infer(self._h, None, pb, _lib.ptr(slot.out_host), self._stream()), "b200_infer")
         slot.n = n
         slot.busy = True
         slot.done.record(compute)

@@ -48,8 +48,10 @@ class SlabInputs:
     def __getitem__(self, i):
         import torch
         h, w = int(self._hw[i, 0]), int(self._hw[i, 1])
+        c = self._c if w > 0 else 1                      # negative width: single-channel request
+        w = abs(w)
         off = int(self._slots[i]) * self._q.slot_bytes
-        return torch.from_numpy(self._q.payload[off:off + h * w * self._c].reshape(h, w, self._c))
+        return torch.from_numpy(self._q.payload[off:off + h * w * c].reshape(h, w, c))
 
     def __iter__(self):
         return (self[i] for i in range(len(self)))

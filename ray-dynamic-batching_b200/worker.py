@@ -27,9 +27,10 @@ from typing import Dict, List, Tuple
 import numpy as np
 import torch
 
-from .engine import B200Model, COLLATE_IDENTITY, COLLATE_LETTERBOX
+from .engine import B200Model, COLLATE_IDENTITY, COLLATE_LETTERBOX, COLLATE_RESIZE_SHORT_AA
 from .request_queue import BatchRequest
 
+YOLO_NMS = {"conf": 0.25, "iou": 0.45, "max_det": 300}      # ultralytics' defaults (utils/ops.py non_max_suppression)
 MODEL_KINDS = {'resnet': 'resnet50', 'shufflenet': 'shufflenet_v2_x1_0', 'efficientnet': 'efficientnet_v2_s',
                'yolov8': 'yolov8n'}
 
@@ -96,8 +97,11 @@ class B200GPUWorker:
         if isinstance(entry, dict):
             m = B200Model(entry['kind'], blob=entry['blob'], max_batch=cap, device=0, buckets=self.buckets)
             m.out_logical = entry.get('out_logical', m.out_logical)
-            return m
-        return B200Model(MODEL_KINDS.get(model_name, model_name), entry, max_batch=cap, device=0, buckets=self.buckets)
+        else:
+            m = B200Model(MODEL_KINDS.get(model_name, model_name), entry, max_batch=cap, device=0, buckets=self.buckets)
+        if getattr(m, 'kind', '') == 'yolov8n':
+            m.nms = dict(YOLO_NMS)       # a detection actor returns detections, not the 2.8 MB head of every image
+        return m
 
     def stop(self):
         self.logger.info("Stopping worker %s", self.node_id)
@@ -113,7 +117,10 @@ class B200GPUWorker:
             pend.queue = queue
             sb = queue.slot_bytes
             ident = bool((batch.hw[:, 0] == model.in_h).all() and (batch.hw[:, 1] == model.in_w).all())
-            mode = COLLATE_IDENTITY if ident else COLLATE_LETTERBOX
+            # requests of another size: the detector letterboxes (YOLOv8's LetterBox), the classifiers get the reference's own
+            # preprocessing, transforms.Resize(224) with antialias (profiling/run_profiler.py:63-70) + centre crop
+            mode = COLLATE_IDENTITY if ident else \
+                (COLLATE_LETTERBOX if getattr(model, "kind", "") == "yolov8n" else COLLATE_RESIZE_SHORT_AA)
             for lo in range(0, n, model.max_batch):                               # an oversize batch is split, not refused
                 hi = min(n, lo + model.max_batch)
                 runs, rel = [], np.empty(hi - lo, dtype=np.uint64)

@@ -29,3 +29,54 @@ def test_reference_summary_file_has_the_same_columns():
     assert open(REF_CSV).readline().strip().split(",") == profiler.FIELDNAMES
     d = profiler.load_csv_to_dict(REF_CSV)
     assert abs(d[256]['avg_latency_ms'] - 107.57) < 0.01          # A6000, 107.57 ms at batch 256
+
+
+B200_DIR = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "b200_batch_profiles")
+B200_FILES = {"resnet": "resnet50_b200_summary.csv", "shufflenet": "shufflenet_b200_summary.csv",
+              "efficientnet": "efficientnetv2_b200_summary.csv"}
+
+
+def test_b200_profiles_have_every_integer_batch_size():
+    """nexus.py indexes a profile with arbitrary integers (ceil(duty * rate / 1000), nexus.py:213-214; profile[batch_size],
+    scheduler.py:281): the committed B200 tables must have one row per batch size, with memory growing with the batch."""
+    for model, f in B200_FILES.items():
+        d = profiler.load_csv_to_dict(os.path.join(B200_DIR, f))
+        top = max(d)
+        assert top >= 256 and sorted(d) == list(range(1, top + 1)), model
+        lat = [d[b]['avg_latency_ms'] for b in range(1, top + 1)]
+        mem = [d[b]['peak_memory_mb'] for b in range(1, top + 1)]
+        assert all(x > 0 for x in lat) and all(b >= a for a, b in zip(mem, mem[1:])), model
+
+
+def test_packing_policy_consumes_the_b200_profiles():
+    from rdb_b200 import packing
+    prof = {m: profiler.load_csv_to_dict(os.path.join(B200_DIR, f)) for m, f in B200_FILES.items()}
+    for rates in ((300.0, 500.0, 20.0), (26000.0, 90000.0, 7000.0), (140000.0, 15.0, 2.5), (7.0, 3.0, 1.0)):
+        sessions = [packing.session("resnet", 2000 / 2.2, rates[0]), packing.session("shufflenet", 1500 / 2.2, rates[1]),
+                    packing.session("efficientnet", 40 / 2.2, rates[2])]
+        nodes = packing.nexus(prof).squishyBinPacking(sessions)
+        assert nodes and all(0 < n.get_occupancy() <= 1.0 + 1e-9 for n in nodes)
+
+
+def test_reference_nexus_consumes_the_b200_profiles():
+    """The reference's own policy module, unmodified, on the B200 tables: load_csv_to_dict, squishyBinPacking and
+    mergeNodes (nexus.py:129-133, 204-234) run without a KeyError at arbitrary rates."""
+    ref = "/root/reference/293-project/src/nexus.py"
+    if not os.path.exists(ref):
+        import pytest
+        pytest.skip("reference tree not present on this machine")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_nexus_b200", ref)
+    nx = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(nx)
+    prof = {m: nx.load_csv_to_dict(os.path.join(B200_DIR, f)) for m, f in B200_FILES.items()}
+    nx.gpu_mem = 160
+    pol = nx.nexus(prof)
+    for rates in ((300.0, 500.0, 20.0), (26000.0, 90000.0, 7000.0), (140000.0, 15.0, 2.5), (3333.3, 77.7, 911.0)):
+        sessions = [nx.session("resnet", 2000 / 2.2, rates[0]), nx.session("shufflenet", 1500 / 2.2, rates[1]),
+                    nx.session("efficientnet", 40 / 2.2, rates[2])]
+        nodes = pol.squishyBinPacking(sessions)
+        assert nodes
+        for a in nodes:
+            for b in nodes:
+                pol.mergeNodes(a, b)               # every pair: indexes profile[ceil(duty * rate / 1000)]
