@@ -346,22 +346,27 @@ static constexpr int NMS_CAP = 16384;  // >= anchors (8400 at 640x640), power of
 __global__ void __launch_bounds__(NMS_THREADS)
 yolo_nms_kernel(const float* __restrict__ pred, int nc, int a_total, float conf, float iou_thr, int max_det,
                 float max_wh, float* __restrict__ boxes, int* __restrict__ counts) {
-  extern __shared__ __align__(16) unsigned long long s_key[];  // [NMS_CAP] (score bits << 32) | ~anchor
+  extern __shared__ __align__(16) unsigned long long s_key[];  // [NMS_CAP] (score bits << 32) | ~anchor, then [NMS_CAP] class bytes
+  unsigned char* s_cls = reinterpret_cast<unsigned char*>(s_key + NMS_CAP);   // best class of anchor a (candidates only)
   __shared__ int s_n;
-  __shared__ float s_kept[300 * 5];  // shifted x1,y1,x2,y2 + unused
-  __shared__ int s_nkept, s_sup;
+  __shared__ float s_kept[300 * 4];  // class-shifted x1,y1,x2,y2 of the boxes kept so far
   const int n = blockIdx.x;
   const float* p = pred + static_cast<size_t>(n) * (4 + nc) * a_total;
-  if (threadIdx.x == 0) { s_n = 0; s_nkept = 0; }
+  if (threadIdx.x == 0) s_n = 0;
   for (int i = threadIdx.x; i < NMS_CAP; i += NMS_THREADS) s_key[i] = 0ull;
   __syncthreads();
   for (int a = threadIdx.x; a < a_total; a += NMS_THREADS) {
     float best = -1.f;
-    for (int c = 0; c < nc; ++c) best = fmaxf(best, p[static_cast<size_t>(4 + c) * a_total + a]);
+    int cls = 0;
+    for (int c = 0; c < nc; ++c) {       // first class attaining the best score (torch.max semantics)
+      const float v = p[static_cast<size_t>(4 + c) * a_total + a];
+      if (v > best) { best = v; cls = c; }
+    }
     if (best > conf) {
       const int slot = atomicAdd(&s_n, 1);
       // scores are in (0,1): their float bits order like unsigned ints; ~anchor makes the lower anchor win ties
       s_key[slot] = (static_cast<unsigned long long>(__float_as_uint(best)) << 32) | (0xFFFFFFFFu - static_cast<unsigned>(a));
+      s_cls[a] = static_cast<unsigned char>(cls);
     }
   }
   __syncthreads();
@@ -380,45 +385,53 @@ yolo_nms_kernel(const float* __restrict__ pred, int nc, int a_total, float conf,
       }
       __syncthreads();
     }
+  // Greedy suppression by ONE warp, no block-wide barriers: each lane fetches the box of one of the next 32 candidates (the
+  // global loads of a whole group are in flight together), then the group is walked in score order, every candidate
+  // broadcast by shuffles and tested by the 32 lanes against the kept list in shared memory.
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
   float* ob = boxes + static_cast<size_t>(n) * max_det * 6;
   const int cap = max_det < 300 ? max_det : 300;
-  for (int i = 0; i < ncand; ++i) {
-    if (s_nkept >= cap) break;
-    const unsigned long long key = s_key[i];
-    const int a = static_cast<int>(0xFFFFFFFFu - static_cast<unsigned>(key & 0xFFFFFFFFull));
-    const float score = __uint_as_float(static_cast<unsigned>(key >> 32));
+  int nk = 0;
+  for (int base = 0; base < ncand && nk < cap; base += 32) {
+    float x1 = 0.f, y1 = 0.f, x2 = 0.f, y2 = 0.f, score = 0.f, off = 0.f;
     int cls = 0;
-    {  // first class attaining the best score (torch.max semantics)
-      for (int c = 0; c < nc; ++c)
-        if (p[static_cast<size_t>(4 + c) * a_total + a] == score) { cls = c; break; }
+    if (base + lane < ncand) {
+      const unsigned long long key = s_key[base + lane];
+      const int a = static_cast<int>(0xFFFFFFFFu - static_cast<unsigned>(key & 0xFFFFFFFFull));
+      score = __uint_as_float(static_cast<unsigned>(key >> 32));
+      cls = s_cls[a];
+      const float cx = p[a], cy = p[static_cast<size_t>(a_total) + a], w = p[static_cast<size_t>(2) * a_total + a],
+                  h = p[static_cast<size_t>(3) * a_total + a];
+      x1 = cx - w / 2; y1 = cy - h / 2; x2 = cx + w / 2; y2 = cy + h / 2;
+      off = static_cast<float>(cls) * max_wh;
     }
-    const float cx = p[a], cy = p[static_cast<size_t>(a_total) + a], w = p[static_cast<size_t>(2) * a_total + a],
-                h = p[static_cast<size_t>(3) * a_total + a];
-    const float x1 = cx - w / 2, y1 = cy - h / 2, x2 = cx + w / 2, y2 = cy + h / 2;
-    const float off = static_cast<float>(cls) * max_wh;
-    const float sx1 = x1 + off, sy1 = y1 + off, sx2 = x2 + off, sy2 = y2 + off;
-    if (threadIdx.x == 0) s_sup = 0;
-    __syncthreads();
-    const int nk = s_nkept;
-    for (int k = threadIdx.x; k < nk; k += NMS_THREADS) {
-      const float kx1 = s_kept[k * 5], ky1 = s_kept[k * 5 + 1], kx2 = s_kept[k * 5 + 2], ky2 = s_kept[k * 5 + 3];
-      const float iw = fmaxf(fminf(sx2, kx2) - fmaxf(sx1, kx1), 0.f), ih = fmaxf(fminf(sy2, ky2) - fmaxf(sy1, ky1), 0.f);
-      const float inter = iw * ih;
-      const float iou = inter / ((sx2 - sx1) * (sy2 - sy1) + (kx2 - kx1) * (ky2 - ky1) - inter + 1e-7f);
-      if (iou > iou_thr) s_sup = 1;
-    }
-    __syncthreads();
-    if (!s_sup) {
-      if (threadIdx.x == 0) {
-        s_kept[nk * 5] = sx1; s_kept[nk * 5 + 1] = sy1; s_kept[nk * 5 + 2] = sx2; s_kept[nk * 5 + 3] = sy2;
-        ob[nk * 6] = x1; ob[nk * 6 + 1] = y1; ob[nk * 6 + 2] = x2; ob[nk * 6 + 3] = y2; ob[nk * 6 + 4] = score;
-        ob[nk * 6 + 5] = static_cast<float>(cls);
-        s_nkept = nk + 1;
+    const int in_group = min(32, ncand - base);
+    for (int j = 0; j < in_group && nk < cap; ++j) {
+      const float bx1 = __shfl_sync(0xffffffffu, x1, j), by1 = __shfl_sync(0xffffffffu, y1, j);
+      const float bx2 = __shfl_sync(0xffffffffu, x2, j), by2 = __shfl_sync(0xffffffffu, y2, j);
+      const float bo = __shfl_sync(0xffffffffu, off, j);
+      const float sx1 = bx1 + bo, sy1 = by1 + bo, sx2 = bx2 + bo, sy2 = by2 + bo;
+      bool sup = false;
+      for (int k = lane; k < nk; k += 32) {
+        const float kx1 = s_kept[k * 4], ky1 = s_kept[k * 4 + 1], kx2 = s_kept[k * 4 + 2], ky2 = s_kept[k * 4 + 3];
+        const float iw = fmaxf(fminf(sx2, kx2) - fmaxf(sx1, kx1), 0.f), ih = fmaxf(fminf(sy2, ky2) - fmaxf(sy1, ky1), 0.f);
+        const float inter = iw * ih;
+        const float iou = inter / ((sx2 - sx1) * (sy2 - sy1) + (kx2 - kx1) * (ky2 - ky1) - inter + 1e-7f);
+        sup = sup || (iou > iou_thr);
+      }
+      if (!__any_sync(0xffffffffu, sup)) {
+        if (lane == j) {
+          s_kept[nk * 4] = sx1; s_kept[nk * 4 + 1] = sy1; s_kept[nk * 4 + 2] = sx2; s_kept[nk * 4 + 3] = sy2;
+          ob[nk * 6] = x1; ob[nk * 6 + 1] = y1; ob[nk * 6 + 2] = x2; ob[nk * 6 + 3] = y2; ob[nk * 6 + 4] = score;
+          ob[nk * 6 + 5] = static_cast<float>(cls);
+        }
+        ++nk;
+        __syncwarp();
       }
     }
-    __syncthreads();
   }
-  if (threadIdx.x == 0) counts[n] = s_nkept;
+  if (lane == 0) counts[n] = nk;
 }
 
 int yolo_nms_launch(const float* pred, int batch, int nc, int a_total, float conf, float iou, int max_det, float* boxes,
@@ -429,10 +442,10 @@ int yolo_nms_launch(const float* pred, int batch, int nc, int a_total, float con
   int dev = 0;
   B200_CUDA_OK(cudaGetDevice(&dev));
   if (!configured[dev & 63]) {
-    B200_CUDA_OK(cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NMS_CAP * 8));
+    B200_CUDA_OK(cudaFuncSetAttribute(yolo_nms_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NMS_CAP * 9));
     configured[dev & 63] = true;
   }
-  yolo_nms_kernel<<<batch, NMS_THREADS, NMS_CAP * 8, stream>>>(pred, nc, a_total, conf, iou, max_det, 7680.f, boxes, counts);
+  yolo_nms_kernel<<<batch, NMS_THREADS, NMS_CAP * 9, stream>>>(pred, nc, a_total, conf, iou, max_det, 7680.f, boxes, counts);
   B200_CUDA_OK(cudaGetLastError());
   return B200_OK;
 }

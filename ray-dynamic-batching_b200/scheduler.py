@@ -70,6 +70,40 @@ class RequestTracker:
             return self._total_requests
 
 
+class RingRequestTracker(RequestTracker):
+    """The same rate, read from the request ring's own counters (accepted + dropped submissions): clients that write into
+    the shared-memory ring from other processes never pass through this process's submit_request, and the ring counts
+    every submission wherever it came from.  record_request is therefore a no-op here (the ring already counted it)."""
+
+    def __init__(self, queue, window_size: float = 60.0):
+        super().__init__(window_size)
+        self.queue = queue
+        self._seen = self._submitted()
+        self._window_base = self._seen
+
+    def _submitted(self) -> int:
+        o = self.queue.raw_stats()
+        return int(o[0]) + int(o[1])
+
+    def record_request(self, n: int = 1) -> None:
+        return
+
+    def get_request_rate(self) -> float:
+        with self.lock:
+            now = datetime.now()
+            total = self._submitted()
+            duration = (now - self.last_reset).total_seconds()
+            count = total - self._window_base
+            if duration >= self.window_size:
+                self._window_base = total
+                self.last_reset = now
+                return count / duration
+            return count / duration if duration > 0 else 0.0
+
+    def get_total_requests(self) -> int:
+        return self._submitted()
+
+
 class MetricsWriter:
     """The collector half of MetricsDisplay (scheduler.py:933-983) without the terminal: every `update_interval` seconds
     `metrics.json` = {model: get_stats() + 'request_rate'} -- the schema the reference's viewers read
@@ -237,7 +271,7 @@ class B200Scheduler:
                                                           batch_profile=self.batching_profile, slot_bytes=h * w * 3,
                                                           in_flight_slots=extra, compat=self.opts["compat"],
                                                           slo_ms=self._slo(model))
-            self.request_trackers[model] = RequestTracker(tracker_window)
+            self.request_trackers[model] = RingRequestTracker(self.request_queues[model], tracker_window)
 
     def _init_workers(self):
         """scheduler.py:670-693, for `num_gpus` actors instead of two."""

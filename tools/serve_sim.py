@@ -26,14 +26,13 @@ DEFAULT_BATCH = {"resnet": 256, "shufflenet": 512, "efficientnet": 128, "yolov8"
 PROFILE_CSV = {"resnet": "resnet50", "shufflenet": "shufflenet", "efficientnet": "efficientnetv2", "yolov8": "yolov8n"}
 
 
-def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, start_at, report):
+def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, report):
     """One load-generator process: bursts of `burst` requests at `rate` req/s into one model's ring."""
     import rdb_b200  # noqa: F401
     from rdb_b200 import synth
     pool = synth.synthetic_images(4 * burst, hw, hw, seed=8000 + seed).contiguous().numpy()
     p = pool.shape[0]
-    while time.time() < start_at:
-        time.sleep(0.001)
+    barrier.wait()                     # every client (and the parent's clock) starts together, imports done
     t0 = time.perf_counter()
     i = sub = drop = 0
     while True:
@@ -41,7 +40,7 @@ def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, start_at, 
         if el >= seconds:
             break
         target = slope * el * el / 2 if slope > 0 else rate * el
-        while i + burst <= target:
+        while i + burst <= target and time.perf_counter() - t0 < seconds:
             j = i % p
             if j + burst > p:
                 j = 0
@@ -83,6 +82,7 @@ def main():
     ap.add_argument("--burst", type=int, default=16)
     ap.add_argument("--dynamic", action="store_true")
     ap.add_argument("--pipeline-depth", type=int, default=2)
+    ap.add_argument("--max-batch", type=int, default=0, help="engine capacity (default: the largest batch size; 512 with --dynamic)")
     ap.add_argument("--metrics-file", default=os.path.join(ROOT, "gpurun_out", "metrics.json"))
     ap.add_argument("--out", default="")
     args = ap.parse_args()
@@ -105,7 +105,8 @@ def main():
     os.makedirs(os.path.dirname(args.metrics_file), exist_ok=True)
     t_load = time.time()
     sched = B200Scheduler(profile, monitoring_interval=1.0, rate_change_threshold=0.05, model_registry=registry,
-                          num_gpus=args.gpus, worker_mode="process", max_batch=max(batches), preload=models,
+                          num_gpus=args.gpus, worker_mode="process",
+                          max_batch=args.max_batch or (512 if args.dynamic else max(batches)), preload=models,
                           pipeline_depth=args.pipeline_depth, metrics_file=args.metrics_file, metrics_interval=1.0,
                           max_queue_size=max(2000, 6 * max(batches) * args.gpus),
                           in_flight_slots=4 * max(batches) * args.gpus + 256)
@@ -131,18 +132,17 @@ def main():
         ctx = mp.get_context("spawn")
         report = ctx.Queue()
         n_clients = args.clients or min(16, 2 * args.gpus)
-        start_at = time.time() + 6.0 + 0.5 * n_clients * len(models)       # spawned clients import torch first
+        barrier = ctx.Barrier(n_clients * len(models) + 1)
         procs = []
         for m, r in zip(models, rates):
             for c in range(n_clients):
                 procs.append(ctx.Process(target=client_main, daemon=True,
                                          args=(sched.request_queues[m], sched.model_registry[m]['in_hw'][0], r / n_clients,
                                                args.seconds, args.slope / n_clients, args.burst, "%s_c%d_" % (m, c),
-                                               100 * len(procs), start_at, report)))
+                                               100 * len(procs), barrier, report)))
         for p in procs:
             p.start()
-        while time.time() < start_at:
-            time.sleep(0.01)
+        barrier.wait(timeout=300)
         t0 = time.time()
         reports = [report.get(timeout=args.seconds + 120) for _ in procs]
         t_feed = time.time() - t0
