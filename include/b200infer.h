@@ -320,6 +320,9 @@ B200_API int b200_ring_record(void* mem, double latency_ms, int n_requests, doub
  * latency recorded since init (the window above holds only the last 900-1000 requests).  Visible to every process that maps the ring
  * (the reference's actors update a pickled copy of the metrics that the driver never sees). */
 B200_API int b200_ring_stats(void* mem, double* out, int n_out);
+/* The latency window those percentiles are taken over (the reference's metrics['latencies'] list, scheduler.py:333-336),
+ * oldest first, at most `cap` values; returns the count.  For merging the windows of a queue sharded over several rings. */
+B200_API int b200_ring_latencies(void* mem, double* out, int cap);
 
 #ifdef __cplusplus
 }

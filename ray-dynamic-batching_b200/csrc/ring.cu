@@ -200,7 +200,11 @@ int b200_ring_push_many(void* mem, int n, const char* ids, const char* id_prefix
     const int rc = b200_ring_push(mem, id, static_cast<const char*>(payloads) + size_t(i) * stride, nbytes, h_px, w_px, c,
                                   arrival);
     if (rc < 0) return rc;
-    if (rc == 0) break;
+    if (rc == 0) {                                  // full: the rest of the burst is dropped with it (one was counted by push)
+      RingHeader* h = hdr_of(mem);
+      h->dropped_requests.fetch_add(uint64_t(n - i - 1), std::memory_order_relaxed);
+      break;
+    }
     ++done;
   }
   return done;
@@ -281,6 +285,18 @@ int b200_ring_record(void* mem, double latency_ms, int n_requests, double slo_ms
   h->completed_requests.fetch_add(uint64_t(n_requests), std::memory_order_relaxed);
   h->completed_batches.fetch_add(1, std::memory_order_relaxed);
   return viol;
+}
+
+// The latency window get_stats reads, oldest first (what the reference's `metrics['latencies']` list holds): up to `cap`
+// values into `out`; returns how many.  Lets a caller that shards one model's queue over several rings merge their windows.
+int b200_ring_latencies(void* mem, double* out, int cap) {
+  RingHeader* h;
+  B200_TRY(check(mem, &h));
+  const uint64_t n = h->lat_count.load(std::memory_order_acquire);
+  uint64_t win = n <= 1000 ? n : 901 + (n - 1001) % 100;
+  if (win > uint64_t(cap)) win = uint64_t(cap);
+  for (uint64_t i = 0; i < win; ++i) out[i] = h->lat[(n - win + i) % LAT_CAP];
+  return static_cast<int>(win);
 }
 
 // get_stats (scheduler.py:343-372).  out[0..10] = total_requests, dropped_requests, slo_violations, queue_size,

@@ -74,6 +74,7 @@ class B200Model:
         # detection models: {"conf", "iou", "max_det"} makes the asynchronous path run the class-aware NMS on the device
         # and hand back detections [n, max_det, 6]; None hands back the raw [84][A] head.  Set before the first async call.
         self.nms = None
+        self.timing = {"batches": 0, "h2d_ms": 0.0, "gpu_ms": 0.0}
         # batch-size buckets: a served batch of n requests is padded (zero images) to the next bucket, so the engine only
         # ever runs the sizes it captured graphs for at load.  None = every size runs as is (one graph per distinct size).
         self.buckets = None
@@ -223,11 +224,13 @@ class B200Model:
                 self.counts_host = torch.empty(model.max_batch, dtype=torch.int32, pin_memory=True)
             else:
                 self.out_host = torch.empty(model.max_batch, model.out_dim, dtype=torch.float32, pin_memory=True)
-            self.copied = torch.cuda.Event()
-            self.done = torch.cuda.Event()
+            self.copy_start = torch.cuda.Event(enable_timing=True)
+            self.copied = torch.cuda.Event(enable_timing=True)
+            self.done = torch.cuda.Event(enable_timing=True)
             self.n = 0
             self.busy = False
             self.out_logical = model.out_logical
+            self.model = model
 
         def result(self):
             """Blocks until this batch is finished; returns the fp32 outputs [n, out] -- a VIEW of this slot's pinned
@@ -235,6 +238,10 @@ class B200Model:
             With NMS on (model.nms): [n, max_det, 6] = x1, y1, x2, y2, score, class; rows past an image's count are zero."""
             self.done.synchronize()
             self.busy = False
+            t = self.model.timing                   # device-side split of this batch: upload, then wait + collate + forward + D2H
+            t["batches"] += 1
+            t["h2d_ms"] += self.copy_start.elapsed_time(self.copied)
+            t["gpu_ms"] += self.copied.elapsed_time(self.done)
             if self.nms:
                 return self.out_host[:self.n]
             return self.out_host[:self.n, :self.out_logical]
@@ -280,6 +287,7 @@ class B200Model:
         total = int(total_bytes if total_bytes is not None else packed_host.numel())
         slot = self._next_slot(total)
         with torch.cuda.stream(self._copy_stream):
+            slot.copy_start.record(self._copy_stream)
             slot.staging[:total].copy_(packed_host[:total], non_blocking=True)
             slot.copied.record(self._copy_stream)
         return self._launch_slot(slot, offsets, hw, n, padded_batch, mode, total)
@@ -291,6 +299,7 @@ class B200Model:
         total = int(total_bytes)
         slot = self._next_slot(total)
         with torch.cuda.stream(self._copy_stream):
+            slot.copy_start.record(self._copy_stream)
             for src, nbytes, dst in runs:
                 slot.staging[dst:dst + nbytes].copy_(slab[src:src + nbytes], non_blocking=True)
             slot.copied.record(self._copy_stream)

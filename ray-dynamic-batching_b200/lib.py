@@ -97,6 +97,7 @@ SIGNATURES = {
     "b200_ring_qsize": (ctypes.c_longlong, [c_void_p]),
     "b200_ring_record": (c_int, [c_void_p, ctypes.c_double, c_int, ctypes.c_double]),
     "b200_ring_stats": (c_int, [c_void_p, c_void_p, c_int]),
+    "b200_ring_latencies": (c_int, [c_void_p, c_void_p, c_int]),
 }
 
 

@@ -32,7 +32,7 @@ from typing import Dict, List, Optional
 
 from . import packing
 from .request_queue import models_config
-from .slab_queue import SlabRequestQueue
+from .slab_queue import ShardedRequestQueue, SlabRequestQueue  # noqa: F401
 
 SLO_hack = 2.2          # scheduler.py:28
 
@@ -180,6 +180,7 @@ def _worker_main(node_id, gpu_index, request_queues, update_queue, registry, opt
     logging.basicConfig(level=getattr(logging, opts.get("log_level", "WARNING")),
                         format='%(asctime)s - %(name)s - %(levelname)s - %(message)s')
     from .worker import B200GPUWorker
+    request_queues = {m: (q.bind(gpu_index) if hasattr(q, "bind") else q) for m, q in request_queues.items()}
     try:
         worker = B200GPUWorker(node_id, 0, [], 1, registry, max_batch=opts.get("max_batch", 256),
                                compat_overshoot=opts.get("compat", False), buckets=opts.get("buckets", "auto"),
@@ -217,7 +218,8 @@ class B200Scheduler:
                  max_queue_size: int = 2000, worker_mode: str = "process", policy=None, compat: bool = False,
                  pipeline_depth: int = 2, buckets="auto", max_batch: int = 256, in_flight_slots: Optional[int] = None,
                  metrics_file: Optional[str] = "metrics.json", metrics_interval: float = 5.0, preload=(),
-                 slo_ms: Optional[Dict[str, float]] = None, tracker_window: float = 1.0, log_level: str = "WARNING"):
+                 slo_ms: Optional[Dict[str, float]] = None, tracker_window: float = 1.0, log_level: str = "WARNING",
+                 max_ring_bytes: int = 4 << 30, shard_queues: bool = True):
         self.batching_profile = batching_profile
         self.nexus_instance = policy if policy is not None else packing.nexus(batching_profile)
         self.sessions: Dict[str, packing.session] = {}
@@ -232,6 +234,8 @@ class B200Scheduler:
         self.logger = logging.getLogger("NexusScheduler")
         self.worker_mode = worker_mode
         self.slo_ms = dict(slo_ms or {})
+        self.max_ring_bytes = int(max_ring_bytes)
+        self.shard_queues = bool(shard_queues)
         self.opts = dict(compat=compat, pipeline_depth=pipeline_depth, buckets=buckets, max_batch=max_batch,
                          preload=tuple(preload), log_level=log_level)
         self.model_registry = lower_registry(model_registry)
@@ -240,7 +244,7 @@ class B200Scheduler:
             num_gpus = torch.cuda.device_count()
         self.num_gpus = int(num_gpus)
 
-        self.request_queues: Dict[str, SlabRequestQueue] = {}
+        self.request_queues: Dict[str, ShardedRequestQueue] = {}
         self.update_queues = []
         self._init_queues(max_queue_size, in_flight_slots, tracker_window)
         self.workers = []
@@ -267,10 +271,20 @@ class B200Scheduler:
         for model, entry in self.model_registry.items():
             h, w = entry.get('in_hw', (224, 224))
             extra = in_flight_slots if in_flight_slots is not None else max(1024, 4 * self.opts["max_batch"] * max(1, self.num_gpus))
-            self.request_queues[model] = SlabRequestQueue(model_name=model, max_size=max_queue_size,
-                                                          batch_profile=self.batching_profile, slot_bytes=h * w * 3,
-                                                          in_flight_slots=extra, compat=self.opts["compat"],
-                                                          slo_ms=self._slo(model))
+            # large requests (a 640 x 640 image is 1.2 MB): keep the segment, which every actor page-locks, within max_ring_bytes
+            slot = (h * w * 3 + 255) // 256 * 256
+            budget = max(64, int(self.max_ring_bytes // slot))
+            if max_queue_size + extra > budget:
+                max_queue_size_m = max(32, min(max_queue_size, budget * 3 // 5))
+                extra = max(32, budget - max_queue_size_m)
+            else:
+                max_queue_size_m = max_queue_size
+            # one ring per actor (each page-locked by its own actor only); a single ring when the actors are threads
+            shards = max(1, self.num_gpus) if self.worker_mode == "process" and self.shard_queues else 1
+            self.request_queues[model] = ShardedRequestQueue(model_name=model, max_size=max_queue_size_m,
+                                                             batch_profile=self.batching_profile, shards=shards,
+                                                             slot_bytes=h * w * 3, in_flight_slots=extra,
+                                                             compat=self.opts["compat"], slo_ms=self._slo(model))
             self.request_trackers[model] = RingRequestTracker(self.request_queues[model], tracker_window)
 
     def _init_workers(self):

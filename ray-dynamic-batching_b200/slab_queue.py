@@ -318,3 +318,143 @@ class SlabBatch(BatchRequest):
 
     def __len__(self):
         return self.batch_size
+
+
+def _latency_window(q):
+    out = np.zeros(1024, np.float64)
+    n = q._lib.b200_ring_latencies(q._mem, out.ctypes.data, 1024)
+    if n < 0:
+        _lib.check(n, "b200_ring_latencies")
+    return out[:n]
+
+
+SlabRequestQueue.latency_window = _latency_window
+
+
+class ShardedRequestQueue:
+    """One model's RequestQueue (scheduler.py:190-372) as one request ring PER MODEL ACTOR.
+
+    The reference has a single queue per model that every actor pulls from (scheduler.py:546-551); with one shared
+    segment page-locked by eight actor processes and written by two dozen clients, that single ring is also the single
+    point every process meets.  Here each actor owns a ring (and is the only process that page-locks it): a submission goes
+    to one shard, round-robin from the submitter's preferred shard, spilling to the next when that one is full; an actor
+    serves its own shard and takes from another only when its own is empty (the work sharing the shared FIFO gave).
+    Same five methods, so the scheduler and the actor loop use it unchanged; `bind(i)` gives actor or client i its view.
+    get_stats sums the counters and takes avg / p95 / p99 over the shards' latency windows together -- with one shard this
+    is exactly the single-ring result."""
+
+    def __init__(self, model_name: str, max_size: int = 2000, batch_profile: dict = None, *, shards: int = 1,
+                 slot_bytes: int = 224 * 224 * 3, in_flight_slots: int = 2048, compat: bool = False, clock=time.time,
+                 slo_ms: Optional[float] = None, names=None):
+        self.model_name = model_name
+        self.compat, self.clock = compat, clock
+        self.profile = (batch_profile or {}).get(model_name, {})
+        if names is None:
+            per = max(32, -(-int(max_size) // shards))
+            self.shards = [SlabRequestQueue(model_name, per, batch_profile, slot_bytes=slot_bytes,
+                                            in_flight_slots=max(32, -(-int(in_flight_slots) // shards)), compat=compat,
+                                            clock=clock, slo_ms=slo_ms) for _ in range(shards)]
+        else:
+            self.shards = [SlabRequestQueue(model_name, batch_profile=batch_profile, compat=compat, clock=clock, slo_ms=slo_ms,
+                                            name=n, create=False) for n in names]
+        self.slo_target = self.shards[0].slo_target
+        self.slot_bytes = self.shards[0].slot_bytes
+        self.max_size = sum(q.max_size for q in self.shards)
+        self.home = 0                 # this process's preferred shard
+        self._next = 0
+
+    def bind(self, index: int):
+        self.home = int(index) % len(self.shards)
+        self._next = self.home
+        return self
+
+    def __getstate__(self):
+        return dict(model_name=self.model_name, names=[q.name for q in self.shards], compat=self.compat,
+                    slo=self.slo_target, profile=self.profile, home=self.home)
+
+    def __setstate__(self, st):
+        self.__init__(st["model_name"], batch_profile={st["model_name"]: st["profile"]}, compat=st["compat"],
+                      slo_ms=st["slo"], names=st["names"])
+        self.bind(st["home"])
+
+    # ---- RequestQueue surface ----
+    def qsize(self) -> int:
+        return sum(q.qsize() for q in self.shards)
+
+    def empty(self) -> bool:
+        return all(q.empty() for q in self.shards)
+
+    def add_request(self, request_id: str, input_tensor) -> bool:
+        n = len(self.shards)
+        first = self._next
+        self._next = (first + 1) % n
+        for k in range(n):
+            q = self.shards[(first + k) % n]
+            if k < n - 1 and q.qsize() >= q.max_size:
+                continue                             # full: try the next shard before counting a drop
+            if q.add_request(request_id, input_tensor):
+                return True
+        return False
+
+    def add_requests(self, images, id_prefix="r", first_index=0) -> int:
+        n = len(self.shards)
+        first = self._next
+        self._next = (first + 1) % n
+        total, done = len(images), 0
+        for k in range(n):
+            q = self.shards[(first + k) % n]
+            if k < n - 1 and q.qsize() + (total - done) > q.max_size:
+                continue
+            done += q.add_requests(images[done:], id_prefix, first_index + done)
+            if done >= total:
+                break
+        return done
+
+    def get_batch(self, batch_size: int):
+        n = len(self.shards)
+        own = self.shards[self.home]
+        batch, discard = own.get_batch(batch_size)
+        if batch is not None or n == 1:
+            return batch, discard
+        for k in range(1, n):                        # own shard empty: share another actor's work
+            q = self.shards[(self.home + k) % n]
+            if q.qsize() == 0:
+                continue
+            b2, d2 = q.get_batch(batch_size)
+            if b2 is not None:
+                return b2, discard + d2
+            discard += d2
+        return None, 0 if self.compat else discard
+
+    def release(self, batch):
+        batch.queue.release(batch)
+
+    def record_batch_completion(self, batch, completion_time: float) -> int:
+        q = getattr(batch, "queue", None) or self.shards[self.home]
+        return q.record_batch_completion(batch, completion_time)
+
+    def pin(self):
+        self.shards[self.home].pin()                 # the others are page-locked the first time this actor takes from them
+
+    def raw_stats(self):
+        return np.sum([q.raw_stats() for q in self.shards], axis=0)
+
+    def get_stats(self) -> Dict:
+        per = [q.raw_stats() for q in self.shards]
+        tot = np.sum(per, axis=0)
+        stats = {'total_requests': int(tot[0]), 'dropped_requests': int(tot[1]), 'slo_violations': int(tot[2]),
+                 'queue_size': int(tot[3]), 'last_latency': float(max(p[4] for p in per))}
+        lat = np.concatenate([q.latency_window() for q in self.shards]) if int(tot[9]) else np.zeros(0)
+        if lat.size == 0:
+            stats.update(avg_latency=0, p95_latency=0, p99_latency=0)
+        else:
+            s = np.sort(lat)
+            stats.update(avg_latency=float(sum(lat.tolist()) / lat.size), p95_latency=float(s[int(lat.size * 0.95)]),
+                         p99_latency=float(s[int(lat.size * 0.99)]))
+        stats.update(discarded_stale=int(tot[8]), completed_requests=int(tot[9]), completed_batches=int(tot[10]),
+                     max_latency=float(max(p[11] for p in per)), shards=len(self.shards))
+        return stats
+
+    def close(self, unlink=None):
+        for q in self.shards:
+            q.close(unlink)

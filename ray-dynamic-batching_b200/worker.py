@@ -264,10 +264,16 @@ class B200GPUWorker:
             time_slice = total_time * occupancy
             t_slice = time.time()
             batch, discard_count = request_queues[s.model_name].get_batch(s.batch_size)
+            lt = self.stats.setdefault('loop_s', {'get_batch': 0.0, 'submit': 0.0, 'finish': 0.0, 'sleep': 0.0})
+            t1 = time.time()
+            lt['get_batch'] += t1 - t_slice
             if batch:
                 self._inflight.append(self.process_batch_async(batch, request_queues, discard_count))
+                t2 = time.time()
+                lt['submit'] += t2 - t1
                 before = len(results)
                 self._drain(request_queues, results, keep=self.pipeline_depth - 1)
+                lt['finish'] += time.time() - t2
                 if self.pipeline_depth == 1:
                     spent = results[-1]['processing_time'] if len(results) > before else (time.time() - t_slice) * 1000
                 else:
@@ -315,8 +321,22 @@ class B200GPUWorker:
     def get_stats(self) -> Dict:
         """scheduler.py:590-600."""
         pt = self.stats['processing_times'][-100:]
-        return {'node_id': self.node_id, 'gpu_id': self.gpu_id, 'processed_batches': self.stats['processed_batches'],
-                'total_requests': self.stats['total_requests'], 'avg_processing_time': sum(pt) / len(pt) if pt else 0}
+        out = {'node_id': self.node_id, 'gpu_id': self.gpu_id, 'processed_batches': self.stats['processed_batches'],
+               'total_requests': self.stats['total_requests'], 'avg_processing_time': sum(pt) / len(pt) if pt else 0}
+        # ours, beyond the reference's five keys: where a batch's time goes (device-side upload and compute, host-side loop)
+        for name, m in self.models.items():
+            t = getattr(m, "timing", None)
+            if t and t["batches"]:
+                out.setdefault('engines', {})[name] = {'batches': t["batches"], 'h2d_ms': t["h2d_ms"] / t["batches"],
+                                                       'gpu_ms': t["gpu_ms"] / t["batches"]}
+        lt = self.stats.get('loop_s')
+        if lt:
+            out['loop_s'] = dict(lt)
+        try:
+            out['device'] = str(torch.cuda.get_device_properties(0).uuid)
+        except Exception:  # noqa: BLE001
+            pass
+        return out
 
 
 GPUWorker = B200GPUWorker   # the reference's name

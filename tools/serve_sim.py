@@ -30,6 +30,8 @@ def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, r
     """One load-generator process: bursts of `burst` requests at `rate` req/s into one model's ring."""
     import rdb_b200  # noqa: F401
     from rdb_b200 import synth
+    if hasattr(queue, "bind"):
+        queue.bind(seed // 100)            # clients start their round-robin on different shards
     pool = synth.synthetic_images(4 * burst, hw, hw, seed=8000 + seed).contiguous().numpy()
     p = pool.shape[0]
     barrier.wait()                     # every client (and the parent's clock) starts together, imports done
@@ -48,6 +50,8 @@ def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, r
             sub += ok
             drop += burst - ok
             i += burst
+            if ok < burst:
+                time.sleep(0.0005)     # full queue: the burst is dropped (counted); do not hammer the ring's counters
         time.sleep(0.0002)
     report.put((prefix, sub, drop, time.perf_counter() - t0))
     queue.close()
@@ -82,6 +86,7 @@ def main():
     ap.add_argument("--burst", type=int, default=16)
     ap.add_argument("--dynamic", action="store_true")
     ap.add_argument("--pipeline-depth", type=int, default=2)
+    ap.add_argument("--no-shards", action="store_true", help="one shared ring per model instead of one per actor")
     ap.add_argument("--max-batch", type=int, default=0, help="engine capacity (default: the largest batch size; 512 with --dynamic)")
     ap.add_argument("--metrics-file", default=os.path.join(ROOT, "gpurun_out", "metrics.json"))
     ap.add_argument("--out", default="")
@@ -109,7 +114,7 @@ def main():
                           max_batch=args.max_batch or (512 if args.dynamic else max(batches)), preload=models,
                           pipeline_depth=args.pipeline_depth, metrics_file=args.metrics_file, metrics_interval=1.0,
                           max_queue_size=max(2000, 6 * max(batches) * args.gpus),
-                          in_flight_slots=4 * max(batches) * args.gpus + 256)
+                          in_flight_slots=4 * max(batches) * args.gpus + 256, shard_queues=not args.no_shards)
     out = {"models": models, "gpus": args.gpus, "seconds": args.seconds, "batches": dict(zip(models, batches))}
     try:
         if not sched.wait_ready(900):
@@ -157,7 +162,7 @@ def main():
             p.join(timeout=10)
         out.update(wall_s=wall, feed_s=t_feed, pattern=("slope %.0f/s^2" % args.slope) if args.slope else "constant",
                    clients_per_model=n_clients, burst=args.burst, dynamic=args.dynamic,
-                   pipeline_depth=args.pipeline_depth)
+                   pipeline_depth=args.pipeline_depth, shards=1 if args.no_shards else args.gpus)
         per = {}
         total_served = 0
         for m, r in zip(models, rates):
