@@ -176,10 +176,20 @@ def lower_registry(model_registry: Dict) -> Dict:
 
 def _worker_main(node_id, gpu_index, request_queues, update_queue, registry, opts, report_queue, stop_event):
     """Body of one model-actor process: pins its GPU, then runs GPUWorker.execute_schedule until told to stop."""
-    os.environ["CUDA_VISIBLE_DEVICES"] = str(gpu_index)          # what @ray.remote(num_gpus=1) does (scheduler.py:374)
+    # what @ray.remote(num_gpus=1) does (scheduler.py:374): this process sees one GPU -- the gpu_index-th of those the
+    # scheduler process itself was allowed to see
+    visible = [v for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip()]
+    os.environ["CUDA_VISIBLE_DEVICES"] = visible[gpu_index] if gpu_index < len(visible) else str(gpu_index)
+    # An actor's host work is a serving loop, not tensor math: one intra-op thread.  Left at the default, every actor
+    # starts a pool of as many OpenMP threads as the box has cores for its 1 MB output copies, and those pools spin after
+    # each use -- eight actors on a 32-core box then fight over the cores and the loops slow down by an order of magnitude.
+    os.environ.setdefault("OMP_NUM_THREADS", str(opts.get("cpu_threads", 1)))
+    os.environ.setdefault("MKL_NUM_THREADS", str(opts.get("cpu_threads", 1)))
     logging.basicConfig(level=getattr(logging, opts.get("log_level", "WARNING")),
                         format='%(asctime)s - %(name)s - %(levelname)s - %(message)s')
     from .worker import B200GPUWorker
+    import torch
+    torch.set_num_threads(int(opts.get("cpu_threads", 1)))
     request_queues = {m: (q.bind(gpu_index) if hasattr(q, "bind") else q) for m, q in request_queues.items()}
     try:
         worker = B200GPUWorker(node_id, 0, [], 1, registry, max_batch=opts.get("max_batch", 256),

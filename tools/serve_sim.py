@@ -28,6 +28,9 @@ PROFILE_CSV = {"resnet": "resnet50", "shufflenet": "shufflenet", "efficientnet":
 
 def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, report):
     """One load-generator process: bursts of `burst` requests at `rate` req/s into one model's ring."""
+    os.environ.setdefault("OMP_NUM_THREADS", "1")      # a client copies bytes; it must not bring a thread pool per process
+    import torch
+    torch.set_num_threads(1)
     import rdb_b200  # noqa: F401
     from rdb_b200 import synth
     if hasattr(queue, "bind"):
