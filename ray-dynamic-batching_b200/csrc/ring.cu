@@ -20,6 +20,9 @@
 //
 // Host code only (no kernels); compiled into libb200infer.so because it is the other half of the same boundary.
 #include <atomic>
+#if defined(__x86_64__) || defined(_M_X64)
+#include <emmintrin.h>
+#endif
 #include <algorithm>
 #include <math.h>
 #include <new>
@@ -76,6 +79,33 @@ inline int check(void* mem, RingHeader** out) {
 }
 
 inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// A request's bytes are written once by a client and read once by a GPU's copy engine; nothing on the host reads them in
+// between.  Non-temporal stores skip the read-for-ownership of every destination line and leave the payload in DRAM, where
+// the DMA finds it, instead of dirty in the writer's caches: with twenty clients feeding eight GPUs the host's memory
+// traffic per request drops by a third.  dst is 256-byte aligned (slots are), src is whatever the caller has.
+inline void stream_copy(void* dst, const void* src, size_t n) {
+#if defined(__x86_64__) || defined(_M_X64)
+  if (n >= 4096 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+    const size_t blocks = n / 64;
+    __m128i* d = static_cast<__m128i*>(dst);
+    const __m128i* s = static_cast<const __m128i*>(src);
+    for (size_t i = 0; i < blocks; ++i) {
+      const __m128i a = _mm_loadu_si128(s + 4 * i), b = _mm_loadu_si128(s + 4 * i + 1);
+      const __m128i c = _mm_loadu_si128(s + 4 * i + 2), e = _mm_loadu_si128(s + 4 * i + 3);
+      _mm_stream_si128(d + 4 * i, a);
+      _mm_stream_si128(d + 4 * i + 1, b);
+      _mm_stream_si128(d + 4 * i + 2, c);
+      _mm_stream_si128(d + 4 * i + 3, e);
+    }
+    const size_t done = blocks * 64;
+    if (done < n) memcpy(static_cast<char*>(dst) + done, static_cast<const char*>(src) + done, n - done);
+    _mm_sfence();                      // the streamed lines are globally visible before the slot is published
+    return;
+  }
+#endif
+  memcpy(dst, src, n);
+}
 
 }  // namespace
 
@@ -170,7 +200,7 @@ int b200_ring_push(void* mem, const char* request_id, const void* payload, uint3
     }
   }
   RingDesc& d = descs[pos % h->nslots];
-  memcpy(payload_of(h) + size_t(pos % h->nslots) * h->slot_bytes, payload, nbytes);
+  stream_copy(payload_of(h) + size_t(pos % h->nslots) * h->slot_bytes, payload, nbytes);
   d.arrival = arrival;
   d.nbytes = nbytes;
   d.h = static_cast<uint16_t>(h_px);

@@ -246,6 +246,14 @@ class B200Model:
                 return self.out_host[:self.n]
             return self.out_host[:self.n, :self.out_logical]
 
+    def prepare_async(self, total_bytes=None):
+        """Allocates everything the asynchronous path needs (pinned output slots, device staging for a full batch, the copy
+        stream) now, so that the first served batch does not pay for it: an actor calls this while it loads."""
+        total = int(total_bytes or self.max_batch * self.in_h * self.in_w * 3)
+        for _ in range(self.N_SLOTS):
+            self._next_slot(total)
+        self._slot_i = 0
+
     def _next_slot(self, total):
         if self._slots is None:
             self._slots = [B200Model._Slot(self) for _ in range(self.N_SLOTS)]

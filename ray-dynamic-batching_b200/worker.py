@@ -101,6 +101,8 @@ class B200GPUWorker:
             m = B200Model(MODEL_KINDS.get(model_name, model_name), entry, max_batch=cap, device=0, buckets=self.buckets)
         if getattr(m, 'kind', '') == 'yolov8n':
             m.nms = dict(YOLO_NMS)       # a detection actor returns detections, not the 2.8 MB head of every image
+        if self.pipeline_depth > 1 and hasattr(m, 'prepare_async'):
+            m.prepare_async()            # slots and staging now, not inside the first batch's latency
         return m
 
     def stop(self):
