@@ -42,6 +42,9 @@ struct StemCfg {
   // when it is done; with four slots the drain groups could run one row ahead of the pooling group and waited for a
   // free slot half of the time (ncu, 3x3 stem).  Eight (six next to the 7x7 stem's larger input ring) decouple them.
   static constexpr int POOL_RING = KS == 3 ? 8 : 6;
+  // pooling threads of the fused kernel: two warpgroups for the 3x3 stems (measured 197.7 -> 174.8 us, ShuffleNetV2 @512);
+  // the 7x7 / 64-wide stem is paced by its 14 MMAs per row and ran 3 % slower with the second group (188 -> 194 us)
+  static constexpr int POOL_THREADS = KS == 3 ? 256 : 128;
   static constexpr int PAD = KS / 2;
   static constexpr int KC = (KS + 2) / 2 & ~1;        // 7 -> 4 chunks (8 pixels), 3 -> 2 chunks (4 pixels)
   static constexpr int MMAS = KC / 2;                 // K = 16 (two chunks) per MMA
@@ -253,7 +256,12 @@ __device__ __forceinline__ uint32_t bf16x2_max_u32(uint32_t a, uint32_t b) {
   return *reinterpret_cast<uint32_t*>(&m);
 }
 
-static constexpr int SP_THREADS = 512;   // warps 0: TMA, 1: MMA, 4-7 / 8-11: drain of accumulator 0 / 1, 12-15: pooling
+// warps 0: TMA, 1: MMA, 4-7 / 8-11: drain of accumulator 0 / 1, 12-19: pooling.  Two pooling warpgroups: an ncu capture of the
+// 3x3 / 32-wide variant (ShuffleNetV2 @512) had the drain warps waiting for a free row slot 57 % of the time and the single
+// pooling warpgroup busy or waiting for the last row of its window the rest -- the pooled row (224 to 448 items of nine
+// dependent shared-memory loads and a max tree each) was the serial stage of the kernel; with 256 threads it is one
+// item per thread for 32 channels and under two for 64.
+static constexpr int SP_THREADS = 384 + 256;     // upper bound; a variant runs 384 + StemCfg::POOL_THREADS
 
 template <int KS, int NOUT, int ACT>
 __global__ void __launch_bounds__(SP_THREADS, 1)
@@ -276,7 +284,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   const int my_units = max(0, min(per_cta, p.total_units - unit0));
   const int Hp = p.Ho >> 1, Wp = p.Wo >> 1;
 
-  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SP_THREADS) {
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += static_cast<int>(blockDim.x)) {
     const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
   }
@@ -293,7 +301,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     }
     for (int r = 0; r < G::POOL_RING; ++r) {
       mbar_init(smem_u32(&bar_row_ready[r]), 128);
-      mbar_init(smem_u32(&bar_row_free[r]), 128);
+      mbar_init(smem_u32(&bar_row_free[r]), G::POOL_THREADS);
     }
     fence_barrier_init();
   } else if (warp == 1) {
@@ -413,7 +421,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     }
   } else if (warp >= 12) {
     // =========================== pooling warps: 3x3 / stride 2 max over the row ring, coalesced stores ===========================
-    const int ptid = threadIdx.x - 384;       // 0..127
+    const int ptid = threadIdx.x - 384;       // 0..G::POOL_THREADS-1
     int it = 0;
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
@@ -426,7 +434,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
           const int ph = y >> 1;
           uint16_t* orow = p.out + (static_cast<size_t>(n) * Hp + ph) * Wp * p.out_ps;
           const int CH = p.cout >> 3;               // 16-byte chunks per pooled pixel
-          for (int item = ptid; item < Wp * CH; item += 128) {
+          for (int item = ptid; item < Wp * CH; item += G::POOL_THREADS) {
             const int pw = fast_div(item, CH, p.mul_ch), chunk = item - pw * CH;
             // Branch-free window: a tap outside the image is replaced by its in-window neighbour (max is idempotent), so
             // the nine 16-byte loads are independent and issue back to back; with a branch per tap this loop was
@@ -509,7 +517,7 @@ static int stem_pool_launch_t(const CUtensorMap& in_map, const StemPoolParams& p
     configured[dev & 63] = true;
   }
   const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
-  B200_CUDA_OK(launch_pdl_if(p.total_units >= pdl_min_waves() * device_sm_count(), stem_pool_kernel<KS, NOUT, ACT>, dim3(ctas), dim3(SP_THREADS), smem, stream, in_map, p));
+  B200_CUDA_OK(launch_pdl_if(p.total_units >= pdl_min_waves() * device_sm_count(), stem_pool_kernel<KS, NOUT, ACT>, dim3(ctas), dim3(384 + G::POOL_THREADS), smem, stream, in_map, p));
   return B200_OK;
 }
 
