@@ -13,6 +13,8 @@
 //   warps 4-7 : epilogue (TMEM -> +bias -> ReLU -> bf16 -> swizzled smem -> TMA store clipped at the row end)
 //
 // Replaces tv resnet.py:268-270 (conv1 + bn1 + relu) as reached from scheduler.py:450.
+#include <stdlib.h>
+
 #include "kernels.cuh"
 #include "ptx.cuh"
 
@@ -53,6 +55,10 @@ struct StemCfg {
   static constexpr int STAGE_BYTES = KR * SR_ROW_BYTES;
   static constexpr int W_BYTES = KR * KC * NOUT * 16; // weights: [kernel row][k chunk][cout][8 bf16]
   static constexpr int TMEM_COLS = 2 * NOUT < 32 ? 32 : 2 * NOUT;
+  // fused kernels: four accumulators, so the MMAs of row it + 2 do not wait for the drain of row it
+  // (measured on the ring kernel: 174.8 -> 172.8 us for the 3x3 stem, 188.4 -> 185.8 us for the 7x7 one)
+  static constexpr int POOL_ACCS = 4;
+  static constexpr int POOL_TMEM_COLS = POOL_ACCS * NOUT;
   static_assert(KS == 7 || KS == 3, "stem kernel size");
   static_assert(NOUT == 32 || NOUT == 64, "stem accumulator width");
 };
@@ -269,7 +275,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   using G = StemCfg<KS, NOUT>;
   constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[2], bar_t_empty[2];
+  __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[G::POOL_ACCS], bar_t_empty[G::POOL_ACCS];
   __shared__ __align__(8) uint64_t bar_row_ready[G::POOL_RING], bar_row_free[G::POOL_RING];
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[64];
@@ -295,7 +301,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       mbar_init(smem_u32(&bar_full[s]), 1);
       mbar_init(smem_u32(&bar_empty[s]), 1);
     }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < G::POOL_ACCS; ++b) {
       mbar_init(smem_u32(&bar_t_full[b]), 1);
       mbar_init(smem_u32(&bar_t_empty[b]), 128);
     }
@@ -305,7 +311,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     }
     fence_barrier_init();
   } else if (warp == 1) {
-    tmem_alloc<G::TMEM_COLS>(smem_u32(&tmem_base_s));
+    tmem_alloc<G::POOL_TMEM_COLS>(smem_u32(&tmem_base_s));
   }
   fence_proxy_async_smem();
   tc_fence_before();
@@ -350,8 +356,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         int n, ph0, ph1, y_lo, y_hi;
         unit_rows(u, n, ph0, ph1, y_lo, y_hi);
         for (int y = y_lo; y <= y_hi; ++y, ++it) {
-          const int b = it & 1, s = it % G::STAGES;
-          mbar_wait(smem_u32(&bar_t_empty[b]), ((it >> 1) & 1) ^ 1);
+          const int b = it & (G::POOL_ACCS - 1), s = it % G::STAGES;
+          mbar_wait(smem_u32(&bar_t_empty[b]), ((it / G::POOL_ACCS) & 1) ^ 1);
           mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
           tc_fence_after();
           const uint32_t a0 = ring + s * SR_STAGE_BYTES;
@@ -385,10 +391,10 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
-        const int b = it & 1, slot = it % G::POOL_RING;
-        if (b != dwg) continue;
+        const int b = it & (G::POOL_ACCS - 1), slot = it % G::POOL_RING;
+        if ((b & 1) != dwg) continue;
         mbar_wait(smem_u32(&bar_row_free[slot]), ((it / G::POOL_RING) & 1) ^ 1);   // pooling is done with the row that lived here
-        mbar_wait(smem_u32(&bar_t_full[b]), (it >> 1) & 1);
+        mbar_wait(smem_u32(&bar_t_full[b]), (it / G::POOL_ACCS) & 1);
         tc_fence_after();
         const uint32_t dst_row = rows + slot * SR_OUT_BYTES + row * 128;
         const uint32_t acc = tmem_base + b * NOUT + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -473,7 +479,221 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<G::TMEM_COLS>(tmem_base);
+    tmem_dealloc<G::POOL_TMEM_COLS>(tmem_base);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------------
+// The same fused stem + MaxPool2d(3, 2, 1) with the pooling done in REGISTERS by the warps that drain the accumulators.
+// An ncu capture of the kernel above (3x3 / 32-wide, ShuffleNetV2 @512) after its waits had been tuned away showed the
+// two stages simply executing: 1,920 warp instructions per stem row -- ~870 to drain a row into the shared-memory ring
+// (TMEM load, bias, ReLU, pack, swizzled stores, two barriers) and ~940 to pool it back out (nine 16-byte loads and a max
+// tree per item, index arithmetic, three barriers) -- 64 % of the issue slots of the SM, for a kernel whose MMAs need 240
+// cycles per row.  Here a thread owns stem pixel ow (its TMEM lane) for ALL rows and HALF = NOUT / 2 channels (warpgroup
+// g drains channel half g): the vertical 3-max is a running bf16x2 max in registers, the horizontal one takes the two
+// neighbour pixels from the neighbouring lanes by shuffle (the one neighbour that sits in another warp comes through a
+// small shared-memory mailbox and one named barrier per pooled row), even pixels store their pooled pixel.  No row ring,
+// no pooling warps: ~800 warp instructions per row.  Bit-identical with the unfused pair (max is exact in bf16).
+// ----------------------------------------------------------------------------------------------------------------
+static constexpr int SPR_THREADS = 384;   // warps 0: TMA, 1: MMA, 4-7: channel half 0, 8-11: channel half 1
+
+template <int KS, int NOUT, int ACT>
+__global__ void __launch_bounds__(SPR_THREADS, 1)
+stem_pool_reg_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ StemPoolParams p) {
+  using G = StemCfg<KS, NOUT>;
+  constexpr int SR_STAGE_BYTES = G::STAGE_BYTES, SR_W_BYTES = G::W_BYTES, SR_LEAD_BYTES = G::LEAD_BYTES;
+  constexpr int HALF = NOUT / 2;            // channels per drain thread
+  constexpr int HP = HALF / 2;              // packed bf16x2 registers per thread
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bar_full[G::STAGES], bar_empty[G::STAGES], bar_t_full[G::POOL_ACCS], bar_t_empty[G::POOL_ACCS];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ __align__(16) float bias_s[64];
+  __shared__ __align__(16) uint32_t xch[2][2][4][HP];   // [mailbox copy][channel half][warp quarter]: lane 31's running max
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t ring = base;
+  const uint32_t wsm = ring + G::STAGES * SR_STAGE_BYTES + 256;
+  const int per_cta = (p.total_units + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int unit0 = static_cast<int>(blockIdx.x) * per_cta;
+  const int my_units = max(0, min(per_cta, p.total_units - unit0));
+  const int Hp = p.Ho >> 1, Wp = p.Wo >> 1;
+
+  for (int i = threadIdx.x; i < SR_W_BYTES / 16; i += SPR_THREADS) {
+    const uint4 v = reinterpret_cast<const uint4*>(p.w)[i];
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(wsm + i * 16), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+  }
+  if (threadIdx.x < NOUT) bias_s[threadIdx.x] = p.bias[threadIdx.x];
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&in_map);
+    for (int s = 0; s < G::STAGES; ++s) {
+      mbar_init(smem_u32(&bar_full[s]), 1);
+      mbar_init(smem_u32(&bar_empty[s]), 1);
+    }
+    for (int b = 0; b < G::POOL_ACCS; ++b) {
+      mbar_init(smem_u32(&bar_t_full[b]), 1);
+      mbar_init(smem_u32(&bar_t_empty[b]), 256);      // both channel halves have read the accumulator
+    }
+    fence_barrier_init();
+  } else if (warp == 1) {
+    tmem_alloc<G::POOL_TMEM_COLS>(smem_u32(&tmem_base_s));
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+  pdl_launch_dependents();
+  pdl_wait();
+
+  auto unit_rows = [&](int u, int& n, int& ph0, int& ph1, int& y_lo, int& y_hi) {
+    n = u / p.bands;
+    ph0 = (u - n * p.bands) * SP_BAND;
+    ph1 = min(ph0 + SP_BAND, Hp);                 // pooled rows [ph0, ph1)
+    y_lo = max(0, 2 * ph0 - 1);
+    y_hi = 2 * (ph1 - 1) + 1;
+  };
+
+  if (warp == 0) {
+    int it = 0;
+    for (int u = unit0; u < unit0 + my_units; ++u) {
+      int n, ph0, ph1, y_lo, y_hi;
+      unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+      for (int y = y_lo; y <= y_hi; ++y, ++it) {
+        const int s = it % G::STAGES;
+        mbar_wait(smem_u32(&bar_empty[s]), ((it / G::STAGES) & 1) ^ 1);
+        const uint32_t full = smem_u32(&bar_full[s]);
+        if (elect_one()) {
+          mbar_expect_tx(full, G::KR * SR_ROW_BYTES);
+          tma_load_4d(&in_map, full, ring + s * SR_STAGE_BYTES, 0, -1, 2 * y - G::PAD, n);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
+    int it = 0;
+    for (int u = unit0; u < unit0 + my_units; ++u) {
+      int n, ph0, ph1, y_lo, y_hi;
+      unit_rows(u, n, ph0, ph1, y_lo, y_hi);
+      for (int y = y_lo; y <= y_hi; ++y, ++it) {
+        const int b = it & (G::POOL_ACCS - 1), s = it % G::STAGES;
+        mbar_wait(smem_u32(&bar_t_empty[b]), ((it / G::POOL_ACCS) & 1) ^ 1);
+        mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
+        tc_fence_after();
+        const uint32_t a0 = ring + s * SR_STAGE_BYTES;
+        if (elect_one()) {
+#pragma unroll
+          for (int r = 0; r < G::KR; ++r) {
+#pragma unroll
+            for (int kk = 0; kk < G::MMAS; ++kk) {
+              const uint64_t adesc = umma_desc_noswz(a0 + r * SR_ROW_BYTES + SR_LEAD_BYTES + kk * 32, 16, 128);
+              const uint64_t bdesc = umma_desc_noswz(wsm + (r * G::KC + kk * 2) * (NOUT * 16), NOUT * 16, 128);
+              umma_bf16(tmem_base + b * NOUT, adesc, bdesc, idesc, (r | kk) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(smem_u32(&bar_empty[s]));
+          umma_commit(smem_u32(&bar_t_full[b]));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    const int g = (warp - 4) >> 2;            // channel half
+    const int quarter = warp & 3;
+    const int ow = quarter * 32 + lane;       // stem pixel owned by this thread
+    const bool emits = (ow & 1) == 0 && ow < p.Wo;
+    const int nchunk = max(0, min(HALF / 8, (p.cout - g * HALF) / 8));   // 16-byte chunks of this half that are stored
+    const uint32_t lane_base = tmem_base + g * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
+    // The rows of this CTA as one sequence, so that the TMEM load of row it + 1 is issued before the arithmetic of row it:
+    // every drain warp sees every row, and with the wait for the MMA, the load and the pooling in one dependent chain a
+    // row took ~760 cycles whatever the instruction count (first version of this kernel: no faster than the row ring).
+    struct RowIt { int u, n, ph0, y_lo, y_hi, y; bool valid; };
+    auto open_unit = [&](RowIt& r) {
+      r.valid = r.u < unit0 + my_units;
+      if (r.valid) {
+        int ph1;
+        unit_rows(r.u, r.n, r.ph0, ph1, r.y_lo, r.y_hi);
+        r.y = r.y_lo;
+      }
+    };
+    auto advance = [&](RowIt& r) {
+      if (r.y < r.y_hi) { ++r.y; return; }
+      ++r.u;
+      open_unit(r);
+    };
+    auto issue_load = [&](int it, uint32_t (&v)[HALF]) {
+      const int b = it & (G::POOL_ACCS - 1);
+      mbar_wait(smem_u32(&bar_t_full[b]), (it / G::POOL_ACCS) & 1);
+      tc_fence_after();
+      if constexpr (HALF == 32) tmem_ld_32x32(lane_base + b * NOUT, v); else tmem_ld_32x16(lane_base + b * NOUT, v);
+    };
+    uint32_t vm[HP];
+    int emitted = 0;                          // alternates the mailbox: a writer is never one barrier ahead of a reader of the same copy
+    // one row: `v` holds its accumulator (load already issued), `vnext` receives the next row's
+    auto row = [&](int it, RowIt& cur, uint32_t (&v)[HALF], uint32_t (&vnext)[HALF]) {
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(smem_u32(&bar_t_empty[it & (G::POOL_ACCS - 1)]));   // the accumulator is free as soon as it is in registers
+      const RowIt me = cur;
+      advance(cur);
+      if (cur.valid) issue_load(it + 1, vnext);
+      uint32_t pk[HP];
+#pragma unroll
+      for (int j = 0; j < HP; ++j)
+        pk[j] = pack_bf16x2(apply_act(__uint_as_float(v[2 * j]) + bias_s[g * HALF + 2 * j], ACT),
+                            apply_act(__uint_as_float(v[2 * j + 1]) + bias_s[g * HALF + 2 * j + 1], ACT));
+      if (me.y == me.y_lo) {
+#pragma unroll
+        for (int j = 0; j < HP; ++j) vm[j] = pk[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < HP; ++j) vm[j] = bf16x2_max_u32(vm[j], pk[j]);
+      }
+      if ((me.y & 1) && (me.y >> 1) >= me.ph0) {       // row 2*ph + 1 completes pooled row ph (rows y-2, y-1, y are in vm)
+        const int ph = me.y >> 1;
+        const int par = emitted++ & 1;
+        uint32_t* box = xch[par][g][quarter];
+        if (lane == 31) {
+#pragma unroll
+          for (int j = 0; j < HP; ++j) box[j] = vm[j];
+        }
+        named_bar_sync(1 + g, 128);
+        uint32_t m[HP];
+#pragma unroll
+        for (int j = 0; j < HP; ++j) {
+          uint32_t left = __shfl_up_sync(0xffffffffu, vm[j], 1);
+          const uint32_t right = __shfl_down_sync(0xffffffffu, vm[j], 1);
+          // pixel ow - 1 of lane 0 lives in the previous warp (mailbox); pixel -1 is padding: max is idempotent, use own
+          if (lane == 0) left = quarter > 0 ? xch[par][g][quarter - 1][j] : vm[j];
+          m[j] = bf16x2_max_u32(bf16x2_max_u32(left, vm[j]), right);
+        }
+        if (emits) {
+          uint16_t* dst = p.out + ((static_cast<size_t>(me.n) * Hp + ph) * Wp + (ow >> 1)) * p.out_ps + g * HALF;
+#pragma unroll
+          for (int c = 0; c < HALF / 8; ++c)
+            if (c < nchunk) *reinterpret_cast<uint4*>(dst + c * 8) = make_uint4(m[4 * c], m[4 * c + 1], m[4 * c + 2], m[4 * c + 3]);
+        }
+#pragma unroll
+        for (int j = 0; j < HP; ++j) vm[j] = pk[j];   // row y is also the top row of the next pooled row's window
+      }
+    };
+    RowIt cur;
+    cur.u = unit0;
+    open_unit(cur);
+    uint32_t va[HALF], vb[HALF];
+    if (cur.valid) issue_load(0, va);
+    for (int it = 0; cur.valid; it += 2) {
+      row(it, cur, va, vb);
+      if (!cur.valid) break;
+      row(it + 1, cur, vb, va);
+    }
+  }
+
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<G::POOL_TMEM_COLS>(tmem_base);
   }
 }
 
@@ -503,6 +723,22 @@ static int stem_in_map(CUtensorMap* m, const View& in, int krows) {
   const uint64_t str[3] = {128, uint64_t(in.W) * 8, uint64_t(in.W) * 8 * in.H};
   const uint32_t box[4] = {64, uint32_t(SR_GROUPS), uint32_t(krows), 1};
   return encode_tmap(m, in.base, 4, dims, str, box, SWZ_NONE);
+}
+
+template <int KS, int NOUT, int ACT>
+static int stem_pool_reg_launch_t(const CUtensorMap& in_map, const StemPoolParams& p, cudaStream_t stream) {
+  using G = StemCfg<KS, NOUT>;
+  const size_t smem = size_t(G::STAGES) * G::STAGE_BYTES + 256 + G::W_BYTES + 2048;
+  static bool configured[64] = {};
+  int dev = 0;
+  B200_CUDA_OK(cudaGetDevice(&dev));
+  if (!configured[dev & 63]) {
+    B200_CUDA_OK(cudaFuncSetAttribute(stem_pool_reg_kernel<KS, NOUT, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    configured[dev & 63] = true;
+  }
+  const int ctas = p.total_units < device_sm_count() ? p.total_units : device_sm_count();
+  B200_CUDA_OK(launch_pdl_if(p.total_units >= pdl_min_waves() * device_sm_count(), stem_pool_reg_kernel<KS, NOUT, ACT>, dim3(ctas), dim3(SPR_THREADS), smem, stream, in_map, p));
+  return B200_OK;
 }
 
 template <int KS, int NOUT, int ACT>
@@ -568,6 +804,12 @@ int stem_pool_launch_k(const View& in, const View& out, const void* w, const flo
   p.total_units = in.N * p.bands;
   p.mul_ch = fast_div_mul(p.cout >> 3);
   const int nout = stem_nout(out.C);
+  static int reg_pool = -1;
+  if (reg_pool < 0) {
+    const char* e = getenv("B200_STEM_POOL_REG");
+    reg_pool = (e && e[0] == '0') ? 0 : 1;      // B200_STEM_POOL_REG=0: the shared-memory row ring + pooling warps above
+  }
+  if (reg_pool && out.pix_stride % 8 == 0) B200_STEM_DISPATCH(stem_pool_reg_launch_t, in_map, p, stream);
   B200_STEM_DISPATCH(stem_pool_launch_t, in_map, p, stream);
 }
 
