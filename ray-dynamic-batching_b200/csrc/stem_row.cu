@@ -330,13 +330,17 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
     y_hi = 2 * (ph1 - 1) + 1;
   };
 
-  if (warp == 0) {
+  if (warp == 0 || warp == 3) {
+    // two producer warps and two MMA-issuing warps, rows dealt alternately: a single warp's ~110 dependent instructions per
+    // row (coordinates, descriptors, barriers) are ~760 cycles -- that loop, not the MMAs or the epilogue, paced the kernel
+    const int mine = warp == 0 ? 0 : 1;
     {
       int it = 0;
       for (int u = unit0; u < unit0 + my_units; ++u) {
         int n, ph0, ph1, y_lo, y_hi;
         unit_rows(u, n, ph0, ph1, y_lo, y_hi);
         for (int y = y_lo; y <= y_hi; ++y, ++it) {
+          if ((it & 1) != mine) continue;
           const int s = it % G::STAGES;
           mbar_wait(smem_u32(&bar_empty[s]), ((it / G::STAGES) & 1) ^ 1);
           const uint32_t full = smem_u32(&bar_full[s]);
@@ -348,7 +352,8 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == 1 || warp == 2) {
+    const int mine = warp - 1;
     {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
       int it = 0;
@@ -356,6 +361,7 @@ stem_pool_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_consta
         int n, ph0, ph1, y_lo, y_hi;
         unit_rows(u, n, ph0, ph1, y_lo, y_hi);
         for (int y = y_lo; y <= y_hi; ++y, ++it) {
+          if ((it & 1) != mine) continue;
           const int b = it & (G::POOL_ACCS - 1), s = it % G::STAGES;
           mbar_wait(smem_u32(&bar_t_empty[b]), ((it / G::POOL_ACCS) & 1) ^ 1);
           mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
@@ -554,12 +560,16 @@ stem_pool_reg_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
     y_hi = 2 * (ph1 - 1) + 1;
   };
 
-  if (warp == 0) {
+  if (warp == 0 || warp == 3) {
+    // two producer warps and two MMA-issuing warps, rows dealt alternately: a single warp's ~110 dependent instructions per
+    // row (coordinates, descriptors, barriers) are ~760 cycles -- that loop, not the MMAs or the epilogue, paced the kernel
+    const int mine = warp == 0 ? 0 : 1;
     int it = 0;
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
+        if ((it & 1) != mine) continue;
         const int s = it % G::STAGES;
         mbar_wait(smem_u32(&bar_empty[s]), ((it / G::STAGES) & 1) ^ 1);
         const uint32_t full = smem_u32(&bar_full[s]);
@@ -570,14 +580,16 @@ stem_pool_reg_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_co
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == 1 || warp == 2) {
+    const int mine = warp - 1;
     constexpr uint32_t idesc = umma_idesc_bf16_f32(128, NOUT);
     int it = 0;
     for (int u = unit0; u < unit0 + my_units; ++u) {
       int n, ph0, ph1, y_lo, y_hi;
       unit_rows(u, n, ph0, ph1, y_lo, y_hi);
       for (int y = y_lo; y <= y_hi; ++y, ++it) {
-        const int b = it & (G::POOL_ACCS - 1), s = it % G::STAGES;
+        if ((it & 1) != mine) continue;
+          const int b = it & (G::POOL_ACCS - 1), s = it % G::STAGES;
         mbar_wait(smem_u32(&bar_t_empty[b]), ((it / G::POOL_ACCS) & 1) ^ 1);
         mbar_wait(smem_u32(&bar_full[s]), (it / G::STAGES) & 1);
         tc_fence_after();
@@ -806,8 +818,12 @@ int stem_pool_launch_k(const View& in, const View& out, const void* w, const flo
   const int nout = stem_nout(out.C);
   static int reg_pool = -1;
   if (reg_pool < 0) {
+    // B200_STEM_POOL_REG=1: the register-pooling kernel.  Measured on the same box (ShuffleNetV2 @512 / ResNet-50 @256):
+    // 1.511 / 3.133 ms against 1.489 / 3.096 ms for the row ring -- it executes fewer instructions (91 M vs 118 M) but every
+    // drain warp walks every row, ~190 dependent instructions per row per warp, and a row takes as long as that chain;
+    // in the ring kernel two drain groups and the pooling groups work on different rows at once.  Kept as an opt-in.
     const char* e = getenv("B200_STEM_POOL_REG");
-    reg_pool = (e && e[0] == '0') ? 0 : 1;      // B200_STEM_POOL_REG=0: the shared-memory row ring + pooling warps above
+    reg_pool = (e && e[0] == '1') ? 1 : 0;
   }
   if (reg_pool && out.pix_stride % 8 == 0) B200_STEM_DISPATCH(stem_pool_reg_launch_t, in_map, p, stream);
   B200_STEM_DISPATCH(stem_pool_launch_t, in_map, p, stream);
