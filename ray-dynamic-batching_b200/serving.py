@@ -80,6 +80,41 @@ class Feeder(threading.Thread):
             time.sleep(0.0002)
 
 
+def client_process_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, report):
+    """One load-generator PROCESS: bursts of `burst` uint8 requests at `rate` req/s (or rate = t * slope, the reference
+    driver's pattern, src/test_scheduler.py:77-79) written straight into a model's request ring(s).  Starts on `barrier`."""
+    import os
+    os.environ.setdefault("OMP_NUM_THREADS", "1")      # a client copies bytes; it must not bring a thread pool per process
+    import torch
+    torch.set_num_threads(1)
+    from . import synth
+    if hasattr(queue, "bind"):
+        queue.bind(seed // 100)            # clients start their round-robin on different shards
+    pool = synth.synthetic_images(4 * burst, hw, hw, seed=8000 + seed).contiguous().numpy()
+    p = pool.shape[0]
+    barrier.wait()                     # every client (and the parent's clock) starts together, imports done
+    t0 = time.perf_counter()
+    i = sub = drop = 0
+    while True:
+        el = time.perf_counter() - t0
+        if el >= seconds:
+            break
+        target = slope * el * el / 2 if slope > 0 else rate * el
+        while i + burst <= target and time.perf_counter() - t0 < seconds:
+            j = i % p
+            if j + burst > p:
+                j = 0
+            ok = queue.add_requests(pool[j:j + burst], prefix, i)
+            sub += ok
+            drop += burst - ok
+            i += burst
+            if ok < burst:
+                time.sleep(0.0005)     # full queue: the burst is dropped (counted); do not hammer the ring's counters
+        time.sleep(0.0002)
+    report.put((prefix, sub, drop, time.perf_counter() - t0))
+    queue.close()
+
+
 def serve_loop(worker, queue, model_name, batch_size, until, idle_sleep=0.0001):
     """The saturated form of GPUWorker.execute_schedule for one session with occupancy 1 (no slack to sleep away):
     get_batch -> process_batch_async, one batch in flight while the next is formed.  Returns the batch sizes served."""
@@ -101,11 +136,12 @@ def serve_loop(worker, queue, model_name, batch_size, until, idle_sleep=0.0001):
     return sizes
 
 
-def bench_serving(model, kind, model_name, batch, capacity_img_s, seconds=3.0, load=0.8, slo_ms=None):
-    """One GPU, in process: feeder thread -> SlabRequestQueue -> B200GPUWorker at `load` x capacity.  Returns the p99 batch
-    latency (RequestQueue.get_stats) against the model's SLO, the served rate and the mean batch size."""
-    import torch
-    from . import synth
+def bench_serving(model, kind, model_name, batch, capacity_img_s, seconds=3.0, load=0.8, slo_ms=None, max_clients=6):
+    """One GPU: client PROCESSES -> SlabRequestQueue -> B200GPUWorker (in this process) at `load` x capacity.  Returns the
+    p99 batch latency (RequestQueue.get_stats) against the model's SLO, the served rate and the mean batch size.  A Python
+    client moves ~25 k requests of 224 x 224 per second; the offered load is what the clients managed, and is reported."""
+    import multiprocessing as mp
+    import os
     from .request_queue import models_config
     from .slab_queue import SlabRequestQueue
     from .worker import B200GPUWorker
@@ -119,24 +155,47 @@ def bench_serving(model, kind, model_name, batch, capacity_img_s, seconds=3.0, l
                          in_flight_slots=4 * batch + 64, compat=False, slo_ms=slo)
     worker = B200GPUWorker("B200_0", 0, [(Session(model_name, batch), 1.0)], 1.0, {model_name: model},
                            max_batch=model.max_batch, compat_overshoot=False, pipeline_depth=2)
-    pool = synth.synthetic_images(64, h, w, seed=8000).contiguous().numpy()
     rate = load * capacity_img_s
-    feeder = Feeder(q, pool, rate, seconds, burst=16)
+    per_client = 25000.0 * (224 * 224) / float(h * w)
+    n_clients = int(max(1, min(max_clients, (os.cpu_count() or 4) // 2, -(-rate // per_client))))
+    ctx = mp.get_context("spawn")
+    barrier, report = ctx.Barrier(n_clients + 1), ctx.Queue()
+    procs = [ctx.Process(target=client_process_main, daemon=True,
+                         args=(q, h, rate / n_clients, seconds, 0.0, 16, "c%d_" % c, 100 * c, barrier, report))
+             for c in range(n_clients)]
     try:
         q.pin()
+        if hasattr(model, "prepare_async"):
+            model.prepare_async()
+        for p in procs:
+            p.start()
+        barrier.wait(timeout=300)
         t0 = time.perf_counter()
-        feeder.start()
-        sizes = serve_loop(worker, q, model_name, batch, until=lambda: not feeder.is_alive() and q.empty())
+        alive = lambda: any(p.is_alive() for p in procs)
+        sizes = serve_loop(worker, q, model_name, batch, until=lambda: not alive() and q.empty())
         wall = time.perf_counter() - t0
+        reports = []
+        while len(reports) < n_clients:
+            try:
+                reports.append(report.get(timeout=5))
+            except Exception:  # noqa: BLE001
+                break
         st = q.get_stats()
-        return {"pattern": "constant", "offered_rate": rate, "load_fraction_of_capacity": load, "seconds": seconds,
-                "submitted": feeder.submitted, "dropped_full_queue": feeder.dropped, "served": int(sum(sizes)),
+        sub, drop = sum(r[1] for r in reports), sum(r[2] for r in reports)
+        feed_s = max([r[3] for r in reports] or [seconds])
+        return {"pattern": "constant", "target_rate": rate, "offered_rate": (sub + drop) / feed_s,
+                "load_fraction_of_capacity": load, "seconds": seconds, "client_processes": n_clients,
+                "submitted": sub, "dropped_full_queue": drop, "served": int(sum(sizes)),
                 "batches": len(sizes), "mean_batch": float(np.mean(sizes)) if sizes else 0.0, "batch_target": batch,
                 "throughput_img_s": sum(sizes) / wall, "slo_ms": slo, "slo_violations": st["slo_violations"],
                 "discarded_stale": st["discarded_stale"], "avg_latency_ms": st["avg_latency"],
                 "p95_latency_ms": st["p95_latency"], "p99_latency_ms": st["p99_latency"], "max_latency_ms": st["max_latency"],
-                "path": "Feeder.add_requests (16 per call) -> shared-memory ring -> get_batch -> process_batch_async "
-                        "(2 in flight) -> record_batch_completion; percentiles from get_stats (scheduler.py:343-372)"}
+                "path": "client processes: add_requests (16 per call) -> shared-memory ring -> get_batch -> "
+                        "process_batch_async (2 in flight) -> record_batch_completion; percentiles from get_stats "
+                        "(scheduler.py:343-372)"}
     finally:
-        feeder.stop_flag = True
+        for p in procs:
+            p.join(timeout=10)
+            if p.is_alive():
+                p.terminate()
         q.close()

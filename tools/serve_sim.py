@@ -26,38 +26,11 @@ DEFAULT_BATCH = {"resnet": 256, "shufflenet": 512, "efficientnet": 128, "yolov8"
 PROFILE_CSV = {"resnet": "resnet50", "shufflenet": "shufflenet", "efficientnet": "efficientnetv2", "yolov8": "yolov8n"}
 
 
-def client_main(queue, hw, rate, seconds, slope, burst, prefix, seed, barrier, report):
-    """One load-generator process: bursts of `burst` requests at `rate` req/s into one model's ring."""
-    os.environ.setdefault("OMP_NUM_THREADS", "1")      # a client copies bytes; it must not bring a thread pool per process
-    import torch
-    torch.set_num_threads(1)
+def client_main(*args):
+    """One load-generator process (rdb_b200.serving.client_process_main)."""
     import rdb_b200  # noqa: F401
-    from rdb_b200 import synth
-    if hasattr(queue, "bind"):
-        queue.bind(seed // 100)            # clients start their round-robin on different shards
-    pool = synth.synthetic_images(4 * burst, hw, hw, seed=8000 + seed).contiguous().numpy()
-    p = pool.shape[0]
-    barrier.wait()                     # every client (and the parent's clock) starts together, imports done
-    t0 = time.perf_counter()
-    i = sub = drop = 0
-    while True:
-        el = time.perf_counter() - t0
-        if el >= seconds:
-            break
-        target = slope * el * el / 2 if slope > 0 else rate * el
-        while i + burst <= target and time.perf_counter() - t0 < seconds:
-            j = i % p
-            if j + burst > p:
-                j = 0
-            ok = queue.add_requests(pool[j:j + burst], prefix, i)
-            sub += ok
-            drop += burst - ok
-            i += burst
-            if ok < burst:
-                time.sleep(0.0005)     # full queue: the burst is dropped (counted); do not hammer the ring's counters
-        time.sleep(0.0002)
-    report.put((prefix, sub, drop, time.perf_counter() - t0))
-    queue.close()
+    from rdb_b200.serving import client_process_main
+    return client_process_main(*args)
 
 
 def load_profiles(models, max_bs=512):
