@@ -185,7 +185,11 @@ class B200GPUWorker:
             self.logger.error("Error processing batch: %s", e)
             q = getattr(batch, "queue", None)
             if q is not None:
-                q.release(batch)
+                q.release(batch)                     # the slots of a failed batch go back to the clients
+            if getattr(batch, "slab", None) is not None and batch.slab_offsets:
+                for off in batch.slab_offsets:       # same for the in-process pinned slab
+                    batch.slab.release(off)
+                batch.slab_offsets = None
             raise
         return pend
 
