@@ -71,6 +71,17 @@ B200_API int b200_conv1x1_scaled_nhwc(const void* in, int n, int h, int w, int c
                                       const void* weight, const float* bias, const void* residual, int res_pix_stride,
                                       void* out, int cout, int out_pix_stride, int act, void* stream);
 
+/* The tail of a ShuffleNetV2 unit in one kernel: out = channel_shuffle(cat(other, relu(W . in + bias)), groups = 2)
+ * (tv models/shufflenetv2.py:24-38 channel_shuffle, :96-103 InvertedResidual.forward), written by the epilogue of the 1x1
+ * conv that ends branch2; replaces b200_conv2d_nhwc followed by b200_shuffle_concat_nhwc, and `other`'s values are copied
+ * bit for bit. other: c channels in logical order, padded to cp; out: the halves layout of b200_shuffle_concat_nhwc with
+ * half width cp (logical l at l for l < c, at cp + l - c above; pads zero). cp = 64 or a multiple of 128, c even.
+ * weight: bf16 [cp][cin] in "slots" -- output channel i < c/2 in row i, i >= c/2 in row cp/2 + (i - c/2), other rows zero --
+ * and bias fp32 [cp] likewise: slot s lands on physical channel 2 s + 1, other's value of the same slot on 2 s. */
+B200_API int b200_conv1x1_shuffle_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* other,
+                                       int other_pix_stride, int c, int cp, const void* weight, const float* bias,
+                                       void* out, int out_pix_stride, void* stream);
+
 /* Same contract as b200_conv2d_nhwc for layers with few input channels (cin <= 56, cout <= 256): GEMM-K packs the filter
  * taps (k = tap * cin + c), the im2col tile is gathered into shared memory by cp.async producers. Serves the
  * FusedMBConv 3x3 convolutions of EfficientNetV2 (tv efficientnet.py:172-231) and YOLOv8n's early layers.

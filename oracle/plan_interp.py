@@ -62,6 +62,16 @@ class PlanInterpreter:
                 if p[17] > 0:      # SE gate folded into the conv input: x * gate, rounded to bf16 like the scale op's output
                     x = _bf16(x * B[p[17] - 1].view(n, 1, 1, -1)[..., :cin])
                 x = x.permute(0, 3, 1, 2)
+                if p[18] > 0:      # ShuffleNetV2 unit tail: channel_shuffle(cat(other, relu(conv)), 2) in halves layout;
+                    c, cp = p[18], cout // 2          # weights in cp slots (channel i < c/2 in slot i, else cp/2 + i - c/2)
+                    w = self._bf16w(op["w_off"], cp * cin).view(cp, cin)
+                    y = _bf16(_act(F.conv2d(x, w[:, :, None, None], self._f32(op["b_off"], cp)), act)).permute(0, 2, 3, 1)
+                    other = B[p[6]][..., p[7]:p[7] + cp]
+                    xs = torch.zeros_like(y)
+                    xs[..., :c // 2] = other[..., :c // 2]
+                    xs[..., cp // 2:cp // 2 + c // 2] = other[..., c // 2:c]
+                    B[p[3]][..., p[4]:p[4] + 2 * cp] = torch.stack([xs, y], dim=-1).reshape(*y.shape[:-1], 2 * cp)
+                    continue
                 b = self._f32(op["b_off"], cout)
                 if p[13] > 0:      # K-concatenated 1x1 conv: W[:, :cin] . x + W[:, cin:] . x2[::s2, ::s2]
                     cin2, s2 = p[15], p[16]

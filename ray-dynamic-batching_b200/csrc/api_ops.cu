@@ -73,6 +73,26 @@ int b200_conv1x1_scaled_nhwc(const void* in, int n, int h, int w, int cin, int i
   return conv_launch(l, static_cast<cudaStream_t>(stream));
 }
 
+int b200_conv1x1_shuffle_nhwc(const void* in, int n, int h, int w, int cin, int in_pix_stride, const void* other,
+                              int other_pix_stride, int c, int cp, const void* weight, const float* bias, void* out,
+                              int out_pix_stride, void* stream) {
+  if (n <= 0 || h <= 0 || w <= 0 || !other || c <= 0) return fail(B200_ERR_INVALID, "b200_conv1x1_shuffle_nhwc: empty input");
+  ConvSpec s;
+  s.in = make_view(const_cast<void*>(in), n, h, w, cin, in_pix_stride);
+  s.res = make_view(const_cast<void*>(other), n, h, w, cp, other_pix_stride);
+  s.out = make_view(out, n, h, w, 2 * cp, out_pix_stride);
+  s.interleave_c = c;
+  s.w = weight;
+  s.bias = bias;
+  s.ksize = 1;
+  s.stride = 1;
+  s.pad = 0;
+  s.act = 1;      // b200::ACT_RELU
+  ConvLaunch l;
+  B200_TRY(conv_prepare(s, &l));
+  return conv_launch(l, static_cast<cudaStream_t>(stream));
+}
+
 int b200_gather_conv_npad(int cout) { return gather_conv_npad(cout); }
 int b200_gather_conv_kpad(int cin, int ksize) { return gather_conv_kpad(cin, ksize); }
 

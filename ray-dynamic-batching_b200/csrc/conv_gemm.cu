@@ -227,15 +227,22 @@ struct PConvCfg {
   // DEEP == 2: thin-K layers (one or two k-blocks per tile: 1x1 convs with Cin <= 128 and no residual) are paced by the
   // store path -- measured on a 24 -> 64 1x1 conv: the DMA thread sat in cp.async.bulk.wait_group.read 80 % of the time and
   // the epilogue waited for a staging buffer -- so the shared memory goes into staging buffers instead of ring stages.
-  static constexpr int STAGES = DEEP == 2 ? (BLOCK_N == 64 ? 4 : 3)
+  // RES == 3 (ShuffleNetV2 unit tail, BLOCK_N = 64 only): a staging buffer holds the other branch's tile (X1_BYTES) and,
+  // behind it, the interleaved output tile of twice the width; these layers have one to four k-blocks, three stages do.
+  static constexpr int STAGES = RES == 3 ? 3
+                              : DEEP == 2 ? (BLOCK_N == 64 ? 4 : 3)
                               : DEEP == 1 ? (BLOCK_N == 64 ? 8 : 5)
                                           : (RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4));   // A/B ring
-  static constexpr int OUT_BUFS = DEEP == 2 ? (BLOCK_N == 64 ? 8 : 4)
+  static constexpr int OUT_BUFS = RES == 3 ? 3
+                                : DEEP == 2 ? (BLOCK_N == 64 ? 8 : 4)
                                 : DEEP == 1 ? 2 : (RES ? (BLOCK_N == 64 ? 6 : 4) : 3);         // output / residual staging ring
-  static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
+  static constexpr int LOOKAHEAD = OUT_BUFS - (RES == 3 ? 1 : 2);   // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
-  static constexpr int OUT_BYTES = BLOCK_M * BLOCK_N * 2;
+  // the other branch's tile: 64 channels (128-byte swizzled rows) + the next 8 (16-byte rows): its channels for a tile's
+  // slots start at a channel that is not a multiple of 8 in the second half-group, and TMA coordinates must be
+  static constexpr int X1_BYTES = RES == 3 ? BLOCK_M * (BLOCK_N + 8) * 2 : 0;
+  static constexpr int OUT_BYTES = RES == 3 ? X1_BYTES + BLOCK_M * BLOCK_N * 4 : BLOCK_M * BLOCK_N * 2;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + 1024;
   static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
 };
@@ -292,6 +299,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   __shared__ __align__(8) uint64_t bar_out_ready[NB];    // epilogue finished writing the staging buffer
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[2][BLOCK_N];   // one per epilogue warpgroup
+  __shared__ __align__(16) uint32_t keep_s[2][BLOCK_N / 2];   // RES == 3: 0xFFFF per valid slot of the other branch (pairs of slots)
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -305,6 +313,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
     tma_prefetch_desc(&maps.b);
     tma_prefetch_desc(&maps.d);
     if (RES) tma_prefetch_desc(&maps.r);
+    if (RES == 3) tma_prefetch_desc(&maps.a[3]);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(smem_u32(&bar_full[s]), 1);
       mbar_init(smem_u32(&bar_empty[s]), 1);
@@ -396,7 +405,21 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
         const int tile0_ = blockIdx.x + j * gridDim.x;
         const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
         const uint32_t rdy = smem_u32(&bar_stage_ready[j % NB]);
-        if (RES) {
+        if (RES == 3) {
+          // the other branch's channels for this tile's 64 slots: slot s holds channel s below il_group and channel
+          // il_half + (s - il_group) above it.  TMA wants the channel coordinate on a 16-byte boundary, il_half is not:
+          // the boxes start at the multiple of 8 below the first channel (64 + 8 channels), the epilogue shifts.
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          if (elect_one()) {
+            mbar_expect_tx(rdy, Cfg::X1_BYTES);
+            const uint32_t dst = staging + (j % NB) * Cfg::OUT_BYTES;
+            const int slot = n_tile * BLOCK_N;
+            const int ch8 = (slot < p.il_group ? slot : p.il_half + (slot - p.il_group)) & ~7;
+            tma_load_4d(&maps.r, rdy, dst, ch8, w0, h0, nb0);
+            tma_load_4d(&maps.a[3], rdy, dst + BLOCK_M * BLOCK_N * 2, ch8 + BLOCK_N, w0, h0, nb0);
+          }
+        } else if (RES) {
           int n_tile, w0, h0, nb0;
           tile_coords(p, tile, n_tile, w0, h0, nb0);
           if (elect_one()) {
@@ -427,18 +450,27 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const int ob = it % NB;
           mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
           if (elect_one()) {
+            if (RES == 3) {      // slots [n0, n0 + 64) -> physical channels [2 n0, 2 n0 + 128) of the unit's output
 #pragma unroll
-            for (int q = 0; q < BLOCK_N / 64; ++q)
-              if (n0 + q * 64 < p.cout)
-                tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+              for (int q = 0; q < BLOCK_N / 32; ++q)
+                if (n0 + q * 32 < p.cout)
+                  tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + Cfg::X1_BYTES + q * (BLOCK_M * 128), 2 * n0 + q * 64,
+                               w0, h0, nb0);
+            } else {
+#pragma unroll
+              for (int q = 0; q < BLOCK_N / 64; ++q)
+                if (n0 + q * 64 < p.cout)
+                  tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
+            }
             tma_store_commit();
           }
         }
-        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2);
-        // stores issued so far are tiles <= it, so allowing the 2 most recent groups to be pending is enough.
+        // staging for tile it + LA: its buffer was last read by the store of tile it + LA - NB (= it - 2, or it - 1 with
+        // the three big buffers of RES == 3); stores issued so far are tiles <= it, so allowing the NB - LA most recent
+        // groups to be pending is enough.
         const int j = it + LA;
         if (LA > 0 && j < my_tiles) {
-          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+          if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - LA) : "memory");
           acquire_staging(j);
         }
       }
@@ -525,10 +557,21 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       const int bb = wg;
       const int ob = it % NB;
       const int n0 = (tile - static_cast<int>(fast_div(tile, p.n_tiles, p.mul_n_tiles)) * p.n_tiles) * BLOCK_N;
+      const int x1_ch8 = RES == 3 ? ((n0 < p.il_group ? n0 : p.il_half + (n0 - p.il_group)) & ~7) : 0;   // as in the DMA warp
       named_bar_sync(1 + wg, 128);               // every thread of the group is done reading the previous tile's bias
       for (int i = epi_tid; i < BLOCK_N; i += 128) {
         const int c = n0 + i;
         bias_s[bb][i] = (c < p.cout) ? p.bias[c] : 0.f;
+      }
+      if (RES == 3 && epi_tid < BLOCK_N / 2) {      // slots past the valid channels of a half-group hold the NEXT channels
+        uint32_t m = 0;                             // of the other branch (the boxes are contiguous): masked to zero
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int slot = n0 + 2 * epi_tid + e;
+          const int in_group = slot < p.il_group ? slot : slot - p.il_group;
+          if (in_group < p.il_half) m |= 0xFFFFu << (16 * e);
+        }
+        keep_s[bb][epi_tid] = m;
       }
       named_bar_sync(1 + wg, 128);
       mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
@@ -553,6 +596,49 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           f[2] = __uint_as_float(v[g * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[g * 8 + 3]) + b0.w;
           f[4] = __uint_as_float(v[g * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[g * 8 + 5]) + b1.y;
           f[6] = __uint_as_float(v[g * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[g * 8 + 7]) + b1.w;
+          if (RES == 3) {
+            // cat + channel_shuffle(groups = 2): slots 8 k8 .. 8 k8 + 7 of this row and the other branch's values of the
+            // same slots become 16 consecutive output channels (other branch on the even ones, bits copied as they are).
+            // The other branch's tile starts at channel x1_ch8 (a multiple of 8): 64 channels in 128-byte swizzled rows.
+            const int k8 = cc * 4 + g;
+            const int slot0 = n0 + k8 * 8;
+            const int off = (slot0 < p.il_group ? slot0 : p.il_half + (slot0 - p.il_group)) - x1_ch8;   // first channel, from the box start
+            const int q = off >> 3, dl = off & 7;
+            uint32_t r0, r1, r2, r3;
+            if (dl == 0) {
+              asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                           : "r"(stage_d + row_off + ((q ^ sw) << 4)));
+            } else {
+              // 16 bytes that start 2 dl bytes into chunk q: five words from chunks q and q + 1 (chunk 8 = the 8-channel
+              // box behind the 64-channel one), then a 16-bit funnel shift when dl is odd
+              uint32_t wv[5];
+#pragma unroll
+              for (int t = 0; t < 5; ++t) {
+                const int wi = (dl >> 1) + t;
+                const int ch = q + (wi >> 2);
+                const uint32_t a = ch < 8 ? stage_d + row_off + ((ch ^ sw) << 4) + ((wi & 3) << 2)
+                                          : stage_d + BLOCK_M * BLOCK_N * 2 + row * 16 + ((wi & 3) << 2);
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(wv[t]) : "r"(a));
+              }
+              const uint32_t sh = (dl & 1) * 16;
+              r0 = __funnelshift_r(wv[0], wv[1], sh); r1 = __funnelshift_r(wv[1], wv[2], sh);
+              r2 = __funnelshift_r(wv[2], wv[3], sh); r3 = __funnelshift_r(wv[3], wv[4], sh);
+            }
+            const uint4 kp = *reinterpret_cast<const uint4*>(&keep_s[bb][k8 * 4]);
+            r0 &= kp.x; r1 &= kp.y; r2 &= kp.z; r3 &= kp.w;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
+            const uint32_t q0 = pack_bf16x2(f[0], f[1]), q1 = pack_bf16x2(f[2], f[3]);
+            const uint32_t q2 = pack_bf16x2(f[4], f[5]), q3 = pack_bf16x2(f[6], f[7]);
+            const uint32_t osub = stage_d + Cfg::X1_BYTES + cc * (BLOCK_M * 128) + row_off;
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(osub + (((2 * g) ^ sw) << 4)),
+                         "r"(__byte_perm(r0, q0, 0x5410)), "r"(__byte_perm(r0, q0, 0x7632)),
+                         "r"(__byte_perm(r1, q1, 0x5410)), "r"(__byte_perm(r1, q1, 0x7632)) : "memory");
+            asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(osub + (((2 * g + 1) ^ sw) << 4)),
+                         "r"(__byte_perm(r2, q2, 0x5410)), "r"(__byte_perm(r2, q2, 0x7632)),
+                         "r"(__byte_perm(r3, q3, 0x5410)), "r"(__byte_perm(r3, q3, 0x7632)) : "memory");
+            continue;
+          }
           if (RES) {
             uint32_t r0, r1, r2, r3;
             asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
@@ -1240,6 +1326,14 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   if (Ho != out.H || Wo != out.W || in.N != out.N) return fail(B200_ERR_INVALID, "conv: output geometry mismatch");
   const bool has_res = s.res.base != nullptr;
   const bool dual = s.in2.base != nullptr;
+  const bool il = s.interleave_c > 0;      // output = channel_shuffle(cat(res, conv), 2): see ConvSpec::interleave_c
+  const int cout = il ? out.C / 2 : out.C;   // GEMM-N (weight rows): the conv's own channels ("slots" when interleaving)
+  if (il) {
+    if (s.ksize != 1 || s.stride != 1 || s.pad != 0 || dual || s.a_scale || !has_res || s.res_after_act)
+      return fail(B200_ERR_INVALID, "conv: interleaving needs a plain 1x1 / stride 1 conv and the other branch as `res`");
+    if (out.C % 128 || (cout != 64 && cout % 128) || (s.interleave_c & 1) || s.interleave_c > cout || s.act != ACT_RELU)
+      return fail(B200_ERR_INVALID, "conv: interleaving needs 64 or a multiple of 128 slots per branch, an even channel count and ReLU");
+  }
   if (s.a_scale && (s.ksize != 1 || s.stride != 1 || s.pad != 0 || dual))
     return fail(B200_ERR_INVALID, "conv: input scaling needs a plain 1x1 / stride 1 conv");
   if (dual) {
@@ -1252,7 +1346,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
       return fail(B200_ERR_INVALID, "conv: second input geometry mismatch");
     if (has_res) return fail(B200_ERR_INVALID, "conv: a K-concatenated conv takes no residual (the second input replaces it)");
   }
-  if (has_res && (s.res.H != out.H || s.res.W != out.W || s.res.C != out.C || s.res.N != out.N))
+  if (has_res && (s.res.H != out.H || s.res.W != out.W || s.res.C != cout || s.res.N != out.N))
     return fail(B200_ERR_INVALID, "conv: residual geometry mismatch");
 
   ConvParams& p = L->p;
@@ -1267,9 +1361,12 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     p.kb_split = in.C / BLOCK_K;
     p.num_kb = p.kb_split + (s.in2.C + BLOCK_K - 1) / BLOCK_K;
   }
-  p.cout = out.C;
+  p.cout = cout;
   p.act = s.act;
-  p.has_res = has_res ? (s.res_after_act ? 2 : 1) : 0;
+  p.has_res = il ? 3 : (has_res ? (s.res_after_act ? 2 : 1) : 0);
+  p.il_group = cout / 2;
+  p.il_half = s.interleave_c / 2;
+
   p.bias = s.bias;
   p.reverse = s.reverse_tiles ? 1 : 0;
   p.a_scale = s.a_scale;
@@ -1294,10 +1391,11 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     const char* e = getenv("B200_PAIR128_MIN_K");
     pair128_min_k = e ? atoi(e) : 0;
   }
-  bool two_cta = use_2cta() && ((out.C >= 256 && k_total >= 256) ||
-                                (out.C >= 128 && pair128_min_k > 0 && k_total >= pair128_min_k));
-  int block_n = two_cta ? (out.C >= 256 ? 256 : 128) : (out.C <= 64 ? 64 : 128);
-  if (s.a_scale) two_cta = false, block_n = out.C <= 64 ? 64 : 128;      // the scaler role lives in the single-CTA kernel
+  bool two_cta = use_2cta() && ((cout >= 256 && k_total >= 256) ||
+                                (cout >= 128 && pair128_min_k > 0 && k_total >= pair128_min_k));
+  int block_n = two_cta ? (cout >= 256 ? 256 : 128) : (cout <= 64 ? 64 : 128);
+  if (s.a_scale) two_cta = false, block_n = cout <= 64 ? 64 : 128;      // the scaler role lives in the single-CTA kernel
+  if (il) two_cta = false, block_n = 64;      // the interleaving epilogue lives in the single-CTA kernel, 64 slots per tile
   if (two_cta && has_res) {
     // residual layers: CTA pairs pay off only with enough K per tile to hide the residual prefetch (layer4 conv3: K = 512)
     if (res_mode == 0 || (res_mode == 2 && k_total < res_min_k)) { two_cta = false; block_n = 128; }
@@ -1319,11 +1417,11 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   // stride 2 (Cin <= 32 only: a stage holds four parity planes): YOLOv8n layers 1 and 3, EfficientNetV2 features.2.0
   const bool halo_s2 = use_halo_s2 && s.stride == 2 && in.C <= 32 && in.W >= 2 && in.H >= 2;
   const bool halo = use_halo && !dual && s.ksize == 3 && (s.stride == 1 || halo_s2) && s.pad == 1 && in.C <= 64 &&
-                    s.act != ACT_SIGMOID && (out.C <= 64 || (in.C < 64 && out.C <= 256)) &&
+                    s.act != ACT_SIGMOID && (cout <= 64 || (in.C < 64 && cout <= 256)) &&
                     halo_cover * 100 <= (long long)out.W * out.H * 135;
   if (halo) {
     two_cta = false;
-    block_n = out.C <= 32 ? 32 : 64;
+    block_n = cout <= 32 ? 32 : 64;
     p.pb = in.C <= 16 ? 32 : (in.C <= 32 ? 64 : 128);
     p.block_n = block_n;
     p.halo_s2 = s.stride == 2 ? 1 : 0;
@@ -1338,7 +1436,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   L->halo = halo;
   L->block_n = block_n;
   L->two_cta = two_cta;
-  p.n_tiles = (out.C + block_n - 1) / block_n;
+  p.n_tiles = (cout + block_n - 1) / block_n;
 
   const uint64_t ips = uint64_t(in.pix_stride) * 2, ops = uint64_t(out.pix_stride) * 2;
   const bool flat = (s.ksize == 1 && s.stride == 1 && s.pad == 0) && !(dual && s.stride2 != 1);
@@ -1420,16 +1518,23 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   {
     const uint64_t rowb = ops * oW, imgb = rowb * oH;
     B200_TRY(encode_act_view(&L->maps.d, out.base, out.C, oW, oH, oN, ops, rowb, imgb, p.tw, p.th, p.tn));
-    if (has_res) {
+    if (il) {      // the other branch: a 64-channel box and the 8 channels behind it (see the kernel's DMA warp)
       const uint64_t rps = uint64_t(s.res.pix_stride) * 2;
-      B200_TRY(encode_act_view(&L->maps.r, s.res.base, out.C, oW, oH, oN, rps, rps * oW, rps * oW * oH, p.tw, p.th,
+      const uint64_t dims[4] = {uint64_t(cout), uint64_t(oW), 1u, 1u};
+      const uint64_t str[3] = {rps, rps * oW, rps * oW};
+      const uint32_t box[4] = {64u, 128u, 1u, 1u}, box8[4] = {8u, 128u, 1u, 1u};
+      B200_TRY(encode_tmap(&L->maps.r, s.res.base, 4, dims, str, box, SWZ_128B));
+      B200_TRY(encode_tmap(&L->maps.a[3], s.res.base, 4, dims, str, box8, SWZ_NONE));
+    } else if (has_res) {
+      const uint64_t rps = uint64_t(s.res.pix_stride) * 2;
+      B200_TRY(encode_act_view(&L->maps.r, s.res.base, cout, oW, oH, oN, rps, rps * oW, rps * oW * oH, p.tw, p.th,
                                p.tn));
     }
   }
   // weights: [Cin, taps, Cout]
   {
     const uint64_t kc = uint64_t(in.C) + (dual ? uint64_t(s.in2.C) : 0);   // K-concatenated: one weight row [Ca + Cb]
-    const uint64_t dims[3] = {kc, uint64_t(taps), uint64_t(out.C)};
+    const uint64_t dims[3] = {kc, uint64_t(taps), uint64_t(cout)};
     const uint64_t str[2] = {kc * 2, kc * 2 * taps};
     const uint32_t box[3] = {halo ? uint32_t(p.pb / 2) : 64u, 1u, uint32_t(two_cta ? block_n / 2 : block_n)};  // a CTA pair loads half each
     B200_TRY(encode_tmap(&L->maps.b, s.w, 3, dims, str, box,
@@ -1438,7 +1543,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   const long long m_tiles = (long long)p.tiles_w * p.tiles_h * p.tiles_n;
   if (m_tiles * p.n_tiles > 0x7fffffffLL) return fail(B200_ERR_INVALID, "conv: grid too large");
   L->grid = unsigned(m_tiles * p.n_tiles);
-  L->flops = 2.0 * double(out.N) * out.H * out.W * out.C * double(k_total);
+  L->flops = 2.0 * double(out.N) * out.H * out.W * (il ? s.interleave_c : cout) * double(k_total);
   return B200_OK;
 }
 
@@ -1517,6 +1622,10 @@ static int launch_persistent_act(const ConvLaunch& l, cudaStream_t stream) {
 
 template <int BLOCK_N>
 static int launch_persistent_res(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.p.has_res == 3) {      // ShuffleNetV2 unit tail: conv_prepare only lets 64-slot tiles with ReLU through
+    if constexpr (BLOCK_N == 64) return launch_persistent_t<64, 3, ACT_RELU>(l, stream);
+    return fail(B200_ERR_INVALID, "conv: interleaving runs on 64-slot tiles");
+  }
   if (l.p.has_res == 0) return launch_persistent_act<BLOCK_N, 0>(l, stream);
   if (l.p.has_res == 1) return launch_persistent_act<BLOCK_N, 1>(l, stream);
   return launch_persistent_act<BLOCK_N, 2>(l, stream);
@@ -1623,6 +1732,7 @@ static int launch_t(const ConvLaunch& l, cudaStream_t stream) {
 }
 
 int conv_launch(const ConvLaunch& l, cudaStream_t stream) {
+  if (l.p.has_res == 3) return launch_persistent_res<64>(l, stream);      // the interleaving epilogue exists in this kernel only
   if (l.halo) {
     if (l.p.pb == 128) return launch_halo_res<128>(l, stream);
     if (l.p.pb == 64) return launch_halo_res<64>(l, stream);

@@ -17,10 +17,17 @@ struct ConvSpec {
   int act = 0;               // b200::Act
   bool res_after_act = false;
   bool reverse_tiles = false;  // false: act(acc + bias + res) (ResNet); true: act(acc + bias) + res (FusedMBConv e=1)
+  // ShuffleNetV2 unit tail (tv models/shufflenetv2.py:24-38,96-103: cat + channel_shuffle(groups=2)) folded into the 1x1
+  // conv that ends branch2: interleave_c = c > 0 logical channels per branch.  `res` is then the OTHER branch (x1, c
+  // channels in logical order, res.C = cp physical) and `out` the unit's whole output in halves layout [cp | cp]
+  // (out.C = 2 cp): logical channel l = 2 i + e (e = 0: x1[i], e = 1: this conv's channel i) lives at l for l < c and at
+  // cp + (l - c) above.  The weights hold cp "slots": channel i < c/2 in slot i, channel i >= c/2 in slot cp/2 + i - c/2,
+  // the others zero, so that slot s goes to physical channel 2 s + 1 and the x1 value beside it to 2 s.
+  int interleave_c = 0;
 };
 
 struct alignas(64) ConvMaps {
-  CUtensorMap a[4];  // input views (index = parity (py*2+px) for stride 2, else 0)
+  CUtensorMap a[4];  // input views (index = parity (py*2+px) for stride 2, else 0; a[3] of an interleaving conv: see r)
   CUtensorMap b;     // weights [Cin, taps, Cout]
   CUtensorMap d;     // output
   CUtensorMap r;     // residual (aliases d's geometry)
@@ -34,7 +41,8 @@ struct ConvParams {
   int num_taps, kb_per_tap;
   int num_kb;                     // k-blocks per tile (num_taps * kb_per_tap, or both inputs' blocks of a K-concatenated conv)
   int kb_split;                   // K-concatenated conv: k-blocks [0, kb_split) come from input 0, the rest from input 1; 0 = off
-  int cout, act, has_res;  // has_res: 0 none, 1 add before the activation, 2 add after it
+  int cout, act, has_res;  // has_res: 0 none, 1 add before the activation, 2 add after it, 3 interleave with `res` (cout = slots)
+  int il_group, il_half;   // interleave: slots per half (cp / 2), valid channels per half-group (c / 2)
   int pb;                  // halo kernel: bytes per pixel of the staged halo (32 / 64 / 128 = swizzle span), K per tap = pb / 2
   int block_n;             // halo kernel: accumulator width (32 or 64)
   int halo_stages;         // halo kernel: halo boxes in flight (2 or 4)

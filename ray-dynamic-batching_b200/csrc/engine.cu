@@ -83,6 +83,8 @@ int Engine::parse(const char* kind_in, const void* blob, size_t nbytes, int max_
           int64_t(bufs[o.p[17] - 1].h) * bufs[o.p[17] - 1].w * bufs[o.p[17] - 1].c < o.p[2])
         return fail(B200_ERR_BLOB, "engine: conv input-scale buffer does not match its input channels");
     }
+    if (o.type == OP_CONV && o.p[18] != 0 && (o.p[18] < 0 || o.p[6] < 0 || o.p[18] > o.p[5] / 2))
+      return fail(B200_ERR_BLOB, "engine: interleaving conv needs the other branch and at most half the output channels");
     if (o.type == OP_CONV && (o.p[13] < 0 || o.p[13] > int(hdr.n_bufs)))
       return fail(B200_ERR_BLOB, "engine: conv references an unknown second input");
     const int64_t offs[4] = {o.w_off, o.b_off, o.w2_off, o.b2_off};
@@ -246,7 +248,8 @@ int Engine::plan_for(int batch, BatchPlan** out) {
       ConvSpec s;
       s.in = view(p[0], p[1], p[2], batch);
       s.out = view(p[3], p[4], p[5], batch);
-      if (p[6] >= 0) s.res = view(p[6], p[7], p[5], batch);
+      s.interleave_c = p[18];      // ShuffleNetV2 unit tail: p[5] = 2 cp output channels, residual slot = the other branch (cp)
+      if (p[6] >= 0) s.res = view(p[6], p[7], p[18] > 0 ? p[5] / 2 : p[5], batch);
       s.w = weights_dev + po.rec.w_off;
       s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
       s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];

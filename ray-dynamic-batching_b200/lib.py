@@ -24,6 +24,8 @@ SIGNATURES = {
                                  c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "b200_conv1x1_dual_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int, c_int,
                                        c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b200_conv1x1_shuffle_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int, c_int,
+                                          c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "b200_conv1x1_scaled_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_int, c_void_p, c_int, c_int, c_int, c_void_p]),
     "b200_gather_conv_npad": (c_int, [c_int]),

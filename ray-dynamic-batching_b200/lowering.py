@@ -158,6 +158,8 @@ class PlanBuilder:
         self.tensor_core_stem = True
         self.toeplitz_stem = True
         self.fuse_stem_pool = os.environ.get('B200_FUSE_STEM_POOL', '1') != '0'   # conv1 + bn1 + relu + maxpool in one kernel
+        # ShuffleNetV2 cat + channel_shuffle written by the epilogue of the conv that ends branch2 (no shuffle pass)
+        self.fuse_shuffle = os.environ.get('B200_FUSE_SHUFFLE', '1') != '0'
         self.gather_small_cin = os.environ.get('B200_GATHER_SMALL_CIN', '1') != '0'   # 3x3 convs with Cin <= 56 the halo kernel does not take: packed-K gather kernel
         self.fuse_downsample = os.environ.get('B200_FUSE_DOWNSAMPLE', '1') != '0'   # ResNet conv3 + downsample as one GEMM
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
@@ -462,6 +464,32 @@ class PlanBuilder:
         self._op(OP_SHUFFLE, [a.buf, a.coff, a.cphys, ob, 0, 2 * cp, -1, 0, 0, 0, 0, 0, b.buf, b.coff, c, cp], name=name)
         return T(ob, 0, 2 * c, a.h, a.w, 2 * cp, cmap)
 
+    def conv_shuffle(self, x: T, weight, bias, other: T, name=""):
+        """relu(conv1x1(x)) interleaved with `other` by the conv's own epilogue: the result is shuffle(other, conv) in the
+        halves layout of `shuffle` (csrc/conv_gemm.cu, ConvSpec::interleave_c). The weights are laid out in cp "slots":
+        output channel i < c/2 in slot i, i >= c/2 in slot cp/2 + (i - c/2); slot s lands on physical channel 2 s + 1 of
+        the output and other's channel of the same slot on 2 s. Returns None when the shapes do not allow it."""
+        c, cin = weight.shape[:2]
+        cp = line_channels(c)
+        if not (weight.shape[2:] == (1, 1) and other.c == c and other.cphys == cp and c % 2 == 0 and x.cphys % 8 == 0
+                and (cp == 64 or cp % 128 == 0) and (x.h, x.w) == (other.h, other.w)
+                and np.array_equal(other.cmap, np.arange(c))):
+            return None
+        assert cin == x.c
+        slot = np.concatenate([np.arange(c // 2), cp // 2 + np.arange(c - c // 2)])
+        wp = torch.zeros(cp, x.cphys)
+        wfull = torch.zeros(c, x.cphys)
+        wfull[:, torch.as_tensor(x.cmap)] = weight.reshape(c, cin)
+        wp[torch.as_tensor(slot)] = wfull
+        bp = torch.zeros(cp)
+        bp[torch.as_tensor(slot)] = bias
+        w_off = self.add_weights(self.bf16_bits(wp))
+        b_off = self.add_weights(bp.numpy().astype(np.float32))
+        ob = self.new_buf(x.h, x.w, 2 * cp)
+        pr = [x.buf, x.coff, x.cphys, ob, 0, 2 * cp, other.buf, other.coff, 1, 1, 0, ACT_RELU, 0, 0, 0, 0, 0, 0, c]
+        self._op(OP_CONV, pr, w_off, b_off, name=name)
+        return T(ob, 0, 2 * c, x.h, x.w, 2 * cp, np.concatenate([np.arange(c), cp + np.arange(c)]))
+
     @staticmethod
     def chunk2(x: T):
         """x.chunk(2, dim=1) of a halves-layout tensor: two aligned slices, no copy."""
@@ -603,6 +631,10 @@ def lower_shufflenet(model, in_hw=(224, 224)) -> PlanBuilder:
             w, b = fold_bn(b2[3], b2[4])
             t = pb.dwconv(t, w, b, unit.stride, ACT_NONE, name=nm + "branch2.dw")
             w, b = fold_bn(b2[5], b2[6])
+            fused = pb.conv_shuffle(t, w, b, a, name=nm + "branch2.pw2+shuffle") if pb.fuse_shuffle else None
+            if fused is not None:
+                x = fused
+                continue
             t = pb.conv(t, w, b, 1, 0, ACT_RELU, name=nm + "branch2.pw2")
             x = pb.shuffle(a, t, name=nm + "shuffle")
     w, b = fold_bn(model.conv5[0], model.conv5[1])

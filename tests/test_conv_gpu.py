@@ -234,3 +234,61 @@ def test_gather_conv_matches_fp32_reference(b200lib, cuda, case):
     err = (out.float() - ref).abs()
     tol = ref.abs() * 2.0 ** -8 + 2e-3
     assert (err <= tol).all(), "max err %.4g" % err.max().item()
+
+
+SHUFFLE_CASES = [
+    # n, h, w, cin (physical), c, cp
+    (3, 28, 28, 64, 58, 64),        # stage 2: both half-groups in one 64-slot tile (two 32-channel boxes of the other branch)
+    (5, 14, 14, 128, 116, 128),     # stage 3: one tile per half-group, ragged M (980 pixels)
+    (2, 7, 7, 256, 232, 256),       # stage 4: two tiles per half-group, a single partial M tile
+    (64, 28, 28, 64, 58, 64),       # 392 tiles on 148 CTAs: the staging ring wraps
+    (128, 14, 14, 128, 116, 128),   # the same with two channel tiles
+    (1, 5, 5, 8, 40, 64),           # thin K, 20 valid slots per half-group
+]
+
+
+@pytest.mark.parametrize("case", SHUFFLE_CASES, ids=[str(c) for c in SHUFFLE_CASES])
+def test_conv1x1_shuffle_tail(b200lib, cuda, case):
+    """channel_shuffle(cat(other, relu(conv1x1(x))), 2) from the conv's own epilogue (tv shufflenetv2.py:24-38,96-103):
+    the other branch's channels are copied bit for bit, the conv's meet the fp32 reference, pads are zero, and the whole
+    tensor equals b200_conv2d_nhwc followed by b200_shuffle_concat_nhwc."""
+    from torchvision.models.shufflenetv2 import channel_shuffle
+    n, h, w, cin, c, cp = case
+    g = torch.Generator(device="cpu").manual_seed(_case_seed(case))
+    x = torch.randn(n, h, w, cin, generator=g).to(cuda).to(torch.bfloat16)
+    # the other branch is the first half of the unit's input [x1 | x2] (pixel stride 2 cp); its pad channels hold junk
+    parent = torch.randn(n, h, w, 2 * cp, generator=g).to(cuda).to(torch.bfloat16)
+    wt = (torch.randn(c, cin, generator=g) / cin ** 0.5).to(torch.bfloat16)
+    bias = torch.randn(c, generator=g)
+    slot = torch.cat([torch.arange(c // 2), cp // 2 + torch.arange(c // 2)])
+    wslots = torch.zeros(cp, cin, dtype=torch.bfloat16)
+    wslots[slot] = wt
+    bslots = torch.zeros(cp)
+    bslots[slot] = bias
+    wslots, bslots = wslots.to(cuda), bslots.to(cuda)
+    out = torch.full((n, h, w, 2 * cp), float("nan"), device=cuda, dtype=torch.bfloat16)
+    check(b200lib.b200_conv1x1_shuffle_nhwc(ptr(x), n, h, w, cin, 0, ptr(parent), 2 * cp, c, cp, ptr(wslots), ptr(bslots),
+                                            ptr(out), 0, stream_ptr()), "b200_conv1x1_shuffle_nhwc")
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "unwritten output elements"
+    other = parent[..., :c]
+    y = F.relu(F.conv2d(x.float().permute(0, 3, 1, 2), wt.to(cuda).float()[:, :, None, None], bias.to(cuda)))
+    ref = channel_shuffle(torch.cat([other.float().permute(0, 3, 1, 2), y], dim=1), 2).permute(0, 2, 3, 1)
+    got = torch.cat([out[..., :c], out[..., cp:cp + c]], dim=-1).float()
+    assert torch.equal(got[..., 0::2], ref[..., 0::2]), "other branch not copied exactly"
+    err = (got[..., 1::2] - ref[..., 1::2]).abs()
+    tol = ref[..., 1::2].abs() * 2.0 ** -8 + 2e-3
+    assert (err > tol).sum().item() == 0, "max err %.4g" % err.max().item()
+    assert not out[..., c:cp].float().abs().any() and not out[..., cp + c:].float().abs().any(), "pads not zero"
+    # the two-kernel path it replaces
+    wplain = torch.zeros(cp, 1, 1, cin, dtype=torch.bfloat16, device=cuda)
+    wplain[:c, 0, 0] = wt.to(cuda)
+    bplain = torch.zeros(cp, device=cuda)
+    bplain[:c] = bias.to(cuda)
+    t = run_conv(b200lib, x, wplain, bplain, None, 1, 0, "relu")
+    two_cp = (c + 7) // 8 * 8      # b200_shuffle_concat_nhwc pads its halves to 8 channels
+    two = torch.full((n, h, w, 2 * two_cp), float("nan"), device=cuda, dtype=torch.bfloat16)
+    a = parent[..., :cp].contiguous()
+    check(b200lib.b200_shuffle_concat_nhwc(ptr(a), cp, ptr(t), cp, n, h, w, c, ptr(two), 0, stream_ptr()))
+    torch.cuda.synchronize()
+    assert torch.equal(out[..., :c], two[..., :c]) and torch.equal(out[..., cp:cp + c], two[..., two_cp:two_cp + c])

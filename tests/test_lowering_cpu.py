@@ -31,9 +31,10 @@ def test_physical_channel_rules():
         assert p >= c and p % 8 == 0 and p * 100 <= lowering.pad8(c) * 112
 
 
-def test_shufflenet_halves_are_line_aligned():
+def test_shufflenet_halves_are_line_aligned(monkeypatch):
     """Every shuffle writes two halves of `line_channels(c)` channels; the chunk(2) views of the next unit start on a
     128-byte line, and every logical channel maps inside its half."""
+    monkeypatch.setenv("B200_FUSE_SHUFFLE", "0")
     pb = lowering.lower("shufflenet_v2_x1_0", synth.make_model("shufflenet_v2_x1_0", n_proto=8))
     _, _, ops, _ = lowering.parse_blob(pb.to_blob())
     shuffles = [op for op in ops if op["type"] == lowering.OP_SHUFFLE]
@@ -43,6 +44,42 @@ def test_shufflenet_halves_are_line_aligned():
         c, cp, out_c = p[14], p[15], p[5]
         assert cp == lowering.line_channels(c) and out_c == 2 * cp
         assert (cp * 2) % 128 == 0          # second half starts on a 128-byte line
+
+
+def test_shufflenet_shuffle_folded_into_the_last_conv_of_branch2():
+    """Default lowering: no shuffle pass is left; each unit ends in a 1x1 conv that writes cat + channel_shuffle itself
+    (tv models/shufflenetv2.py:24-38,96-103). Its weight rows sit in `cp` slots: channel i < c/2 in slot i, the others from
+    slot cp/2 on, the remaining rows zero; the plan interpreter gives the same logits as the plan with shuffle passes."""
+    import os
+    import numpy as np
+    import torch
+    from oracle import plan_interp
+    m = synth.make_model("shufflenet_v2_x1_0", n_proto=8)
+    pb = lowering.lower("shufflenet_v2_x1_0", m)
+    blob = pb.to_blob()
+    _, bufs, ops, weights = lowering.parse_blob(blob)
+    assert not [op for op in ops if op["type"] == lowering.OP_SHUFFLE]
+    tails = [op for op in ops if op["type"] == lowering.OP_CONV and op["p"][18] > 0]
+    assert len(tails) == 16
+    wb = np.frombuffer(weights, dtype=np.uint8)
+    for op in tails:
+        p = op["p"]
+        c, cp, cin = p[18], p[5] // 2, p[2]
+        assert cp == lowering.line_channels(c) and bufs[p[3]][2] == 2 * cp and p[6] >= 0 and p[11] == lowering.ACT_RELU
+        rows = wb[op["w_off"]:op["w_off"] + cp * cin * 2].view(np.uint16).reshape(cp, cin)
+        used = np.zeros(cp, bool)
+        used[:c // 2] = True
+        used[cp // 2:cp // 2 + c // 2] = True
+        assert not rows[~used].any() and rows[used].any(axis=1).all()
+    x = synth.normalize_u8(synth.heldout_images(2, 224, 224), synth.IMAGENET_MEAN, synth.IMAGENET_STD)
+    fused, _ = plan_interp.PlanInterpreter(blob, lowering.parse_blob).run(plan_interp.to_nhwc4(x))
+    os.environ["B200_FUSE_SHUFFLE"] = "0"
+    try:
+        plain = lowering.lower("shufflenet_v2_x1_0", m).to_blob()
+    finally:
+        del os.environ["B200_FUSE_SHUFFLE"]
+    ref, _ = plan_interp.PlanInterpreter(plain, lowering.parse_blob).run(plan_interp.to_nhwc4(x))
+    assert torch.equal(torch.as_tensor(fused), torch.as_tensor(ref))
 
 
 def _fast_div(n, d):
