@@ -227,23 +227,27 @@ struct PConvCfg {
   // DEEP == 2: thin-K layers (one or two k-blocks per tile: 1x1 convs with Cin <= 128 and no residual) are paced by the
   // store path -- measured on a 24 -> 64 1x1 conv: the DMA thread sat in cp.async.bulk.wait_group.read 80 % of the time and
   // the epilogue waited for a staging buffer -- so the shared memory goes into staging buffers instead of ring stages.
-  // RES == 3 (ShuffleNetV2 unit tail, BLOCK_N = 64 only): a staging buffer holds the other branch's tile (X1_BYTES) and,
-  // behind it, the interleaved output tile of twice the width; these layers have one to four k-blocks, three stages do.
+  // RES == 3 (ShuffleNetV2 unit tail, BLOCK_N = 64 only): OUT_BUFS counts the ring of the other branch's tiles (X1_BYTES
+  // each, loaded OUT_BUFS tiles ahead); the interleaved output tiles of twice the width have two buffers of their own,
+  // one per epilogue warpgroup.  These layers have one to four k-blocks, three stages do.
   static constexpr int STAGES = RES == 3 ? 3
+                              : DEEP == 3 ? (BLOCK_N == 64 ? 6 : 4)
                               : DEEP == 2 ? (BLOCK_N == 64 ? 4 : 3)
                               : DEEP == 1 ? (BLOCK_N == 64 ? 8 : 5)
                                           : (RES ? (BLOCK_N == 64 ? 4 : 3) : (BLOCK_N == 64 ? 7 : 4));   // A/B ring
-  static constexpr int OUT_BUFS = RES == 3 ? 3
+  static constexpr int OUT_BUFS = RES == 3 ? 4
+                                : DEEP == 3 ? (BLOCK_N == 64 ? 5 : 3)
                                 : DEEP == 2 ? (BLOCK_N == 64 ? 8 : 4)
                                 : DEEP == 1 ? 2 : (RES ? (BLOCK_N == 64 ? 6 : 4) : 3);         // output / residual staging ring
-  static constexpr int LOOKAHEAD = OUT_BUFS - (RES == 3 ? 1 : 2);   // tiles the residual prefetch runs ahead of the epilogue
+  static constexpr int LOOKAHEAD = OUT_BUFS - 2;            // tiles the residual prefetch runs ahead of the epilogue
   static constexpr int B_STAGE_BYTES = BLOCK_N * BLOCK_K * 2;
   static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
   // the other branch's tile: 64 channels (128-byte swizzled rows) + the next 8 (16-byte rows): its channels for a tile's
   // slots start at a channel that is not a multiple of 8 in the second half-group, and TMA coordinates must be
   static constexpr int X1_BYTES = RES == 3 ? BLOCK_M * (BLOCK_N + 8) * 2 : 0;
-  static constexpr int OUT_BYTES = RES == 3 ? X1_BYTES + BLOCK_M * BLOCK_N * 4 : BLOCK_M * BLOCK_N * 2;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + 1024;
+  static constexpr int IL_OUT_BYTES = BLOCK_M * BLOCK_N * 4;
+  static constexpr int OUT_BYTES = RES == 3 ? X1_BYTES : BLOCK_M * BLOCK_N * 2;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + OUT_BUFS * OUT_BYTES + (RES == 3 ? 2 * IL_OUT_BYTES : 0) + 1024;
   static_assert(SMEM_BYTES <= 230 * 1024, "smem budget");
 };
 
@@ -297,6 +301,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
   __shared__ __align__(8) uint64_t bar_tmem_empty[2];
   __shared__ __align__(8) uint64_t bar_stage_ready[NB];  // staging buffer free (and residual landed, if any)
   __shared__ __align__(8) uint64_t bar_out_ready[NB];    // epilogue finished writing the staging buffer
+  __shared__ __align__(8) uint64_t bar_out_free[2];      // RES == 3: the store of the output buffer's previous tile has read it
   __shared__ uint32_t tmem_base_s;
   __shared__ __align__(16) float bias_s[2][BLOCK_N];   // one per epilogue warpgroup
   __shared__ __align__(16) uint32_t keep_s[2][BLOCK_N / 2];   // RES == 3: 0xFFFF per valid slot of the other branch (pairs of slots)
@@ -327,6 +332,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       mbar_init(smem_u32(&bar_stage_ready[b]), 1);
       mbar_init(smem_u32(&bar_out_ready[b]), 128);
     }
+    mbar_init(smem_u32(&bar_out_free[0]), 1);
+    mbar_init(smem_u32(&bar_out_free[1]), 1);
     fence_barrier_init();
   } else if (warp == 1) {
     tmem_alloc<2 * BLOCK_N>(smem_u32(&tmem_base_s));
@@ -433,6 +440,33 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           if (elect_one()) mbar_arrive(rdy);
         }
       };
+      if (RES == 3) {
+        // The other branch's tiles run NB tiles ahead in a ring of their own: slot it % NB is free again once the epilogue
+        // of tile it is through (bar_out_ready).  Output buffer it & 1 goes back to its warpgroup when the store has read it.
+        for (int j = 0; j < NB && j < my_tiles; ++j) acquire_staging(j);
+        for (int it = 0; it < my_tiles; ++it) {
+          const int tile0_ = blockIdx.x + it * gridDim.x;
+          const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
+          int n_tile, w0, h0, nb0;
+          tile_coords(p, tile, n_tile, w0, h0, nb0);
+          const int n0 = n_tile * BLOCK_N;
+          const int ob = it & 1;
+          mbar_wait(smem_u32(&bar_out_ready[ob]), (it >> 1) & 1);
+          if (elect_one()) {      // slots [n0, n0 + 64) -> physical channels [2 n0, 2 n0 + 128) of the unit's output
+#pragma unroll
+            for (int q = 0; q < BLOCK_N / 32; ++q)
+              if (n0 + q * 32 < p.cout)
+                tma_store_4d(&maps.d, staging + NB * Cfg::X1_BYTES + ob * Cfg::IL_OUT_BYTES + q * (BLOCK_M * 128),
+                             2 * n0 + q * 64, w0, h0, nb0);
+            tma_store_commit();
+          }
+          if (it + NB < my_tiles) acquire_staging(it + NB);
+          if (elect_one()) {
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            mbar_arrive(smem_u32(&bar_out_free[ob]));
+          }
+        }
+      } else {
       for (int j = 0; j < LA && j < my_tiles; ++j) acquire_staging(j);
       for (int it = 0; it < my_tiles; ++it) {
         if (LA == 0) {
@@ -450,18 +484,10 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           const int ob = it % NB;
           mbar_wait(smem_u32(&bar_out_ready[ob]), (it / NB) & 1);
           if (elect_one()) {
-            if (RES == 3) {      // slots [n0, n0 + 64) -> physical channels [2 n0, 2 n0 + 128) of the unit's output
 #pragma unroll
-              for (int q = 0; q < BLOCK_N / 32; ++q)
-                if (n0 + q * 32 < p.cout)
-                  tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + Cfg::X1_BYTES + q * (BLOCK_M * 128), 2 * n0 + q * 64,
-                               w0, h0, nb0);
-            } else {
-#pragma unroll
-              for (int q = 0; q < BLOCK_N / 64; ++q)
-                if (n0 + q * 64 < p.cout)
-                  tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
-            }
+            for (int q = 0; q < BLOCK_N / 64; ++q)
+              if (n0 + q * 64 < p.cout)
+                tma_store_4d(&maps.d, staging + ob * Cfg::OUT_BYTES + q * (BLOCK_M * 128), n0 + q * 64, w0, h0, nb0);
             tma_store_commit();
           }
         }
@@ -473,6 +499,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
           if (elect_one()) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(NB - LA) : "memory");
           acquire_staging(j);
         }
+      }
       }
       if (elect_one()) tma_store_wait_all();
     }
@@ -555,7 +582,8 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       const int tile = (p.reverse & 1) ? total_tiles - 1 - tile0_ : tile0_;
       const int b = it & 1;
       const int bb = wg;
-      const int ob = it % NB;
+      const int sb = it % NB;                       // staging buffer (RES == 3: slot of the other branch's tile)
+      const int ob = RES == 3 ? (it & 1) : sb;      // buffer the output is staged in
       const int n0 = (tile - static_cast<int>(fast_div(tile, p.n_tiles, p.mul_n_tiles)) * p.n_tiles) * BLOCK_N;
       const int x1_ch8 = RES == 3 ? ((n0 < p.il_group ? n0 : p.il_half + (n0 - p.il_group)) & ~7) : 0;   // as in the DMA warp
       named_bar_sync(1 + wg, 128);               // every thread of the group is done reading the previous tile's bias
@@ -576,8 +604,10 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
       named_bar_sync(1 + wg, 128);
       mbar_wait(smem_u32(&bar_tmem_full[b]), (it >> 1) & 1);
       tc_fence_after();
-      mbar_wait(smem_u32(&bar_stage_ready[ob]), (it / NB) & 1);
-      const uint32_t stage_d = staging + ob * Cfg::OUT_BYTES;
+      mbar_wait(smem_u32(&bar_stage_ready[sb]), (it / NB) & 1);
+      if (RES == 3) mbar_wait(smem_u32(&bar_out_free[ob]), ((it >> 1) & 1) ^ 1);
+      const uint32_t stage_d = staging + sb * Cfg::OUT_BYTES;
+      const uint32_t out_d = staging + NB * Cfg::OUT_BYTES + ob * Cfg::IL_OUT_BYTES;      // RES == 3 only
       const uint32_t acc = tmem_base + b * BLOCK_N + (static_cast<uint32_t>(quarter * 32) << 16);
 #pragma unroll 1
       for (int cc = 0; cc < BLOCK_N / 32; ++cc) {
@@ -630,7 +660,7 @@ conv_gemm_persistent_kernel(const __grid_constant__ ConvMaps maps, const __grid_
             for (int i = 0; i < 8; ++i) f[i] = act_t<ACT>(f[i]);
             const uint32_t q0 = pack_bf16x2(f[0], f[1]), q1 = pack_bf16x2(f[2], f[3]);
             const uint32_t q2 = pack_bf16x2(f[4], f[5]), q3 = pack_bf16x2(f[6], f[7]);
-            const uint32_t osub = stage_d + Cfg::X1_BYTES + cc * (BLOCK_M * 128) + row_off;
+            const uint32_t osub = out_d + cc * (BLOCK_M * 128) + row_off;
             asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(osub + (((2 * g) ^ sw) << 4)),
                          "r"(__byte_perm(r0, q0, 0x5410)), "r"(__byte_perm(r0, q0, 0x7632)),
                          "r"(__byte_perm(r1, q1, 0x5410)), "r"(__byte_perm(r1, q1, 0x7632)) : "memory");
@@ -1593,6 +1623,18 @@ static bool deep_ring(const ConvLaunch& l) {     // B200_CONV_DEEP=0 turns the d
   return v == 1 && l.p.num_kb >= 8 && static_cast<long long>(l.grid) <= 8LL * device_sm_count();
 }
 
+// Thin-K layers: 2 = four ring stages + eight staging buffers (the store path was the limit when this was tuned), 3 = six
+// stages + five buffers (ncu on ShuffleNetV2's 24 -> 58 conv at 56 x 56: producer 66 % of its time waiting for a free
+// stage while the MMA warp waits for a full one -- load latency, not stores).  B200_CONV_THIN_MODE picks.
+static int thin_mode() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("B200_CONV_THIN_MODE");
+    v = e ? atoi(e) : 2;
+  }
+  return v;
+}
+
 static bool deep_staging(const ConvLaunch& l) {     // B200_CONV_THIN=0 turns the deep-staging variant off
   static int v = -1;
   if (v < 0) {
@@ -1607,12 +1649,15 @@ static int launch_persistent_act(const ConvLaunch& l, cudaStream_t stream) {
   switch (l.p.act) {
     case ACT_NONE:
       if (BLOCK_N == 128 && RES != 2 && deep_ring(l)) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, (BLOCK_N == 128 && RES != 2) ? 1 : 0>(l, stream);
+      if (RES == 0 && deep_staging(l) && thin_mode() == 3) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, RES == 0 ? 3 : 0>(l, stream);
       if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_NONE, RES == 0 ? 2 : 0>(l, stream);
       return launch_persistent_t<BLOCK_N, RES, ACT_NONE>(l, stream);
     case ACT_RELU:
+      if (RES == 0 && deep_staging(l) && thin_mode() == 3) return launch_persistent_t<BLOCK_N, RES, ACT_RELU, RES == 0 ? 3 : 0>(l, stream);
       if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_RELU, RES == 0 ? 2 : 0>(l, stream);
       return launch_persistent_t<BLOCK_N, RES, ACT_RELU>(l, stream);
     case ACT_SILU:
+      if (RES == 0 && deep_staging(l) && thin_mode() == 3) return launch_persistent_t<BLOCK_N, RES, ACT_SILU, RES == 0 ? 3 : 0>(l, stream);
       if (RES == 0 && deep_staging(l)) return launch_persistent_t<BLOCK_N, RES, ACT_SILU, RES == 0 ? 2 : 0>(l, stream);
       return launch_persistent_t<BLOCK_N, RES, ACT_SILU>(l, stream);
     case ACT_SIGMOID: return launch_persistent_t<BLOCK_N, RES, ACT_SIGMOID>(l, stream);
