@@ -73,14 +73,18 @@ class PlanInterpreter:
                     B[p[3]][..., p[4]:p[4] + 2 * cp] = torch.stack([xs, y], dim=-1).reshape(*y.shape[:-1], 2 * cp)
                     continue
                 b = self._f32(op["b_off"], cout)
+                rows = p[20] if p[20] > 0 else cout      # weights stored as [rows][k*k][kpad], zero padded (0 = exact)
                 if p[13] > 0:      # K-concatenated 1x1 conv: W[:, :cin] . x + W[:, cin:] . x2[::s2, ::s2]
                     cin2, s2 = p[15], p[16]
-                    wk = self._bf16w(op["w_off"], cout * (cin + cin2)).view(cout, cin + cin2)
+                    kpad = p[19] if p[19] > 0 else cin + cin2
+                    wk = self._bf16w(op["w_off"], rows * kpad).view(rows, kpad)[:cout]
                     x2 = B[p[13] - 1][..., p[14]:p[14] + cin2].permute(0, 3, 1, 2)
-                    y = F.conv2d(x, wk[:, :cin, None, None], b) + F.conv2d(x2, wk[:, cin:, None, None], None, stride=s2)
+                    y = F.conv2d(x, wk[:, :cin, None, None], b) + \
+                        F.conv2d(x2, wk[:, cin:cin + cin2, None, None], None, stride=s2)
                 else:
-                    w = self._bf16w(op["w_off"], cout * k * k * cin).view(cout, k, k, cin).permute(0, 3, 1, 2)
-                    y = F.conv2d(x, w, b, stride=s, padding=pad)
+                    kpad = p[19] if p[19] > 0 else cin
+                    w = self._bf16w(op["w_off"], rows * k * k * kpad).view(rows, k, k, kpad)[:cout, :, :, :cin]
+                    y = F.conv2d(x, w.permute(0, 3, 1, 2), b, stride=s, padding=pad)
                 if p[6] >= 0:
                     r = B[p[6]][..., p[7]:p[7] + cout].permute(0, 3, 1, 2)
                     y = _act(y, act) + r if p[12] else _act(y + r, act)

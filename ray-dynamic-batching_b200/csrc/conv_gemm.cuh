@@ -12,6 +12,11 @@ struct ConvSpec {
   View in2;                  // optional second input of a K-concatenated 1x1 conv (base == nullptr -> none): the output is
   int stride2 = 1;           //   act(W[:, :Ca] . in + W[:, Ca:] . in2[::stride2, ::stride2] + bias), w = [Cout][Ca + Cb]
   const void* w = nullptr;   // bf16 [Cout][k*k][Cin], BatchNorm already folded in
+  int w_cin = 0, w_rows = 0;  // physical extent of `w`: [w_rows >= Cout][k*k][w_cin >= Cin (+ Cin2)], zero padded; 0 = exact.
+                              //   Measured on B200: a weight box that is partly out of bounds of its tensor map (zero-filled
+                              //   by TMA) loads about twice as slowly, and a thin layer loads one per 128-pixel tile
+                              //   (24 -> 58 1x1 at 56 x 56 x 512: 99 -> 55 us with the weights padded to the 64 x 64 box).
+                              //   Input boxes clipped the same way, clipped stores and residual boxes cost nothing measurable.
   const float* bias = nullptr;  // fp32 [Cout]
   int ksize = 1, stride = 1, pad = 0;
   int act = 0;               // b200::Act

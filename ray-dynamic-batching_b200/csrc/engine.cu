@@ -253,12 +253,16 @@ int Engine::plan_for(int batch, BatchPlan** out) {
       s.w = weights_dev + po.rec.w_off;
       s.bias = reinterpret_cast<const float*>(weights_dev + po.rec.b_off);
       s.ksize = p[8]; s.stride = p[9]; s.pad = p[10]; s.act = p[11];
+      s.w_cin = p[19]; s.w_rows = p[20];      // weights stored padded to the TMA box sizes (0 = exact)
       s.res_after_act = p[12] != 0;
       if (p[17] > 0) s.a_scale = reinterpret_cast<const float*>(buf_dev[p[17] - 1]);   // SE gate [N][Cin] fp32, buffer id + 1
       if (p[13] > 0) {      // K-concatenated second input: buffer id + 1, channel offset, channels, stride
         s.in2 = view(p[13] - 1, p[14], p[15], batch);
         s.stride2 = p[16];
       }
+      // every bf16 buffer lives in the zero-initialised arena with 256 spare bytes behind it and only ever holds finite
+      // activations: input boxes may read past a pixel's channels (ConvSpec::in_overread)
+      s.in_overread = true;
       s.reverse_tiles = alt && (conv_index++ & 1);   // consecutive conv layers walk their tiles in opposite directions
       int rc = conv_prepare(s, &po.conv);
       if (rc != 0) return fail(rc, "op " + std::to_string(i) + ": " + last_error_cstr());

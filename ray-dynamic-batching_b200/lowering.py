@@ -59,6 +59,24 @@ def line_channels(c):
     return p8
 
 
+def weight_rows(cout_p):
+    """Rows a conv's weight matrix is stored with: the output channels rounded up to the channel tile the kernel will use
+    (64, 128, or 256 for CTA pairs), so that no TMA box over the weights is partly out of bounds (see `weight_k`)."""
+    if cout_p <= 64:
+        return 64
+    return (cout_p + 127) // 128 * 128 if cout_p < 256 else (cout_p + 255) // 256 * 256
+
+
+def weight_k(cin_p, halo):
+    """Input channels per filter tap the weights are stored with: rounded up to the K box of the kernel (64 channels; the
+    halo 3x3 kernel uses 16 / 32 / 64). Measured on B200: a TMA box that is partly out of bounds loads about twice as slowly
+    as one inside the tensor, and a thin layer loads its weight box once per 128-pixel tile. B200_PAD_WEIGHTS=0 stores the
+    exact extents (the tensor map then zero-fills the rest of the box)."""
+    if halo:
+        return 16 if cin_p <= 16 else (32 if cin_p <= 32 else 64)
+    return (cin_p + 63) // 64 * 64
+
+
 def stem_cout_tile(cout):
     """Mirror of b200_stem_cout_tile (csrc/stem.cu)."""
     return 32 if cout % 32 == 0 else (24 if cout % 24 == 0 else 16)
@@ -160,6 +178,7 @@ class PlanBuilder:
         self.fuse_stem_pool = os.environ.get('B200_FUSE_STEM_POOL', '1') != '0'   # conv1 + bn1 + relu + maxpool in one kernel
         # ShuffleNetV2 cat + channel_shuffle written by the epilogue of the conv that ends branch2 (no shuffle pass)
         self.fuse_shuffle = os.environ.get('B200_FUSE_SHUFFLE', '1') != '0'
+        self.pad_weights = os.environ.get('B200_PAD_WEIGHTS', '1') != '0'   # conv weights stored padded to the TMA box sizes
         self.gather_small_cin = os.environ.get('B200_GATHER_SMALL_CIN', '1') != '0'   # 3x3 convs with Cin <= 56 the halo kernel does not take: packed-K gather kernel
         self.fuse_downsample = os.environ.get('B200_FUSE_DOWNSAMPLE', '1') != '0'   # ResNet conv3 + downsample as one GEMM
         self.halo_small_cin = os.environ.get('B200_HALO_SMALL_CIN', '1') != '0'   # 3x3/s1 with Cin < 64 on the halo kernel
@@ -211,8 +230,9 @@ class PlanBuilder:
         if in_scale is None and not halo and self.gather_small_cin and cout_p <= 256 and ((k == 3 and cin_p <= 56) or
                                                        (k == 1 and cin_p % 64 != 0 and cin_p <= self.gather_1x1_max_cin)):
             return self._gather_conv(x, weight, bias, stride, pad, act, res, out, name, res_after_act)
-        wp = torch.zeros(cout_p, k * k, cin_p)
-        wfull = torch.zeros(cout, k * k, cin_p)
+        kpad, rows = (weight_k(cin_p, halo), weight_rows(cout_p)) if self.pad_weights else (cin_p, cout_p)
+        wp = torch.zeros(rows, k * k, kpad)
+        wfull = torch.zeros(cout, k * k, kpad)
         wfull[:, :, torch.as_tensor(x.cmap)] = weight.permute(0, 2, 3, 1).reshape(cout, k * k, cin)
         wp[torch.as_tensor(out.cmap)] = wfull
         bp = torch.zeros(cout_p)
@@ -227,6 +247,8 @@ class PlanBuilder:
             assert (k, stride, pad) == (1, 1, 0) and self.bufs[in_scale.buf][3] == 1 and in_scale.cphys == cin_p
             assert x.coff == 0 and self.bufs[x.buf][2] == cin_p
             pr += [0, 0, 0, 0, in_scale.buf + 1]
+        if self.pad_weights:          # physical extent of the weights: [rows][k*k][kpad]
+            pr += [0] * (19 - len(pr)) + [kpad, rows]
         self._op(OP_CONV, pr, w_off, b_off, name=name)
         return out
 
@@ -241,18 +263,21 @@ class PlanBuilder:
         assert ((x2.h - 1) // stride2 + 1, (x2.w - 1) // stride2 + 1) == (x.h, x.w)
         out = self.new_act(x.h, x.w, cout)
         cap, cbp, cout_p = x.cphys, x2.cphys, out.cphys
-        wp = torch.zeros(cout_p, cap + cbp)
+        kpad, rows = (cap + weight_k(cbp, False), weight_rows(cout_p)) if self.pad_weights else (cap + cbp, cout_p)
+        wp = torch.zeros(rows, kpad)
         wa = torch.zeros(cout, cap)
         wa[:, torch.as_tensor(x.cmap)] = weight.reshape(cout, ca)
         wb = torch.zeros(cout, cbp)
         wb[:, torch.as_tensor(x2.cmap)] = weight2.reshape(cout, cb)
-        wp[torch.as_tensor(out.cmap)] = torch.cat([wa, wb], dim=1)
+        wp[torch.as_tensor(out.cmap), :cap + cbp] = torch.cat([wa, wb], dim=1)
         bp = torch.zeros(cout_p)
         bp[torch.as_tensor(out.cmap)] = bias + bias2
         w_off = self.add_weights(self.bf16_bits(wp))
         b_off = self.add_weights(bp.numpy().astype(np.float32))
-        self._op(OP_CONV, [x.buf, x.coff, cap, out.buf, out.coff, cout_p, -1, 0, 1, 1, 0, act, 0,
-                           x2.buf + 1, x2.coff, cbp, stride2], w_off, b_off, name=name)
+        pr = [x.buf, x.coff, cap, out.buf, out.coff, cout_p, -1, 0, 1, 1, 0, act, 0, x2.buf + 1, x2.coff, cbp, stride2]
+        if self.pad_weights:
+            pr += [0] * (19 - len(pr)) + [kpad, rows]
+        self._op(OP_CONV, pr, w_off, b_off, name=name)
         return out
 
     def _gather_conv(self, x, weight, bias, stride, pad, act, res, out, name, res_after_act):

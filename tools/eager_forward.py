@@ -1,3 +1,6 @@
+#!/usr/bin/env python
+"""Three eager (no CUDA graph) forwards of one model at one batch size: the command ncu captures kernels from.
+Usage: python tools/eager_forward.py kind batch"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
