@@ -1379,13 +1379,6 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   if (has_res && (s.res.H != out.H || s.res.W != out.W || s.res.C != cout || s.res.N != out.N))
     return fail(B200_ERR_INVALID, "conv: residual geometry mismatch");
 
-  static int overread_env = -1;      // B200_TMA_OVERREAD=0: input maps keep their exact channel count (boxes partly out of bounds)
-  if (overread_env < 0) {
-    const char* e = getenv("B200_TMA_OVERREAD");
-    overread_env = (e && e[0] == '0') ? 0 : 1;
-  }
-  const bool ovr = s.in_overread && overread_env == 1;
-  const int a_c = ovr ? (in.C + BLOCK_K - 1) / BLOCK_K * BLOCK_K : in.C;      // channels the input maps declare
   ConvParams& p = L->p;
   memset(&p, 0, sizeof(p));
   memset(&L->maps, 0, sizeof(L->maps));
@@ -1481,17 +1474,17 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
   if (flat) {
     oW = out.N * out.H * out.W; oH = 1; oN = 1;
     p.tw = 128; p.th = 1; p.tn = 1;
-    B200_TRY(encode_act_view(&L->maps.a[0], in.base, a_c, oW, 1, 1, ips, ips * oW, ips * oW, 128, 1, 1));
+    B200_TRY(encode_act_view(&L->maps.a[0], in.base, in.C, oW, 1, 1, ips, ips * oW, ips * oW, 128, 1, 1));
     p.tap_map[0] = 0; p.tap_dx[0] = 0; p.tap_dy[0] = 0;
     if (dual) {
       const uint64_t ips2 = uint64_t(s.in2.pix_stride) * 2;
-      B200_TRY(encode_act_view(&L->maps.a[1], s.in2.base, ovr ? (s.in2.C + BLOCK_K - 1) / BLOCK_K * BLOCK_K : s.in2.C, oW, 1, 1, ips2, ips2 * oW, ips2 * oW, 128, 1, 1));
+      B200_TRY(encode_act_view(&L->maps.a[1], s.in2.base, s.in2.C, oW, 1, 1, ips2, ips2 * oW, ips2 * oW, 128, 1, 1));
       p.tap_map[1] = 1; p.tap_dx[1] = 0; p.tap_dy[1] = 0;
     }
   } else if (halo) {
     p.tw = 8; p.th = 16; p.tn = 1;
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
-    const uint64_t dims[4] = {uint64_t(ovr ? p.pb / 2 : in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
+    const uint64_t dims[4] = {uint64_t(in.C), uint64_t(in.W), uint64_t(in.H), uint64_t(in.N)};
     const uint64_t str[3] = {ips, rowb, imgb};
     const uint32_t box[4] = {uint32_t(p.pb / 2), uint32_t(HALO_PITCH_PX), uint32_t(HALO_ROWS), 1u};
     const Swizzle swz = p.pb == 128 ? SWZ_128B : (p.pb == 64 ? SWZ_64B : SWZ_32B);
@@ -1500,7 +1493,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     } else {
       for (int py = 0; py < 2; ++py)
         for (int px = 0; px < 2; ++px) {      // parity plane (py, px)(i, j) = in(2i + py, 2j + px): a view with doubled strides
-          const uint64_t pd[4] = {uint64_t(ovr ? p.pb / 2 : in.C), uint64_t((in.W - px + 1) / 2), uint64_t((in.H - py + 1) / 2), uint64_t(in.N)};
+          const uint64_t pd[4] = {uint64_t(in.C), uint64_t((in.W - px + 1) / 2), uint64_t((in.H - py + 1) / 2), uint64_t(in.N)};
           const uint64_t ps[3] = {2 * ips, 2 * rowb, imgb};
           const char* base = static_cast<const char*>(in.base) + (uint64_t(py) * in.W + px) * ips;
           B200_TRY(encode_tmap(&L->maps.a[py * 2 + px], base, 4, pd, ps, box, swz));
@@ -1510,14 +1503,14 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
     pick_tile(oW, oH, oN, &p.tw, &p.th, &p.tn);
     const uint64_t rowb = ips * in.W, imgb = rowb * in.H;
     if (s.stride == 1) {
-      B200_TRY(encode_act_view(&L->maps.a[0], in.base, a_c, in.W, in.H, in.N, ips, rowb, imgb, p.tw, p.th, p.tn));
+      B200_TRY(encode_act_view(&L->maps.a[0], in.base, in.C, in.W, in.H, in.N, ips, rowb, imgb, p.tw, p.th, p.tn));
     } else {
       for (int py = 0; py < 2; ++py)
         for (int px = 0; px < 2; ++px) {
           const int Wp = (in.W - px + 1) / 2, Hp = (in.H - py + 1) / 2;
           if (Wp <= 0 || Hp <= 0) continue;
           const char* base = static_cast<const char*>(in.base) + (uint64_t(py) * in.W + px) * ips;
-          B200_TRY(encode_act_view(&L->maps.a[py * 2 + px], base, a_c, Wp, Hp, in.N, 2 * ips, 2 * rowb, imgb, p.tw,
+          B200_TRY(encode_act_view(&L->maps.a[py * 2 + px], base, in.C, Wp, Hp, in.N, 2 * ips, 2 * rowb, imgb, p.tw,
                                    p.th, p.tn));
         }
     }
@@ -1525,7 +1518,7 @@ int conv_prepare(const ConvSpec& s, ConvLaunch* L) {
       // second input sampled at (stride2 * y, stride2 * x): a view with multiplied strides, tiled like the output
       const View& b2 = s.in2;
       const uint64_t ips2 = uint64_t(b2.pix_stride) * 2, rowb2 = ips2 * b2.W, imgb2 = rowb2 * b2.H;
-      B200_TRY(encode_act_view(&L->maps.a[1], b2.base, ovr ? (b2.C + BLOCK_K - 1) / BLOCK_K * BLOCK_K : b2.C, out.W, out.H, out.N, s.stride2 * ips2, s.stride2 * rowb2, imgb2,
+      B200_TRY(encode_act_view(&L->maps.a[1], b2.base, b2.C, out.W, out.H, out.N, s.stride2 * ips2, s.stride2 * rowb2, imgb2,
                                p.tw, p.th, p.tn));
       p.tap_map[1] = 1; p.tap_dx[1] = 0; p.tap_dy[1] = 0;
     }
