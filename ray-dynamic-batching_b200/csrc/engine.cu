@@ -260,9 +260,6 @@ int Engine::plan_for(int batch, BatchPlan** out) {
         s.in2 = view(p[13] - 1, p[14], p[15], batch);
         s.stride2 = p[16];
       }
-      // every bf16 buffer lives in the zero-initialised arena with 256 spare bytes behind it and only ever holds finite
-      // activations: input boxes may read past a pixel's channels (ConvSpec::in_overread)
-      s.in_overread = true;
       s.reverse_tiles = alt && (conv_index++ & 1);   // consecutive conv layers walk their tiles in opposite directions
       int rc = conv_prepare(s, &po.conv);
       if (rc != 0) return fail(rc, "op " + std::to_string(i) + ": " + last_error_cstr());
