@@ -4,8 +4,9 @@ and TFLOP/s against the sustained bf16 peak (the figures north_star asks for, pe
 
   python tools/launch_table.py kind batch launches.csv [hw] > profiles/r02_kernels_<kind>.md
 
-The launch list is `ncu --metrics gpu__time_duration.sum --clock-control none --csv` of bench.py (its per-launch times are
-cold-cache and serialised: shares and ratios are what to read, not the absolute step time).  The LAST run of collate +
+The launch list is `ncu --metrics gpu__time_duration.sum --clock-control none --csv` of bench.py or of
+tools/eager_forward.py (its per-launch times are cold-cache and serialised: shares and ratios are what to read, not the
+absolute step time).  The LAST run of collate +
 n_ops kernels in the list is taken as the step and joined, in order, with the plan's ops (bench.plan_traffic)."""
 import collections
 import csv
@@ -30,9 +31,9 @@ def main():
     rows = list(csv.reader(open(path)))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     hdr = rows[hi]
-    ik, iv = hdr.index("Kernel Name"), hdr.index("Metric Value")
+    ik, iv, im = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Name")
     launches = [(re.sub(r"\(.*", "", r[ik]).replace("void ", ""), float(r[iv].replace(",", "")) / 1e3)
-                for r in rows[hi + 1:] if len(r) > iv]
+                for r in rows[hi + 1:] if len(r) > iv and r[im] == "gpu__time_duration.sum"]      # other metrics may share the file
     # the last "collate + n_ops kernels" block
     idx = [i for i, l in enumerate(launches) if "collate" in l[0] and i + len(names) < len(launches) + 0]
     start = next(i for i in reversed(idx) if i + 1 + len(names) <= len(launches))
