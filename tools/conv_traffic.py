@@ -41,11 +41,10 @@ def parse(path):
         if kid not in per_id:
             per_id[kid] = [row["Kernel Name"], 0.0, 0.0]
             order.append(kid)
-        b = to_bytes(row["Metric Value"], row["Metric Unit"])
-        if row["Metric Name"] == "dram__bytes_read.sum":
-            per_id[kid][1] = b
+        if row["Metric Name"] == "dram__bytes_read.sum":      # other metrics (durations) may share the file
+            per_id[kid][1] = to_bytes(row["Metric Value"], row["Metric Unit"])
         elif row["Metric Name"] == "dram__bytes_write.sum":
-            per_id[kid][2] = b
+            per_id[kid][2] = to_bytes(row["Metric Value"], row["Metric Unit"])
     return [tuple(per_id[k]) for k in order]
 
 

@@ -8,7 +8,8 @@ import rdb_b200
 from rdb_b200 import synth
 from rdb_b200.engine import B200Model
 kind, batch = sys.argv[1], int(sys.argv[2])
-m = B200Model(kind, synth.make_model(kind, n_proto=8), max_batch=batch, use_graphs=False)
+module = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
+m = B200Model(kind, module, max_batch=batch, use_graphs=False)
 per = m.in_h * m.in_w * 3
 src = torch.randint(0, 256, (batch * per,), dtype=torch.uint8).to(m.device)
 offsets = np.arange(batch, dtype=np.uint64) * per

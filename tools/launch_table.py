@@ -32,7 +32,7 @@ def main():
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     hdr = rows[hi]
     ik, iv, im = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Metric Name")
-    launches = [(re.sub(r"\(.*", "", r[ik]).replace("void ", ""), float(r[iv].replace(",", "")) / 1e3)
+    launches = [(re.sub(r"\(.*", "", r[ik]).replace("void ", "").replace("b200::", ""), float(r[iv].replace(",", "")) / 1e3)
                 for r in rows[hi + 1:] if len(r) > iv and r[im] == "gpu__time_duration.sum"]      # other metrics may share the file
     # the last "collate + n_ops kernels" block
     idx = [i for i, l in enumerate(launches) if "collate" in l[0] and i + len(names) < len(launches) + 0]
