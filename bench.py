@@ -133,7 +133,7 @@ def plan_traffic(blob, batch):
             # ShuffleNetV2 unit tail: 1x1 conv of p[18] channels written interleaved with the other branch (p[18] logical
             # channels read) into the unit's output of p[5] physical channels; weights hold p[5] / 2 slots
             b = batch * oh * ow * (p[2] * 2 + p[18] * 2 + p[5] * 2) + (p[5] // 2) * p[2] * 2 + (p[5] // 2) * 4
-            fl = 2.0 * batch * oh * ow * p[18] * p[2]
+            fl = 2.0 * batch * oh * ow * (p[5] // 2) * p[2]      # physical channels, as for every other conv of the table
         elif t in (lowering.OP_CONV, lowering.OP_GATHER_CONV):
             k = p[8]
             b += p[5] * k * k * p[2] * 2 + p[5] * 4
