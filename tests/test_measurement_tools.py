@@ -111,12 +111,12 @@ def test_traffic_file_counts_only_for_the_running_sources(tmp_path, monkeypatch)
         tj = json.load(open(path))
         assert tj["traffic_bytes_per_launch"] > 0 and tj["launches"] > 0 and tj["commit"]
         assert tj["source_stamp"] == stamp, "%s was captured on other sources: recapture it (tools/conv_traffic.py)" % path
-    # any change to a kernel source changes the hash
-    src = os.path.join(ROOT, "ray-dynamic-batching_b200", "csrc", "pool.cu")
-    orig = open(src).read()
-    try:
-        open(src, "a").write("\n// touched\n")
-        assert build.source_stamp() != stamp
-    finally:
-        open(src, "w").write(orig)
+    # any change to a kernel source changes the hash (checked on a copy of the sources)
+    import shutil
+    copy = tmp_path / "csrc"
+    shutil.copytree(build.CSRC, copy)
+    monkeypatch.setattr(build, "CSRC", str(copy))
     assert build.source_stamp() == stamp
+    with open(copy / "pool.cu", "a") as f:
+        f.write("\n// touched\n")
+    assert build.source_stamp() != stamp
