@@ -45,7 +45,31 @@ def _time_batch(model, bs, out, warmup_runs, num_runs):
     return lat
 
 
-def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_runs: int = 10, dense: bool = False) -> List[dict]:
+def _time_batch_end_to_end(model, bs, warmup_runs, num_runs):
+    """What an actor spends on a batch it serves alone: uint8 requests in page-locked host memory -> H2D -> collate ->
+    forward -> D2H of the outputs (detections for a model with device NMS), wall clock, one batch at a time.  The
+    reference's profile is forward-only from device-resident inputs (ModelProfiler._measure_latency), and so is the default
+    here; a policy that fills a node to the forward-only throughput promises more than the actor delivers, which
+    is what this variant is for.  Two batches in flight overlap the copies with the compute, so an actor does better than
+    1 / this latency; the figure is the conservative one."""
+    import time
+    import numpy as np
+    per = model.in_h * model.in_w * 3
+    host = torch.randint(0, 256, (bs * per,), dtype=torch.uint8).pin_memory()
+    offsets = np.arange(bs, dtype=np.uint64) * per
+    hw = np.tile(np.array([[model.in_h, model.in_w]], dtype=np.int32), (bs, 1))
+    for _ in range(warmup_runs + 2):
+        model.infer_packed_async(host, offsets, hw, bs, bs, 0, bs * per).result()
+    lat = []
+    for _ in range(num_runs):
+        t0 = time.perf_counter()
+        model.infer_packed_async(host, offsets, hw, bs, bs, 0, bs * per).result()
+        lat.append((time.perf_counter() - t0) * 1e3)
+    return lat
+
+
+def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_runs: int = 10, dense: bool = False,
+                    end_to_end: bool = False) -> List[dict]:
     """One row per batch size (ModelProfiler.profile_batch_size, :114-178).
 
     dense=True emits EVERY integer batch size from 1 to max(batch_sizes), like the reference's sweep
@@ -58,6 +82,9 @@ def profile_batches(model, batch_sizes: List[int], warmup_runs: int = 3, num_run
     timed = {}
     for bs in sorted(set(batch_sizes)):
         if bs > model.max_batch:
+            continue
+        if end_to_end:
+            timed[bs] = _time_batch_end_to_end(model, bs, warmup_runs, num_runs)
             continue
         out = torch.empty(bs, model.out_dim, device=dev, dtype=torch.float32)
         timed[bs] = _time_batch(model, bs, out, warmup_runs, num_runs)

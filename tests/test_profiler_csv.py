@@ -80,3 +80,24 @@ def test_reference_nexus_consumes_the_b200_profiles():
         for a in nodes:
             for b in nodes:
                 pol.mergeNodes(a, b)               # every pair: indexes profile[ceil(duty * rate / 1000)]
+
+
+def test_end_to_end_profiles_are_the_conservative_ones():
+    """profiles/b200_batch_profiles_e2e/ (tools/profile_batches.py --e2e): same schema and the same integer rows as the
+    forward-only profiles, the memory column of the same planner, and a latency that is never below the forward-only one -- so a policy
+    that packs with them (nexus.py:129-133) promises at most what the forward-only profile promises."""
+    import os
+    from rdb_b200 import profiler
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles")
+    for name in ("resnet50", "shufflenet", "efficientnetv2", "yolov8n"):
+        fwd = profiler.load_csv_to_dict(os.path.join(root, "b200_batch_profiles", "%s_b200_summary.csv" % name))
+        e2e = profiler.load_csv_to_dict(os.path.join(root, "b200_batch_profiles_e2e", "%s_b200_e2e_summary.csv" % name))
+        assert e2e and set(e2e) == set(range(1, max(e2e) + 1))
+        common = sorted(set(fwd) & set(e2e))
+        assert len(common) >= 128
+        for b in common:
+            assert e2e[b]['avg_latency_ms'] >= fwd[b]['avg_latency_ms'] * 0.98, (name, b)
+            # the same planner; the padded conv weights added a few MB to the engines profiled later
+            assert abs(e2e[b]['peak_memory_mb'] - fwd[b]['peak_memory_mb']) <= 0.1 * fwd[b]['peak_memory_mb']
+        top = max(common)
+        assert top / e2e[top]['avg_latency_ms'] < top / fwd[top]['avg_latency_ms']

@@ -33,11 +33,15 @@ def client_main(*args):
     return client_process_main(*args)
 
 
-def load_profiles(models, max_bs=512):
+def load_profiles(models, max_bs=512, kind="forward"):
+    """kind "forward": the reference's forward-only profile; "e2e": a batch served alone from host memory
+    (tools/profile_batches.py --e2e), the one that does not over-promise a saturated node."""
     from rdb_b200 import profiler, serving
     out = {}
     for m in models:
         path = os.path.join(ROOT, "profiles", "b200_batch_profiles", "%s_b200_summary.csv" % PROFILE_CSV[m])
+        if kind == "e2e":
+            path = os.path.join(ROOT, "profiles", "b200_batch_profiles_e2e", "%s_b200_e2e_summary.csv" % PROFILE_CSV[m])
         d = profiler.load_csv_to_dict(path) if os.path.exists(path) else {}
         d = {k: v for k, v in d.items() if 'avg_latency_ms' in v}
         if not d:
@@ -61,6 +65,8 @@ def main():
     ap.add_argument("--clients", type=int, default=0, help="client processes per model (default: 2 per GPU, at most 16)")
     ap.add_argument("--burst", type=int, default=16)
     ap.add_argument("--dynamic", action="store_true")
+    ap.add_argument("--profiles", default="forward", choices=("forward", "e2e"),
+                    help="batch profiles the policy and the stale-request rule use")
     ap.add_argument("--pipeline-depth", type=int, default=2)
     ap.add_argument("--no-shards", action="store_true", help="one shared ring per model instead of one per actor")
     ap.add_argument("--max-batch", type=int, default=0, help="engine capacity (default: the largest batch size; 512 with --dynamic)")
@@ -78,7 +84,7 @@ def main():
     rates = [float(x) for x in args.rates.split(",")] if args.rates else [args.rate / len(models)] * len(models)
     batches = [int(x) for x in args.batches.split(",")] if args.batches else \
         [args.batch or DEFAULT_BATCH[m] for m in models]
-    profile = load_profiles(models)
+    profile = load_profiles(models, kind=args.profiles)
     registry = {}
     for m in models:
         kind = MODEL_KINDS[m]
