@@ -114,3 +114,41 @@ def test_fast_div_exhaustive_small_range(d):
     if d == 1:
         q = n
     assert np.array_equal(q, want)
+
+
+@pytest.mark.parametrize("kind,hw", [("resnet50", 224), ("efficientnet_v2_s", 224), ("yolov8n", 640), ("shufflenet_v2_x1_0", 224)])
+def test_padded_weight_extents_do_not_change_the_plan_results(monkeypatch, kind, hw):
+    """Conv weights are stored padded to the TMA box sizes (lowering.weight_k / weight_rows, recorded in p[19] / p[20]);
+    the plan interpreter must produce bit-identical outputs from the padded and the exact layouts, every padded element
+    must be zero, and the extents must cover the layer."""
+    import numpy as np
+    import torch
+    from oracle import plan_interp
+    m = synth.make_model(kind) if kind == "yolov8n" else synth.make_model(kind, n_proto=8)
+    kw = {"in_hw": (hw, hw)} if kind in ("efficientnet_v2_s", "yolov8n") else {}
+    padded = lowering.lower(kind, m, **kw).to_blob()
+    monkeypatch.setenv("B200_PAD_WEIGHTS", "0")
+    exact = lowering.lower(kind, m, **kw).to_blob()
+    monkeypatch.delenv("B200_PAD_WEIGHTS")
+    _, _, ops_p, w_p = lowering.parse_blob(padded)
+    _, _, ops_e, _ = lowering.parse_blob(exact)
+    assert len(ops_p) == len(ops_e)
+    wb = np.frombuffer(w_p, dtype=np.uint8)
+    n_padded = 0
+    for op, oe in zip(ops_p, ops_e):
+        if op["type"] != lowering.OP_CONV or op["p"][18] > 0:
+            continue
+        p = op["p"]
+        assert oe["p"][19] == 0 and oe["p"][20] == 0
+        k, cin, cout = p[8], p[2] + (p[15] if p[13] > 0 else 0), p[5]
+        kpad, rows = p[19], p[20]
+        assert kpad >= cin and kpad % 8 == 0 and rows >= cout and rows % 64 == 0
+        w = wb[op["w_off"]:op["w_off"] + rows * k * k * kpad * 2].view(np.uint16).reshape(rows, k * k, kpad)
+        assert not w[cout:].any() and not w[:, :, cin:].any()
+        n_padded += int(kpad > cin or rows > cout)
+    assert n_padded > 0 or kind == "resnet50"       # ResNet-50's channel counts already are multiples of the boxes
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(1, hw, hw, 3, generator=g)
+    a, _ = plan_interp.PlanInterpreter(padded, lowering.parse_blob).run(plan_interp.to_nhwc4(x.permute(0, 3, 1, 2)))
+    b, _ = plan_interp.PlanInterpreter(exact, lowering.parse_blob).run(plan_interp.to_nhwc4(x.permute(0, 3, 1, 2)))
+    assert torch.equal(torch.as_tensor(a), torch.as_tensor(b))
